@@ -1,0 +1,371 @@
+/* TEST INFRASTRUCTURE ONLY -- never linked into the product library.
+ *
+ * Flat-array (ctypes-friendly) wrappers around the UNMODIFIED reference CPU
+ * implementation.  This file is compiled together with the reference's own
+ * sources, taken where they lie under /root/reference, into
+ * oracle/_ref/libbwaref.so (see oracle/Makefile).  No reference source is
+ * copied into this repository; only its public headers are #included at build
+ * time.
+ *
+ * Seams exposed:
+ *   (1) bwt_occ4 / bwt_2occ4 / bwt_extend / bwt_sa on arrays of inputs
+ *   (2) bwt_smem1a per (read, x); mem_collect_intv output (through mem_chain)
+ *   (3) mem_chain, mem_chain_flt outputs
+ *   (4) ksw_extend2 / ksw_align2 / ksw_global2 batches
+ *   (5) mem_align1_core -> mem_alnreg_t per read
+ *   (7) mem_process_seqs -> SAM text
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdint.h>
+#include <zlib.h>
+#include "bwa.h"
+#include "bwamem.h"
+#include "bwt.h"
+#include "bntseq.h"
+#include "ksw.h"
+#include "kvec.h"
+#include "utils.h"
+
+extern void kt_for(int n_threads, void (*func)(void*, long, int), void *data, long n);
+extern mem_alnreg_v mem_align1_core(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns,
+                                    const uint8_t *pac, int l_seq, char *seq, void *buf);
+extern mem_chain_v mem_chain(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, int len, const uint8_t *seq, void *buf);
+extern int mem_chain_flt(const mem_opt_t *opt, int n_chn, mem_chain_t *a);
+extern void mem_flt_chained_seeds(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac,
+                                  int l_query, const uint8_t *query, int n_chn, mem_chain_t *a);
+
+/* ---------------------------------------------------------------- index */
+
+int ref_index_build(const char *fa, const char *prefix)
+{
+	return bwa_idx_build(fa, prefix, BWTALGO_AUTO, 10000000);
+}
+
+void *ref_index_load(const char *prefix)
+{
+	return bwa_idx_load(prefix, BWA_IDX_ALL);
+}
+
+void ref_index_destroy(void *p) { bwa_idx_destroy((bwaidx_t*)p); }
+
+/* out[0]=l_pac [1]=seq_len [2]=primary [3..7]=L2 [8]=bwt_size(words) [9]=n_sa
+ * [10]=sa_intv [11]=n_seqs [12]=n_holes */
+void ref_index_info(void *p, int64_t *out)
+{
+	bwaidx_t *idx = (bwaidx_t*)p;
+	int i;
+	out[0] = idx->bns->l_pac; out[1] = idx->bwt->seq_len; out[2] = idx->bwt->primary;
+	for (i = 0; i < 5; ++i) out[3+i] = idx->bwt->L2[i];
+	out[8] = idx->bwt->bwt_size; out[9] = idx->bwt->n_sa; out[10] = idx->bwt->sa_intv;
+	out[11] = idx->bns->n_seqs; out[12] = idx->bns->n_holes;
+}
+const uint32_t *ref_index_bwt(void *p) { return ((bwaidx_t*)p)->bwt->bwt; }
+const uint64_t *ref_index_sa(void *p)  { return ((bwaidx_t*)p)->bwt->sa; }
+const uint8_t  *ref_index_pac(void *p) { return ((bwaidx_t*)p)->pac; }
+const void *ref_index_bwt_struct(void *p) { return ((bwaidx_t*)p)->bwt; }
+const void *ref_index_bns_struct(void *p) { return ((bwaidx_t*)p)->bns; }
+void ref_index_anns(void *p, int64_t *offset, int32_t *len, int32_t *is_alt)
+{
+	bwaidx_t *idx = (bwaidx_t*)p;
+	int i;
+	for (i = 0; i < idx->bns->n_seqs; ++i) {
+		offset[i] = idx->bns->anns[i].offset; len[i] = idx->bns->anns[i].len;
+		is_alt[i] = idx->bns->anns[i].is_alt;
+	}
+}
+const char *ref_index_ann_name(void *p, int i) { return ((bwaidx_t*)p)->bns->anns[i].name; }
+
+/* ---------------------------------------------------------------- options */
+
+void *ref_opt_init(void) { return mem_opt_init(); }
+void ref_free(void *p) { free(p); }
+void ref_fill_scmat(int a, int b, int8_t *mat) { bwa_fill_scmat(a, b, mat); }
+int ref_sizeof(int what)
+{
+	switch (what) {
+	case 0: return sizeof(mem_opt_t);
+	case 1: return sizeof(mem_seed_t);
+	case 2: return sizeof(mem_chain_t);
+	case 3: return sizeof(mem_alnreg_t);
+	case 4: return sizeof(bwtintv_t);
+	case 5: return sizeof(bwt_t);
+	case 6: return sizeof(bntseq_t);
+	case 7: return sizeof(bntann1_t);
+	case 8: return sizeof(bseq1_t);
+	case 9: return sizeof(mem_pestat_t);
+	case 10: return sizeof(kswr_t);
+	}
+	return -1;
+}
+
+/* ---------------------------------------------------------------- FM-index primitives */
+
+void ref_occ4(void *p, int64_t n, const uint64_t *k, uint64_t *out)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt; int64_t i;
+	for (i = 0; i < n; ++i) bwt_occ4(bwt, k[i], &out[4*i]);
+}
+void ref_2occ4(void *p, int64_t n, const uint64_t *k, const uint64_t *l, uint64_t *outk, uint64_t *outl)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt; int64_t i;
+	for (i = 0; i < n; ++i) bwt_2occ4(bwt, k[i], l[i], &outk[4*i], &outl[4*i]);
+}
+/* ik: n x 3 (x0,x1,x2); out: n x 4 x 3 */
+void ref_extend(void *p, int64_t n, const uint64_t *ik, int is_back, uint64_t *out)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt; int64_t i; int c;
+	for (i = 0; i < n; ++i) {
+		bwtintv_t in, ok[4];
+		in.x[0] = ik[3*i]; in.x[1] = ik[3*i+1]; in.x[2] = ik[3*i+2]; in.info = 0;
+		bwt_extend(bwt, &in, ok, is_back);
+		for (c = 0; c < 4; ++c) {
+			out[12*i + 3*c + 0] = ok[c].x[0]; out[12*i + 3*c + 1] = ok[c].x[1]; out[12*i + 3*c + 2] = ok[c].x[2];
+		}
+	}
+}
+void ref_sa(void *p, int64_t n, const uint64_t *k, uint64_t *out)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt; int64_t i;
+	for (i = 0; i < n; ++i) out[i] = bwt_sa(bwt, k[i]);
+}
+
+/* one bwt_smem1a call; out: cap x 4 (x0,x1,x2,info); returns n (or -needed if cap too small) */
+int ref_smem1a(void *p, int len, const uint8_t *q, int x, int min_intv, uint64_t max_intv, int cap, uint64_t *out, int *ret)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt;
+	bwtintv_v mem = {0,0,0};
+	int i, n;
+	*ret = bwt_smem1a(bwt, len, q, x, min_intv, max_intv, &mem, 0);
+	n = mem.n;
+	if (n > cap) { free(mem.a); return -n; }
+	for (i = 0; i < n; ++i) {
+		out[4*i] = mem.a[i].x[0]; out[4*i+1] = mem.a[i].x[1]; out[4*i+2] = mem.a[i].x[2]; out[4*i+3] = mem.a[i].info;
+	}
+	free(mem.a);
+	return n;
+}
+
+int ref_seed_strategy1(void *p, int len, const uint8_t *q, int x, int min_len, int max_intv, uint64_t *out)
+{
+	const bwt_t *bwt = ((bwaidx_t*)p)->bwt;
+	bwtintv_t m; int r;
+	r = bwt_seed_strategy1(bwt, len, q, x, min_len, max_intv, &m);
+	out[0] = m.x[0]; out[1] = m.x[1]; out[2] = m.x[2]; out[3] = m.info;
+	return r;
+}
+
+/* ---------------------------------------------------------------- per-read helpers */
+
+static smem_aux_t *aux_new(void)
+{
+	smem_aux_t *a = calloc(1, sizeof(smem_aux_t));
+	a->tmpv[0] = calloc(1, sizeof(bwtintv_v));
+	a->tmpv[1] = calloc(1, sizeof(bwtintv_v));
+	return a;
+}
+static void aux_del(smem_aux_t *a)
+{
+	free(a->tmpv[0]->a); free(a->tmpv[0]); free(a->tmpv[1]->a); free(a->tmpv[1]);
+	free(a->mem.a); free(a->mem1.a); free(a);
+}
+static uint8_t *nt4_copy(const uint8_t *s, int l)
+{
+	uint8_t *r = malloc(l + 1); int i;
+	for (i = 0; i < l; ++i) r[i] = s[i] < 4 ? s[i] : nst_nt4_table[s[i]];
+	return r;
+}
+
+/* mem_collect_intv output for each read (reached through mem_chain with our own aux).
+ * out_intv: cap x 4 u64; out_n[n_reads]; returns total or -1 on overflow */
+int64_t ref_collect_intv(void *p, const void *opt_, int n_reads, const uint8_t *seqs, const int64_t *off,
+                         int64_t cap, uint64_t *out_intv, int32_t *out_n)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	smem_aux_t *aux = aux_new();
+	int64_t tot = 0; int r, i;
+	for (r = 0; r < n_reads; ++r) {
+		int l = (int)(off[r+1] - off[r]);
+		uint8_t *s = nt4_copy(seqs + off[r], l);
+		mem_chain_v chn;
+		aux->mem.n = 0;
+		chn = mem_chain(opt, idx->bwt, idx->bns, l, s, aux);
+		for (i = 0; i < chn.n; ++i) free(chn.a[i].seeds);
+		free(chn.a);
+		out_n[r] = l < opt->min_seed_len ? 0 : aux->mem.n;
+		if (tot + out_n[r] > cap) { free(s); aux_del(aux); return -1; }
+		for (i = 0; i < out_n[r]; ++i, ++tot) {
+			out_intv[4*tot] = aux->mem.a[i].x[0]; out_intv[4*tot+1] = aux->mem.a[i].x[1];
+			out_intv[4*tot+2] = aux->mem.a[i].x[2]; out_intv[4*tot+3] = aux->mem.a[i].info;
+		}
+		free(s);
+	}
+	aux_del(aux);
+	return tot;
+}
+
+/* mem_chain (stage: 0), + mem_chain_flt (stage: 1), + mem_flt_chained_seeds (stage: 2).
+ * Per chain (8 x int64): pos, n, rid, w, kept, first, is_alt, frac_rep (float bits)
+ * Per seed  (4 x int64): rbeg, qbeg, len, score
+ * returns 0 or -1 on overflow */
+int ref_chains(void *p, const void *opt_, int stage, int n_reads, const uint8_t *seqs, const int64_t *off,
+               int64_t cap_chn, int64_t *out_chn, int32_t *out_nchn,
+               int64_t cap_seed, int64_t *out_seed, int64_t *totals)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	int64_t nc = 0, ns = 0; int r, i, j, ovf = 0;
+	for (r = 0; r < n_reads; ++r) {
+		int l = (int)(off[r+1] - off[r]);
+		uint8_t *s = nt4_copy(seqs + off[r], l);
+		mem_chain_v chn = mem_chain(opt, idx->bwt, idx->bns, l, s, 0);
+		if (stage >= 1) chn.n = mem_chain_flt(opt, chn.n, chn.a);
+		if (stage >= 2) mem_flt_chained_seeds(opt, idx->bns, idx->pac, l, s, chn.n, chn.a);
+		out_nchn[r] = chn.n;
+		for (i = 0; i < chn.n; ++i) {
+			mem_chain_t *c = &chn.a[i];
+			if (nc >= cap_chn || ns + c->n > cap_seed) ovf = 1;
+			if (!ovf) {
+				int64_t *o = &out_chn[8*nc]; float fr = c->frac_rep; uint32_t fb;
+				memcpy(&fb, &fr, 4);
+				o[0] = c->pos; o[1] = c->n; o[2] = c->rid; o[3] = stage >= 1 ? c->w : 0;
+				o[4] = stage >= 1 ? c->kept : 0; o[5] = stage >= 1 ? c->first : 0; o[6] = c->is_alt; o[7] = fb;
+				for (j = 0; j < c->n; ++j) {
+					int64_t *q = &out_seed[4*(ns+j)];
+					q[0] = c->seeds[j].rbeg; q[1] = c->seeds[j].qbeg; q[2] = c->seeds[j].len; q[3] = c->seeds[j].score;
+				}
+			}
+			++nc; ns += c->n;
+			free(c->seeds);
+		}
+		free(chn.a); free(s);
+	}
+	totals[0] = nc; totals[1] = ns;
+	return ovf ? -1 : 0;
+}
+
+/* ---------------------------------------------------------------- mem_align1_core over a batch (worker1) */
+
+typedef struct {
+	bwaidx_t *idx; const mem_opt_t *opt; const uint8_t *seqs; const int64_t *off;
+	mem_alnreg_v *regs; smem_aux_t **aux;
+} aln_task_t;
+
+static void aln_worker(void *data, long i, int tid)
+{
+	aln_task_t *t = (aln_task_t*)data;
+	int l = (int)(t->off[i+1] - t->off[i]);
+	char *s = malloc(l + 1);
+	memcpy(s, t->seqs + t->off[i], l); s[l] = 0;
+	t->regs[i] = mem_align1_core(t->opt, t->idx->bwt, t->idx->bns, t->idx->pac, l, s, t->aux[tid]);
+	free(s);
+}
+
+/* out_regs: raw mem_alnreg_t records (88 B each); returns total regs, or -(needed) on overflow.
+ * If out_regs == NULL only counts (used for timing the worker1 path). */
+int64_t ref_align(void *p, const void *opt_, int n_reads, const uint8_t *seqs, const int64_t *off, int n_threads,
+                  int64_t cap, void *out_regs, int32_t *out_n)
+{
+	aln_task_t t; int64_t tot = 0; int i;
+	t.idx = (bwaidx_t*)p; t.opt = (const mem_opt_t*)opt_; t.seqs = seqs; t.off = off;
+	t.regs = calloc(n_reads, sizeof(mem_alnreg_v));
+	if (n_threads < 1) n_threads = 1;
+	t.aux = malloc(n_threads * sizeof(void*));
+	for (i = 0; i < n_threads; ++i) t.aux[i] = aux_new();
+	kt_for(n_threads, aln_worker, &t, n_reads);
+	for (i = 0; i < n_threads; ++i) aux_del(t.aux[i]);
+	free(t.aux);
+	for (i = 0; i < n_reads; ++i) tot += t.regs[i].n;
+	if (out_regs && tot <= cap) {
+		mem_alnreg_t *o = (mem_alnreg_t*)out_regs;
+		for (i = 0; i < n_reads; ++i) {
+			if (t.regs[i].n) memcpy(o, t.regs[i].a, t.regs[i].n * sizeof(mem_alnreg_t));
+			o += t.regs[i].n;
+		}
+	}
+	for (i = 0; i < n_reads; ++i) { if (out_n) out_n[i] = t.regs[i].n; free(t.regs[i].a); }
+	free(t.regs);
+	return (out_regs && tot > cap) ? -tot : tot;
+}
+
+/* ---------------------------------------------------------------- DP primitives */
+
+/* out: n x 6: score, qle, tle, gtle, gscore, max_off */
+void ref_ksw_extend2(int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                     const int32_t *tlen, const int64_t *toff, const uint8_t *t,
+                     const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins,
+                     const int32_t *w, int end_bonus, int zdrop, const int32_t *h0, int32_t *out)
+{
+	int64_t i;
+	for (i = 0; i < n; ++i) {
+		int qle, tle, gtle, gscore, max_off;
+		int sc = ksw_extend2(qlen[i], q + qoff[i], tlen[i], t + toff[i], 5, mat, o_del, e_del, o_ins, e_ins,
+		                     w[i], end_bonus, zdrop, h0[i], &qle, &tle, &gtle, &gscore, &max_off);
+		int32_t *o = &out[6*i];
+		o[0] = sc; o[1] = qle; o[2] = tle; o[3] = gtle; o[4] = gscore; o[5] = max_off;
+	}
+}
+
+/* out: n x 7: score, te, qe, score2, te2, tb, qb */
+void ref_ksw_align2(int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                    const int32_t *tlen, const int64_t *toff, const uint8_t *t,
+                    const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins, const int32_t *xtra, int32_t *out)
+{
+	int64_t i;
+	for (i = 0; i < n; ++i) {
+		kswr_t r = ksw_align2(qlen[i], (uint8_t*)q + qoff[i], tlen[i], (uint8_t*)t + toff[i], 5, mat,
+		                      o_del, e_del, o_ins, e_ins, xtra[i], 0);
+		int32_t *o = &out[7*i];
+		o[0] = r.score; o[1] = r.te; o[2] = r.qe; o[3] = r.score2; o[4] = r.te2; o[5] = r.tb; o[6] = r.qb;
+	}
+}
+
+/* score only (cigar==NULL) or with cigar: out_cigar cap words per problem */
+void ref_ksw_global2(int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                     const int32_t *tlen, const int64_t *toff, const uint8_t *t,
+                     const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins, const int32_t *w,
+                     int32_t *out_score, int cap_cigar, uint32_t *out_cigar, int32_t *out_ncigar)
+{
+	int64_t i;
+	for (i = 0; i < n; ++i) {
+		int nc = 0; uint32_t *cg = 0;
+		out_score[i] = ksw_global2(qlen[i], q + qoff[i], tlen[i], t + toff[i], 5, mat, o_del, e_del, o_ins, e_ins,
+		                           w[i], out_cigar ? &nc : 0, out_cigar ? &cg : 0);
+		if (out_cigar) {
+			out_ncigar[i] = nc;
+			if (nc <= cap_cigar) memcpy(out_cigar + i * cap_cigar, cg, nc * 4);
+			free(cg);
+		}
+	}
+}
+
+/* ---------------------------------------------------------------- full mem_process_seqs -> SAM */
+
+/* names: NUL-separated list of n names; quals may be NULL.  SAM records are concatenated into out
+ * (cap bytes). pes0 may be NULL.  Returns bytes written or -(needed). */
+int64_t ref_process_seqs(void *p, const void *opt_, int64_t n_processed, int n, const char *names,
+                         const uint8_t *seqs, const int64_t *off, const uint8_t *quals,
+                         const void *pes0, int64_t cap, char *out)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	bseq1_t *bs = calloc(n, sizeof(bseq1_t));
+	const char *nm = names; int64_t tot = 0; int i;
+	for (i = 0; i < n; ++i) {
+		int l = (int)(off[i+1] - off[i]);
+		bs[i].name = strdup(nm); nm += strlen(nm) + 1;
+		bs[i].seq = malloc(l + 1); memcpy(bs[i].seq, seqs + off[i], l); bs[i].seq[l] = 0;
+		if (quals) { bs[i].qual = malloc(l + 1); memcpy(bs[i].qual, quals + off[i], l); bs[i].qual[l] = 0; }
+		bs[i].l_seq = l; bs[i].id = i;
+	}
+	mem_process_seqs(opt, idx->bwt, idx->bns, idx->pac, n_processed, n, bs, (const mem_pestat_t*)pes0);
+	for (i = 0; i < n; ++i) tot += strlen(bs[i].sam);
+	if (tot <= cap) {
+		char *o = out;
+		for (i = 0; i < n; ++i) { size_t l = strlen(bs[i].sam); memcpy(o, bs[i].sam, l); o += l; }
+	}
+	for (i = 0; i < n; ++i) { free(bs[i].name); free(bs[i].seq); free(bs[i].qual); free(bs[i].sam); }
+	free(bs);
+	return tot <= cap ? tot : -tot;
+}
+
+void ref_set_verbose(int v) { bwa_verbose = v; }

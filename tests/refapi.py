@@ -1,0 +1,226 @@
+"""ctypes binding of oracle/_ref/libbwaref.so (the unmodified reference CPU code + oracle/ref_shim.c).
+
+TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from bwa_mem_gpu_b200.abi import ALNREG_DTYPE, INTV_DTYPE, MemOpt  # noqa: E402
+
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libbwaref.so")
+
+
+def available() -> bool:
+    return os.path.exists(REF_SO)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class RefLib:
+    def __init__(self):
+        self.lib = C.CDLL(REF_SO, mode=os.RTLD_LOCAL)
+        L = self.lib
+        L.ref_index_load.restype = C.c_void_p
+        L.ref_index_load.argtypes = [C.c_char_p]
+        L.ref_index_build.argtypes = [C.c_char_p, C.c_char_p]
+        L.ref_index_destroy.argtypes = [C.c_void_p]
+        L.ref_index_info.argtypes = [C.c_void_p, C.c_void_p]
+        for f in ("ref_index_bwt", "ref_index_sa", "ref_index_pac", "ref_index_bwt_struct", "ref_index_bns_struct"):
+            getattr(L, f).restype = C.c_void_p
+            getattr(L, f).argtypes = [C.c_void_p]
+        L.ref_index_ann_name.restype = C.c_char_p
+        L.ref_index_ann_name.argtypes = [C.c_void_p, C.c_int]
+        L.ref_opt_init.restype = C.c_void_p
+        L.ref_collect_intv.restype = C.c_int64
+        L.ref_align.restype = C.c_int64
+        L.ref_process_seqs.restype = C.c_int64
+
+    # ---------------- index
+    def index_build(self, fa: str, prefix: str) -> None:
+        rc = self.lib.ref_index_build(fa.encode(), prefix.encode())
+        assert rc == 0
+
+    def index_load(self, prefix: str) -> "RefIndex":
+        h = self.lib.ref_index_load(prefix.encode())
+        assert h, f"cannot load {prefix}"
+        return RefIndex(self, h)
+
+    def opt_init(self) -> MemOpt:
+        p = self.lib.ref_opt_init()
+        o = MemOpt.from_buffer_copy(C.string_at(p, C.sizeof(MemOpt)))
+        self.lib.ref_free(C.c_void_p(p))
+        return o
+
+    def sizeof(self, what: int) -> int:
+        return self.lib.ref_sizeof(what)
+
+    # ---------------- DP primitives
+    def ksw_extend2(self, qlen, qoff, q, tlen, toff, t, opt: MemOpt, w, end_bonus, zdrop, h0):
+        n = len(qlen)
+        out = np.zeros((n, 6), dtype=np.int32)
+        self.lib.ref_ksw_extend2(C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8),
+                                 _p(tlen, C.c_int32), _p(toff, C.c_int64), _p(t, C.c_uint8),
+                                 opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+                                 _p(w, C.c_int32), C.c_int(end_bonus), C.c_int(zdrop), _p(h0, C.c_int32),
+                                 _p(out, C.c_int32))
+        return out
+
+    def ksw_align2(self, qlen, qoff, q, tlen, toff, t, opt: MemOpt, xtra):
+        n = len(qlen)
+        out = np.zeros((n, 7), dtype=np.int32)
+        self.lib.ref_ksw_align2(C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8),
+                                _p(tlen, C.c_int32), _p(toff, C.c_int64), _p(t, C.c_uint8),
+                                opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+                                _p(xtra, C.c_int32), _p(out, C.c_int32))
+        return out
+
+    def ksw_global2_score(self, qlen, qoff, q, tlen, toff, t, opt: MemOpt, w):
+        n = len(qlen)
+        out = np.zeros(n, dtype=np.int32)
+        self.lib.ref_ksw_global2(C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8),
+                                 _p(tlen, C.c_int32), _p(toff, C.c_int64), _p(t, C.c_uint8),
+                                 opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+                                 _p(w, C.c_int32), _p(out, C.c_int32), 0, None, None)
+        return out
+
+
+class RefIndex:
+    def __init__(self, lib: RefLib, h):
+        self.rl, self.lib, self.h = lib, lib.lib, C.c_void_p(h)
+        info = np.zeros(16, dtype=np.int64)
+        self.lib.ref_index_info(self.h, _p(info, C.c_int64))
+        self.l_pac, self.seq_len, self.primary = int(info[0]), int(info[1]), int(info[2])
+        self.L2 = [int(x) for x in info[3:8]]
+        self.bwt_size, self.n_sa, self.sa_intv = int(info[8]), int(info[9]), int(info[10])
+        self.n_seqs, self.n_holes = int(info[11]), int(info[12])
+
+    def close(self):
+        if self.h:
+            self.lib.ref_index_destroy(self.h)
+            self.h = None
+
+    # raw arrays (views over the reference's memory; copy if kept)
+    def bwt_words(self):
+        p = self.lib.ref_index_bwt(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), shape=(self.bwt_size,))
+
+    def sa(self):
+        p = self.lib.ref_index_sa(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint64)), shape=(self.n_sa,))
+
+    def pac(self):
+        p = self.lib.ref_index_pac(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(self.l_pac // 4 + 1,))
+
+    def bwt_struct(self):
+        return self.lib.ref_index_bwt_struct(self.h)
+
+    def bns_struct(self):
+        return self.lib.ref_index_bns_struct(self.h)
+
+    def anns(self):
+        off = np.zeros(self.n_seqs, dtype=np.int64)
+        ln = np.zeros(self.n_seqs, dtype=np.int32)
+        alt = np.zeros(self.n_seqs, dtype=np.int32)
+        self.lib.ref_index_anns(self.h, _p(off, C.c_int64), _p(ln, C.c_int32), _p(alt, C.c_int32))
+        names = [self.lib.ref_index_ann_name(self.h, i).decode() for i in range(self.n_seqs)]
+        return off, ln, alt, names
+
+    # FM-index primitives
+    def occ4(self, k):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        out = np.zeros((len(k), 4), dtype=np.uint64)
+        self.lib.ref_occ4(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(out, C.c_uint64))
+        return out
+
+    def occ2x4(self, k, l):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        l = np.ascontiguousarray(l, dtype=np.uint64)
+        ok = np.zeros((len(k), 4), dtype=np.uint64)
+        ol = np.zeros((len(k), 4), dtype=np.uint64)
+        self.lib.ref_2occ4(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(l, C.c_uint64),
+                           _p(ok, C.c_uint64), _p(ol, C.c_uint64))
+        return ok, ol
+
+    def extend(self, ik, is_back: int):
+        ik = np.ascontiguousarray(ik, dtype=np.uint64)
+        out = np.zeros((len(ik), 4, 3), dtype=np.uint64)
+        self.lib.ref_extend(self.h, C.c_int64(len(ik)), _p(ik, C.c_uint64), C.c_int(is_back), _p(out, C.c_uint64))
+        return out
+
+    def sa_lookup(self, k):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        out = np.zeros(len(k), dtype=np.uint64)
+        self.lib.ref_sa(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(out, C.c_uint64))
+        return out
+
+    def smem1a(self, q, x, min_intv=1, max_intv=0, cap=4096):
+        q = np.ascontiguousarray(q, dtype=np.uint8)
+        out = np.zeros(cap, dtype=INTV_DTYPE)
+        ret = C.c_int(0)
+        n = self.lib.ref_smem1a(self.h, C.c_int(len(q)), _p(q, C.c_uint8), C.c_int(x), C.c_int(min_intv),
+                                C.c_uint64(max_intv), C.c_int(cap), C.c_void_p(out.ctypes.data), C.byref(ret))
+        assert n >= 0
+        return out[:n].copy(), ret.value
+
+    # batched stage seams
+    def collect_intv(self, opt: MemOpt, seqs, off, cap_per_read=256):
+        n = len(off) - 1
+        cap = n * cap_per_read
+        out = np.zeros(cap, dtype=INTV_DTYPE)
+        cnt = np.zeros(n, dtype=np.int32)
+        tot = self.lib.ref_collect_intv(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                        C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
+        assert tot >= 0
+        return out[:tot].copy(), cnt
+
+    def chains(self, opt: MemOpt, seqs, off, stage=1, cap_chn_per_read=64, cap_seed_per_read=1024):
+        n = len(off) - 1
+        cc, cs = n * cap_chn_per_read, n * cap_seed_per_read
+        chn = np.zeros((cc, 8), dtype=np.int64)
+        sd = np.zeros((cs, 4), dtype=np.int64)
+        nch = np.zeros(n, dtype=np.int32)
+        tot = np.zeros(2, dtype=np.int64)
+        rc = self.lib.ref_chains(self.h, C.byref(opt), C.c_int(stage), C.c_int(n), _p(seqs, C.c_uint8),
+                                 _p(off, C.c_int64), C.c_int64(cc), _p(chn, C.c_int64), _p(nch, C.c_int32),
+                                 C.c_int64(cs), _p(sd, C.c_int64), _p(tot, C.c_int64))
+        assert rc == 0, "chain buffers too small"
+        return chn[:tot[0]].copy(), nch, sd[:tot[1]].copy()
+
+    def align(self, opt: MemOpt, seqs, off, n_threads=1, cap_per_read=64, count_only=False):
+        n = len(off) - 1
+        cnt = np.zeros(n, dtype=np.int32)
+        if count_only:
+            tot = self.lib.ref_align(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                     C.c_int(n_threads), C.c_int64(0), None, _p(cnt, C.c_int32))
+            return None, cnt
+        cap = n * cap_per_read
+        out = np.zeros(cap, dtype=ALNREG_DTYPE)
+        tot = self.lib.ref_align(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                 C.c_int(n_threads), C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
+        assert tot >= 0
+        return out[:tot].copy(), cnt
+
+    def process_seqs(self, opt: MemOpt, seqs, off, names=None, quals=None, n_processed=0, pes0=None):
+        n = len(off) - 1
+        if names is None:
+            names = [f"r{n_processed + i}" for i in range(n)]
+        nm = b"\0".join(s.encode() for s in names) + b"\0"
+        cap = int(off[-1]) * 6 + n * 512 + 4096
+        buf = C.create_string_buffer(cap)
+        tot = self.lib.ref_process_seqs(self.h, C.byref(opt), C.c_int64(n_processed), C.c_int(n), nm,
+                                        _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                        _p(quals, C.c_uint8) if quals is not None else None,
+                                        C.byref(pes0) if pes0 is not None else None, C.c_int64(cap), buf)
+        assert tot >= 0, f"SAM buffer too small ({-tot})"
+        return buf.raw[:tot]
