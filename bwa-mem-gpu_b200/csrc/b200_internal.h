@@ -1,0 +1,118 @@
+// Internal declarations shared by the kernels and the host-side pipeline.
+#pragma once
+#include "simt.h"
+#include "fmindex.cuh"
+#include "../../include/bwamem_b200.h"
+
+#define B200_CHECK(call)                                                                         \
+    do {                                                                                         \
+        cudaError_t e_ = (call);                                                                 \
+        if (e_ != cudaSuccess) {                                                                 \
+            b200_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return -1;                                                                           \
+        }                                                                                        \
+    } while (0)
+
+void b200_set_error(const char *fmt, ...);
+
+// ---- device-side records -------------------------------------------------------------------
+struct Seed {            // one SA hit of one interval (mem_seed_t, bwa.h:121, without the fork's padding)
+    i64 rbeg;            // K2a stores the SA row here, K2b replaces it by the text position
+    i32 qbeg, len;
+    i32 rid;             // bns_intv2rid result; < 0 = discarded (bwamem.c:294)
+    i32 score;
+};
+
+struct ChainRec {        // one kept chain after mem_chain_flt
+    i64 pos;
+    i64 seed_off;        // into the chain-seed arena
+    i32 n, rid, w, kept, first, is_alt;
+    float frac_rep;
+    i32 read;
+};
+
+enum {                   // work / traffic counters (u64 each)
+    CNT_EXTEND = 0, CNT_TWO_BLOCK, CNT_SA, CNT_LF, CNT_KSW, CNT_CELLS, CNT_SEEDS, CNT_CHAINS, CNT_REGS,
+    CNT_LAUNCH, CNT_N = 16
+};
+
+// ---- stage parameter blocks (passed by value to the kernels) ---------------------------------
+struct SmemParams {
+    DevIndex ix;
+    const u8 *seq; const i64 *off; int n_reads;
+    int min_seed_len, split_len, split_width; u64 max_mem_intv;
+    Intv *out; int cap_out; i32 *out_n;          // cap_out slots per read
+    Intv *lists; int list_cap;                   // 2 * list_cap per resident thread
+    unsigned *work_counter;
+    unsigned long long *stats; int *overflow;
+    // single-call mode (b200_smem1a_batch): per problem x / min_intv, no length filter
+    const i32 *px, *pmin_intv; u64 max_intv; i32 *out_ret;
+};
+
+struct SeedParams {
+    DevIndex ix;
+    const i64 *off; int n_reads;
+    const Intv *intv; int cap_intv; const i32 *intv_n;
+    int max_occ;
+    i32 *seed_n; const i64 *seed_off;            // per read
+    Seed *seeds; i64 n_seeds;
+    i32 *l_rep;                                  // per read (bwamem.c:272-279)
+    unsigned long long *stats;
+};
+
+struct ChainParams {
+    DevIndex ix;
+    mem_opt_t opt;
+    const i64 *off; int n_reads;
+    const Seed *seeds; const i64 *seed_off; const i32 *seed_n; const i32 *l_rep;
+    int *scratch;                                // 16 ints per seed + 128 per read
+    int stage;                                   // 0: mem_chain only, 1: + mem_chain_flt
+    // pass A: count; pass B: emit
+    i32 *chn_n, *cseed_n;                        // per read: kept chains, their seeds
+    const i64 *chn_off, *cseed_off;
+    ChainRec *chains; Seed *cseeds;
+    int *overflow;
+};
+
+struct ExtParams {
+    DevIndex ix;
+    mem_opt_t opt;
+    const u8 *seq; const i64 *off; int n_reads;
+    const ChainRec *chains; const i64 *chn_off; const i32 *chn_n;
+    const Seed *cseeds;
+    mem_alnreg_t *regs; int cap_regs;            // staging: cap_regs per resident warp
+    i32 *eh; int eh_cap;                         // per resident warp: 2 * eh_cap ints (H,E rows)
+    u64 *srt; int srt_cap;                       // per resident warp: seed sort keys
+    mem_alnreg_t *out; i64 out_cap; unsigned long long *out_used;
+    i64 *reg_off; i32 *reg_n;                    // per read
+    unsigned *work_counter;
+    unsigned long long *stats; int *overflow;
+};
+
+struct KswBatchParams {
+    i64 n;
+    const i32 *qlen; const i64 *qoff; const u8 *q;
+    const i32 *tlen; const i64 *toff; const u8 *t;
+    int8_t mat[25];
+    int o_del, e_del, o_ins, e_ins; const i32 *w; int end_bonus, zdrop; const i32 *h0;
+    i32 *out; i32 *eh; int eh_cap;
+    unsigned *work_counter;
+};
+
+// ---- stage launchers (each returns 0 / -1) ----------------------------------------------------
+int launch_pack_reads(u8 *seq, i64 n_bytes, cudaStream_t st);
+int launch_smem_collect(const SmemParams &p, int grid, int block, cudaStream_t st);
+int launch_smem_single(const SmemParams &p, int grid, int block, cudaStream_t st);
+int launch_seed_count(const SeedParams &p, cudaStream_t st);
+int launch_seed_fill(const SeedParams &p, cudaStream_t st);
+int launch_sa_locate(const SeedParams &p, cudaStream_t st);
+int launch_chain(const ChainParams &p, int emit, cudaStream_t st);
+int launch_extend(const ExtParams &p, int grid, int block, cudaStream_t st);
+int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
+int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,
+                       int n_reads, mem_alnreg_t *dst, cudaStream_t st);
+int launch_exclusive_scan(const i32 *in, i64 *out /* n+1 */, int n, i64 *tmp, cudaStream_t st);
+int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl, cudaStream_t st);
+int launch_extend_batch(const DevIndex &ix, i64 n, const u64 *ik, int is_back, u64 *ok, cudaStream_t st);
+int launch_sa_batch(const DevIndex &ix, i64 n, const u64 *k, u64 *out, int use_full, cudaStream_t st);
+int launch_build_full_sa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st);

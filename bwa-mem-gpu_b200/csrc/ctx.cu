@@ -1,0 +1,244 @@
+// Context, device index loader and the batched FM-index primitive entry points of the C ABI.
+#include "ctx.h"
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+
+static thread_local char g_err[512] = "";
+
+void b200_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *b200_last_error(void) { return g_err; }
+
+extern "C" b200_ctx_t *b200_ctx_create(int device)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        b200_set_error("no CUDA device available (this library has no CPU path)");
+        return nullptr;
+    }
+    if (device < 0 || device >= ndev) { b200_set_error("device %d out of range (%d devices)", device, ndev); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { b200_set_error("cudaSetDevice(%d) failed", device); return nullptr; }
+    b200_ctx *ctx = new b200_ctx();
+    ctx->device = device;
+#ifdef B200_EMU
+    ctx->n_sms = 2;
+#else
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->n_sms = prop.multiProcessorCount;
+#endif
+    if (cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking) != cudaSuccess) {
+        b200_set_error("cudaStreamCreate failed");
+        delete ctx;
+        return nullptr;
+    }
+    memset(&ctx->ix, 0, sizeof(ctx->ix));
+    return ctx;
+}
+
+extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->st);
+    DevBuf *bufs[] = { &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+                       &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
+                       &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
+                       &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,
+                       &ctx->d_dst_off, &ctx->d_scan_tmp, &ctx->d_ctl, &ctx->d_final, &ctx->d_final_n,
+                       &ctx->d_pa, &ctx->d_pb, &ctx->d_pc, &ctx->d_pd, &ctx->d_pe, &ctx->d_pf, &ctx->d_pg, &ctx->d_ph };
+    for (DevBuf *b : bufs) b->release();
+    cudaStreamDestroy(ctx->st);
+    delete ctx;
+}
+
+extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_size, uint64_t primary,
+                                     const uint64_t L2[5], uint64_t seq_len, const uint64_t *sa, uint64_t n_sa, int sa_intv,
+                                     const uint8_t *pac, int64_t l_pac, int n_seqs, const int64_t *ann_offset,
+                                     const int32_t *ann_len, const int32_t *ann_is_alt, int flags)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    if (sa_intv <= 0 || (sa_intv & (sa_intv - 1))) { b200_set_error("sa_intv must be a power of two"); return -1; }
+    // Occ blocks: verbatim, padded to a whole number of 64-byte blocks (+1 so that row seq_len-1 is always inside)
+    size_t bwt_bytes = ((size_t)bwt_size * 4 + 63) / 64 * 64 + 64;
+    if (ctx->d_bwt.ensure(bwt_bytes)) return -1;
+    B200_CHECK(cudaMemsetAsync(ctx->d_bwt.p, 0, bwt_bytes, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_bwt.p, bwt, (size_t)bwt_size * 4, cudaMemcpyHostToDevice, ctx->st));
+    if (ctx->d_sa.ensure((size_t)n_sa * 8)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_sa.p, sa, (size_t)n_sa * 8, cudaMemcpyHostToDevice, ctx->st));
+    size_t pac_bytes = (size_t)(l_pac / 4 + 1);
+    if (ctx->d_pac.ensure(pac_bytes)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pac.p, pac, pac_bytes, cudaMemcpyHostToDevice, ctx->st));
+    if (ctx->d_ann_off.ensure((size_t)n_seqs * 8) || ctx->d_ann_len.ensure((size_t)n_seqs * 4) || ctx->d_ann_alt.ensure((size_t)n_seqs * 4)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_ann_off.p, ann_offset, (size_t)n_seqs * 8, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_ann_len.p, ann_len, (size_t)n_seqs * 4, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_ann_alt.p, ann_is_alt, (size_t)n_seqs * 4, cudaMemcpyHostToDevice, ctx->st));
+
+    DevIndex &ix = ctx->ix;
+    memset(&ix, 0, sizeof(ix));
+    ix.bwt = ctx->d_bwt.as<uint4>();
+    ix.primary = primary; ix.seq_len = seq_len;
+    for (int i = 0; i < 5; ++i) ix.L2[i] = L2[i];
+    ix.sa = ctx->d_sa.as<u64>(); ix.n_sa = n_sa; ix.sa_intv = sa_intv;
+    ix.pac = ctx->d_pac.as<u8>(); ix.l_pac = l_pac; ix.n_seqs = n_seqs;
+    ix.ann_off = ctx->d_ann_off.as<i64>(); ix.ann_len = ctx->d_ann_len.as<i32>(); ix.ann_alt = ctx->d_ann_alt.as<i32>();
+    if (flags & B200_IDX_FULL_SA) {
+        const bool narrow = seq_len < 0xffffffffull;
+        if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
+        if (launch_build_full_sa(ix, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
+        if (narrow) ix.sa_full32 = ctx->d_sa_full.as<u32>(); else ix.sa_full64 = ctx->d_sa_full.as<u64>();
+    }
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    ctx->has_index = true;
+    return 0;
+}
+
+extern "C" int b200_index_upload(b200_ctx_t *ctx, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac, int flags)
+{
+    if (!bwt || !bns || !pac) { b200_set_error("null index component"); return -1; }
+    std::vector<int64_t> off(bns->n_seqs);
+    std::vector<int32_t> len(bns->n_seqs), alt(bns->n_seqs);
+    for (int i = 0; i < bns->n_seqs; ++i) { off[i] = bns->anns[i].offset; len[i] = bns->anns[i].len; alt[i] = bns->anns[i].is_alt; }
+    int rc = b200_index_upload_raw(ctx, bwt->bwt, bwt->bwt_size, bwt->primary, bwt->L2, bwt->seq_len, bwt->sa, bwt->n_sa,
+                                   bwt->sa_intv, pac, bns->l_pac, bns->n_seqs, off.data(), len.data(), alt.data(), flags);
+    if (rc == 0) ctx->bwt_identity = bwt;
+    return rc;
+}
+
+// ---- drop-in registry: one context per host bwt_t (created lazily)
+static std::mutex g_reg_mu;
+static std::vector<b200_ctx *> g_reg;
+
+b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac)
+{
+    std::lock_guard<std::mutex> lk(g_reg_mu);
+    for (b200_ctx *c : g_reg) if (c->bwt_identity == bwt) return c;
+    b200_ctx *c = b200_ctx_create(0);
+    if (!c) { fprintf(stderr, "[b200] %s\n", b200_last_error()); exit(1); }
+    // primitives that only need the FM-index may arrive without bns/pac: upload a 1-contig stub
+    bntseq_t stub; bntann1_t ann; uint8_t zero = 0;
+    if (!bns) {
+        memset(&stub, 0, sizeof(stub)); memset(&ann, 0, sizeof(ann));
+        stub.l_pac = (int64_t)(bwt->seq_len / 2); stub.n_seqs = 1; stub.anns = &ann; ann.len = (int32_t)stub.l_pac;
+        bns = &stub;
+    }
+    int rc;
+    if (pac) rc = b200_index_upload(c, bwt, bns, pac, B200_IDX_FULL_SA);
+    else {
+        std::vector<uint8_t> z((size_t)(bns->l_pac / 4 + 1), zero);
+        rc = b200_index_upload(c, bwt, bns, z.data(), 0);
+    }
+    if (rc) { fprintf(stderr, "[b200] %s\n", b200_last_error()); exit(1); }
+    c->bwt_identity = bwt;
+    g_reg.push_back(c);
+    return c;
+}
+
+// ---- primitive batches -----------------------------------------------------------------------
+static int need_index(b200_ctx *ctx)
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { b200_set_error("cudaSetDevice failed"); return -1; }
+    return 0;
+}
+
+extern "C" int b200_occ4_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, uint64_t *cnt)
+{
+    if (need_index(ctx)) return -1;
+    if (n <= 0) return 0;
+    if (ctx->d_pa.ensure(n * 8) || ctx->d_pb.ensure(n * 32)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, k, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    if (launch_occ_batch(ctx->ix, n, ctx->d_pa.as<u64>(), nullptr, ctx->d_pb.as<u64>(), nullptr, ctx->st)) return -1;
+    B200_CHECK(cudaMemcpyAsync(cnt, ctx->d_pb.p, n * 32, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int b200_2occ4_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, const uint64_t *l, uint64_t *cntk, uint64_t *cntl)
+{
+    if (need_index(ctx)) return -1;
+    if (n <= 0) return 0;
+    if (ctx->d_pa.ensure(n * 8) || ctx->d_pb.ensure(n * 32) || ctx->d_pc.ensure(n * 8) || ctx->d_pd.ensure(n * 32)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, k, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pc.p, l, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    if (launch_occ_batch(ctx->ix, n, ctx->d_pa.as<u64>(), ctx->d_pc.as<u64>(), ctx->d_pb.as<u64>(), ctx->d_pd.as<u64>(), ctx->st)) return -1;
+    B200_CHECK(cudaMemcpyAsync(cntk, ctx->d_pb.p, n * 32, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(cntl, ctx->d_pd.p, n * 32, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int b200_extend_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *ik, int is_back, uint64_t *ok)
+{
+    if (need_index(ctx)) return -1;
+    if (n <= 0) return 0;
+    if (ctx->d_pa.ensure(n * 24) || ctx->d_pb.ensure(n * 96)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, ik, n * 24, cudaMemcpyHostToDevice, ctx->st));
+    if (launch_extend_batch(ctx->ix, n, ctx->d_pa.as<u64>(), is_back, ctx->d_pb.as<u64>(), ctx->st)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ok, ctx->d_pb.p, n * 96, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int b200_sa_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, uint64_t *sa, int use_full_sa)
+{
+    if (need_index(ctx)) return -1;
+    if (n <= 0) return 0;
+    if (ctx->d_pa.ensure(n * 8) || ctx->d_pb.ensure(n * 8)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, k, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    if (launch_sa_batch(ctx->ix, n, ctx->d_pa.as<u64>(), ctx->d_pb.as<u64>(), use_full_sa, ctx->st)) return -1;
+    B200_CHECK(cudaMemcpyAsync(sa, ctx->d_pb.p, n * 8, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int b200_ksw_extend2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                                      const int32_t *tlen, const int64_t *toff, const uint8_t *t, const int8_t *mat,
+                                      int o_del, int e_del, int o_ins, int e_ins, const int32_t *w, int end_bonus,
+                                      int zdrop, const int32_t *h0, int32_t *out)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    if (n <= 0) return 0;
+    i64 qbytes = 0, tbytes = 0; int maxq = 0;
+    for (i64 i = 0; i < n; ++i) {
+        if (qoff[i] + qlen[i] > qbytes) qbytes = qoff[i] + qlen[i];
+        if (toff[i] + tlen[i] > tbytes) tbytes = toff[i] + tlen[i];
+        if (qlen[i] > maxq) maxq = qlen[i];
+        if (h0[i] <= 0) { b200_set_error("ksw_extend2 requires h0 > 0 (ksw.c:385)"); return -1; }
+    }
+    const int grid = ctx->n_sms * 4;
+    const int eh_cap = maxq + 2;
+    if (ctx->d_pa.ensure(n * 4) || ctx->d_pb.ensure(n * 8) || ctx->d_pc.ensure(qbytes + 1) || ctx->d_pd.ensure(n * 4) ||
+        ctx->d_pe.ensure(n * 8) || ctx->d_pf.ensure(tbytes + 1) || ctx->d_pg.ensure(n * 8) || ctx->d_ph.ensure(n * 24) ||
+        ctx->d_eh.ensure((size_t)grid * 4 * 2 * eh_cap * 4) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, qlen, n * 4, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pb.p, qoff, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pc.p, q, qbytes, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pd.p, tlen, n * 4, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pe.p, toff, n * 8, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pf.p, t, tbytes, cudaMemcpyHostToDevice, ctx->st));
+    i32 *wh = ctx->d_pg.as<i32>();
+    B200_CHECK(cudaMemcpyAsync(wh, w, n * 4, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(wh + n, h0, n * 4, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemsetAsync(ctx->d_ctl.p, 0, CTL_SLOTS * 8, ctx->st));
+    KswBatchParams P;
+    P.n = n; P.qlen = ctx->d_pa.as<i32>(); P.qoff = ctx->d_pb.as<i64>(); P.q = ctx->d_pc.as<u8>();
+    P.tlen = ctx->d_pd.as<i32>(); P.toff = ctx->d_pe.as<i64>(); P.t = ctx->d_pf.as<u8>();
+    memcpy(P.mat, mat, 25);
+    P.o_del = o_del; P.e_del = e_del; P.o_ins = o_ins; P.e_ins = e_ins; P.w = wh; P.end_bonus = end_bonus; P.zdrop = zdrop;
+    P.h0 = wh + n; P.out = ctx->d_ph.as<i32>(); P.eh = ctx->d_eh.as<i32>(); P.eh_cap = eh_cap;
+    P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK);
+    if (launch_ksw_batch(P, grid, 128, ctx->st)) return -1;
+    B200_CHECK(cudaMemcpyAsync(out, ctx->d_ph.p, n * 24, cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}

@@ -1,0 +1,57 @@
+// Host-side context: device index + grow-only device buffers for the batch pipeline.
+#pragma once
+#include "b200_internal.h"
+#include <vector>
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need)            // grow-only; contents are NOT preserved
+    {
+        if (need <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        size_t want = need + need / 8 + 256;
+        if (cudaMalloc(&p, want) != cudaSuccess) { p = nullptr; b200_set_error("cudaMalloc(%zu) failed", want); return -1; }
+        bytes = want;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <class T> T *as() const { return (T *)p; }
+};
+
+struct b200_ctx {
+    int device = 0;
+    int n_sms = 148;
+    cudaStream_t st = nullptr;
+    bool has_index = false;
+    DevIndex ix;
+    DevBuf d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
+    const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
+
+    // resident input batch
+    DevBuf d_seq, d_off;
+    int n_reads = 0; i64 n_bytes = 0; int max_len = 0;
+    std::vector<i64> h_off;
+
+    // tunables
+    int chunk_reads = 1 << 20;
+    int cap_intv = 0;                          // 0 = auto from read length
+
+    // per-chunk intermediates
+    DevBuf d_intv, d_intv_n, d_lists, d_seed_n, d_seed_off, d_l_rep, d_seeds, d_cseeds, d_chains, d_chn_n,
+           d_cseed_n, d_scratch, d_stage, d_eh, d_srt, d_arena, d_reg_off, d_reg_n, d_dst_off, d_scan_tmp,
+           d_ctl;                              // counters / flags / stats block
+    // whole-batch result
+    DevBuf d_final, d_final_n;
+    i64 total_regs = 0;
+    unsigned long long stats[CNT_N] = {0};
+    // scratch for the primitive batches
+    DevBuf d_pa, d_pb, d_pc, d_pd, d_pe, d_pf, d_pg, d_ph;
+};
+
+// layout of d_ctl (all 8-byte slots)
+enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };
+
+int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
+b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac);

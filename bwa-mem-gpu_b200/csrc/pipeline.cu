@@ -1,0 +1,374 @@
+// Batch pipeline (the new "batched read scheduler"): reads resident on the device are pushed through
+// pack -> SMEM -> seeds/SA -> chain/filter -> extend/dedup in chunks that reuse grow-only intermediate
+// buffers; results are compacted in read order.  Replaces mem_align_GPU / miniBatchMain
+// (cuda/bwamem_GPU.cu:3457, cuda/minibatch_process.cpp:188) and worker1 of mem_process_seqs
+// (bwamem.c:1183-1195, 1232).
+#include "ctx.h"
+#include <string.h>
+#include <stdlib.h>
+#include <stdio.h>
+#include <algorithm>
+
+static inline unsigned *ctl_u32(b200_ctx *c, int slot) { return (unsigned *)(c->d_ctl.as<u64>() + slot); }
+static inline unsigned long long *ctl_u64(b200_ctx *c, int slot) { return (unsigned long long *)(c->d_ctl.as<u64>() + slot); }
+
+static int ctl_zero(b200_ctx *c, int slot, int n = 1)
+{
+    B200_CHECK(cudaMemsetAsync(c->d_ctl.as<u64>() + slot, 0, 8 * (size_t)n, c->st));
+    return 0;
+}
+static int ctl_read(b200_ctx *c, int slot, int n, u64 *out)
+{
+    B200_CHECK(cudaMemcpyAsync(out, c->d_ctl.as<u64>() + slot, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->st));
+    B200_CHECK(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+extern "C" int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *seqs, const int64_t *off)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    const i64 base = n_reads ? off[0] : 0, nbytes = n_reads ? off[n_reads] - base : 0;
+    ctx->h_off.resize((size_t)n_reads + 1);
+    int mx = 0;
+    for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
+    for (int i = 0; i < n_reads; ++i) mx = std::max<int>(mx, (int)(off[i + 1] - off[i]));
+    if (ctx->d_seq.ensure((size_t)nbytes + 64) || ctx->d_off.ensure(((size_t)n_reads + 1) * 8)) return -1;
+    if (nbytes) B200_CHECK(cudaMemcpyAsync(ctx->d_seq.p, seqs + base, (size_t)nbytes, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_off.p, ctx->h_off.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    ctx->n_reads = n_reads; ctx->n_bytes = nbytes; ctx->max_len = mx;
+    ctx->total_regs = 0;
+    return 0;
+}
+
+static int auto_cap_intv(const b200_ctx *ctx, const mem_opt_t *opt)
+{
+    if (ctx->cap_intv > 0) return ctx->cap_intv;
+    // SMEMs of length >= min_seed_len: pass 1 can emit at most len - min_seed_len + 1, in practice a handful;
+    // size for len/4 + 16 (>= 53 for 150 bp) and report an overflow instead of truncating silently.
+    int c = ctx->max_len / 4 + 16;
+    return c < 32 ? 32 : c;
+}
+
+struct StageTimer {
+    cudaEvent_t ev[8]; int n = 0; bool on = false;
+    void init(bool enable) { on = enable; if (on) for (auto &e : ev) cudaEventCreate(&e); }
+    void mark(cudaStream_t st) { if (on && n < 8) cudaEventRecord(ev[n++], st); }
+    void fini() { if (on) for (auto &e : ev) cudaEventDestroy(e); }
+};
+
+// stop_after: 1 = SMEM intervals, 2 = seeds, 3 = chains (opt stage in chain_stage), 5 = everything
+static int g_chain_stage = 1;
+
+int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms)
+{
+    cudaStream_t st = ctx->st;
+    const i64 *d_off = ctx->d_off.as<i64>() + r0;
+    const i64 byte0 = ctx->h_off[r0], nbytes = ctx->h_off[r0 + n] - byte0;
+    (void)nbytes;
+    StageTimer tm; tm.init(stage_ms != nullptr);
+    if (ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
+    if (ctl_zero(ctx, 0, CTL_SLOTS)) return -1;
+    u64 launches = 0;
+
+    tm.mark(st);
+    // ---- K0: ASCII -> nt4 (idempotent on already-packed input)
+    if (launch_pack_reads(ctx->d_seq.as<u8>() + byte0, ctx->h_off[r0 + n] - byte0, st)) return -1;
+    ++launches;
+    tm.mark(st);
+
+    // ---- K1: SMEM collection
+    const int cap_intv = auto_cap_intv(ctx, opt);
+    int blocks = std::min((n + 127) / 128, ctx->n_sms * 8);
+    const int list_cap = ctx->max_len + 1;
+    {   // keep the interval-list scratch under ~2 GB for long reads
+        size_t per_block = (size_t)128 * 2 * list_cap * sizeof(Intv);
+        size_t max_blocks = std::max<size_t>(ctx->n_sms, ((size_t)2 << 30) / per_block);
+        blocks = (int)std::min<size_t>(blocks, max_blocks);
+    }
+    if (ctx->d_intv.ensure((size_t)n * cap_intv * sizeof(Intv)) || ctx->d_intv_n.ensure((size_t)n * 4) ||
+        ctx->d_lists.ensure((size_t)blocks * 128 * 2 * list_cap * sizeof(Intv))) return -1;
+    SmemParams SP;
+    memset(&SP, 0, sizeof(SP));
+    SP.ix = ctx->ix; SP.seq = ctx->d_seq.as<u8>(); SP.off = d_off; SP.n_reads = n;
+    SP.min_seed_len = opt->min_seed_len;
+    SP.split_len = (int)(opt->min_seed_len * opt->split_factor + .499);      // bwamem.c:141
+    SP.split_width = opt->split_width; SP.max_mem_intv = opt->max_mem_intv;
+    SP.out = ctx->d_intv.as<Intv>(); SP.cap_out = cap_intv; SP.out_n = ctx->d_intv_n.as<i32>();
+    SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap;
+    SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
+    if (launch_smem_collect(SP, blocks, 128, st)) return -1;
+    ++launches;
+    tm.mark(st);
+    if (stop_after == 1) {
+        u64 ovf;
+        if (ctl_read(ctx, CTL_OVF, 1, &ovf)) return -1;
+        if ((int)(ovf & 0xffffffff)) { b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
+        if (ovf >> 32) { b200_set_error("interval list scratch overflow"); return -2; }
+        tm.fini();
+        return 0;
+    }
+
+    // ---- K2: seeds + SA location
+    if (ctx->d_seed_n.ensure((size_t)n * 4) || ctx->d_seed_off.ensure(((size_t)n + 1) * 8) || ctx->d_l_rep.ensure((size_t)n * 4) ||
+        ctx->d_scan_tmp.ensure(((size_t)n / 1024 + 2) * 8)) return -1;
+    SeedParams DP;
+    memset(&DP, 0, sizeof(DP));
+    DP.ix = ctx->ix; DP.off = d_off; DP.n_reads = n;
+    DP.intv = ctx->d_intv.as<Intv>(); DP.cap_intv = cap_intv; DP.intv_n = ctx->d_intv_n.as<i32>();
+    DP.max_occ = opt->max_occ;
+    DP.seed_n = ctx->d_seed_n.as<i32>(); DP.seed_off = ctx->d_seed_off.as<i64>(); DP.l_rep = ctx->d_l_rep.as<i32>();
+    DP.stats = ctl_u64(ctx, CTL_STATS);
+    if (launch_seed_count(DP, st)) return -1;
+    if (launch_exclusive_scan(DP.seed_n, ctx->d_seed_off.as<i64>(), n, ctx->d_scan_tmp.as<i64>(), st)) return -1;
+    launches += 4;
+    i64 tot_seeds = 0;
+    u64 ovf = 0;
+    B200_CHECK(cudaMemcpyAsync(&tot_seeds, ctx->d_seed_off.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
+    if (ctl_read(ctx, CTL_OVF, 1, &ovf)) return -1;                         // also synchronises
+    if ((int)(ovf & 0xffffffff)) { b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
+    if (ovf >> 32) { b200_set_error("interval list scratch overflow"); return -2; }
+    if (ctx->d_seeds.ensure((size_t)(tot_seeds + 1) * sizeof(Seed))) return -1;
+    DP.seeds = ctx->d_seeds.as<Seed>(); DP.n_seeds = tot_seeds;
+    if (launch_seed_fill(DP, st)) return -1;
+    if (launch_sa_locate(DP, st)) return -1;
+    launches += 2;
+    ctx->stats[CNT_SEEDS] += tot_seeds;
+    ctx->stats[CNT_SA] += tot_seeds;
+    tm.mark(st);
+    if (stop_after == 2) { B200_CHECK(cudaStreamSynchronize(st)); tm.fini(); return 0; }
+
+    // ---- K3: chaining + filtering
+    if (ctx->d_cseeds.ensure((size_t)(tot_seeds + 1) * sizeof(Seed)) || ctx->d_chains.ensure((size_t)(tot_seeds + 1) * sizeof(ChainRec)) ||
+        ctx->d_chn_n.ensure((size_t)n * 4) || ctx->d_cseed_n.ensure((size_t)n * 4) ||
+        ctx->d_scratch.ensure(((size_t)16 * tot_seeds + (size_t)128 * n + 64) * 4)) return -1;
+    ChainParams CP;
+    memset(&CP, 0, sizeof(CP));
+    CP.ix = ctx->ix; CP.opt = *opt; CP.off = d_off; CP.n_reads = n;
+    CP.seeds = ctx->d_seeds.as<Seed>(); CP.seed_off = ctx->d_seed_off.as<i64>(); CP.seed_n = ctx->d_seed_n.as<i32>();
+    CP.l_rep = ctx->d_l_rep.as<i32>(); CP.scratch = ctx->d_scratch.as<int>(); CP.stage = stop_after == 3 ? g_chain_stage : 1;
+    CP.chn_n = ctx->d_chn_n.as<i32>(); CP.cseed_n = ctx->d_cseed_n.as<i32>();
+    CP.chn_off = ctx->d_seed_off.as<i64>(); CP.cseed_off = ctx->d_seed_off.as<i64>();
+    CP.chains = ctx->d_chains.as<ChainRec>(); CP.cseeds = ctx->d_cseeds.as<Seed>();
+    CP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
+    if (launch_chain(CP, 1, st)) return -1;
+    ++launches;
+    tm.mark(st);
+    if (stop_after == 3) {
+        if (ctl_read(ctx, CTL_OVF2, 1, &ovf)) return -1;
+        if (ovf) { b200_set_error("chain B-tree pool overflow"); return -2; }
+        tm.fini();
+        return 0;
+    }
+
+    // ---- K4: extension + dedup
+    const int ext_blocks = std::max(1, std::min((n + 3) / 4, ctx->n_sms * 8));
+    const int cap_stage = 512, srt_cap = 8192, eh_cap = ctx->max_len + 2;
+    const i64 arena_cap = tot_seeds + 1;
+    if (ctx->d_stage.ensure((size_t)ext_blocks * 4 * cap_stage * sizeof(mem_alnreg_t)) ||
+        ctx->d_eh.ensure((size_t)ext_blocks * 4 * 2 * eh_cap * 4) || ctx->d_srt.ensure((size_t)ext_blocks * 4 * srt_cap * 8) ||
+        ctx->d_arena.ensure((size_t)arena_cap * sizeof(mem_alnreg_t)) || ctx->d_reg_off.ensure((size_t)n * 8) ||
+        ctx->d_reg_n.ensure((size_t)n * 4) || ctx->d_dst_off.ensure(((size_t)n + 1) * 8)) return -1;
+    if (ctl_zero(ctx, CTL_WORK)) return -1;
+    ExtParams EP;
+    memset(&EP, 0, sizeof(EP));
+    EP.ix = ctx->ix; EP.opt = *opt; EP.seq = ctx->d_seq.as<u8>(); EP.off = d_off; EP.n_reads = n;
+    EP.chains = ctx->d_chains.as<ChainRec>(); EP.chn_off = ctx->d_seed_off.as<i64>(); EP.chn_n = ctx->d_chn_n.as<i32>();
+    EP.cseeds = ctx->d_cseeds.as<Seed>();
+    EP.regs = ctx->d_stage.as<mem_alnreg_t>(); EP.cap_regs = cap_stage;
+    EP.eh = ctx->d_eh.as<i32>(); EP.eh_cap = eh_cap; EP.srt = ctx->d_srt.as<u64>(); EP.srt_cap = srt_cap;
+    EP.out = ctx->d_arena.as<mem_alnreg_t>(); EP.out_cap = arena_cap; EP.out_used = ctl_u64(ctx, CTL_ARENA_USED);
+    EP.reg_off = ctx->d_reg_off.as<i64>(); EP.reg_n = ctx->d_reg_n.as<i32>();
+    EP.work_counter = ctl_u32(ctx, CTL_WORK); EP.stats = ctl_u64(ctx, CTL_STATS); EP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
+    if (launch_extend(EP, ext_blocks, 128, st)) return -1;
+    ++launches;
+    // read-ordered compaction into the batch result
+    if (launch_exclusive_scan(EP.reg_n, ctx->d_dst_off.as<i64>(), n, ctx->d_scan_tmp.as<i64>(), st)) return -1;
+    launches += 3;
+    i64 tot_regs = 0;
+    u64 ctl[CTL_SLOTS];
+    B200_CHECK(cudaMemcpyAsync(&tot_regs, ctx->d_dst_off.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
+    if (ctl_read(ctx, 0, CTL_SLOTS, ctl)) return -1;
+    if (ctl[CTL_OVF2]) { b200_set_error("extension stage overflow (code %d)", (int)ctl[CTL_OVF2]); return -2; }
+    // grow the final buffer preserving earlier chunks
+    {
+        size_t need = (size_t)(ctx->total_regs + tot_regs + 1) * sizeof(mem_alnreg_t);
+        if (need > ctx->d_final.bytes) {
+            DevBuf nb;
+            if (nb.ensure(need * 2)) return -1;
+            if (ctx->total_regs) B200_CHECK(cudaMemcpyAsync(nb.p, ctx->d_final.p, (size_t)ctx->total_regs * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st));
+            B200_CHECK(cudaStreamSynchronize(st));
+            ctx->d_final.release();
+            ctx->d_final = nb;
+        }
+    }
+    if (launch_gather_regs(ctx->d_arena.as<mem_alnreg_t>(), EP.reg_off, EP.reg_n, ctx->d_dst_off.as<i64>(), n,
+                           ctx->d_final.as<mem_alnreg_t>() + ctx->total_regs, st)) return -1;
+    ++launches;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_final_n.as<i32>() + r0, EP.reg_n, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    tm.mark(st);
+    B200_CHECK(cudaStreamSynchronize(st));
+    ctx->total_regs += tot_regs;
+    for (int i = 0; i < CNT_N; ++i) ctx->stats[i] += ctl[CTL_STATS + i];
+    ctx->stats[CNT_REGS] += tot_regs;
+    ctx->stats[CNT_LAUNCH] += launches;
+    if (stage_ms) {
+        for (int i = 0; i + 1 < tm.n && i < 5; ++i) { float ms = 0; cudaEventElapsedTime(&ms, tm.ev[i], tm.ev[i + 1]); stage_ms[i] += ms; }
+        float ms = 0; cudaEventElapsedTime(&ms, tm.ev[0], tm.ev[tm.n - 1]); stage_ms[5] += ms;
+    }
+    tm.fini();
+    return 0;
+}
+
+extern "C" int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stage_ms)
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    if (stage_ms) for (int i = 0; i < 6; ++i) stage_ms[i] = 0;
+    memset(ctx->stats, 0, sizeof(ctx->stats));
+    ctx->total_regs = 0;
+    if (ctx->d_final_n.ensure((size_t)ctx->n_reads * 4 + 4)) return -1;
+    for (int r0 = 0; r0 < ctx->n_reads; r0 += ctx->chunk_reads) {
+        int n = std::min(ctx->chunk_reads, ctx->n_reads - r0);
+        int rc = b200_run_chunk(ctx, opt, r0, n, 5, stage_ms);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+extern "C" int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    if (out_n && ctx->n_reads) B200_CHECK(cudaMemcpyAsync(out_n, ctx->d_final_n.p, (size_t)ctx->n_reads * 4, cudaMemcpyDeviceToHost, ctx->st));
+    if (ctx->total_regs > cap) { cudaStreamSynchronize(ctx->st); return -ctx->total_regs; }
+    if (ctx->total_regs) B200_CHECK(cudaMemcpyAsync(out_regs, ctx->d_final.p, (size_t)ctx->total_regs * sizeof(mem_alnreg_t), cudaMemcpyDeviceToHost, ctx->st));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return ctx->total_regs;
+}
+
+extern "C" int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out)
+{
+    if (!ctx) return -1;
+    for (int i = 0; i < CNT_N; ++i) out[i] = ctx->stats[i];
+    return 0;
+}
+
+extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                                    const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
+{
+    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    int rc = b200_batch_run(ctx, opt, nullptr);
+    if (rc) return rc;
+    return b200_batch_download(ctx, cap, out_regs, out_n);
+}
+
+// ---- stage seams (parity tests) -----------------------------------------------------------------
+extern "C" int64_t b200_collect_intv_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                                           const int64_t *off, int64_t cap_total, bwtintv_t *out_intv, int32_t *out_n)
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    i64 tot = 0;
+    std::vector<Intv> tmp;
+    for (int r0 = 0; r0 < n_reads; r0 += ctx->chunk_reads) {
+        int n = std::min(ctx->chunk_reads, n_reads - r0);
+        int rc = b200_run_chunk(ctx, opt, r0, n, 1, nullptr);
+        if (rc) return rc;
+        const int cap_intv = auto_cap_intv(ctx, opt);
+        tmp.resize((size_t)n * cap_intv);
+        B200_CHECK(cudaMemcpyAsync(out_n + r0, ctx->d_intv_n.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->st));
+        B200_CHECK(cudaMemcpyAsync(tmp.data(), ctx->d_intv.p, tmp.size() * sizeof(Intv), cudaMemcpyDeviceToHost, ctx->st));
+        B200_CHECK(cudaStreamSynchronize(ctx->st));
+        for (int r = 0; r < n; ++r) {
+            int k = out_n[r0 + r];
+            if (tot + k > cap_total) { b200_set_error("interval output capacity too small"); return -2; }
+            memcpy(out_intv + tot, &tmp[(size_t)r * cap_intv], (size_t)k * sizeof(Intv));
+            tot += k;
+        }
+    }
+    return tot;
+}
+
+extern "C" int b200_chain_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int stage, int n_reads, const uint8_t *seqs,
+                                const int64_t *off, int64_t cap_chn, int64_t *out_chn, int32_t *out_nchn,
+                                int64_t cap_seed, int64_t *out_seed, int64_t *totals)
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    i64 nc = 0, ns = 0;
+    g_chain_stage = stage;
+    for (int r0 = 0; r0 < n_reads; r0 += ctx->chunk_reads) {
+        int n = std::min(ctx->chunk_reads, n_reads - r0);
+        int rc = b200_run_chunk(ctx, opt, r0, n, 3, nullptr);
+        if (rc) { g_chain_stage = 1; return rc; }
+        std::vector<i64> soff((size_t)n + 1);
+        std::vector<i32> cn(n), sn(n);
+        B200_CHECK(cudaMemcpyAsync(soff.data(), ctx->d_seed_off.p, ((size_t)n + 1) * 8, cudaMemcpyDeviceToHost, ctx->st));
+        B200_CHECK(cudaMemcpyAsync(cn.data(), ctx->d_chn_n.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->st));
+        B200_CHECK(cudaMemcpyAsync(sn.data(), ctx->d_cseed_n.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->st));
+        B200_CHECK(cudaStreamSynchronize(ctx->st));
+        std::vector<ChainRec> ch((size_t)soff[n] + 1);
+        std::vector<Seed> sd((size_t)soff[n] + 1);
+        if (soff[n]) {
+            B200_CHECK(cudaMemcpyAsync(ch.data(), ctx->d_chains.p, (size_t)soff[n] * sizeof(ChainRec), cudaMemcpyDeviceToHost, ctx->st));
+            B200_CHECK(cudaMemcpyAsync(sd.data(), ctx->d_cseeds.p, (size_t)soff[n] * sizeof(Seed), cudaMemcpyDeviceToHost, ctx->st));
+            B200_CHECK(cudaStreamSynchronize(ctx->st));
+        }
+        for (int r = 0; r < n; ++r) {
+            out_nchn[r0 + r] = cn[r];
+            for (int i = 0; i < cn[r]; ++i) {
+                const ChainRec &c = ch[(size_t)soff[r] + i];
+                if (nc >= cap_chn || ns + c.n > cap_seed) { g_chain_stage = 1; b200_set_error("chain output capacity too small"); return -2; }
+                i64 *o = out_chn + 8 * nc;
+                u32 fb; memcpy(&fb, &c.frac_rep, 4);
+                o[0] = c.pos; o[1] = c.n; o[2] = c.rid; o[3] = c.w; o[4] = c.kept; o[5] = c.first; o[6] = c.is_alt; o[7] = fb;
+                for (int j = 0; j < c.n; ++j) {
+                    const Seed &s = sd[(size_t)c.seed_off + j];
+                    i64 *q = out_seed + 4 * (ns + j);
+                    q[0] = s.rbeg; q[1] = s.qbeg; q[2] = s.len; q[3] = s.score;
+                }
+                ++nc; ns += c.n;
+            }
+        }
+    }
+    g_chain_stage = 1;
+    totals[0] = nc; totals[1] = ns;
+    return 0;
+}
+
+extern "C" int b200_smem1a_batch(b200_ctx_t *ctx, int64_t n, const uint8_t *seqs, const int64_t *off, const int32_t *x,
+                                 const int32_t *min_intv, uint64_t max_intv, int cap, bwtintv_t *out_intv,
+                                 int32_t *out_n, int32_t *out_ret)
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    if (n <= 0) return 0;
+    if (b200_batch_upload(ctx, (int)n, seqs, off)) return -1;
+    cudaStream_t st = ctx->st;
+    if (launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;
+    int blocks = (int)std::min<i64>((n + 127) / 128, ctx->n_sms * 4);
+    const int list_cap = ctx->max_len + 1;
+    if (ctx->d_intv.ensure((size_t)n * cap * sizeof(Intv)) || ctx->d_intv_n.ensure((size_t)n * 4) || ctx->d_pa.ensure((size_t)n * 4) ||
+        ctx->d_pb.ensure((size_t)n * 4) || ctx->d_pc.ensure((size_t)n * 4) ||
+        ctx->d_lists.ensure((size_t)blocks * 128 * 2 * list_cap * sizeof(Intv)) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
+    if (ctl_zero(ctx, 0, CTL_SLOTS)) return -1;
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, x, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_pb.p, min_intv, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    SmemParams SP;
+    memset(&SP, 0, sizeof(SP));
+    SP.ix = ctx->ix; SP.seq = ctx->d_seq.as<u8>(); SP.off = ctx->d_off.as<i64>(); SP.n_reads = (int)n;
+    SP.out = ctx->d_intv.as<Intv>(); SP.cap_out = cap; SP.out_n = ctx->d_intv_n.as<i32>();
+    SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap;
+    SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
+    SP.px = ctx->d_pa.as<i32>(); SP.pmin_intv = ctx->d_pb.as<i32>(); SP.max_intv = max_intv; SP.out_ret = ctx->d_pc.as<i32>();
+    if (launch_smem_single(SP, blocks, 128, st)) return -1;
+    u64 ovf = 0;
+    if (ctl_read(ctx, CTL_OVF, 1, &ovf)) return -1;
+    if ((int)(ovf & 0xffffffff)) { b200_set_error("interval capacity too small (need %d)", (int)(ovf & 0xffffffff)); return -(int)(ovf & 0xffffffff); }
+    B200_CHECK(cudaMemcpyAsync(out_intv, ctx->d_intv.p, (size_t)n * cap * sizeof(Intv), cudaMemcpyDeviceToHost, st));
+    B200_CHECK(cudaMemcpyAsync(out_n, ctx->d_intv_n.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    B200_CHECK(cudaMemcpyAsync(out_ret, ctx->d_pc.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    B200_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}

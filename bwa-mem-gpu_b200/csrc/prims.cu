@@ -1,0 +1,74 @@
+// Batched FM-index primitives (one problem per thread) and the device-side SA expansion.
+#include "b200_internal.h"
+
+__global__ void occ_batch_kernel(DevIndex ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl)
+{
+    i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    u64 a[4], b[4];
+    if (l) {                       // bwt_2occ4 (bwt.c:189)
+        dev_2occ4(ix, k[t], l[t], a, b, nullptr);
+        for (int c = 0; c < 4; ++c) { ck[4 * t + c] = a[c]; cl[4 * t + c] = b[c]; }
+    } else {                       // bwt_occ4 (bwt.c:169)
+        dev_occ4(ix, k[t], a);
+        for (int c = 0; c < 4; ++c) ck[4 * t + c] = a[c];
+    }
+}
+
+__global__ void extend_batch_kernel(DevIndex ix, i64 n, const u64 *ik, int is_back, u64 *ok)
+{
+    i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    u64 o0[4], o1[4], o2[4];
+    dev_extend(ix, ik[3 * t], ik[3 * t + 1], ik[3 * t + 2], is_back, o0, o1, o2, nullptr);
+    for (int c = 0; c < 4; ++c) { ok[12 * t + 3 * c] = o0[c]; ok[12 * t + 3 * c + 1] = o1[c]; ok[12 * t + 3 * c + 2] = o2[c]; }
+}
+
+__global__ void sa_batch_kernel(DevIndex ix, i64 n, const u64 *k, u64 *out, int use_full)
+{
+    i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    out[t] = use_full ? dev_sa(ix, k[t], nullptr) : dev_sa_walk(ix, k[t], nullptr);
+}
+
+// Full suffix array from the sampled one: row k walks LF to the next sampled row (bwt_sa, bwt.c:86-96).
+// One-off at index load; afterwards every SA lookup of the hot path is a single gather.
+__global__ void build_full_sa_kernel(DevIndex ix, u32 *out32, u64 *out64)
+{
+    u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (; k <= ix.seq_len; k += stride) {
+        u64 v = dev_sa_walk(ix, k, nullptr);
+        if (out32) out32[k] = (u32)v; else out64[k] = v;
+    }
+}
+
+int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    B200_LAUNCH(occ_batch_kernel, (int)((n + 127) / 128), 128, 0, st, ix, n, k, l, ck, cl);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+int launch_extend_batch(const DevIndex &ix, i64 n, const u64 *ik, int is_back, u64 *ok, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    B200_LAUNCH(extend_batch_kernel, (int)((n + 127) / 128), 128, 0, st, ix, n, ik, is_back, ok);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+int launch_sa_batch(const DevIndex &ix, i64 n, const u64 *k, u64 *out, int use_full, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    B200_LAUNCH(sa_batch_kernel, (int)((n + 127) / 128), 128, 0, st, ix, n, k, out, use_full);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+int launch_build_full_sa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st)
+{
+    u64 n = ix.seq_len + 1;
+    int grid = (int)((n + 255) / 256 < 148 * 32 ? (n + 255) / 256 : 148 * 32);
+    B200_LAUNCH(build_full_sa_kernel, grid, 256, 0, st, ix, out32, out64);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,212 @@
+"""ctypes binding of the C ABI in include/bwamem_b200.h.
+
+The product library is `libbwamem_b200.so` (nvcc, sm_100a), in-tree next to this file.  There is NO
+CPU implementation behind this binding: `load()` raises if the CUDA library is missing, and
+`Context()` raises if no CUDA device is present.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .abi import ALNREG_DTYPE, INTV_DTYPE, MemOpt
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PRODUCT_SO = os.path.join(HERE, "libbwamem_b200.so")
+
+IDX_FULL_SA = 0x1
+
+_SYMBOLS = [
+    "b200_ctx_create", "b200_ctx_destroy", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
+    "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
+    "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_align_batch",
+    "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
+    "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
+]
+
+
+def exported_symbols():
+    return list(_SYMBOLS)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def load(path: str | None = None) -> C.CDLL:
+    path = path or PRODUCT_SO
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)")
+    lib = C.CDLL(path, mode=os.RTLD_LOCAL)
+    lib.b200_ctx_create.restype = C.c_void_p
+    lib.b200_ctx_create.argtypes = [C.c_int]
+    lib.b200_ctx_destroy.argtypes = [C.c_void_p]
+    lib.b200_last_error.restype = C.c_char_p
+    lib.b200_collect_intv_batch.restype = C.c_int64
+    lib.b200_align_batch.restype = C.c_int64
+    lib.b200_batch_download.restype = C.c_int64
+    return lib
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+class Context:
+    """One GPU: device index + batch pipeline (mirrors process_data_t / transferIndex of the reference)."""
+
+    def __init__(self, device: int = 0, lib: C.CDLL | None = None):
+        self.lib = lib or load()
+        h = self.lib.b200_ctx_create(device)
+        if not h:
+            raise B200Error(self.lib.b200_last_error().decode())
+        self.h = C.c_void_p(h)
+
+    def close(self):
+        if self.h:
+            self.lib.b200_ctx_destroy(self.h)
+            self.h = None
+
+    def _chk(self, rc, what):
+        if rc < 0:
+            raise B200Error(f"{what}: {self.lib.b200_last_error().decode()} (rc={rc})")
+        return rc
+
+    # ---------------- index
+    def upload_index_structs(self, bwt_ptr, bns_ptr, pac_ptr, flags=IDX_FULL_SA):
+        self._chk(self.lib.b200_index_upload(self.h, C.c_void_p(bwt_ptr), C.c_void_p(bns_ptr), C.c_void_p(pac_ptr),
+                                             C.c_int(flags)), "index_upload")
+
+    def upload_index(self, bwt_words, primary, L2, seq_len, sa, sa_intv, pac, l_pac, ann_off, ann_len, ann_alt,
+                     flags=IDX_FULL_SA):
+        bwt_words = np.ascontiguousarray(bwt_words, dtype=np.uint32)
+        sa = np.ascontiguousarray(sa, dtype=np.uint64)
+        pac = np.ascontiguousarray(pac, dtype=np.uint8)
+        assert len(pac) >= l_pac // 4 + 1
+        ann_off = np.ascontiguousarray(ann_off, dtype=np.int64)
+        ann_len = np.ascontiguousarray(ann_len, dtype=np.int32)
+        ann_alt = np.ascontiguousarray(ann_alt, dtype=np.int32)
+        l2 = (C.c_uint64 * 5)(*[int(x) for x in L2])
+        self._chk(self.lib.b200_index_upload_raw(
+            self.h, _p(bwt_words, C.c_uint32), C.c_uint64(len(bwt_words)), C.c_uint64(primary), l2,
+            C.c_uint64(seq_len), _p(sa, C.c_uint64), C.c_uint64(len(sa)), C.c_int(sa_intv), _p(pac, C.c_uint8),
+            C.c_int64(l_pac), C.c_int(len(ann_off)), _p(ann_off, C.c_int64), _p(ann_len, C.c_int32),
+            _p(ann_alt, C.c_int32), C.c_int(flags)), "index_upload_raw")
+
+    # ---------------- primitives
+    def occ4(self, k):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        out = np.zeros((len(k), 4), dtype=np.uint64)
+        self._chk(self.lib.b200_occ4_batch(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(out, C.c_uint64)), "occ4")
+        return out
+
+    def occ2x4(self, k, l):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        l = np.ascontiguousarray(l, dtype=np.uint64)
+        ok = np.zeros((len(k), 4), dtype=np.uint64)
+        ol = np.zeros((len(k), 4), dtype=np.uint64)
+        self._chk(self.lib.b200_2occ4_batch(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(l, C.c_uint64),
+                                            _p(ok, C.c_uint64), _p(ol, C.c_uint64)), "2occ4")
+        return ok, ol
+
+    def extend(self, ik, is_back):
+        ik = np.ascontiguousarray(ik, dtype=np.uint64)
+        out = np.zeros((len(ik), 4, 3), dtype=np.uint64)
+        self._chk(self.lib.b200_extend_batch(self.h, C.c_int64(len(ik)), _p(ik, C.c_uint64), C.c_int(is_back),
+                                             _p(out, C.c_uint64)), "extend")
+        return out
+
+    def sa_lookup(self, k, use_full=True):
+        k = np.ascontiguousarray(k, dtype=np.uint64)
+        out = np.zeros(len(k), dtype=np.uint64)
+        self._chk(self.lib.b200_sa_batch(self.h, C.c_int64(len(k)), _p(k, C.c_uint64), _p(out, C.c_uint64),
+                                         C.c_int(1 if use_full else 0)), "sa")
+        return out
+
+    def smem1a(self, seqs, off, x, min_intv, max_intv=0, cap=512):
+        n = len(off) - 1
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        min_intv = np.ascontiguousarray(min_intv, dtype=np.int32)
+        out = np.zeros((n, cap), dtype=INTV_DTYPE)
+        cnt = np.zeros(n, dtype=np.int32)
+        ret = np.zeros(n, dtype=np.int32)
+        self._chk(self.lib.b200_smem1a_batch(self.h, C.c_int64(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                             _p(x, C.c_int32), _p(min_intv, C.c_int32), C.c_uint64(max_intv),
+                                             C.c_int(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32),
+                                             _p(ret, C.c_int32)), "smem1a")
+        return out, cnt, ret
+
+    def ksw_extend2(self, qlen, qoff, q, tlen, toff, t, opt: MemOpt, w, end_bonus, zdrop, h0):
+        n = len(qlen)
+        out = np.zeros((n, 6), dtype=np.int32)
+        self._chk(self.lib.b200_ksw_extend2_batch(
+            self.h, C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8), _p(tlen, C.c_int32),
+            _p(toff, C.c_int64), _p(t, C.c_uint8), opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+            _p(w, C.c_int32), C.c_int(end_bonus), C.c_int(zdrop), _p(h0, C.c_int32), _p(out, C.c_int32)), "ksw_extend2")
+        return out
+
+    # ---------------- stage seams
+    def collect_intv(self, opt: MemOpt, seqs, off, cap_per_read=256):
+        n = len(off) - 1
+        cap = max(1, n * cap_per_read)
+        out = np.zeros(cap, dtype=INTV_DTYPE)
+        cnt = np.zeros(max(n, 1), dtype=np.int32)
+        tot = self._chk(self.lib.b200_collect_intv_batch(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8),
+                                                         _p(off, C.c_int64), C.c_int64(cap),
+                                                         C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32)), "collect_intv")
+        return out[:tot].copy(), cnt[:n]
+
+    def chains(self, opt: MemOpt, seqs, off, stage=1, cap_chn_per_read=64, cap_seed_per_read=1024):
+        n = len(off) - 1
+        cc, cs = max(1, n * cap_chn_per_read), max(1, n * cap_seed_per_read)
+        chn = np.zeros((cc, 8), dtype=np.int64)
+        sd = np.zeros((cs, 4), dtype=np.int64)
+        nch = np.zeros(max(n, 1), dtype=np.int32)
+        tot = np.zeros(2, dtype=np.int64)
+        self._chk(self.lib.b200_chain_batch(self.h, C.byref(opt), C.c_int(stage), C.c_int(n), _p(seqs, C.c_uint8),
+                                            _p(off, C.c_int64), C.c_int64(cc), _p(chn, C.c_int64), _p(nch, C.c_int32),
+                                            C.c_int64(cs), _p(sd, C.c_int64), _p(tot, C.c_int64)), "chains")
+        return chn[:tot[0]].copy(), nch[:n], sd[:tot[1]].copy()
+
+    # ---------------- the hot path: worker1 over a batch
+    def align(self, opt: MemOpt, seqs, off, cap_per_read=8):
+        """mem_align1_core for every read; host buffers in/out (copies included)."""
+        n = len(off) - 1
+        cap = max(64, n * cap_per_read)
+        cnt = np.zeros(max(n, 1), dtype=np.int32)
+        while True:
+            out = np.zeros(cap, dtype=ALNREG_DTYPE)
+            tot = self.lib.b200_align_batch(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                            C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
+            if tot >= 0:
+                return out[:tot], cnt[:n]
+            if -tot > cap:
+                cap = int(-tot)
+                continue
+            self._chk(tot, "align")
+
+    def batch_upload(self, seqs, off):
+        n = len(off) - 1
+        self._chk(self.lib.b200_batch_upload(self.h, C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64)), "batch_upload")
+
+    def batch_run(self, opt: MemOpt, want_stage_ms=False):
+        ms = (C.c_float * 6)()
+        self._chk(self.lib.b200_batch_run(self.h, C.byref(opt), ms if want_stage_ms else None), "batch_run")
+        return list(ms) if want_stage_ms else None
+
+    def batch_download(self, n_reads, cap):
+        out = np.zeros(cap, dtype=ALNREG_DTYPE)
+        cnt = np.zeros(max(n_reads, 1), dtype=np.int32)
+        tot = self.lib.b200_batch_download(self.h, C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
+        if tot < 0:
+            return None, int(-tot)
+        return out[:tot], cnt[:n_reads]
+
+    def counters(self):
+        out = np.zeros(16, dtype=np.uint64)
+        self.lib.b200_batch_counters(self.h, _p(out, C.c_uint64))
+        names = ["extend", "two_block", "sa", "lf_steps", "ksw", "cells", "seeds", "chains", "regs", "launches"]
+        return {k: int(out[i]) for i, k in enumerate(names)}

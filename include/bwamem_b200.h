@@ -1,0 +1,227 @@
+/* bwamem_b200.h -- C ABI of the B200-native BWA-MEM alignment core (libbwamem_b200.so).
+ *
+ * Plain C: pointers and sizes only, no CUDA/torch types.  The struct layouts below are this
+ * fork's layouts (sunwookim028/bwa-mem-gpu, bwa 0.7.17-r1198), re-declared here so that the
+ * reference's host code (bwa mem CLI, bwtindex, SAM formatting) can link against this library
+ * without its own bwt.c / ksw.c / bwamem.c seeding-chaining-extension code.  Each entry point cites
+ * the reference interface it replaces (file:line under the reference tree).
+ *
+ * If the reference's own headers are already included (bwa.h / bwt.h / ksw.h), define
+ * BWAMEM_B200_NO_TYPES before including this file to skip the type re-declarations.
+ */
+#ifndef BWAMEM_B200_H_
+#define BWAMEM_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+#include <stdio.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef BWAMEM_B200_NO_TYPES
+/* ---- FM-index (bwt.h:46-66) */
+typedef uint64_t bwtint_t;
+typedef struct {
+	bwtint_t primary;          /* S^{-1}(0) */
+	bwtint_t L2[5];            /* cumulative base counts */
+	bwtint_t seq_len;          /* forward + reverse-complement text length */
+	bwtint_t bwt_size;         /* number of uint32 words in bwt[] */
+	uint32_t *bwt;             /* 64-byte blocks: 4 x uint64 Occ checkpoint + 128 bases 2-bit BWT */
+	uint32_t cnt_table[256];
+	int sa_intv;
+	bwtint_t n_sa;
+	bwtint_t *sa;
+} bwt_t;
+typedef struct { bwtint_t x[3], info; } bwtintv_t;
+typedef struct { int n, m; bwtintv_t *a; } bwtintv_v;
+
+/* ---- reference sequence store (bntseq.h:41-64) */
+typedef struct {
+	int64_t offset;
+	int32_t len;
+	int32_t n_ambs;
+	uint32_t gi;
+	int32_t is_alt;
+	char *name, *anno;
+} bntann1_t;
+typedef struct { int64_t offset; int32_t len; char amb; } bntamb1_t;
+typedef struct {
+	int64_t l_pac;
+	int32_t n_seqs;
+	uint32_t seed;
+	bntann1_t *anns;
+	int32_t n_holes;
+	bntamb1_t *ambs;
+	FILE *fp_pac;
+} bntseq_t;
+
+/* ---- options and results (bwa.h:86-171) */
+typedef struct {
+	uint64_t max_mem_intv;
+	int a, b;
+	int o_del, e_del;
+	int o_ins, e_ins;
+	int pen_unpaired;
+	int pen_clip5, pen_clip3;
+	int w;
+	int zdrop;
+	int T;
+	int flag;
+	int min_seed_len;
+	int min_chain_weight;
+	int max_chain_extend;
+	float split_factor;
+	int split_width;
+	int max_occ;
+	int max_chain_gap;
+	int n_threads;
+	int chunk_size;
+	float mask_level;
+	float drop_ratio;
+	float XA_drop_ratio;
+	float mask_level_redun;
+	float mapQ_coef_len;
+	int mapQ_coef_fac;
+	int max_ins;
+	int max_matesw;
+	int max_XA_hits, max_XA_hits_alt;
+	int8_t mat[25];
+} mem_opt_t;
+
+typedef struct {
+	int64_t rb, re;
+	uint64_t hash;
+	float frac_rep;
+	int qb, qe;
+	int rid;
+	int score;
+	int truesc;
+	int sub;
+	int alt_sc;
+	int csub;
+	int sub_n;
+	int w;
+	int seedcov;
+	int secondary;
+	int secondary_all;
+	int seedlen0;
+	int n_comp:30, is_alt:2;
+} mem_alnreg_t;
+typedef struct { int n, m; mem_alnreg_t *a; } mem_alnreg_v;
+
+typedef struct { int low, high; int failed; double avg, std; } mem_pestat_t;
+
+typedef struct {
+	int l_seq, id;
+	char *name, *comment, *seq, *qual, *sam;
+	int8_t l_name, l_comment;
+	int16_t l_qual;
+} bseq1_t;
+
+#define MEM_F_PE        0x2
+#endif /* BWAMEM_B200_NO_TYPES */
+
+/* =====================================================================================
+ * Context and device index loader
+ * replaces: transferIndex / newProcess (cuda/streams.cu:8-104,164) -- blocking cudaMalloc+cudaMemcpy
+ * of bwt/sa/bns/pac.  Here: one upload per GPU, the 64-byte Occ blocks verbatim (128-bit aligned),
+ * the sampled SA expanded once on the device into a full SA (HBM is large), contig table and pac.
+ * ===================================================================================== */
+typedef struct b200_ctx b200_ctx_t;
+
+b200_ctx_t *b200_ctx_create(int device);
+void        b200_ctx_destroy(b200_ctx_t *ctx);
+const char *b200_last_error(void);
+/* flags for b200_index_upload */
+#define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device */
+int b200_index_upload(b200_ctx_t *ctx, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac, int flags);
+/* same, from flat arrays (no reference structs needed) */
+int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_size, uint64_t primary,
+                          const uint64_t L2[5], uint64_t seq_len, const uint64_t *sa, uint64_t n_sa, int sa_intv,
+                          const uint8_t *pac, int64_t l_pac, int n_seqs, const int64_t *ann_offset,
+                          const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
+
+/* =====================================================================================
+ * Batched device entry points (arrays of problems; host buffers in, host buffers out).
+ * All return 0 on success, <0 on error (message in b200_last_error()); a capacity overflow
+ * returns -(needed) where stated.
+ * ===================================================================================== */
+
+/* bwt_occ4 (bwt.c:169) / bwt_2occ4 (bwt.c:189) / bwt_extend (bwt.c:262) / bwt_sa (bwt.c:86) */
+int b200_occ4_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, uint64_t *cnt /* n x 4 */);
+int b200_2occ4_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, const uint64_t *l,
+                     uint64_t *cntk /* n x 4 */, uint64_t *cntl /* n x 4 */);
+int b200_extend_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *ik /* n x 3 */, int is_back,
+                      uint64_t *ok /* n x 4 x 3 */);
+int b200_sa_batch(b200_ctx_t *ctx, int64_t n, const uint64_t *k, uint64_t *sa, int use_full_sa);
+
+/* bwt_smem1a (bwt.c:289): problem p = (read[p], x[p], min_intv[p]); out_intv is cap entries per problem,
+ * sorted by start like the reference; out_ret[p] = the function's return value. */
+int b200_smem1a_batch(b200_ctx_t *ctx, int64_t n, const uint8_t *seqs, const int64_t *off, const int32_t *x,
+                      const int32_t *min_intv, uint64_t max_intv, int cap, bwtintv_t *out_intv,
+                      int32_t *out_n, int32_t *out_ret);
+
+/* mem_collect_intv (bwamem.c:137): all three seeding passes + sort, one result list per read.
+ * out_intv: cap_total entries, read r's list at [out_off[r], out_off[r]+out_n[r]). */
+int64_t b200_collect_intv_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                                const int64_t *off, int64_t cap_total, bwtintv_t *out_intv, int32_t *out_n);
+
+/* mem_chain (bwamem.c:258) [stage 0] + mem_chain_flt (bwamem.c:334) [stage 1]
+ * out_chn: 8 x int64 per chain: pos, n, rid, w, kept, first, is_alt, frac_rep(float bits)
+ * out_seed: 4 x int64 per seed: rbeg, qbeg, len, score.  totals[0..1] = chains, seeds written. */
+int b200_chain_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int stage, int n_reads, const uint8_t *seqs,
+                     const int64_t *off, int64_t cap_chn, int64_t *out_chn, int32_t *out_nchn,
+                     int64_t cap_seed, int64_t *out_seed, int64_t *totals);
+
+/* ksw_extend2 (ksw.c:380) over an array of problems; out: 6 x int32 per problem:
+ * score, qle, tle, gtle, gscore, max_off */
+int b200_ksw_extend2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                           const int32_t *tlen, const int64_t *toff, const uint8_t *t, const int8_t *mat,
+                           int o_del, int e_del, int o_ins, int e_ins, const int32_t *w, int end_bonus,
+                           int zdrop, const int32_t *h0, int32_t *out);
+
+/* mem_align1_core (bwamem.c:1061) for a batch = worker1 of mem_process_seqs (bwamem.c:1183):
+ * seeding -> chaining -> filtering -> extension -> mem_sort_dedup_patch.  Reads may be ASCII or nt4.
+ * out_regs holds cap records; read r's regions are the next out_n[r] records in read order.
+ * Returns the total number of regions, or -(needed) if cap is too small. */
+int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                         const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n);
+
+/* Device-resident variant used for kernel-only timing: inputs are uploaded once with
+ * b200_batch_upload(), b200_batch_run() launches the whole stage pipeline without host copies and
+ * b200_batch_download() fetches the regions.  stage_ms (may be NULL) receives CUDA-event times:
+ * [0]=pack [1]=smem [2]=seed/sa [3]=chain [4]=extend [5]=total. */
+int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *seqs, const int64_t *off);
+int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stage_ms);
+int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n);
+/* work counters of the last b200_batch_run (for the roofline arithmetic):
+ * [0]=bwt_extend calls [1]=of which touched two Occ blocks [2]=SA lookups [3]=LF steps walked
+ * [4]=ksw_extend2 calls [5]=DP cells (sum over rows of end-beg) [6]=seeds [7]=chains kept [8]=regions
+ * [9]=kernel launches */
+int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out /* 16 */);
+
+/* =====================================================================================
+ * Drop-in scalar entry points: the reference's own names and signatures.  Each call runs the
+ * device code on a batch of one (parity tests call these one problem at a time).  The device
+ * context/index is created lazily from the bwt_t identity on first use.
+ * ===================================================================================== */
+#ifndef BWAMEM_B200_NO_DROPIN
+void     bwt_occ4(const bwt_t *bwt, bwtint_t k, bwtint_t cnt[4]);                                   /* bwt.h:103 */
+void     bwt_2occ4(const bwt_t *bwt, bwtint_t k, bwtint_t l, bwtint_t cntk[4], bwtint_t cntl[4]);  /* bwt.h:109 */
+void     bwt_extend(const bwt_t *bwt, const bwtintv_t *ik, bwtintv_t ok[4], int is_back);           /* bwt.h:117 */
+bwtint_t bwt_sa(const bwt_t *bwt, bwtint_t k);                                                      /* bwt.h:104 */
+int      bwt_smem1a(const bwt_t *bwt, int len, const uint8_t *q, int x, int min_intv, uint64_t max_intv,
+                    bwtintv_v *mem, bwtintv_v *tmpvec[2]);                                          /* bwt.h:124 */
+int      ksw_extend2(int qlen, const uint8_t *query, int tlen, const uint8_t *target, int m, const int8_t *mat,
+                     int o_del, int e_del, int o_ins, int e_ins, int w, int end_bonus, int zdrop, int h0,
+                     int *qle, int *tle, int *gtle, int *gscore, int *max_off);                     /* ksw.h:108 */
+mem_alnreg_v mem_align1_core(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
+                             int l_seq, char *seq, void *buf);                                      /* bwamem.c:1061 */
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif
