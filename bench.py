@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: aligned reads/s of the BWA-MEM alignment core on B200.
+
+Workload (BASELINE.json configs[1]): synthetic 100 Mbp reference (4 x 25 Mbp, seed 20261104), 10 M x 150 bp
+single-end reads (1 % substitutions, 0.015 %/base 1-bp indels) per GPU.  One "step" = one pass of the hot path
+(SMEM seeding -> SA location -> chaining/filtering -> banded extension -> dedup) over that read batch,
+i.e. worker1 / mem_align1_core of mem_process_seqs for every read: reads in, mem_alnreg_t records out.
+
+  value : whole-job reads/s with the reads already resident in HBM (device pipeline only)
+  e2e   : the same through the C ABI call a host program makes (b200_align_batch) with PINNED HOST buffers:
+          H2D of the reads and D2H of the mem_alnreg_t records are inside the timed region
+  --impl reference : the reference's own CPU code (oracle/_ref, mem_align1_core over kt_for with all host
+          threads) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "aligned_reads_per_sec"
+UNIT = "reads/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU per step")
+    ap.add_argument("--contigs", type=int, default=4)
+    ap.add_argument("--contig-len", type=int, default=25_000_000)
+    ap.add_argument("--read-len", type=int, default=150)
+    ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"synthetic {a.contigs}x{a.contig_len / 1e6:g} Mbp reference (seed 20261104), "
+            f"{a.reads / 1e6:g}M x {a.read_len} bp single-end reads per GPU, 1% sub + 0.015%/bp indel")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index: int):
+        super().__init__(daemon=True)
+        self.idx, self.rows, self.stop_flag, self.proc = gpu_index, [], False, None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_inputs(a, rank):
+    from bwa_mem_gpu_b200 import synth
+    contigs = synth.make_genome([a.contig_len] * a.contigs)
+    t0 = time.time()
+    reads, _ = synth.simulate_reads(contigs, a.reads, read_len=a.read_len, seed=1002 + 7919 * rank)
+    seqs = np.ascontiguousarray(reads.reshape(-1))
+    off = np.arange(0, a.reads + 1, dtype=np.int64) * a.read_len
+    return contigs, seqs, off, time.time() - t0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference(a, hidx, seqs, off, n_sample, threads):
+    """The reference's CPU implementation of the same path (mem_align1_core over kt_for), oracle/_ref."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refapi
+    from bwa_mem_gpu_b200 import abi
+    if not refapi.available():
+        return None
+    rl = refapi.RefLib()
+    idx = rl.index_from_arrays(hidx.bwt_words(), hidx.primary, hidx.L2, hidx.seq_len, hidx.sa(), hidx.sa_intv,
+                               hidx.pac(), hidx.l_pac, hidx.ann_off, hidx.ann_len)
+    opt = abi.default_opt()
+    sub_off = off[: n_sample + 1]
+    t0 = time.time()
+    _, cnt = idx.align(opt, seqs, sub_off, n_threads=threads, count_only=True)
+    dt = time.time() - t0
+    return {"value": n_sample / dt, "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": f"first {n_sample} reads of the step's batch, mem_align1_core via kt_for, {dt:.2f} s",
+            "regions": int(cnt.sum())}
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = os.cpu_count() or 1
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        from bwa_mem_gpu_b200 import lib as L
+        n_sample = a.cpu_sample or min(a.reads, max(20000, 4000 * cores))
+        contigs, seqs, off, _ = build_inputs(a, 0)
+        hidx = L.HostIndex(contigs)          # host-side index construction only (no device work)
+        vals = []
+        for s in range(a.warmup + a.steps):
+            r = cpu_reference(a, hidx, seqs, off, n_sample, cores)
+            if r is None:
+                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libbwaref.so not built"}))
+                return
+            if s >= a.warmup:
+                vals.append(r)
+        v = float(np.mean([x["value"] for x in vals]))
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * n_sample / v, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "path": "mem_align1_core batch (reads -> mem_alnreg_t)",
+                       "sample_reads_per_step": n_sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": vals[-1]["sample"]},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from bwa_mem_gpu_b200 import abi, lib as L
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU implementation")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    t_setup = time.time()
+    contigs, seqs, off, t_reads = build_inputs(a, rank)
+    t0 = time.time()
+    hidx = L.HostIndex(contigs)
+    t_index = time.time() - t0
+    ctx = L.Context(local_rank)
+    t0 = time.time()
+    ctx.upload_host_index(hidx)
+    t_upload = time.time() - t0
+    opt = abi.default_opt()
+
+    # ---------------- device-resident timing ("value")
+    ctx.batch_upload(seqs, off)
+    for _ in range(a.warmup):
+        ctx.batch_run(opt, want_stage_ms=True)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    stage = np.zeros(6)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        stage += np.array(ctx.batch_run(opt, want_stage_ms=True))
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.finish()
+    cnt = ctx.counters()
+    dev_ms = stage[5] / a.steps                       # CUDA-event bracket of the whole batch on the launching stream
+    regs_total = cnt["regs"]
+
+    # ---------------- end-to-end through the C ABI with pinned host buffers ("e2e")
+    pin_seq = torch.empty(len(seqs), dtype=torch.uint8).pin_memory()
+    pin_seq.numpy()[:] = seqs
+    cap = int(regs_total * 1.1) + 1024
+    pin_out = torch.empty(cap * abi.ALNREG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    pin_n = torch.empty(a.reads, dtype=torch.int32).pin_memory()
+    import ctypes as C
+
+    def e2e_step():
+        tot = ctx.lib.b200_align_batch(ctx.h, C.byref(opt), C.c_int(a.reads), C.c_void_p(pin_seq.data_ptr()),
+                                       off.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(cap),
+                                       C.c_void_p(pin_out.data_ptr()), C.c_void_p(pin_n.data_ptr()))
+        if tot < 0:
+            raise SystemExit(f"b200_align_batch failed: {ctx.lib.b200_last_error().decode()} ({tot})")
+        return tot
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        tot = e2e_step()
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+
+    # ---------------- max over ranks
+    tvec = torch.tensor([dev_ms, wall * 1e3 / a.steps, e2e_wall * 1e3 / a.steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tvec, op=dist.ReduceOp.MAX)
+    dev_ms_max, wall_ms_max, e2e_ms_max = [float(x) for x in tvec.cpu()]
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg_bytes = 64.0 * (cnt["extend"] + cnt["two_block"])                 # per batch (counters are per last run)
+        smem_ms = stage[1] / a.steps
+        achieved = alg_bytes / (smem_ms * 1e-3) / 1e9 if smem_ms > 0 else 0.0
+        out = {
+            "metric": METRIC, "value": world * a.reads / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms_max, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "path": "mem_align1_core batch (reads -> mem_alnreg_t)",
+                       "l2": "inputs + intermediates per step are GBs (>> 126 MB L2); no explicit flush",
+                       "sharding": "reads sharded per rank, FM-index replicated, no collective on the data path",
+                       "wall_ms_per_step": wall_ms_max, "index_build_s": t_index, "index_upload_s": t_upload,
+                       "read_sim_s": t_reads},
+            "e2e": {"value": world * a.reads / (e2e_ms_max * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": int(len(seqs) + off.nbytes),
+                    "d2h_bytes_per_step": int(tot * abi.ALNREG_DTYPE.itemsize + 4 * a.reads)},
+            "gpu_launches": int(cnt["launches"]) * a.steps,
+            "clocks": clocks,
+            "stage_ms": {k: float(v) / a.steps for k, v in zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], stage)},
+            "counters": cnt,
+            "roofline": {"bound": "hbm", "kernel": "smem_collect_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes": alg_bytes,
+                         "note": "64 B x Occ blocks touched by bwt_extend (1 or 2 per call), summed over the batch"},
+            "extension": {"gcups": cnt["cells"] / (stage[4] / a.steps * 1e-3) / 1e9 if stage[4] > 0 else None,
+                          "cells": cnt["cells"], "ksw_calls": cnt["ksw"]},
+            "smem_lookups_per_sec": cnt["extend"] / (smem_ms * 1e-3) if smem_ms > 0 else None,
+        }
+        if not a.no_cpu_baseline:
+            n_sample = a.cpu_sample or min(a.reads, max(20000, 4000 * cores))
+            cb = cpu_reference(a, hidx, seqs, off, n_sample, cores)
+            if cb is not None:
+                out["cpu_baseline"] = cb
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -229,10 +229,18 @@ extern "C" int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stag
     memset(ctx->stats, 0, sizeof(ctx->stats));
     ctx->total_regs = 0;
     if (ctx->d_final_n.ensure((size_t)ctx->n_reads * 4 + 4)) return -1;
+    cudaEvent_t ea = nullptr, eb = nullptr;               // device-side bracket of the whole batch on the launching stream
+    if (stage_ms) { cudaEventCreate(&ea); cudaEventCreate(&eb); cudaEventRecord(ea, ctx->st); }
     for (int r0 = 0; r0 < ctx->n_reads; r0 += ctx->chunk_reads) {
         int n = std::min(ctx->chunk_reads, ctx->n_reads - r0);
         int rc = b200_run_chunk(ctx, opt, r0, n, 5, stage_ms);
         if (rc) return rc;
+    }
+    if (stage_ms) {
+        cudaEventRecord(eb, ctx->st);
+        cudaEventSynchronize(eb);
+        cudaEventElapsedTime(&stage_ms[5], ea, eb);
+        cudaEventDestroy(ea); cudaEventDestroy(eb);
     }
     return 0;
 }

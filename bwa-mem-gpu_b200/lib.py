@@ -23,6 +23,8 @@ _SYMBOLS = [
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
+    "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
+    "b200_hostidx_pac", "b200_index_upload_host",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
 
@@ -48,7 +50,54 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_collect_intv_batch.restype = C.c_int64
     lib.b200_align_batch.restype = C.c_int64
     lib.b200_batch_download.restype = C.c_int64
+    lib.b200_hostidx_build.restype = C.c_void_p
+    lib.b200_hostidx_build.argtypes = [C.c_void_p, C.c_int64]
+    lib.b200_hostidx_free.argtypes = [C.c_void_p]
+    lib.b200_hostidx_info.argtypes = [C.c_void_p, C.c_void_p]
+    for f in ("b200_hostidx_bwt", "b200_hostidx_sa", "b200_hostidx_pac"):
+        getattr(lib, f).restype = C.c_void_p
+        getattr(lib, f).argtypes = [C.c_void_p]
     return lib
+
+
+class HostIndex:
+    """In-memory index built by our own SA-IS builder (the arrays `bwa index` would write)."""
+
+    def __init__(self, contigs, lib: C.CDLL | None = None, names=None):
+        self.lib = lib or load()
+        fwd = np.ascontiguousarray(np.concatenate(contigs), dtype=np.uint8)
+        self.l_pac = int(len(fwd))
+        h = self.lib.b200_hostidx_build(C.c_void_p(fwd.ctypes.data), C.c_int64(self.l_pac))
+        if not h:
+            raise B200Error("index build failed (bases must be nt4 codes 0..3)")
+        self.h = C.c_void_p(h)
+        info = np.zeros(11, dtype=np.uint64)
+        self.lib.b200_hostidx_info(self.h, C.c_void_p(info.ctypes.data))
+        self.primary = int(info[0])
+        self.L2 = [int(x) for x in info[1:6]]
+        self.seq_len, self.bwt_size, self.n_sa, self.sa_intv = int(info[6]), int(info[7]), int(info[8]), int(info[9])
+        lens = np.array([len(c) for c in contigs], dtype=np.int64)
+        self.ann_off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+        self.ann_len = lens.astype(np.int32)
+        self.ann_alt = np.zeros(len(contigs), dtype=np.int32)
+        self.names = names or [f"chr{i + 1}" for i in range(len(contigs))]
+
+    def bwt_words(self):
+        p = self.lib.b200_hostidx_bwt(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), shape=(self.bwt_size,))
+
+    def sa(self):
+        p = self.lib.b200_hostidx_sa(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint64)), shape=(self.n_sa,))
+
+    def pac(self):
+        p = self.lib.b200_hostidx_pac(self.h)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(self.l_pac // 4 + 1,))
+
+    def close(self):
+        if self.h:
+            self.lib.b200_hostidx_free(self.h)
+            self.h = None
 
 
 class B200Error(RuntimeError):
@@ -95,6 +144,11 @@ class Context:
             C.c_uint64(seq_len), _p(sa, C.c_uint64), C.c_uint64(len(sa)), C.c_int(sa_intv), _p(pac, C.c_uint8),
             C.c_int64(l_pac), C.c_int(len(ann_off)), _p(ann_off, C.c_int64), _p(ann_len, C.c_int32),
             _p(ann_alt, C.c_int32), C.c_int(flags)), "index_upload_raw")
+
+    def upload_host_index(self, hidx: "HostIndex", flags=IDX_FULL_SA):
+        self._chk(self.lib.b200_index_upload_host(self.h, hidx.h, C.c_int(len(hidx.ann_off)), _p(hidx.ann_off, C.c_int64),
+                                                  _p(hidx.ann_len, C.c_int32), _p(hidx.ann_alt, C.c_int32),
+                                                  C.c_int(flags)), "index_upload_host")
 
     # ---------------- primitives
     def occ4(self, k):

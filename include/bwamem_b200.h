@@ -143,6 +143,20 @@ int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_siz
                           const uint8_t *pac, int64_t l_pac, int n_seqs, const int64_t *ann_offset,
                           const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
 
+/* Host-side index construction for in-memory genomes: the same arrays `bwa index` writes
+ * (bwa_idx_build, bwtindex.c:253-323: pac, BWT+Occ blocks, SA sampled every 32 rows), built with an
+ * own SA-IS suffix sorter.  fwd = nt4 codes 0..3 of the concatenated contigs.
+ * info: [0]=primary [1..5]=L2 [6]=seq_len [7]=bwt_size [8]=n_sa [9]=sa_intv [10]=l_pac */
+typedef struct b200_hostidx b200_hostidx_t;
+b200_hostidx_t *b200_hostidx_build(const uint8_t *fwd, int64_t l_pac);
+void            b200_hostidx_free(b200_hostidx_t *h);
+void            b200_hostidx_info(const b200_hostidx_t *h, uint64_t *info /* 11 */);
+const uint32_t *b200_hostidx_bwt(const b200_hostidx_t *h);
+const uint64_t *b200_hostidx_sa(const b200_hostidx_t *h);
+const uint8_t  *b200_hostidx_pac(const b200_hostidx_t *h);
+int b200_index_upload_host(b200_ctx_t *ctx, const b200_hostidx_t *h, int n_seqs, const int64_t *ann_offset,
+                           const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
+
 /* =====================================================================================
  * Batched device entry points (arrays of problems; host buffers in, host buffers out).
  * All return 0 on success, <0 on error (message in b200_last_error()); a capacity overflow

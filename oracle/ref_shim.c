@@ -369,3 +369,39 @@ int64_t ref_process_seqs(void *p, const void *opt_, int64_t n_processed, int n, 
 }
 
 void ref_set_verbose(int v) { bwa_verbose = v; }
+
+/* ---------------------------------------------------------------- index from in-memory arrays
+ * Wraps caller-owned arrays (e.g. the ones produced by the product's own index builder, which the tests
+ * prove byte-identical to bwa_idx_build's) into the reference's bwaidx_t so that the CPU baseline does not
+ * have to re-run `bwa index` on large synthetic genomes.  Arrays must outlive the handle. */
+void *ref_index_from_arrays(const uint32_t *bwt_words, uint64_t bwt_size, uint64_t primary, const uint64_t *L2,
+                            uint64_t seq_len, const uint64_t *sa, uint64_t n_sa, int sa_intv, const uint8_t *pac,
+                            int64_t l_pac, int n_seqs, const int64_t *ann_off, const int32_t *ann_len)
+{
+	bwaidx_t *idx = calloc(1, sizeof(bwaidx_t));
+	bwt_t *bwt = calloc(1, sizeof(bwt_t));
+	bntseq_t *bns = calloc(1, sizeof(bntseq_t));
+	int i;
+	bwt->primary = primary; bwt->seq_len = seq_len; bwt->bwt_size = bwt_size;
+	for (i = 0; i < 5; ++i) bwt->L2[i] = L2[i];
+	bwt->bwt = (uint32_t*)bwt_words; bwt->sa = (bwtint_t*)sa; bwt->n_sa = n_sa; bwt->sa_intv = sa_intv;
+	bwt_gen_cnt_table(bwt);
+	bns->l_pac = l_pac; bns->n_seqs = n_seqs; bns->seed = 11;
+	bns->anns = calloc(n_seqs, sizeof(bntann1_t));
+	for (i = 0; i < n_seqs; ++i) {
+		char nm[32];
+		snprintf(nm, sizeof(nm), "chr%d", i + 1);
+		bns->anns[i].offset = ann_off[i]; bns->anns[i].len = ann_len[i];
+		bns->anns[i].name = strdup(nm); bns->anns[i].anno = strdup("");
+	}
+	idx->bwt = bwt; idx->bns = bns; idx->pac = (uint8_t*)pac;
+	return idx;
+}
+
+void ref_index_release_wrapped(void *p)
+{
+	bwaidx_t *idx = (bwaidx_t*)p;
+	int i;
+	for (i = 0; i < idx->bns->n_seqs; ++i) { free(idx->bns->anns[i].name); free(idx->bns->anns[i].anno); }
+	free(idx->bns->anns); free(idx->bns); free(idx->bwt); free(idx);
+}

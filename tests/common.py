@@ -1,0 +1,114 @@
+"""Shared helpers for the parity tests.
+
+Backends:
+  "emu"  -- tests/emu/_build/libbwamem_b200_emu.so: the product's kernels compiled against the SIMT emulator
+            (logic check in the GPU-less container; `-m "not gpu"`).
+  "cuda" -- bwa-mem-gpu_b200/libbwamem_b200.so on a real GPU (`-m gpu`).
+The checker is the unmodified reference CPU code (oracle/_ref/libbwaref.so) when present, and the committed
+golden vectors under tests/golden/ (generated from it by tests/golden/make_golden.py) otherwise.
+"""
+from __future__ import annotations
+
+import functools
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DATA = os.path.join(ROOT, "tests", "_data")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+EMU_SO = os.path.join(ROOT, "tests", "emu", "_build", "libbwamem_b200_emu.so")
+
+from bwa_mem_gpu_b200 import abi, lib as L, synth  # noqa: E402
+import refapi  # noqa: E402
+
+
+def have_ref():
+    return refapi.available()
+
+
+@functools.lru_cache(maxsize=None)
+def reflib():
+    return refapi.RefLib()
+
+
+@functools.lru_cache(maxsize=None)
+def backend_lib(backend: str):
+    if backend == "emu":
+        if not os.path.exists(EMU_SO):
+            subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "bwa-mem-gpu_b200", "csrc"), "emu", "-j8"])
+        return L.load(EMU_SO)
+    return L.load()
+
+
+GENOMES = {
+    # name: (contig lengths, seed, repeat_frac)
+    "tiny": ([20000, 12000, 7000], 5, 0.0),
+    "small": ([200000, 100000], 7, 0.0),
+    "rep": ([150000, 90000], 9, 0.08),
+}
+
+
+@functools.lru_cache(maxsize=None)
+def genome(name: str):
+    lens, seed, rep = GENOMES[name]
+    return synth.make_genome(lens, seed=seed, repeat_frac=rep)
+
+
+@functools.lru_cache(maxsize=None)
+def ref_index(name: str):
+    os.makedirs(DATA, exist_ok=True)
+    pre = os.path.join(DATA, f"ref_{name}")
+    if not os.path.exists(pre + ".sa"):
+        synth.write_fasta(pre + ".fa", genome(name))
+        reflib().index_build(pre + ".fa", pre)
+    return reflib().index_load(pre)
+
+
+@functools.lru_cache(maxsize=None)
+def context(backend: str, name: str):
+    """Device context holding the index of genome `name`, built by OUR host index builder."""
+    lib = backend_lib(backend)
+    h = L.HostIndex(genome(name), lib)
+    ctx = L.Context(0, lib)
+    ctx.upload_host_index(h)
+    ctx._host_index = h
+    return ctx
+
+
+def reads_for(name: str, n: int, seed: int = 3, read_len: int = 150, sub=0.01, indel=0.002, n_rate=0.0):
+    r, _ = synth.simulate_reads(genome(name), n, read_len=read_len, sub_rate=sub, indel_rate=indel, seed=seed, n_rate=n_rate)
+    seqs = np.ascontiguousarray(r.reshape(-1))
+    off = np.arange(0, n + 1, dtype=np.int64) * read_len
+    return seqs, off
+
+
+def ragged_reads(name: str, seed: int = 17):
+    """Edge cases: empty read, shorter than min_seed_len, all-N, N-interrupted, ASCII mixed case, long."""
+    rng = np.random.default_rng(seed)
+    g = np.concatenate(genome(name))
+    parts = []
+    parts.append(np.zeros(0, dtype=np.uint8))                       # empty
+    parts.append(g[100:110].copy())                                 # < min_seed_len
+    parts.append(np.full(40, 4, dtype=np.uint8))                    # all N
+    a = g[500:700].copy(); a[60] = 4; a[61] = 4; a[150] = 4
+    parts.append(a)                                                 # N inside
+    parts.append(g[1000:1019].copy())                               # exactly min_seed_len
+    parts.append(g[2000:2400].copy())                               # 400 bp exact
+    b = g[3000:3600].copy()
+    m = rng.random(len(b)) < 0.03
+    b[m] = (b[m] + 1) % 4
+    parts.append(b)                                                 # 600 bp, 3 % subs (just below the seed-SW threshold, bwamem.c:609)
+    c = (3 - g[5000:5250])[::-1].copy()
+    parts.append(c)                                                 # reverse strand
+    parts.append(rng.integers(0, 4, size=200, dtype=np.uint8))      # unrelated random
+    d = np.concatenate([g[6000:6100], g[9000:9100]])
+    parts.append(d)                                                 # chimeric
+    seqs = np.concatenate(parts).astype(np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(p) for p in parts])]).astype(np.int64)
+    return np.ascontiguousarray(seqs), off
+
+
+def golden_path(name):
+    return os.path.join(GOLDEN, name)

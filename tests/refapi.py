@@ -55,6 +55,21 @@ class RefLib:
         assert h, f"cannot load {prefix}"
         return RefIndex(self, h)
 
+    def index_from_arrays(self, bwt_words, primary, L2, seq_len, sa, sa_intv, pac, l_pac, ann_off, ann_len) -> "RefIndex":
+        """Wrap in-memory index arrays (kept alive by the returned object) into the reference's bwaidx_t."""
+        keep = [np.ascontiguousarray(bwt_words, dtype=np.uint32), np.ascontiguousarray(sa, dtype=np.uint64),
+                np.ascontiguousarray(pac, dtype=np.uint8), np.ascontiguousarray(ann_off, dtype=np.int64),
+                np.ascontiguousarray(ann_len, dtype=np.int32), np.array(L2, dtype=np.uint64)]
+        self.lib.ref_index_from_arrays.restype = C.c_void_p
+        h = self.lib.ref_index_from_arrays(_p(keep[0], C.c_uint32), C.c_uint64(len(keep[0])), C.c_uint64(primary),
+                                           _p(keep[5], C.c_uint64), C.c_uint64(seq_len), _p(keep[1], C.c_uint64),
+                                           C.c_uint64(len(keep[1])), C.c_int(sa_intv), _p(keep[2], C.c_uint8),
+                                           C.c_int64(l_pac), C.c_int(len(keep[3])), _p(keep[3], C.c_int64),
+                                           _p(keep[4], C.c_int32))
+        ri = RefIndex(self, h)
+        ri._keep, ri._wrapped = keep, True
+        return ri
+
     def opt_init(self) -> MemOpt:
         p = self.lib.ref_opt_init()
         o = MemOpt.from_buffer_copy(C.string_at(p, C.sizeof(MemOpt)))
@@ -106,7 +121,10 @@ class RefIndex:
 
     def close(self):
         if self.h:
-            self.lib.ref_index_destroy(self.h)
+            if getattr(self, "_wrapped", False):
+                self.lib.ref_index_release_wrapped(self.h)
+            else:
+                self.lib.ref_index_destroy(self.h)
             self.h = None
 
     # raw arrays (views over the reference's memory; copy if kept)

@@ -1,0 +1,211 @@
+"""Stage-seam parity of the device code against the unmodified reference CPU implementation
+(SURVEY.md section 8c seams 1-5).  Bit-exact: every comparison is array equality.
+
+Each test runs on the "emu" backend (the same kernels under the SIMT emulator, CPU, `-m "not gpu"`) and on
+the "cuda" backend (`-m gpu`, through the C ABI of libbwamem_b200.so).
+"""
+import numpy as np
+import pytest
+
+import common as cm
+from bwa_mem_gpu_b200 import abi
+
+BACKENDS = [pytest.param("emu", id="emu"), pytest.param("cuda", id="cuda", marks=pytest.mark.gpu)]
+needs_ref = pytest.mark.skipif(not cm.have_ref(), reason="oracle/_ref not built")
+
+
+def _sizes(backend, emu, cuda):
+    return emu if backend == "emu" else cuda
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["tiny", "small"])
+def test_occ_extend_sa(backend, gname):
+    """bwt_occ4 / bwt_2occ4 / bwt_extend / bwt_sa (bwt.c:169,189,262,86) incl. k=-1, k=primary, k=seq_len."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    rng = np.random.default_rng(1)
+    n = _sizes(backend, 4000, 200000)
+    k = rng.integers(0, idx.seq_len + 1, size=n).astype(np.uint64)
+    k[:6] = [0, idx.primary, idx.seq_len, idx.primary - 1, idx.primary + 1, 127]
+    k[6] = np.uint64(2 ** 64 - 1)
+    assert np.array_equal(idx.occ4(k), ctx.occ4(k))
+    l = np.minimum(k + rng.integers(0, 400, size=n).astype(np.uint64), np.uint64(idx.seq_len))
+    l[6] = k[6]
+    a, b = idx.occ2x4(k, l), ctx.occ2x4(k, l)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    # bi-intervals: start from single-base intervals and random valid sub-intervals
+    ik = np.zeros((n, 3), dtype=np.uint64)
+    c = rng.integers(0, 4, size=n)
+    L2 = np.array(idx.L2, dtype=np.uint64)
+    ik[:, 0] = L2[c] + 1
+    ik[:, 1] = L2[3 - c] + 1
+    ik[:, 2] = L2[c + 1] - L2[c]
+    for is_back in (0, 1):
+        o0, o1 = idx.extend(ik, is_back), ctx.extend(ik, is_back)
+        assert np.array_equal(o0, o1)
+        # second generation: extend the children again
+        ch = o0[np.arange(n), rng.integers(0, 4, size=n)]
+        assert np.array_equal(idx.extend(ch, 1 - is_back), ctx.extend(ch, 1 - is_back))
+    kk = k.copy()
+    kk[6] = 5
+    ref_sa = idx.sa_lookup(kk)
+    assert np.array_equal(ref_sa, ctx.sa_lookup(kk, use_full=False))   # LF walk (bwt_sa)
+    assert np.array_equal(ref_sa, ctx.sa_lookup(kk, use_full=True))    # device-expanded full SA
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_smem1a(backend):
+    """bwt_smem1a (bwt.c:289) per (read, x, min_intv), incl. max_intv > 0 and ambiguous bases."""
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    nreads = _sizes(backend, 60, 400)
+    seqs, off = cm.reads_for("small", nreads, seed=11, n_rate=0.004)
+    rng = np.random.default_rng(2)
+    xs = rng.integers(0, 150, size=nreads).astype(np.int32)
+    mi = rng.integers(0, 4, size=nreads).astype(np.int32)
+    for max_intv in (0, 20):
+        out, cnt, ret = ctx.smem1a(seqs, off, xs, mi, max_intv=max_intv, cap=160)
+        for r in range(nreads):
+            q = seqs[off[r]:off[r + 1]]
+            e, eret = idx.smem1a(q, int(xs[r]), int(mi[r]), max_intv)
+            assert ret[r] == eret and cnt[r] == len(e), (r, max_intv)
+            assert out[r, :cnt[r]].tobytes() == e.tobytes(), (r, max_intv)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_collect_intv(backend, gname):
+    """mem_collect_intv (bwamem.c:137): three passes + sort."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 1500, 50000), seed=21, n_rate=0.001)
+    iv0, c0 = idx.collect_intv(opt, seqs, off)
+    iv1, c1 = ctx.collect_intv(opt, seqs, off)
+    assert np.array_equal(c0, c1)
+    assert iv0.tobytes() == iv1.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+@pytest.mark.parametrize("stage", [0, 1])
+def test_chains(backend, gname, stage):
+    """mem_chain (bwamem.c:258) and mem_chain_flt (bwamem.c:334): chain order, seeds, w, kept, first, frac_rep."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 1200, 40000), seed=31)
+    a = idx.chains(opt, seqs, off, stage=stage, cap_chn_per_read=256, cap_seed_per_read=4096)
+    b = ctx.chains(opt, seqs, off, stage=stage, cap_chn_per_read=256, cap_seed_per_read=4096)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def _ksw_problems(rng, n, maxlen=200):
+    qs, ts, ql, tl = [], [], [], []
+    for _ in range(n):
+        lq = int(rng.integers(1, maxlen))
+        q = rng.integers(0, 4, size=lq, dtype=np.uint8)
+        mode = rng.integers(0, 4)
+        if mode == 0:
+            t = rng.integers(0, 4, size=int(rng.integers(0, maxlen)), dtype=np.uint8)
+        else:
+            t = list(q)
+            out = []
+            for b in t:
+                r = rng.random()
+                if r < 0.04:
+                    out.append(int(rng.integers(0, 4)))
+                elif r < 0.06:
+                    continue
+                elif r < 0.08:
+                    out.extend([b, int(rng.integers(0, 4))])
+                else:
+                    out.append(b)
+            out.extend(rng.integers(0, 4, size=int(rng.integers(0, 60))).tolist())
+            t = np.array(out, dtype=np.uint8)
+            if mode == 3 and len(t) > 10:
+                t = t[: int(rng.integers(1, len(t)))]
+        if rng.random() < 0.1 and lq > 3:
+            q[int(rng.integers(0, lq))] = 4
+        qs.append(q); ts.append(t); ql.append(len(q)); tl.append(len(t))
+    qoff = np.concatenate([[0], np.cumsum(ql)[:-1]]).astype(np.int64)
+    toff = np.concatenate([[0], np.cumsum(tl)[:-1]]).astype(np.int64)
+    q = np.concatenate(qs + [np.zeros(1, np.uint8)]).astype(np.uint8)
+    t = np.concatenate(ts + [np.zeros(1, np.uint8)]).astype(np.uint8)
+    return (np.array(ql, np.int32), qoff, np.ascontiguousarray(q), np.array(tl, np.int32), toff, np.ascontiguousarray(t))
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_ksw_extend2_random(backend):
+    """ksw_extend2 (ksw.c:380): score, qle, tle, gtle, gscore, max_off on random / mutated / truncated pairs,
+    narrow and wide bands, with and without z-drop, empty targets."""
+    ctx = cm.context(backend, "tiny")
+    rl = cm.reflib()
+    rng = np.random.default_rng(5)
+    n = _sizes(backend, 250, 20000)
+    for (zdrop, end_bonus, a, b, o, e) in [(100, 5, 1, 4, 6, 1), (0, 0, 1, 4, 6, 1), (20, 10, 2, 3, 4, 2), (100, 5, 1, 1, 1, 1)]:
+        opt = abi.default_opt()
+        opt.a, opt.b, opt.o_del, opt.o_ins, opt.e_del, opt.e_ins = a, b, o, o + 1, e, e
+        abi.fill_scmat(opt)
+        ql, qoff, q, tl, toff, t = _ksw_problems(rng, n)
+        w = rng.choice([1, 3, 10, 50, 100, 200], size=n).astype(np.int32)
+        h0 = rng.integers(1, 160, size=n).astype(np.int32)
+        exp = rl.ksw_extend2(ql, qoff, q, tl, toff, t, opt, w, end_bonus, zdrop, h0)
+        got = ctx.ksw_extend2(ql, qoff, q, tl, toff, t, opt, w, end_bonus, zdrop, h0)
+        bad = np.nonzero((exp != got).any(axis=1))[0]
+        assert len(bad) == 0, (bad[:5], exp[bad[:5]], got[bad[:5]])
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_align_regs(backend, gname):
+    """mem_align1_core (bwamem.c:1061) for a batch: all 88 bytes of every mem_alnreg_t."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 400, 60000), seed=41, indel=0.004)
+    r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
+    r1, n1 = ctx.align(opt, seqs, off)
+    assert np.array_equal(n0, n1)
+    assert r0.tobytes() == r1.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_align_edge_cases(backend):
+    """Empty / too-short / all-N / N-interrupted / long / reverse / random / chimeric reads; ASCII input."""
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    opt = abi.default_opt()
+    seqs, off = cm.ragged_reads("small")
+    r0, n0 = idx.align(opt, seqs, off, cap_per_read=256)
+    r1, n1 = ctx.align(opt, seqs, off)
+    assert np.array_equal(n0, n1), (n0, n1)
+    assert r0.tobytes() == r1.tobytes()
+    # same reads as upper/lower-case ASCII
+    from bwa_mem_gpu_b200 import synth
+    asc = synth.to_ascii(seqs).copy()
+    asc[::3] = np.char.lower(asc[::3].view("S1")).view(np.uint8)
+    r2, n2 = ctx.align(opt, np.ascontiguousarray(asc), off)
+    assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_align_nondefault_options(backend):
+    """Scoring / band / seed options away from the defaults (-A2 style scaling, small w, -k 15, -r 1.2, -c 50)."""
+    idx, ctx = cm.ref_index("rep"), cm.context(backend, "rep")
+    seqs, off = cm.reads_for("rep", _sizes(backend, 200, 20000), seed=51, sub=0.03, indel=0.006)
+    for kw in (dict(a=2, b=8, o_del=12, o_ins=12, e_del=2, e_ins=2, zdrop=200, pen_clip5=10, pen_clip3=10, T=60),
+               dict(w=8, min_seed_len=15, split_factor=1.2, max_occ=50, zdrop=30),
+               dict(max_mem_intv=0, min_chain_weight=25, drop_ratio=0.3, mask_level=0.3, max_chain_extend=2)):
+        opt = abi.default_opt()
+        for k, v in kw.items():
+            setattr(opt, k, v)
+        abi.fill_scmat(opt)
+        r0, n0 = idx.align(opt, seqs, off, cap_per_read=512)
+        r1, n1 = ctx.align(opt, seqs, off)
+        assert np.array_equal(n0, n1), kw
+        assert r0.tobytes() == r1.tobytes(), kw
