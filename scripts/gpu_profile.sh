@@ -15,6 +15,6 @@ CMD="python bench.py --reads $NCU_READS --steps 1 --warmup 1 --no-cpu-baseline"
 timeout 600 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
 echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'smem_collect|extend_kernel|sa_locate|chain' -c 6 -o $OUT/${TAG}_prof -f $CMD > $OUT/${TAG}_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'smem_collect_kernel|^extend_kernel|chain_kernel' -c 3 -o $OUT/${TAG}_prof -f $CMD > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT
