@@ -47,6 +47,9 @@ struct SmemParams {
     unsigned long long *stats; int *overflow;
     // single-call mode (b200_smem1a_batch): per problem x / min_intv, no length filter
     const i32 *px, *pmin_intv; u64 max_intv; i32 *out_ret;
+    // fast kernel (smem2.cu): reads whose change-point list exceeds the shared-memory capacity are queued
+    // here and re-done by the general kernel, which then takes its read indices from the queue
+    unsigned *retry_n; i32 *retry_ids; int use_retry;
 };
 
 struct SeedParams {
@@ -103,6 +106,8 @@ struct KswBatchParams {
 int launch_pack_reads(u8 *seq, i64 n_bytes, cudaStream_t st);
 int launch_smem_collect(const SmemParams &p, int grid, int block, cudaStream_t st);
 int launch_smem_single(const SmemParams &p, int grid, int block, cudaStream_t st);
+int launch_smem_fast(const SmemParams &p, int grid, int wide, cudaStream_t st);
+int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
 int launch_seed_count(const SeedParams &p, cudaStream_t st);
 int launch_seed_fill(const SeedParams &p, cudaStream_t st);
 int launch_sa_locate(const SeedParams &p, cudaStream_t st);

@@ -43,12 +43,22 @@ extern "C" b200_ctx_t *b200_ctx_create(int device)
     return ctx;
 }
 
+extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
+{
+    if (!ctx || !key) { b200_set_error("null argument"); return -1; }
+    if (!strcmp(key, "chunk_reads")) { if (value < 1) value = 1; ctx->chunk_reads = (int)value; }
+    else if (!strcmp(key, "smem_lcap")) ctx->smem_lcap = (int)value;
+    else if (!strcmp(key, "cap_intv")) ctx->cap_intv = (int)value;
+    else { b200_set_error("unknown tunable '%s'", key); return -1; }
+    return 0;
+}
+
 extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
-    DevBuf *bufs[] = { &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_retry, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
                        &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,
@@ -68,7 +78,7 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
     B200_CHECK(cudaSetDevice(ctx->device));
     if (sa_intv <= 0 || (sa_intv & (sa_intv - 1))) { b200_set_error("sa_intv must be a power of two"); return -1; }
     // Occ blocks: verbatim, padded to a whole number of 64-byte blocks (+1 so that row seq_len-1 is always inside)
-    size_t bwt_bytes = ((size_t)bwt_size * 4 + 63) / 64 * 64 + 64;
+    size_t bwt_bytes = ((size_t)bwt_size * 4 + 63) / 64 * 64 + 128;
     if (ctx->d_bwt.ensure(bwt_bytes)) return -1;
     B200_CHECK(cudaMemsetAsync(ctx->d_bwt.p, 0, bwt_bytes, ctx->st));
     B200_CHECK(cudaMemcpyAsync(ctx->d_bwt.p, bwt, (size_t)bwt_size * 4, cudaMemcpyHostToDevice, ctx->st));
@@ -90,6 +100,20 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
     ix.sa = ctx->d_sa.as<u64>(); ix.n_sa = n_sa; ix.sa_intv = sa_intv;
     ix.pac = ctx->d_pac.as<u8>(); ix.l_pac = l_pac; ix.n_seqs = n_seqs;
     ix.ann_off = ctx->d_ann_off.as<i64>(); ix.ann_len = ctx->d_ann_len.as<i32>(); ix.ann_alt = ctx->d_ann_alt.as<i32>();
+    {   // occ32 re-layout for the seeding kernel (occ32.cuh); superblock bases read from the host checkpoints
+        if (seq_len >> 35) { b200_set_error("seq_len >= 2^35 not supported by the occ32 layout"); return -1; }
+        for (int s = 0; s < 8; ++s)
+            for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = 0;
+        for (u64 s = 1; (s << 32) < seq_len; ++s) {
+            const uint32_t *blk = bwt + (((s << 32) >> 7) << 4);
+            for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = (u64)blk[2 * c] | (u64)blk[2 * c + 1] << 32;
+        }
+        const u64 n_blk = (seq_len >> 6) + 2;
+        if (bwt_bytes < ((n_blk + 1) / 2) * 64) { b200_set_error("internal: bwt padding too small"); return -1; }
+        if (ctx->d_occ32.ensure((size_t)n_blk * 32)) return -1;
+        if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
+        ix.occ32 = ctx->d_occ32.as<uint4>();
+    }
     if (flags & B200_IDX_FULL_SA) {
         const bool narrow = seq_len < 0xffffffffull;
         if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;

@@ -26,7 +26,7 @@ struct b200_ctx {
     cudaStream_t st = nullptr;
     bool has_index = false;
     DevIndex ix;
-    DevBuf d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
+    DevBuf d_occ32, d_retry, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
     const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
 
     // resident input batch
@@ -37,6 +37,7 @@ struct b200_ctx {
     // tunables
     int chunk_reads = 1 << 20;
     int cap_intv = 0;                          // 0 = auto from read length
+    int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
 
     // per-chunk intermediates
     DevBuf d_intv, d_intv_n, d_lists, d_seed_n, d_seed_off, d_l_rep, d_seeds, d_cseeds, d_chains, d_chn_n,
@@ -51,7 +52,7 @@ struct b200_ctx {
 };
 
 // layout of d_ctl (all 8-byte slots)
-enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };
+enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_RETRY = 5, CTL_WORK2 = 6, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
 b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac);

@@ -24,6 +24,9 @@ struct DevIndex {
     const i64 *ann_off;      // contig offsets (n_seqs)
     const i32 *ann_len;
     const i32 *ann_alt;
+    // re-laid Occ index for the seeding kernel (built once on the device, see occ32.cuh)
+    const uint4 *occ32;      // 2 x uint4 per 64-row block
+    u64 sb_cnt[8][4];        // counts at the start of each 2^32-row superblock (rows < 2^35)
 };
 
 struct Intv { u64 x0, x1, x2, info; };   // == bwtintv_t (bwt.h:62)

@@ -78,17 +78,22 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     ++launches;
     tm.mark(st);
 
-    // ---- K1: SMEM collection
+    // ---- K1: SMEM collection: fast kernel (shared-memory lists, occ32 index), then the general kernel on the
+    //      (normally empty) queue of reads whose change-point list did not fit
     const int cap_intv = auto_cap_intv(ctx, opt);
-    int blocks = std::min((n + 127) / 128, ctx->n_sms * 8);
+    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull;
+    const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);
+    const int per_sm = std::max(1, (int)((200 * 1024) / ((size_t)lcap * 128 * (wide ? 32 : 16))));
+    const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * std::min(per_sm, 6)));
+    int blocks = std::min((n + 127) / 128, ctx->n_sms);
     const int list_cap = ctx->max_len + 1;
-    {   // keep the interval-list scratch under ~2 GB for long reads
+    {   // keep the general kernel's interval-list scratch under ~2 GB for long reads
         size_t per_block = (size_t)128 * 2 * list_cap * sizeof(Intv);
-        size_t max_blocks = std::max<size_t>(ctx->n_sms, ((size_t)2 << 30) / per_block);
+        size_t max_blocks = std::max<size_t>(1, ((size_t)2 << 30) / per_block);
         blocks = (int)std::min<size_t>(blocks, max_blocks);
     }
     if (ctx->d_intv.ensure((size_t)n * cap_intv * sizeof(Intv)) || ctx->d_intv_n.ensure((size_t)n * 4) ||
-        ctx->d_lists.ensure((size_t)blocks * 128 * 2 * list_cap * sizeof(Intv))) return -1;
+        ctx->d_lists.ensure((size_t)blocks * 128 * 2 * list_cap * sizeof(Intv)) || ctx->d_retry.ensure((size_t)n * 4 + 4)) return -1;
     SmemParams SP;
     memset(&SP, 0, sizeof(SP));
     SP.ix = ctx->ix; SP.seq = ctx->d_seq.as<u8>(); SP.off = d_off; SP.n_reads = n;
@@ -96,10 +101,14 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     SP.split_len = (int)(opt->min_seed_len * opt->split_factor + .499);      // bwamem.c:141
     SP.split_width = opt->split_width; SP.max_mem_intv = opt->max_mem_intv;
     SP.out = ctx->d_intv.as<Intv>(); SP.cap_out = cap_intv; SP.out_n = ctx->d_intv_n.as<i32>();
-    SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap;
     SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
+    SP.retry_n = ctl_u32(ctx, CTL_RETRY); SP.retry_ids = ctx->d_retry.as<i32>();
+    SP.list_cap = lcap;
+    if (launch_smem_fast(SP, fast_blocks, wide ? 1 : 0, st)) return -1;
+    SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap; SP.use_retry = 1;
+    SP.work_counter = ctl_u32(ctx, CTL_WORK2);
     if (launch_smem_collect(SP, blocks, 128, st)) return -1;
-    ++launches;
+    launches += 2;
     tm.mark(st);
     if (stop_after == 1) {
         u64 ovf;

@@ -43,6 +43,40 @@ __global__ void build_full_sa_kernel(DevIndex ix, u32 *out32, u64 *out64)
     }
 }
 
+// occ32 block b (64 rows) from the reference-layout blocks (bwtindex.c:149-172): counts before the block
+// (relative to its 2^32-row superblock) and the two bit planes of its 64 symbols (occ32.cuh).
+__global__ void build_occ32_kernel(DevIndex ix, uint4 *out, u64 n_blocks)
+{
+    u64 b = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (; b < n_blocks; b += stride) {
+        const uint4 *p = ix.bwt + ((b >> 1) << 2);
+        const uint4 c01 = p[0], c23 = p[1], w0 = p[2], w1 = p[3];
+        u64 cnt[4] = { u64_of(c01.x, c01.y), u64_of(c01.z, c01.w), u64_of(c23.x, c23.y), u64_of(c23.z, c23.w) };
+        const u32 wd[8] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w };
+        if (b & 1)
+            for (int j = 0; j < 64; ++j) ++cnt[(wd[j >> 4] >> ((~j & 15) << 1)) & 3];
+        const int h = (int)(b & 1) * 4;
+        u64 lo = 0, hi = 0;
+        for (int j = 0; j < 64; ++j) {
+            const u32 s = (wd[h + (j >> 4)] >> ((~j & 15) << 1)) & 3;
+            lo |= (u64)(s & 1) << j; hi |= (u64)(s >> 1) << j;
+        }
+        const int sb = (int)(b >> 26);
+        out[2 * b] = make_uint4((u32)(cnt[0] - ix.sb_cnt[sb][0]), (u32)(cnt[1] - ix.sb_cnt[sb][1]),
+                                (u32)(cnt[2] - ix.sb_cnt[sb][2]), (u32)(cnt[3] - ix.sb_cnt[sb][3]));
+        out[2 * b + 1] = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
+    }
+}
+
+int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st)
+{
+    int grid = (int)((n_blocks + 255) / 256 < 148 * 32 ? (n_blocks + 255) / 256 : 148 * 32);
+    B200_LAUNCH(build_occ32_kernel, grid, 256, 0, st, ix, out, n_blocks);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
 int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl, cudaStream_t st)
 {
     if (n <= 0) return 0;

@@ -224,9 +224,11 @@ __global__ void __launch_bounds__(128) smem_collect_kernel(SmemParams P)
     Intv *LA = P.lists + gtid * 2 * (size_t)P.list_cap, *LB = LA + P.list_cap;
     u64 n_ext = 0, n_two = 0;
     int ovf = 0;
+    const unsigned n_work = P.use_retry ? *P.retry_n : (unsigned)P.n_reads;
     for (;;) {
         unsigned r = atomicAdd(P.work_counter, 1u);
-        if (r >= (unsigned)P.n_reads) break;
+        if (r >= n_work) break;
+        if (P.use_retry) r = (unsigned)P.retry_ids[r];
         const i64 o = P.off[r];
         const int len = (int)(P.off[r + 1] - o);
         Intv *out = P.out + (size_t)r * P.cap_out;

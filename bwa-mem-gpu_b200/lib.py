@@ -19,7 +19,7 @@ PRODUCT_SO = os.path.join(HERE, "libbwamem_b200.so")
 IDX_FULL_SA = 0x1
 
 _SYMBOLS = [
-    "b200_ctx_create", "b200_ctx_destroy", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
+    "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
@@ -118,6 +118,9 @@ class Context:
         if self.h:
             self.lib.b200_ctx_destroy(self.h)
             self.h = None
+
+    def tune(self, key: str, value: int):
+        self._chk(self.lib.b200_ctx_tune(self.h, key.encode(), C.c_int64(value)), "tune")
 
     def _chk(self, rc, what):
         if rc < 0:

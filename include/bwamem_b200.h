@@ -134,6 +134,9 @@ typedef struct b200_ctx b200_ctx_t;
 b200_ctx_t *b200_ctx_create(int device);
 void        b200_ctx_destroy(b200_ctx_t *ctx);
 const char *b200_last_error(void);
+/* tunables: "chunk_reads" (reads per pipeline chunk), "smem_lcap" (shared-memory list entries per read in the
+ * seeding kernel; longer lists take the general kernel), "cap_intv" (interval slots per read; 0 = auto) */
+int         b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value);
 /* flags for b200_index_upload */
 #define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device */
 int b200_index_upload(b200_ctx_t *ctx, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac, int flags);

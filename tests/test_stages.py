@@ -209,3 +209,21 @@ def test_align_nondefault_options(backend):
         r1, n1 = ctx.align(opt, seqs, off)
         assert np.array_equal(n0, n1), kw
         assert r0.tobytes() == r1.tobytes(), kw
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_collect_intv_list_spill(backend):
+    """Seeding kernel with a tiny shared-memory list: most reads take the queue + general-kernel path; same result."""
+    idx, ctx = cm.ref_index("rep"), cm.context(backend, "rep")
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for("rep", _sizes(backend, 600, 20000), seed=77, n_rate=0.001)
+    iv0, c0 = idx.collect_intv(opt, seqs, off)
+    for lcap in (2, 9):
+        ctx.tune("smem_lcap", lcap)
+        try:
+            iv1, c1 = ctx.collect_intv(opt, seqs, off)
+        finally:
+            ctx.tune("smem_lcap", 0)
+        assert np.array_equal(c0, c1)
+        assert iv0.tobytes() == iv1.tobytes()
