@@ -92,6 +92,33 @@ struct ExtParams {
     unsigned long long *stats; int *overflow;
 };
 
+// ---- round-based extension (ext2.cu)
+struct ExtJob {          // one seed extension: both sides + band retries (bwamem.c:722-778); 96 bytes
+    i64 rbeg, rmax0, rmax1;          // seed start on the reference, chain window
+    i32 read, qbeg, slen, lq;        // read, seed on the query, query length
+    i32 wl0, wl1, wr0, wr1;          // bands of the two tries per side, already clamped like ksw.c:399-407
+    i64 rb, re;                      // results
+    i32 qb, qe, score, truesc, w, pad;
+};
+struct ExtRead { i32 ci, k, nav, pad; i64 rmax0, rmax1; };   // per-read cursor between rounds
+struct Ext2Params {
+    DevIndex ix;
+    mem_opt_t opt;
+    const u8 *seq; const i64 *off; int n_reads;
+    const ChainRec *chains; const i64 *chn_off; const i32 *chn_n;
+    const Seed *cseeds;
+    mem_alnreg_t *regs;              // per read at chn_off[r], capacity = the read's seed count
+    u64 *srt;                        // per chain at its seed_off
+    ExtRead *rstate;
+    ExtJob *jobs[2];
+    unsigned *njobs;                 // per round
+    int he_cols;                     // shared-memory columns per lane in the DP kernel (max query side + 1)
+    i32 *eh; int eh_cap;             // finish kernel scratch (mem_patch_reg's global alignment)
+    i64 *reg_off; i32 *reg_n;
+    unsigned *work_counter;
+    unsigned long long *stats;
+};
+
 struct KswBatchParams {
     i64 n;
     const i32 *qlen; const i64 *qoff; const u8 *q;
@@ -113,6 +140,9 @@ int launch_seed_fill(const SeedParams &p, cudaStream_t st);
 int launch_sa_locate(const SeedParams &p, cudaStream_t st);
 int launch_chain(const ChainParams &p, int emit, cudaStream_t st);
 int launch_extend(const ExtParams &p, int grid, int block, cudaStream_t st);
+int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t st);
+int launch_ext2_dp(const Ext2Params &p, int round, int grid, cudaStream_t st);
+int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,
                        int n_reads, mem_alnreg_t *dst, cudaStream_t st);

@@ -1,0 +1,441 @@
+// Stage 3, short-read fast path: mem_chain2aln (bwamem.c:639-793) as a round-based pipeline.
+//
+// The reference decides seed by seed whether to extend (the containment test against every region already
+// produced for the read, bwamem.c:678-713), so per read the extensions form a dependent sequence -- but the
+// extension of ONE seed (left ksw_extend2, right ksw_extend2 seeded with the left score, optional wider-band
+// retries, bwamem.c:722-778) is a pure function of the seed and its chain window.  The batch is therefore
+// advanced in rounds:
+//   ext_plan_kernel   one thread per read: consume the finished job (seedcov, bwamem.c:781-790), walk the
+//                     chains/seeds in the reference's order, skip contained seeds, emit the next JOB
+//   ext_dp_kernel     one JOB PER LANE: both sides + retries of one seed, bit-exact ksw_extend2 (ksw.c:380-479)
+//   ext_finish_kernel one thread per read: mem_sort_dedup_patch (bwamem.c:444-496) + is_alt (bwamem.c:1091-1095)
+// Round k holds the k-th extended seed of every read (typically 1-2 rounds carry almost all work).
+//
+// DP kernel.  A warp runs 32 independent DPs in lock step over a flattened cell loop (8 cells, then a control
+// slot for row ends / job changes), which costs ~25 instructions per cell instead of a warp-wide scan per
+// 32-column chunk.  The H/E row of the reference (eh[], including the stale out-of-band entries the algorithm
+// observes) is staged in SHARED memory, one 32-bit word per column = h:14 | e:14 | query base:3, laid out
+// [column][thread] so that lanes at different columns never conflict; the row of a new DP is initialised
+// cooperatively by the whole warp (coalesced query read).  Cell arithmetic uses the DPX fused ops
+// (__vimax3_s32, __viaddmax_s32_relu); z-drop / zero-row / end-of-target exits are per-lane state changes and
+// warp votes (__ballot_sync/__all_sync) drive initialisation and termination.  Used when every score fits
+// 14 bits (max_len * a < 16384) and the row fits the shared-memory budget; otherwise the general warp-per-read
+// kernel (extend.cu) runs.
+#include "b200_internal.h"
+#include "extend_common.cuh"
+
+#define DP_THREADS 64
+#define DP_HMASK 0x3fffu
+#define DP_QMASK 0x70000000u
+
+// ------------------------------------------------------------------------------------------------ planning
+__device__ __forceinline__ int clamp_band(const mem_opt_t &opt, int qlen, int w, int end_bonus)
+{   // ksw.c:399-407 with max = max(mat)
+    int mx = 0;
+    for (int k = 0; k < 25; ++k) mx = mx > opt.mat[k] ? mx : opt.mat[k];
+    int max_ins = (int)((double)(qlen * mx + end_bonus - opt.o_ins) / opt.e_ins + 1.);
+    max_ins = max_ins > 1 ? max_ins : 1;
+    w = w < max_ins ? w : max_ins;
+    int max_del = (int)((double)(qlen * mx + end_bonus - opt.o_del) / opt.e_del + 1.);
+    max_del = max_del > 1 ? max_del : 1;
+    return w < max_del ? w : max_del;
+}
+
+__global__ void __launch_bounds__(128) ext_plan_kernel(Ext2Params P, int round)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const ExtJob *jprev = P.jobs[(round + 1) & 1];
+    ExtJob *jcur = P.jobs[round & 1];
+    int r;
+    const ExtJob *done = nullptr;
+    if (round == 0) { if (t >= P.n_reads) return; r = t; }
+    else { if ((unsigned)t >= P.njobs[round - 1]) return; done = &jprev[t]; r = done->read; }
+    const mem_opt_t &opt = P.opt;
+    const DevIndex &ix = P.ix;
+    const i64 l_pac = ix.l_pac;
+    const u8 *query = P.seq + P.off[r];
+    const int l_query = (int)(P.off[r + 1] - P.off[r]);
+    const int nchn = P.chn_n[r];
+    const ChainRec *chains = P.chains + P.chn_off[r];
+    mem_alnreg_t *av = P.regs + P.chn_off[r];
+    ExtRead er;
+    if (round == 0) { er.ci = 0; er.k = -2; er.nav = 0; er.rmax0 = er.rmax1 = 0; }
+    else er = P.rstate[r];
+    (void)query;
+
+    if (done) {                                                            // finish the region of the last job
+        const ChainRec c = chains[er.ci];
+        const Seed *seeds = P.cseeds + c.seed_off;
+        mem_alnreg_t a;
+        memset(&a, 0, sizeof(a));
+        a.rb = done->rb; a.re = done->re; a.qb = done->qb; a.qe = done->qe;
+        a.score = done->score; a.truesc = done->truesc; a.w = done->w; a.rid = c.rid;
+        a.seedcov = 0;                                                     // bwamem.c:781-790
+        for (int i = 0; i < c.n; ++i) {
+            const Seed s = seeds[i];
+            if (s.qbeg >= a.qb && s.qbeg + s.len <= a.qe && s.rbeg >= a.rb && s.rbeg + s.len <= a.re) a.seedcov += s.len;
+        }
+        a.seedlen0 = done->slen;
+        a.frac_rep = c.frac_rep;
+        av[er.nav++] = a;
+        --er.k;
+    }
+
+    for (;;) {
+        if (er.ci >= nchn) { er.k = -3; break; }                           // read finished
+        const ChainRec c = chains[er.ci];
+        const Seed *seeds = P.cseeds + c.seed_off;
+        u64 *srt = P.srt + c.seed_off;
+        if (er.k == -2) {                                                  // new chain
+            if (c.n == 0) { ++er.ci; continue; }
+            i64 rmax0 = l_pac << 1, rmax1 = 0;                             // bwamem.c:649-664
+            for (int i = 0; i < c.n; ++i) {
+                const Seed s = seeds[i];
+                i64 b = s.rbeg - (s.qbeg + cal_max_gap(opt, s.qbeg));
+                i64 e = s.rbeg + s.len + ((l_query - s.qbeg - s.len) + cal_max_gap(opt, l_query - s.qbeg - s.len));
+                rmax0 = rmax0 < b ? rmax0 : b;
+                rmax1 = rmax1 > e ? rmax1 : e;
+            }
+            rmax0 = rmax0 > 0 ? rmax0 : 0;
+            rmax1 = rmax1 < l_pac << 1 ? rmax1 : l_pac << 1;
+            if (rmax0 < l_pac && l_pac < rmax1) {
+                if (seeds[0].rbeg < l_pac) rmax1 = l_pac; else rmax0 = l_pac;
+            }
+            {   // bns_fetch_seq clamp to the contig of seeds[0].rbeg (bntseq.c:432-443)
+                int is_rev;
+                int rid = dev_pos2rid(ix, dev_depos(ix, seeds[0].rbeg, &is_rev));
+                i64 far_beg = ix.ann_off[rid], far_end = far_beg + ix.ann_len[rid];
+                if (is_rev) { i64 tmp = far_beg; far_beg = (l_pac << 1) - far_end; far_end = (l_pac << 1) - tmp; }
+                rmax0 = rmax0 > far_beg ? rmax0 : far_beg;
+                rmax1 = rmax1 < far_end ? rmax1 : far_end;
+            }
+            er.rmax0 = rmax0; er.rmax1 = rmax1;
+            for (int i = 0; i < c.n; ++i) srt[i] = (u64)(u32)seeds[i].score << 32 | (u32)i;   // bwamem.c:669-672 (unique keys)
+            ks_introsort(srt, c.n, U64Less());
+            er.k = c.n - 1;
+        }
+        bool emitted = false;
+        while (er.k >= 0) {
+            const int k = er.k;
+            const Seed s = seeds[(u32)srt[k]];
+            int i;
+            for (i = 0; i < er.nav; ++i) {                                 // bwamem.c:678-694
+                const mem_alnreg_t *p = &av[i];
+                i64 rd; int qd, w, max_gap;
+                if (s.rbeg < p->rb || s.rbeg + s.len > p->re || s.qbeg < p->qb || s.qbeg + s.len > p->qe) continue;
+                if (s.len - p->seedlen0 > .1 * l_query) continue;
+                qd = s.qbeg - p->qb; rd = s.rbeg - p->rb;
+                max_gap = cal_max_gap(opt, qd < rd ? qd : (int)rd);
+                w = max_gap < p->w ? max_gap : p->w;
+                if (qd - rd < w && rd - qd < w) break;
+                qd = p->qe - (s.qbeg + s.len); rd = p->re - (s.rbeg + s.len);
+                max_gap = cal_max_gap(opt, qd < rd ? qd : (int)rd);
+                w = max_gap < p->w ? max_gap : p->w;
+                if (qd - rd < w && rd - qd < w) break;
+            }
+            if (i < er.nav) {                                              // bwamem.c:695-713
+                for (i = k + 1; i < c.n; ++i) {
+                    if (srt[i] == 0) continue;
+                    const Seed u = seeds[(u32)srt[i]];
+                    if (u.len < s.len * .95) continue;
+                    if (s.qbeg <= u.qbeg && s.qbeg + s.len - u.qbeg >= s.len >> 2 && u.qbeg - s.qbeg != u.rbeg - s.rbeg) break;
+                    if (u.qbeg <= s.qbeg && u.qbeg + u.len - s.qbeg >= s.len >> 2 && s.qbeg - u.qbeg != s.rbeg - u.rbeg) break;
+                }
+                if (i == c.n) { srt[k] = 0; --er.k; continue; }
+            }
+            // extend this seed: one job
+            const unsigned slot = atomicAdd(&P.njobs[round], 1u);
+            ExtJob j;
+            j.rbeg = s.rbeg; j.rmax0 = er.rmax0; j.rmax1 = er.rmax1;
+            j.read = r; j.qbeg = s.qbeg; j.slen = s.len; j.lq = l_query;
+            const int ql = s.qbeg, qr = l_query - (s.qbeg + s.len);
+            j.wl0 = clamp_band(opt, ql, opt.w, opt.pen_clip5); j.wl1 = clamp_band(opt, ql, opt.w << 1, opt.pen_clip5);
+            j.wr0 = clamp_band(opt, qr, opt.w, opt.pen_clip3); j.wr1 = clamp_band(opt, qr, opt.w << 1, opt.pen_clip3);
+            j.rb = j.re = 0; j.qb = j.qe = j.score = j.truesc = j.w = j.pad = 0;
+            jcur[slot] = j;
+            emitted = true;
+            break;
+        }
+        if (emitted) break;
+        ++er.ci; er.k = -2;
+    }
+    P.rstate[r] = er;
+}
+
+// ------------------------------------------------------------------------------------------------ DP
+struct DpLane {
+    // job
+    ExtJob *job;
+    const u8 *qbase;          // first query base of the current side; column j is qbase[j * qstep]
+    int qstep;
+    i64 fpos; int fstep, comp; u32 pacw, pacw_tag;     // forward-strand coordinate of the current target row
+    int side, t, a_score, sc0, prev;
+    // ksw_extend2 state (ksw.c:380-479)
+    int qlen, tlen, w, h0;
+    int i, j, beg, end, h1, f, m, mj, tb5, first_nz, last_nz;
+    int max, max_i, max_j, max_ie, gscore, max_off;
+};
+
+__device__ __forceinline__ int dp_target_base(const DevIndex &ix, DpLane &L)
+{
+    const u32 tag = (u32)(L.fpos >> 4);
+    if (tag != L.pacw_tag) { L.pacw = ((const u32 *)ix.pac)[L.fpos >> 4]; L.pacw_tag = tag; }
+    const int f = (int)L.fpos;
+    const int sh = (((f >> 2) & 3) << 3) + ((~f & 3) << 1);
+    return (int)((L.pacw >> sh) & 3) ^ L.comp;
+}
+
+__global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round)
+{
+    B200_DYN_SMEM(dp_raw);
+    __shared__ int8_t s_mat[32];
+    u32 *he = (u32 *)dp_raw + threadIdx.x;                 // column j of this lane: he[j * DP_THREADS]
+    const unsigned lane = threadIdx.x & 31;
+    u32 *he_warp = (u32 *)dp_raw + (threadIdx.x & ~31u);
+    if (threadIdx.x < 25) s_mat[threadIdx.x] = P.opt.mat[threadIdx.x];
+    __syncthreads();
+    const DevIndex &ix = P.ix;
+    const mem_opt_t &opt = P.opt;
+    const int o_del = opt.o_del, e_del = opt.e_del, o_ins = opt.o_ins, e_ins = opt.e_ins;
+    const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins, zdrop = opt.zdrop;
+    ExtJob *jobs = P.jobs[round & 1];
+    const unsigned njobs = P.njobs[round];
+    const i64 l_pac = ix.l_pac;
+    u64 n_ksw = 0, n_cells = 0;
+
+    DpLane L;
+    memset(&L, 0, sizeof(L));
+    bool active = false, exhausted = false, need_init = false;
+
+    for (;;) {
+        // ---------------------------------------------------------------- hot slot: up to 8 cells of the current row
+        if (active) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                if (L.j < L.end) {
+                    u32 *p = he + L.j * DP_THREADS;
+                    const u32 wv = *p;
+                    int M = (int)(wv & DP_HMASK);
+                    const int e = (int)((wv >> 14) & DP_HMASK);
+                    const int sc = s_mat[L.tb5 + (int)(wv >> 28)];
+                    M = M ? M + sc : 0;                                                   // ksw.c:433
+                    const int h = __vimax3_s32(M, e, L.f);                                // ksw.c:434-435
+                    const int en = __viaddmax_s32_relu(e, -e_del, M - oe_del);            // ksw.c:439-442
+                    *p = (wv & DP_QMASK) | (u32)L.h1 | ((u32)en << 14);                   // ksw.c:432,442
+                    if (L.h1 | en) { L.last_nz = L.j; if (L.first_nz > L.j) L.first_nz = L.j; }
+                    L.h1 = h;
+                    if (h >= L.m) { L.m = h; L.mj = L.j; }                                // ksw.c:437-438 (last column on ties)
+                    L.f = __viaddmax_s32_relu(L.f, -e_ins, M - oe_ins);                   // ksw.c:444-447
+                    ++L.j;
+                }
+            }
+        }
+        // ---------------------------------------------------------------- control slot
+        bool ksw_fin = false;
+        if (active && L.j >= L.end) {                                                     // row i finished
+            const int jexit = L.beg < L.end ? L.end : L.beg;
+            u32 *p = he + L.end * DP_THREADS;
+            *p = (*p & DP_QMASK) | (u32)L.h1;                                             // ksw.c:449
+            if (jexit == L.qlen) {                                                        // ksw.c:450-453
+                L.max_ie = L.gscore > L.h1 ? L.max_ie : L.i;
+                L.gscore = L.gscore > L.h1 ? L.gscore : L.h1;
+            }
+            if (L.m == 0) ksw_fin = true;                                                 // ksw.c:454
+            else {
+                if (L.m > L.max) {
+                    L.max = L.m; L.max_i = L.i; L.max_j = L.mj;
+                    int off = L.mj - L.i; off = off < 0 ? -off : off;
+                    L.max_off = L.max_off > off ? L.max_off : off;
+                } else if (zdrop > 0) {                                                   // ksw.c:458-464
+                    if (L.i - L.max_i > L.mj - L.max_j) {
+                        if (L.max - L.m - ((L.i - L.max_i) - (L.mj - L.max_j)) * e_del > zdrop) ksw_fin = true;
+                    } else {
+                        if (L.max - L.m - ((L.mj - L.max_j) - (L.i - L.max_i)) * e_ins > zdrop) ksw_fin = true;
+                    }
+                }
+                if (!ksw_fin) {                                                           // ksw.c:466-469
+                    const int nbeg = L.first_nz != 0x7fffffff ? L.first_nz : L.end;
+                    int jl;
+                    if (L.h1 != 0) jl = L.end; else jl = L.last_nz >= nbeg ? L.last_nz : nbeg - 1;
+                    L.beg = nbeg;
+                    L.end = jl + 2 < L.qlen ? jl + 2 : L.qlen;
+                    if (++L.i >= L.tlen) ksw_fin = true;
+                    else {                                                                // next row, ksw.c:411-423
+                        L.fpos += L.fstep;
+                        L.tb5 = dp_target_base(ix, L) * 5;
+                        if (L.beg < L.i - L.w) L.beg = L.i - L.w;
+                        if (L.end > L.i + L.w + 1) L.end = L.i + L.w + 1;
+                        if (L.end > L.qlen) L.end = L.qlen;
+                        L.h1 = 0;
+                        if (L.beg == 0) { L.h1 = L.h0 - (o_del + e_del * (L.i + 1)); if (L.h1 < 0) L.h1 = 0; }
+                        L.f = 0; L.m = 0; L.mj = -1; L.first_nz = 0x7fffffff; L.last_nz = -1; L.j = L.beg;
+                        if (L.end > L.beg) n_cells += (u64)(L.end - L.beg);
+                    }
+                }
+            }
+        }
+        // job / side / retry transitions; loops only when a DP has no rows (tlen <= 0)
+        while ((active && ksw_fin) || (!active && !exhausted)) {
+            int next_side = -1, next_t = 0;
+            if (!active) {                                                                // fetch a job
+                const unsigned slot = atomicAdd(P.work_counter, 1u);
+                if (slot >= njobs) { exhausted = true; break; }
+                L.job = &jobs[slot];
+                active = true;
+                L.a_score = -1;
+                if (L.job->qbeg) { next_side = 0; next_t = 0; L.prev = -1; }
+                else {                                                                    // bwamem.c:751
+                    L.a_score = L.job->slen * opt.a;
+                    L.job->truesc = L.a_score; L.job->qb = 0; L.job->rb = L.job->rbeg; L.job->w = opt.w;
+                    next_side = 1;
+                }
+            } else {                                                                      // a ksw_extend2 finished
+                ksw_fin = false;
+                const int score = L.max, qle = L.max_j + 1, tle = L.max_i + 1, gtle = L.max_ie + 1;
+                const int aw = opt.w << L.t;
+                L.a_score = score;
+                const bool again = !(score == L.prev || L.max_off < (aw >> 1) + (aw >> 2)) && L.t == 0;   // bwamem.c:733-741
+                ExtJob *J = L.job;
+                if (L.side == 0) {
+                    if (again) { next_side = 0; next_t = 1; L.prev = score; }
+                    else {
+                        if (L.gscore <= 0 || L.gscore <= score - opt.pen_clip5) {         // bwamem.c:743-749
+                            J->qb = J->qbeg - qle; J->rb = J->rbeg - tle; J->truesc = score;
+                        } else { J->qb = 0; J->rb = J->rbeg - gtle; J->truesc = L.gscore; }
+                        J->w = aw;
+                        next_side = 1;
+                    }
+                } else {
+                    if (again) { next_side = 1; next_t = 1; L.prev = score; }
+                    else {
+                        const int qe = J->qbeg + J->slen;
+                        const i64 re = J->rbeg + J->slen;
+                        if (L.gscore <= 0 || L.gscore <= score - opt.pen_clip3) {         // bwamem.c:771-777
+                            J->qe = qe + qle; J->re = re + tle; J->truesc += score - L.sc0;
+                        } else { J->qe = J->lq; J->re = re + gtle; J->truesc += L.gscore - L.sc0; }
+                        J->w = J->w > aw ? J->w : aw;
+                        J->score = score;
+                        active = false;                                                   // job done
+                        continue;
+                    }
+                }
+            }
+            if (next_side == 1 && next_t == 0) {     // entering the right side
+                ExtJob *J = L.job;
+                if (J->qbeg + J->slen == J->lq) {                                         // bwamem.c:778
+                    J->qe = J->lq; J->re = J->rbeg + J->slen; J->score = L.a_score;
+                    active = false;
+                    continue;
+                }
+                L.sc0 = L.a_score; L.prev = L.a_score;
+            }
+            // set up ksw_extend2 for (next_side, next_t)
+            {
+                ExtJob *J = L.job;
+                L.side = next_side; L.t = next_t;
+                i64 p0;
+                const u8 *rq = P.seq + P.off[J->read];
+                if (next_side == 0) {                                                     // bwamem.c:722-735
+                    L.qlen = J->qbeg; L.tlen = (int)(J->rbeg - J->rmax0); L.h0 = J->slen * opt.a;
+                    L.w = next_t ? J->wl1 : J->wl0;
+                    L.qbase = rq + J->qbeg - 1; L.qstep = -1;
+                    p0 = J->rbeg - 1;
+                } else {                                                                  // bwamem.c:753-765
+                    const int qe = J->qbeg + J->slen;
+                    L.qlen = J->lq - qe; L.tlen = (int)(J->rmax1 - (J->rbeg + J->slen)); L.h0 = L.sc0;
+                    L.w = next_t ? J->wr1 : J->wr0;
+                    L.qbase = rq + qe; L.qstep = 1;
+                    p0 = J->rbeg + J->slen;
+                }
+                const int dir = next_side == 0 ? -1 : 1;
+                if (p0 >= l_pac) { L.fpos = (l_pac << 1) - 1 - p0; L.fstep = -dir; L.comp = 3; }
+                else { L.fpos = p0; L.fstep = dir; L.comp = 0; }
+                L.max = L.h0; L.max_i = L.max_j = L.max_ie = -1; L.gscore = -1; L.max_off = 0;
+                L.beg = 0; L.end = L.qlen; L.i = 0;
+                ++n_ksw;
+                if (L.tlen <= 0) { ksw_fin = true; continue; }                            // no rows: result is the initial state
+                L.pacw_tag = 0xffffffffu;
+                L.tb5 = dp_target_base(ix, L) * 5;
+                if (L.end > L.w + 1) L.end = L.w + 1;                                     // row 0: beg = 0 >= -w
+                if (L.end > L.qlen) L.end = L.qlen;
+                L.h1 = L.h0 - (o_del + e_del); if (L.h1 < 0) L.h1 = 0;
+                L.f = 0; L.m = 0; L.mj = -1; L.first_nz = 0x7fffffff; L.last_nz = -1; L.j = 0;
+                if (L.end > 0) n_cells += (u64)L.end;
+                need_init = true;
+            }
+            break;
+        }
+        // ---------------------------------------------------------------- cooperative first-row initialisation (ksw.c:395-397)
+        unsigned need = __ballot_sync(B200_FULL_MASK, need_init);
+        while (need) {
+            const int src = __ffs((int)need) - 1;
+            need &= need - 1;
+            const int qlen = __shfl_sync(B200_FULL_MASK, L.qlen, src);
+            const int h0 = __shfl_sync(B200_FULL_MASK, L.h0, src);
+            const int qstep = __shfl_sync(B200_FULL_MASK, L.qstep, src);
+            const unsigned long long qb = __shfl_sync(B200_FULL_MASK, (unsigned long long)(size_t)L.qbase, src);
+            const u8 *qp = (const u8 *)(size_t)qb;
+            u32 *col = he_warp + src;
+            for (int j = (int)lane; j <= qlen; j += 32) {
+                int v;
+                if (j == 0) v = h0;
+                else if (j == 1) v = h0 > oe_ins ? h0 - oe_ins : 0;
+                else {
+                    const int vprev = h0 - oe_ins - (j - 2) * e_ins;
+                    v = (h0 > oe_ins && vprev > e_ins) ? vprev - e_ins : 0;
+                }
+                const u32 qv = j < qlen ? (u32)qp[j * qstep] : 0u;
+                col[j * DP_THREADS] = (u32)v | (qv << 28);
+            }
+        }
+        need_init = false;
+        __syncwarp();
+        if (__all_sync(B200_FULL_MASK, exhausted && !active)) break;
+    }
+    if (n_ksw) {
+        atomicAdd(&P.stats[CNT_KSW], (unsigned long long)n_ksw);
+        atomicAdd(&P.stats[CNT_CELLS], (unsigned long long)n_cells);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ finish
+__global__ void __launch_bounds__(128) ext_finish_kernel(Ext2Params P)
+{
+    const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    i32 *H = P.eh + gt * 2 * (size_t)P.eh_cap, *E = H + P.eh_cap;
+    for (;;) {
+        const unsigned r = atomicAdd(P.work_counter, 1u);
+        if (r >= (unsigned)P.n_reads) break;
+        mem_alnreg_t *av = P.regs + P.chn_off[r];
+        int nav = P.rstate[r].nav;
+        if (nav > 1) nav = sort_dedup_patch(P.ix, P.opt, P.seq + P.off[r], nav, av, H, E);   // bwamem.c:1083
+        for (int i = 0; i < nav; ++i)
+            if (av[i].rid >= 0 && P.ix.ann_alt[av[i].rid]) av[i].is_alt = 1;                 // bwamem.c:1091-1095
+        P.reg_off[r] = P.chn_off[r];
+        P.reg_n[r] = nav;
+    }
+}
+
+int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t st)
+{
+    if (n_threads <= 0) return 0;
+    B200_LAUNCH(ext_plan_kernel, (n_threads + 127) / 128, 128, 0, st, p, round);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+int launch_ext2_dp(const Ext2Params &p, int round, int grid, cudaStream_t st)
+{
+    const size_t smem = (size_t)p.he_cols * DP_THREADS * 4;
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute(ext_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#endif
+    B200_LAUNCH(ext_dp_kernel, grid, DP_THREADS, smem, st, p, round);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st)
+{
+    B200_LAUNCH(ext_finish_kernel, grid, 128, 0, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}

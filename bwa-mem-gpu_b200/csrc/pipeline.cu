@@ -172,13 +172,60 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     }
 
     // ---- K4: extension + dedup
+    const i64 arena_cap = tot_seeds + 1;
+    if (ctx->d_arena.ensure((size_t)arena_cap * sizeof(mem_alnreg_t)) || ctx->d_reg_off.ensure((size_t)n * 8) ||
+        ctx->d_reg_n.ensure((size_t)n * 4) || ctx->d_dst_off.ensure(((size_t)n + 1) * 8)) return -1;
+    // round-based fast path (ext2.cu) when scores fit 14 bits and one H/E row per lane fits shared memory
+    const int he_cols = ctx->max_len + 2;
+    bool fast_ext = (i64)ctx->max_len * opt->a < 16384 && (size_t)he_cols * 64 * 4 <= 96 * 1024;
+    for (int k = 0; k < 25; ++k) if (opt->mat[k] > opt->a) fast_ext = false;     // bound above assumes max(mat) == a
+    if (ctx->ext_path == 1) fast_ext = false;
+    i32 *reg_n_ptr = ctx->d_reg_n.as<i32>();
+    i64 *reg_off_ptr = ctx->d_reg_off.as<i64>();
+    if (fast_ext) {
+        const int MAX_ROUNDS = 4096;
+        const int fin_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * 2));
+        const int eh_cap = ctx->max_len + 2;
+        if (ctx->d_jobs0.ensure((size_t)n * sizeof(ExtJob)) || ctx->d_jobs1.ensure((size_t)n * sizeof(ExtJob)) ||
+            ctx->d_rstate.ensure((size_t)n * sizeof(ExtRead)) || ctx->d_njobs.ensure((size_t)MAX_ROUNDS * 4) ||
+            ctx->d_srt.ensure((size_t)(tot_seeds + 1) * 8) || ctx->d_eh.ensure((size_t)fin_blocks * 128 * 2 * eh_cap * 4)) return -1;
+        B200_CHECK(cudaMemsetAsync(ctx->d_njobs.p, 0, (size_t)MAX_ROUNDS * 4, st));
+        Ext2Params XP;
+        memset(&XP, 0, sizeof(XP));
+        XP.ix = ctx->ix; XP.opt = *opt; XP.seq = ctx->d_seq.as<u8>(); XP.off = d_off; XP.n_reads = n;
+        XP.chains = ctx->d_chains.as<ChainRec>(); XP.chn_off = ctx->d_seed_off.as<i64>(); XP.chn_n = ctx->d_chn_n.as<i32>();
+        XP.cseeds = ctx->d_cseeds.as<Seed>();
+        XP.regs = ctx->d_arena.as<mem_alnreg_t>(); XP.srt = ctx->d_srt.as<u64>();
+        XP.rstate = ctx->d_rstate.as<ExtRead>();
+        XP.jobs[0] = ctx->d_jobs0.as<ExtJob>(); XP.jobs[1] = ctx->d_jobs1.as<ExtJob>();
+        XP.njobs = ctx->d_njobs.as<unsigned>();
+        XP.he_cols = he_cols; XP.eh = ctx->d_eh.as<i32>(); XP.eh_cap = eh_cap;
+        XP.reg_off = reg_off_ptr; XP.reg_n = reg_n_ptr;
+        XP.work_counter = ctl_u32(ctx, CTL_WORK); XP.stats = ctl_u64(ctx, CTL_STATS);
+        const int dp_per_sm = std::max(1, std::min(8, (int)((200 * 1024) / ((size_t)he_cols * 64 * 4))));
+        int threads = n;
+        for (int round = 0; ; ++round) {
+            if (round >= MAX_ROUNDS) { b200_set_error("extension: more than %d rounds", MAX_ROUNDS); return -2; }
+            if (launch_ext2_plan(XP, round, threads, st)) return -1;
+            ++launches;
+            unsigned nj = 0;
+            B200_CHECK(cudaMemcpyAsync(&nj, XP.njobs + round, 4, cudaMemcpyDeviceToHost, st));
+            B200_CHECK(cudaStreamSynchronize(st));
+            if (nj == 0) break;
+            if (ctl_zero(ctx, CTL_WORK)) return -1;
+            const int grid = std::max(1, std::min((int)((nj + 63) / 64), ctx->n_sms * dp_per_sm));
+            if (launch_ext2_dp(XP, round, grid, st)) return -1;
+            ++launches;
+            threads = (int)nj;
+        }
+        if (ctl_zero(ctx, CTL_WORK)) return -1;
+        if (launch_ext2_finish(XP, fin_blocks, st)) return -1;
+        ++launches;
+    } else {
     const int ext_blocks = std::max(1, std::min((n + 3) / 4, ctx->n_sms * 8));
     const int cap_stage = 512, srt_cap = 8192, eh_cap = ctx->max_len + 2;
-    const i64 arena_cap = tot_seeds + 1;
     if (ctx->d_stage.ensure((size_t)ext_blocks * 4 * cap_stage * sizeof(mem_alnreg_t)) ||
-        ctx->d_eh.ensure((size_t)ext_blocks * 4 * 2 * eh_cap * 4) || ctx->d_srt.ensure((size_t)ext_blocks * 4 * srt_cap * 8) ||
-        ctx->d_arena.ensure((size_t)arena_cap * sizeof(mem_alnreg_t)) || ctx->d_reg_off.ensure((size_t)n * 8) ||
-        ctx->d_reg_n.ensure((size_t)n * 4) || ctx->d_dst_off.ensure(((size_t)n + 1) * 8)) return -1;
+        ctx->d_eh.ensure((size_t)ext_blocks * 4 * 2 * eh_cap * 4) || ctx->d_srt.ensure((size_t)ext_blocks * 4 * srt_cap * 8)) return -1;
     if (ctl_zero(ctx, CTL_WORK)) return -1;
     ExtParams EP;
     memset(&EP, 0, sizeof(EP));
@@ -188,12 +235,13 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     EP.regs = ctx->d_stage.as<mem_alnreg_t>(); EP.cap_regs = cap_stage;
     EP.eh = ctx->d_eh.as<i32>(); EP.eh_cap = eh_cap; EP.srt = ctx->d_srt.as<u64>(); EP.srt_cap = srt_cap;
     EP.out = ctx->d_arena.as<mem_alnreg_t>(); EP.out_cap = arena_cap; EP.out_used = ctl_u64(ctx, CTL_ARENA_USED);
-    EP.reg_off = ctx->d_reg_off.as<i64>(); EP.reg_n = ctx->d_reg_n.as<i32>();
+    EP.reg_off = reg_off_ptr; EP.reg_n = reg_n_ptr;
     EP.work_counter = ctl_u32(ctx, CTL_WORK); EP.stats = ctl_u64(ctx, CTL_STATS); EP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
     if (launch_extend(EP, ext_blocks, 128, st)) return -1;
     ++launches;
+    }
     // read-ordered compaction into the batch result
-    if (launch_exclusive_scan(EP.reg_n, ctx->d_dst_off.as<i64>(), n, ctx->d_scan_tmp.as<i64>(), st)) return -1;
+    if (launch_exclusive_scan(reg_n_ptr, ctx->d_dst_off.as<i64>(), n, ctx->d_scan_tmp.as<i64>(), st)) return -1;
     launches += 3;
     i64 tot_regs = 0;
     u64 ctl[CTL_SLOTS];
@@ -212,10 +260,10 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
             ctx->d_final = nb;
         }
     }
-    if (launch_gather_regs(ctx->d_arena.as<mem_alnreg_t>(), EP.reg_off, EP.reg_n, ctx->d_dst_off.as<i64>(), n,
+    if (launch_gather_regs(ctx->d_arena.as<mem_alnreg_t>(), reg_off_ptr, reg_n_ptr, ctx->d_dst_off.as<i64>(), n,
                            ctx->d_final.as<mem_alnreg_t>() + ctx->total_regs, st)) return -1;
     ++launches;
-    B200_CHECK(cudaMemcpyAsync(ctx->d_final_n.as<i32>() + r0, EP.reg_n, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_final_n.as<i32>() + r0, reg_n_ptr, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     tm.mark(st);
     B200_CHECK(cudaStreamSynchronize(st));
     ctx->total_regs += tot_regs;

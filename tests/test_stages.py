@@ -227,3 +227,22 @@ def test_collect_intv_list_spill(backend):
             ctx.tune("smem_lcap", 0)
         assert np.array_equal(c0, c1)
         assert iv0.tobytes() == iv1.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_align_general_extension_kernel(backend):
+    """The warp-per-read extension kernel (long reads / wide scores) forced onto short reads: same regions as the
+    round-based fast path and as the reference."""
+    idx, ctx = cm.ref_index("rep"), cm.context(backend, "rep")
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for("rep", _sizes(backend, 300, 30000), seed=61, sub=0.02, indel=0.005)
+    r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
+    ctx.tune("ext_path", 1)
+    try:
+        r1, n1 = ctx.align(opt, seqs, off)
+    finally:
+        ctx.tune("ext_path", 0)
+    r2, n2 = ctx.align(opt, seqs, off)
+    assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
+    assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
