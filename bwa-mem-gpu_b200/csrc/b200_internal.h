@@ -50,6 +50,8 @@ struct SmemParams {
     // fast kernel (smem2.cu): reads whose change-point list exceeds the shared-memory capacity are queued
     // here and re-done by the general kernel, which then takes its read indices from the queue
     unsigned *retry_n; i32 *retry_ids; int use_retry;
+    // smem3.cu: 4-bit packed reads (pk_stride words per read) and the per-thread spill area (spill_cap entries)
+    const u32 *pk; int pk_stride; int spill_cap;
 };
 
 struct SeedParams {
@@ -134,6 +136,9 @@ int launch_pack_reads(u8 *seq, i64 n_bytes, cudaStream_t st);
 int launch_smem_collect(const SmemParams &p, int grid, int block, cudaStream_t st);
 int launch_smem_single(const SmemParams &p, int grid, int block, cudaStream_t st);
 int launch_smem_fast(const SmemParams &p, int grid, int wide, cudaStream_t st);
+int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st);
+size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
+int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
 int launch_seed_count(const SeedParams &p, cudaStream_t st);
 int launch_seed_fill(const SeedParams &p, cudaStream_t st);

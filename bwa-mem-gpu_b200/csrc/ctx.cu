@@ -50,6 +50,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "smem_lcap")) ctx->smem_lcap = (int)value;
     else if (!strcmp(key, "cap_intv")) ctx->cap_intv = (int)value;
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
+    else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else { b200_set_error("unknown tunable '%s'", key); return -1; }
     return 0;
 }
@@ -59,7 +60,7 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
-    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_retry, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
                        &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,

@@ -26,7 +26,7 @@ struct b200_ctx {
     cudaStream_t st = nullptr;
     bool has_index = false;
     DevIndex ix;
-    DevBuf d_occ32, d_retry, d_jobs0, d_jobs1, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
+    DevBuf d_occ32, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
     const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
 
     // resident input batch
@@ -38,6 +38,7 @@ struct b200_ctx {
     int chunk_reads = 1 << 20;
     int cap_intv = 0;                          // 0 = auto from read length
     int ext_path = 0;                          // 0 = auto, 1 = force the general warp-per-read kernel, 2 = force the round-based fast path
+    int smem_path = 0;                         // 0 = auto (smem3 for short reads), 2 = smem2 kernel, 1 = general kernel only
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
 
     // per-chunk intermediates

@@ -27,9 +27,9 @@ __device__ __forceinline__ Occ32Blk occ32_load(const uint4 *occ32, u64 blk)
 __device__ __forceinline__ void occ32_pair(const Occ32Blk &b, int off, int c, u32 &n_eq, u32 &n_gt)
 {
     const u32 m1 = (u32)-(c >> 1), m0 = (u32)-(c & 1);             // all-ones when the bit of c is set
-    // 64-bit inclusive mask of rows 0..off as two halves
-    const u32 mlo = off >= 31 ? 0xffffffffu : (2u << off) - 1u;
-    const u32 mhi = off < 32 ? 0u : (off >= 63 ? 0xffffffffu : (2u << (off - 32)) - 1u);
+    // 64-bit inclusive mask of rows 0..off (off = 63 shifts the single zero bit out: all ones)
+    const u64 m64 = ~(~1ull << off);
+    const u32 mlo = (u32)m64, mhi = (u32)(m64 >> 32);
     const u32 lo0 = b.pl.x, lo1 = b.pl.y, hi0 = b.pl.z, hi1 = b.pl.w;
     const u32 e0 = ~(hi0 ^ m1) & ~(lo0 ^ m0) & mlo, e1 = ~(hi1 ^ m1) & ~(lo1 ^ m0) & mhi;
     const u32 w0 = lo0 & ~m0, w1 = lo1 & ~m0;

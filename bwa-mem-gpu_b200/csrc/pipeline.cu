@@ -73,18 +73,23 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     u64 launches = 0;
 
     tm.mark(st);
-    // ---- K0: ASCII -> nt4 (idempotent on already-packed input)
-    if (launch_pack_reads(ctx->d_seq.as<u8>() + byte0, ctx->h_off[r0 + n] - byte0, st)) return -1;
+    // ---- K1 setup: which seeding kernel
+    const int cap_intv = auto_cap_intv(ctx, opt);
+    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull;
+    const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
+    int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 12;
+    lcap3 = lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);
+    const bool use3 = ctx->smem_path == 0 && smem_fast3_bytes(wide, lcap3, pk_stride) <= 100 * 1024;
+    // ---- K0: ASCII -> nt4 (idempotent on already-packed input) [+ 4-bit packed copy for the seeding kernel]
+    if (use3) {
+        if (ctx->d_pk.ensure((size_t)n * pk_stride * 4 + 64)) return -1;
+        if (launch_pack4(ctx->d_seq.as<u8>(), d_off, n, ctx->d_pk.as<u32>(), pk_stride, st)) return -1;
+    } else if (launch_pack_reads(ctx->d_seq.as<u8>() + byte0, ctx->h_off[r0 + n] - byte0, st)) return -1;
     ++launches;
     tm.mark(st);
 
     // ---- K1: SMEM collection: fast kernel (shared-memory lists, occ32 index), then the general kernel on the
-    //      (normally empty) queue of reads whose change-point list did not fit
-    const int cap_intv = auto_cap_intv(ctx, opt);
-    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull;
-    const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);
-    const int per_sm = std::max(1, (int)((200 * 1024) / ((size_t)lcap * 128 * (wide ? 32 : 16))));
-    const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * std::min(per_sm, 6)));
+    //      (normally empty) queue of reads the fast kernel could not hold
     int blocks = std::min((n + 127) / 128, ctx->n_sms);
     const int list_cap = ctx->max_len + 1;
     {   // keep the general kernel's interval-list scratch under ~2 GB for long reads
@@ -92,6 +97,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         size_t max_blocks = std::max<size_t>(1, ((size_t)2 << 30) / per_block);
         blocks = (int)std::min<size_t>(blocks, max_blocks);
     }
+    if (ctx->smem_path == 1) blocks = std::min((n + 127) / 128, ctx->n_sms * 8);
     if (ctx->d_intv.ensure((size_t)n * cap_intv * sizeof(Intv)) || ctx->d_intv_n.ensure((size_t)n * 4) ||
         ctx->d_lists.ensure((size_t)blocks * 128 * 2 * list_cap * sizeof(Intv)) || ctx->d_retry.ensure((size_t)n * 4 + 4)) return -1;
     SmemParams SP;
@@ -103,12 +109,30 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     SP.out = ctx->d_intv.as<Intv>(); SP.cap_out = cap_intv; SP.out_n = ctx->d_intv_n.as<i32>();
     SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
     SP.retry_n = ctl_u32(ctx, CTL_RETRY); SP.retry_ids = ctx->d_retry.as<i32>();
-    SP.list_cap = lcap;
-    if (launch_smem_fast(SP, fast_blocks, wide ? 1 : 0, st)) return -1;
-    SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap; SP.use_retry = 1;
-    SP.work_counter = ctl_u32(ctx, CTL_WORK2);
-    if (launch_smem_collect(SP, blocks, 128, st)) return -1;
-    launches += 2;
+    if (use3) {
+        const size_t smem = smem_fast3_bytes(wide, lcap3, pk_stride);
+        const int per_sm = std::max(1, std::min(8, (int)((224 * 1024) / (smem + 1024))));
+        const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * per_sm));
+        const int spill_cap = std::max(1, ctx->max_len + 1 - lcap3);
+        if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;
+        SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
+        SP.lists = (Intv *)ctx->d_spill.p;
+        if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, st)) return -1;
+        ++launches;
+    } else if (ctx->smem_path != 1) {
+        const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);
+        const int per_sm = std::max(1, (int)((200 * 1024) / ((size_t)lcap * 128 * (wide ? 32 : 16))));
+        const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * std::min(per_sm, 6)));
+        SP.list_cap = lcap;
+        if (launch_smem_fast(SP, fast_blocks, wide ? 1 : 0, st)) return -1;
+        ++launches;
+    }
+    if (!use3) {                                                             // general kernel: retry queue, or everything
+        SP.lists = ctx->d_lists.as<Intv>(); SP.list_cap = list_cap; SP.use_retry = ctx->smem_path != 1;
+        SP.work_counter = ctl_u32(ctx, CTL_WORK2);
+        if (launch_smem_collect(SP, blocks, 128, st)) return -1;
+        ++launches;
+    }
     tm.mark(st);
     if (stop_after == 1) {
         u64 ovf;

@@ -1,0 +1,329 @@
+// Stage 1, fast path: mem_collect_intv (bwamem.c:137-185) = three seeding passes built from bwt_smem1a
+// (bwt.c:289-351) and bwt_seed_strategy1 (bwt.c:358-379), one read per lane over the occ32 index.
+//
+// Why this shape.  Per 150-bp read the reference issues ~700 DEPENDENT bwt_extend calls; each is one or two
+// random index sectors followed by a little integer work.  The batch holds millions of independent reads, so
+// the machine is filled across reads (one read per lane, persistent lanes pulling reads from an atomic
+// counter) and the per-lane code is a flattened state machine with exactly ONE extension site per iteration:
+// whatever phase the 32 reads of a warp are in (forward sweep, lock-step backward sweep, re-seeding,
+// LAST-like sweep) all lanes meet at the gather, issue their sector loads together and do the same popcount
+// arithmetic.  Everything around the gather is kept uniform and small:
+//   * one register triple holds "the interval to extend next" in every phase and one index holds "the query
+//     position to extend with", so forming the request is the same three instructions for all phases;
+//   * only the child ok[c] that the algorithm consumes is computed (occ32.cuh);
+//   * the read is staged once in SHARED memory as 4-bit codes ([word][thread] interleaved), so the per-step
+//     base fetch is a conflict-free LDS instead of a global byte load;
+//   * the forward change-point list lives in SHARED memory as a ring of the last LCAP entries ([slot][thread]
+//     interleaved 16/32-byte records, conflict-free 128-bit accesses); older entries spill to a per-thread
+//     global area; the backward sweep compacts the list IN PLACE (survivors overwrite consumed entries);
+//   * positions are 32-bit when seq_len < 2^32 (template PT), 64-bit otherwise;
+//   * chain restarts (pass-1 continuation, pass-3 restart) are inlined after the consume step; only pass
+//     changes, pass-2 candidate scans and read changes take the slow path.
+// The emitted interval set equals the reference's; records are determined by (start,end), so after the sort
+// by `info` (bwamem.c:184) the order is unique.
+#include "b200_internal.h"
+#include "occ32.cuh"
+
+#define S3_THREADS 128
+
+enum { S3_TASK = 0, S3_FWD = 1, S3_BWD = 2, S3_P3 = 3, S3_FIN = 4 };
+
+template <class PT> struct Ent;
+template <> struct Ent<u32> {
+    static constexpr int kQuads = 1;
+    static __device__ __forceinline__ void st(uint4 *p, int stride, u32 x0, u32 x1, u32 x2, u32 end)
+    { p[0] = make_uint4(x0, x1, x2, end); (void)stride; }
+    static __device__ __forceinline__ void ld(const uint4 *p, int stride, u32 &x0, u32 &x1, u32 &x2, u32 &end)
+    { const uint4 v = p[0]; x0 = v.x; x1 = v.y; x2 = v.z; end = v.w; (void)stride; }
+};
+template <> struct Ent<u64> {
+    static constexpr int kQuads = 2;
+    static __device__ __forceinline__ void st(uint4 *p, int stride, u64 x0, u64 x1, u64 x2, u32 end)
+    {
+        p[0] = make_uint4((u32)x0, (u32)(x0 >> 32), (u32)x1, (u32)(x1 >> 32));
+        p[stride] = make_uint4((u32)x2, (u32)(x2 >> 32), end, 0);
+    }
+    static __device__ __forceinline__ void ld(const uint4 *p, int stride, u64 &x0, u64 &x1, u64 &x2, u32 &end)
+    {
+        const uint4 a = p[0], b = p[stride];
+        x0 = (u64)a.y << 32 | a.x; x1 = (u64)a.w << 32 | a.z; x2 = (u64)b.y << 32 | b.x; end = b.z;
+    }
+};
+
+__device__ __forceinline__ void s3_emit(Intv *out, int &n_out, int cap_out, u64 x0, u64 x1, u64 x2, int start, int end)
+{
+    if (n_out < cap_out) {
+        uint4 *q = (uint4 *)&out[n_out];
+        q[0] = make_uint4((u32)x0, (u32)(x0 >> 32), (u32)x1, (u32)(x1 >> 32));
+        q[1] = make_uint4((u32)x2, (u32)(x2 >> 32), (u32)end, (u32)start);
+    }
+    ++n_out;
+}
+
+// ASCII / nt4 bytes -> nt4 in place (nst_nt4_table, bntseq.c:40-57; mem_align1_core, bwamem.c:1067-1068) and a
+// 4-bit packed copy, `stride` words per read, for the seeding kernel.
+__global__ void pack4_kernel(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride)
+{
+    const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const i64 o = off[r];
+    const int len = (int)(off[r + 1] - o);
+    u32 *dst = pk + (size_t)r * stride;
+    for (int w = (int)lane; w < stride; w += 32) {
+        u32 v = 0;
+        for (int k = 0; k < 8; ++k) {
+            const int i = w * 8 + k;
+            u32 code = 4;
+            if (i < len) {
+                u8 c = seq[o + i];
+                if (c >= 4) {
+                    const u8 u = c & 0xdf;
+                    c = u == 'A' ? 0 : u == 'C' ? 1 : u == 'G' ? 2 : u == 'T' ? 3 : (c == '-' ? 5 : 4);
+                    seq[o + i] = c;
+                }
+                code = c < 4 ? c : 4;
+            }
+            v |= code << (4 * k);
+        }
+        dst[w] = v;
+    }
+}
+
+template <class PT, int LCAP>
+__global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
+{
+    B200_DYN_SMEM(s3_raw);
+    typedef Ent<PT> E;
+    constexpr int EQ = E::kQuads;
+    uint4 *L = (uint4 *)s3_raw + threadIdx.x;                            // slot s: L[s * EQ * S3_THREADS]
+    u32 *Q = (u32 *)((uint4 *)s3_raw + LCAP * EQ * S3_THREADS) + threadIdx.x;   // word w: Q[w * S3_THREADS]
+    const size_t gtid = (size_t)blockIdx.x * S3_THREADS + threadIdx.x;
+    uint4 *SP = (uint4 *)P.lists + gtid * (size_t)P.spill_cap * EQ;      // spilled entry e: SP[e * EQ]
+    const DevIndex &ix = P.ix;
+    const int min_seed_len = P.min_seed_len;
+    const PT max_mem_intv = (PT)P.max_mem_intv;
+    u64 n_ext = 0, n_two = 0;
+
+    Intv *out = nullptr;
+    int len = 0, r = -1, n_out = 0;
+    int st = S3_FIN, pass = 0, x = 0, k2 = 0, old_n = 0;
+    int i = -1, sx = 0, nfw = 0, base = 0, nprev = 0, ncurr = 0, j = 0, last_start = 0, ret = 0;
+    PT min_intv = 1, k0 = 0, k1 = 0, kk2 = 0, last_x2 = 0;              // (k0,k1,kk2): the interval to extend next
+    u32 pend = 0;
+
+#define S3_QGET(pos) ((Q[((pos) >> 3) * S3_THREADS] >> (((pos) & 7) << 2)) & 7u)
+#define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
+#define S3_PUSH(endv)                                                                                   \
+    do {                                                                                                \
+        if (nfw >= LCAP) {                                 /* evict entry nfw - LCAP to the spill area */ \
+            PT t0, t1, t2; u32 te;                                                                      \
+            E::ld(S3_SLOT(nfw), S3_THREADS, t0, t1, t2, te);                                            \
+            if (nfw - LCAP < P.spill_cap) E::st(SP + (size_t)(nfw - LCAP) * EQ, 1, t0, t1, t2, te);     \
+        }                                                                                               \
+        E::st(S3_SLOT(nfw), S3_THREADS, k0, k1, kk2, (u32)(endv));                                      \
+        ++nfw;                                                                                          \
+    } while (0)
+#define S3_LOAD_ENTRY(jj)                                                                               \
+    do {                                                                                                \
+        const int e_ = base - (jj);                                                                     \
+        if ((jj) < LCAP) E::ld(S3_SLOT(e_), S3_THREADS, k0, k1, kk2, pend);                             \
+        else E::ld(SP + (size_t)e_ * EQ, 1, k0, k1, kk2, pend);                                         \
+    } while (0)
+#define S3_STORE_ENTRY(jj, a0, a1, a2, ev)                                                              \
+    do {                                                                                                \
+        const int e_ = base - (jj);                                                                     \
+        if ((jj) < LCAP) E::st(S3_SLOT(e_), S3_THREADS, a0, a1, a2, ev);                                \
+        else E::st(SP + (size_t)e_ * EQ, 1, a0, a1, a2, ev);                                            \
+    } while (0)
+#define S3_START_BWD()                                                                                  \
+    do {                                                                                                \
+        ret = i; base = nfw - 1; nprev = nfw; ncurr = 0; j = 0; i = sx - 1; last_start = 0x7fffffff;    \
+        st = S3_BWD;                                                                                    \
+        S3_LOAD_ENTRY(0);                                                                               \
+    } while (0)
+#define S3_SET_INTV(b0)                                                                                 \
+    do {                                                                                                \
+        k0 = (PT)ix.L2[b0] + 1; kk2 = (PT)(ix.L2[(b0) + 1] - ix.L2[b0]); k1 = (PT)ix.L2[3 - (b0)] + 1;  \
+    } while (0)
+
+    for (;;) {
+        // ------------------------------------------------------------ request: base at position i, or slow path
+        u32 b = 4;
+        if ((unsigned)i < (unsigned)len) b = S3_QGET(i);
+        while (b > 3) {
+            if (st == S3_FWD) {                                             // read end or N: bwt.c:316-318, 321
+                if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; continue; }
+                S3_PUSH(i);
+                S3_START_BWD();
+            } else if (st == S3_BWD) {                                      // i < 0 or N: the longest entry is emitted, sweep ends
+                if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
+                if (pass == 1) x = ret; else ++k2;
+                st = S3_TASK; i = -1;
+            } else if (st == S3_P3) {                                       // bwt.c:366-378
+                if (i >= len) { st = S3_FIN; i = -1; }
+                else { x = i + 1; st = S3_TASK; i = -1; }
+            } else if (st == S3_TASK) {
+                if (pass == 1) {                                            // bwamem.c:144-154
+                    while (x < len && S3_QGET(x) > 3) ++x;
+                    if (x >= len) { pass = 2; old_n = n_out < P.cap_out ? n_out : P.cap_out; k2 = 0; continue; }
+                    sx = x; min_intv = 1;
+                } else if (pass == 2) {                                     // bwamem.c:156-165
+                    bool found = false;
+                    while (k2 < old_n) {
+                        const uint4 v1 = ((const uint4 *)&out[k2])[1];
+                        const u64 sz = (u64)v1.y << 32 | v1.x;
+                        const int s0 = (int)v1.w, e0 = (int)v1.z;
+                        if (e0 - s0 < P.split_len || sz > (u64)P.split_width) { ++k2; continue; }
+                        sx = (s0 + e0) >> 1; min_intv = (PT)sz + 1; found = true;
+                        break;
+                    }
+                    if (!found) { pass = 3; x = 0; continue; }
+                } else {                                                    // bwamem.c:167-182
+                    if (max_mem_intv == 0) { st = S3_FIN; continue; }
+                    while (x < len && S3_QGET(x) > 3) ++x;
+                    if (x >= len) { st = S3_FIN; continue; }
+                    const int b0 = (int)S3_QGET(x);
+                    S3_SET_INTV(b0);
+                    i = x + 1; st = S3_P3;
+                    b = 4; if (i < len) b = S3_QGET(i);
+                    continue;
+                }
+                {                                                           // bwt.c:301-304
+                    const int b0 = (int)S3_QGET(sx);
+                    S3_SET_INTV(b0);
+                    i = sx + 1; nfw = 0; st = S3_FWD;
+                }
+            } else {                                                        // S3_FIN: finish this read, take the next
+                if (r >= 0) {
+                    int n = n_out;
+                    if (n > P.cap_out) { atomicMax(P.overflow, n); n = P.cap_out; }
+                    for (int a = 1; a < n; ++a) {                           // sort by info (bwamem.c:184)
+                        const uint4 v0 = ((uint4 *)&out[a])[0], v1 = ((uint4 *)&out[a])[1];
+                        const u64 key = (u64)v1.w << 32 | v1.z;
+                        int bb = a;
+                        while (bb > 0) {
+                            const uint4 u1 = ((uint4 *)&out[bb - 1])[1];
+                            if (((u64)u1.w << 32 | u1.z) <= key) break;
+                            ((uint4 *)&out[bb])[0] = ((uint4 *)&out[bb - 1])[0]; ((uint4 *)&out[bb])[1] = u1;
+                            --bb;
+                        }
+                        if (bb != a) { ((uint4 *)&out[bb])[0] = v0; ((uint4 *)&out[bb])[1] = v1; }
+                    }
+                    P.out_n[r] = n;
+                }
+                const unsigned nr = atomicAdd(P.work_counter, 1u);
+                if (nr >= (unsigned)P.n_reads) { r = -1; break; }
+                r = (int)nr;
+                len = (int)(P.off[r + 1] - P.off[r]);
+                out = P.out + (size_t)r * P.cap_out;
+                n_out = 0; i = -1;
+                if (len < min_seed_len) continue;                           // bwamem.c:267 (FIN again -> out_n = 0)
+                {                                                           // stage the packed read
+                    const uint4 *src = (const uint4 *)(P.pk + (size_t)r * P.pk_stride);
+                    const int nq = (len + 31) >> 5;
+                    for (int w = 0; w < nq; ++w) {
+                        const uint4 v = __ldg(src + w);
+                        Q[(4 * w) * S3_THREADS] = v.x; Q[(4 * w + 1) * S3_THREADS] = v.y;
+                        Q[(4 * w + 2) * S3_THREADS] = v.z; Q[(4 * w + 3) * S3_THREADS] = v.w;
+                    }
+                }
+                pass = 1; x = 0; st = S3_TASK;
+                continue;
+            }
+            b = 4;
+            if ((unsigned)i < (unsigned)len) b = S3_QGET(i);
+        }
+        if (r < 0) break;                                                   // no reads left for this lane
+
+        // ------------------------------------------------------------ the single gather site
+        const int is_back = st == S3_BWD;
+        const int c = is_back ? (int)b : 3 - (int)b;
+        PT n0, n1, n2; int two;
+        occ32_child<PT>(ix, k0, k1, kk2, is_back, c, n0, n1, n2, two);
+        ++n_ext; n_two += two;
+
+        // ------------------------------------------------------------ consume
+        bool adv = false;                                                   // forward phases: continue with the child
+        int restart = -1;                                                   // >= 0: start a new forward chain of this kind at x
+        if (st == S3_FWD) {                                                 // bwt.c:308-315
+            adv = true;
+            if (n2 != kk2) {
+                if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; adv = false; }
+                else {
+                    S3_PUSH(i);
+                    if (n2 < min_intv) { S3_START_BWD(); adv = false; }
+                }
+            }
+        } else if (st == S3_P3) {                                           // bwt.c:369-375
+            if (n2 < max_mem_intv && i - x >= min_seed_len) {
+                if (n2 > 0) s3_emit(out, n_out, P.cap_out, n0, n1, n2, x, i + 1);   // bwamem.c:174
+                x = i + 1; restart = S3_P3;
+            } else adv = true;
+        } else {                                                            // S3_BWD, bwt.c:331-341
+            if (n2 < min_intv) {
+                if (ncurr == 0 && i + 1 < last_start) {
+                    last_start = i + 1;
+                    if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
+                }
+            } else if (ncurr == 0 || n2 != last_x2) {
+                S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                    // ncurr <= j: slot already consumed
+                ++ncurr; last_x2 = n2;
+            }
+            if (++j == nprev) {                                             // bwt.c:343-344
+                if (ncurr == 0) {
+                    if (pass == 1) { x = ret; restart = S3_FWD; } else { ++k2; st = S3_TASK; i = -1; }
+                } else { nprev = ncurr; ncurr = 0; j = 0; --i; }
+            }
+            if (restart < 0 && st == S3_BWD) S3_LOAD_ENTRY(j);
+        }
+        if (adv) { k0 = n0; k1 = n1; kk2 = n2; ++i; }
+        if (restart >= 0) {                                                 // inline restart of a forward chain at x
+            u32 b0 = 4;
+            if (x < len) b0 = S3_QGET(x);
+            if (b0 < 4) {
+                S3_SET_INTV((int)b0);
+                i = x + 1; st = restart;
+                if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; }
+            } else { st = S3_TASK; i = -1; }                                // N or end of read: slow path decides
+        }
+    }
+    if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
+}
+
+int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st)
+{
+    if (n_reads <= 0) return 0;
+    B200_LAUNCH(pack4_kernel, (int)(((i64)n_reads * 32 + 255) / 256), 256, 0, st, seq, off, n_reads, pk, stride);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
+size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)
+{
+    return (size_t)lcap * (wide ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
+}
+
+template <class PT, int LCAP>
+static int launch_fast3_t(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
+{
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute(smem_fast3_kernel<PT, LCAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+#endif
+    B200_LAUNCH((smem_fast3_kernel<PT, LCAP>), grid, S3_THREADS, smem, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st)
+{
+    const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
+    if (wide) {
+        if (lcap == 8) return launch_fast3_t<u64, 8>(p, grid, smem, st);
+        if (lcap == 12) return launch_fast3_t<u64, 12>(p, grid, smem, st);
+        return launch_fast3_t<u64, 16>(p, grid, smem, st);
+    }
+    if (lcap == 8) return launch_fast3_t<u32, 8>(p, grid, smem, st);
+    if (lcap == 12) return launch_fast3_t<u32, 12>(p, grid, smem, st);
+    return launch_fast3_t<u32, 16>(p, grid, smem, st);
+}

@@ -219,14 +219,18 @@ def test_collect_intv_list_spill(backend):
     opt = abi.default_opt()
     seqs, off = cm.reads_for("rep", _sizes(backend, 600, 20000), seed=77, n_rate=0.001)
     iv0, c0 = idx.collect_intv(opt, seqs, off)
-    for lcap in (2, 9):
+    # smem_path 0: ring-list kernel (smem3.cu, lcap 8 / 12 / 16 with spill to global); 2: fixed-list kernel with the
+    # retry queue (smem2.cu); 1: general kernel only (smem.cu)
+    for path, lcap in ((0, 8), (0, 12), (0, 16), (2, 2), (2, 9), (1, 0)):
+        ctx.tune("smem_path", path)
         ctx.tune("smem_lcap", lcap)
         try:
             iv1, c1 = ctx.collect_intv(opt, seqs, off)
         finally:
             ctx.tune("smem_lcap", 0)
-        assert np.array_equal(c0, c1)
-        assert iv0.tobytes() == iv1.tobytes()
+            ctx.tune("smem_path", 0)
+        assert np.array_equal(c0, c1), (path, lcap)
+        assert iv0.tobytes() == iv1.tobytes(), (path, lcap)
 
 
 @needs_ref
