@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--read-len", type=int, default=150)
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tune", default="", help="comma-separated key=value context tunables (b200_ctx_tune)")
     return ap.parse_args()
 
 
@@ -184,6 +185,9 @@ def main():
     hidx = L.HostIndex(contigs)
     t_index = time.time() - t0
     ctx = L.Context(local_rank)
+    for kv in filter(None, a.tune.split(",")):
+        k, v = kv.split("=")
+        ctx.tune(k, int(v))
     t0 = time.time()
     ctx.upload_host_index(hidx)
     t_upload = time.time() - t0
