@@ -1,0 +1,144 @@
+// Drop-in mem_process_seqs (bwamem.h:69, bwamem.c:1215-1244): worker1 (mem_align1_core for every read,
+// bwamem.c:1183-1195) runs on the GPU through b200_align_batch; everything after it stays the REFERENCE's own
+// host code -- mem_pestat (bwamem_pair.c:72), worker2 = mem_mark_primary_se / mem_reg2sam / mem_sam_pe
+// (bwamem.c:1197-1213) -- which this library does not contain: those symbols are resolved from the host
+// program the library is linked into (weak references, or the global symbol scope when loaded dynamically).
+// Nothing here computes alignments on the CPU; if the host functions are missing the call fails loudly.
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <thread>
+#include <vector>
+#include <atomic>
+#include "../../include/bwamem_b200.h"
+
+#define MEM_F_PRIMARY5_ 0x800        /* bwamem.h:47 */
+
+extern "C" {
+int  mem_mark_primary_se(const mem_opt_t *opt, int n, mem_alnreg_t *a, int64_t id) __attribute__((weak));
+void mem_reg2sam(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, bseq1_t *s, mem_alnreg_v *a,
+                 int extra_flag, const void *m) __attribute__((weak));
+int  mem_sam_pe(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, const mem_pestat_t pes[4], uint64_t id,
+                bseq1_t s[2], mem_alnreg_v a[2]) __attribute__((weak));
+void mem_pestat(const mem_opt_t *opt, int64_t l_pac, int n, const mem_alnreg_v *regs, mem_pestat_t pes[4]) __attribute__((weak));
+}
+
+typedef int  (*mark_fn)(const mem_opt_t *, int, mem_alnreg_t *, int64_t);
+typedef void (*reg2sam_fn)(const mem_opt_t *, const bntseq_t *, const uint8_t *, bseq1_t *, mem_alnreg_v *, int, const void *);
+typedef int  (*sam_pe_fn)(const mem_opt_t *, const bntseq_t *, const uint8_t *, const mem_pestat_t *, uint64_t, bseq1_t *, mem_alnreg_v *);
+typedef void (*pestat_fn)(const mem_opt_t *, int64_t, int, const mem_alnreg_v *, mem_pestat_t *);
+
+static void *host_symbol(void *weak_addr, const char *name)
+{
+    if (weak_addr) return weak_addr;
+    void *p = dlsym(RTLD_DEFAULT, name);
+    if (!p) {
+        fprintf(stderr, "[b200::mem_process_seqs] host function %s not found: link this library into the reference's "
+                        "host code (see INTEGRATION.md); there is no CPU path in libbwamem_b200\n", name);
+        exit(1);
+    }
+    return p;
+}
+
+// nst_nt4_table (bntseq.c:40-57) restricted to what mem_align1_core needs (bwamem.c:1067-1068)
+static inline uint8_t nt4_of(uint8_t c)
+{
+    if (c < 4) return c;
+    switch (c & 0xdf) { case 'A': return 0; case 'C': return 1; case 'G': return 2; case 'T': return 3; }
+    return c == '-' ? 5 : 4;
+}
+
+static b200_ctx_t *g_ps_ctx = nullptr;
+static const bwt_t *g_ps_bwt = nullptr;
+
+extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctx = ctx; g_ps_bwt = nullptr; }
+
+extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
+                                      int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
+{
+    mark_fn f_mark = (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
+    reg2sam_fn f_reg2sam = (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
+    const bool pe = (opt->flag & MEM_F_PE) != 0;
+    sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
+    pestat_fn f_pestat = (pe && !pes0) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
+
+    if (!g_ps_ctx || (g_ps_bwt && g_ps_bwt != bwt)) {                 // lazy context from the index identity
+        g_ps_ctx = b200_ctx_create(0);
+        if (!g_ps_ctx || b200_index_upload(g_ps_ctx, bwt, bns, pac, B200_IDX_FULL_SA)) {
+            fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
+            exit(1);
+        }
+        g_ps_bwt = bwt;
+    }
+
+    // ---- worker1 on the device
+    std::vector<int64_t> off((size_t)n + 1);
+    int64_t tot = 0;
+    for (int i = 0; i < n; ++i) { off[i] = tot; tot += seqs[i].l_seq; }
+    off[n] = tot;
+    std::vector<uint8_t> flat((size_t)tot + 1);
+    for (int i = 0; i < n; ++i) memcpy(flat.data() + off[i], seqs[i].seq, (size_t)seqs[i].l_seq);
+    std::vector<int32_t> cnt((size_t)n + 1);
+    std::vector<mem_alnreg_t> regs;
+    int64_t cap = 2 * (int64_t)n + 64;
+    for (;;) {
+        regs.resize((size_t)cap);
+        int64_t got = b200_align_batch(g_ps_ctx, opt, n, flat.data(), off.data(), cap, regs.data(), cnt.data());
+        if (got >= 0) break;
+        if (-got > cap) { cap = -got; continue; }
+        fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
+        exit(1);
+    }
+    mem_alnreg_v *rv = (mem_alnreg_v *)malloc((size_t)(n > 0 ? n : 1) * sizeof(mem_alnreg_v));
+    for (int64_t i = 0, k = 0; i < n; ++i) {
+        rv[i].n = rv[i].m = cnt[i];
+        rv[i].a = (mem_alnreg_t *)malloc((size_t)(cnt[i] > 0 ? cnt[i] : 1) * sizeof(mem_alnreg_t));
+        memcpy(rv[i].a, regs.data() + k, (size_t)cnt[i] * sizeof(mem_alnreg_t));
+        k += cnt[i];
+        for (int j = 0; j < seqs[i].l_seq; ++j) seqs[i].seq[j] = (char)nt4_of((uint8_t)seqs[i].seq[j]);   // bwamem.c:1067-1068
+    }
+
+    // ---- batch-level insert-size statistics and worker2: the reference's own host code
+    mem_pestat_t pes[4];
+    if (pe) {
+        if (pes0) memcpy(pes, pes0, 4 * sizeof(mem_pestat_t));        // bwamem.c:1237
+        else f_pestat(opt, bns->l_pac, n, rv, pes);                   // bwamem.c:1238
+    }
+    const int n_units = pe ? n >> 1 : n;
+    int n_threads = opt->n_threads > 0 ? opt->n_threads : 1;
+    if (n_threads > n_units) n_threads = n_units > 0 ? n_units : 1;
+    std::atomic<int> next(0);
+    auto work = [&]() {
+        for (;;) {
+            const int i = next.fetch_add(1);
+            if (i >= n_units) break;
+            if (!pe) {                                                // bwamem.c:1202-1207
+                f_mark(opt, rv[i].n, rv[i].a, n_processed + i);
+                f_reg2sam(opt, bns, pac, &seqs[i], &rv[i], 0, nullptr);
+                free(rv[i].a);
+            } else {                                                  // bwamem.c:1208-1212
+                f_sam_pe(opt, bns, pac, pes, (uint64_t)((n_processed >> 1) + i), &seqs[i << 1], &rv[i << 1]);
+                free(rv[i << 1 | 0].a); free(rv[i << 1 | 1].a);
+            }
+        }
+    };
+    if (opt->flag & MEM_F_PRIMARY5_) {
+        fprintf(stderr, "[b200::mem_process_seqs] -5 (MEM_F_PRIMARY5) needs the reference's static mem_reorder_primary5; not supported\n");
+        exit(1);
+    }
+    std::vector<std::thread> pool;
+    for (int t = 1; t < n_threads; ++t) pool.emplace_back(work);
+    work();
+    for (auto &th : pool) th.join();
+    free(rv);
+}
+
+#ifndef BWAMEM_B200_NO_DROPIN
+// the reference's own name (bwamem.h:69)
+extern "C" void mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
+                                 int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
+{
+    b200_mem_process_seqs(opt, bwt, bns, pac, n_processed, n, seqs, pes0);
+}
+#endif

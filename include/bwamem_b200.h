@@ -224,7 +224,18 @@ int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out /* 16 */);
  * device code on a batch of one (parity tests call these one problem at a time).  The device
  * context/index is created lazily from the bwt_t identity on first use.
  * ===================================================================================== */
+/* mem_process_seqs (bwamem.h:69, bwamem.c:1215): worker1 on the device, then the REFERENCE's own host code for
+ * mem_pestat / worker2 (mem_mark_primary_se, mem_reg2sam, mem_sam_pe), resolved from the program this library is
+ * linked into.  seqs[i].sam is produced by that host code and owned by the caller, as in the reference.
+ * b200_process_seqs_set_ctx() selects an existing context (index already uploaded); otherwise one is created on
+ * device 0 from (bwt, bns, pac) at the first call. */
+void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
+void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
+                           int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
+
 #ifndef BWAMEM_B200_NO_DROPIN
+void     mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
+                          int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);             /* bwamem.h:69 */
 void     bwt_occ4(const bwt_t *bwt, bwtint_t k, bwtint_t cnt[4]);                                   /* bwt.h:103 */
 void     bwt_2occ4(const bwt_t *bwt, bwtint_t k, bwtint_t l, bwtint_t cntk[4], bwtint_t cntl[4]);  /* bwt.h:109 */
 void     bwt_extend(const bwt_t *bwt, const bwtintv_t *ik, bwtintv_t ok[4], int is_back);           /* bwt.h:117 */

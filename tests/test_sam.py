@@ -1,0 +1,80 @@
+"""End-to-end drop-in parity: our mem_process_seqs (worker1 on the device through the C ABI, then the reference's own
+worker2 host code) must produce byte-identical SAM records to the reference's mem_process_seqs (bwamem.c:1215) --
+POS, CIGAR, MAPQ, NM, MD, AS, XS, SA/XA tags, flags -- for single-end and paired-end batches.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import common as cm
+import refapi
+from bwa_mem_gpu_b200 import abi, synth
+
+BACKENDS = [pytest.param("emu", id="emu"), pytest.param("cuda", id="cuda", marks=pytest.mark.gpu)]
+needs_ref = pytest.mark.skipif(not cm.have_ref(), reason="oracle/_ref not built")
+
+
+class BSeq1(C.Structure):          # bseq1_t, bwa.h:56-63
+    _fields_ = [("l_seq", C.c_int), ("id", C.c_int), ("name", C.c_char_p), ("comment", C.c_char_p),
+                ("seq", C.POINTER(C.c_char)), ("qual", C.c_char_p), ("sam", C.c_void_p),
+                ("l_name", C.c_int8), ("l_comment", C.c_int8), ("l_qual", C.c_int16)]
+
+
+def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None):
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    C.CDLL(refapi.REF_SO, mode=os.RTLD_GLOBAL)          # the "host program": the reference's worker2 functions
+    lib = ctx.lib
+    n = len(off) - 1
+    arr = (BSeq1 * n)()
+    keep = []
+    asc = synth.to_ascii(seqs)
+    for i in range(n):
+        s = C.create_string_buffer(bytes(asc[off[i]:off[i + 1]]) + b"\0")
+        nm = (names[i] if names else f"r{n_processed + i}").encode()
+        keep.append((s, nm))
+        arr[i].l_seq = int(off[i + 1] - off[i]); arr[i].id = i
+        arr[i].name = nm; arr[i].comment = None; arr[i].seq = C.cast(s, C.POINTER(C.c_char)); arr[i].qual = None
+    lib.b200_process_seqs_set_ctx(ctx.h)
+    lib.b200_mem_process_seqs(C.byref(opt), C.c_void_p(idx.bwt_struct()), C.c_void_p(idx.bns_struct()),
+                              C.c_void_p(idx.pac().ctypes.data), C.c_int64(n_processed), C.c_int(n), arr, None)
+    out = b"".join(C.string_at(arr[i].sam) for i in range(n))
+    for i in range(n):
+        idx.lib.ref_free(C.c_void_p(arr[i].sam))
+    return out
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_sam_single_end(backend, gname):
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    opt.n_threads = 4
+    n = 400 if backend == "emu" else 20000
+    seqs, off = cm.reads_for(gname, n, seed=71, indel=0.004, sub=0.015)
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, n_processed=1000)
+    got = _our_sam(backend, gname, opt, seqs, off, n_processed=1000)
+    assert got == exp
+    assert exp.count(b"\n") >= n
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_sam_paired_end(backend):
+    """Interleaved pairs (MEM_F_PE): batch-level mem_pestat + mem_sam_pe on the host over device-computed regions."""
+    gname = "small"
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    opt.flag |= 0x2
+    opt.n_threads = 4
+    npairs = 300 if backend == "emu" else 8000
+    reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=81, damaged_frac=0.1)
+    seqs = np.ascontiguousarray(reads.reshape(-1))
+    off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
+    names = [f"p{i // 2}" for i in range(2 * npairs)]
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0)
+    got = _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names)
+    assert got == exp
+    assert exp.count(b"\n") >= 2 * npairs
