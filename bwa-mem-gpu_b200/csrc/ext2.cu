@@ -172,7 +172,8 @@ struct DpLane {
     int side, t, a_score, sc0, prev;
     // ksw_extend2 state (ksw.c:380-479)
     int qlen, tlen, w, h0;
-    int i, j, beg, end, h1, f, m, mj, tb5, first_nz, last_nz;
+    int i, j, beg, end, h1, f, m, mj, first_nz, last_nz;
+    u32 srow_lo, srow_hi;                 // substitution scores of the current target base vs query base 0..7
     int max, max_i, max_j, max_ie, gscore, max_off;
 };
 
@@ -185,14 +186,34 @@ __device__ __forceinline__ int dp_target_base(const DevIndex &ix, DpLane &L)
     return (int)((L.pacw >> sh) & 3) ^ L.comp;
 }
 
+// signed byte q of the 8-byte matrix row {hi:lo}: one PRMT (byte q into the low byte, its sign bit replicated
+// into the three upper bytes).  The __byte_perm intrinsic documents only 3 selector bits, so prmt is spelled out.
+__device__ __forceinline__ int dp_score(u32 lo, u32 hi, u32 q)
+{
+#ifdef B200_EMU
+    return (int)(int8_t)(((u64)hi << 32 | lo) >> (8 * q));
+#else
+    u32 r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(q * 0x1111u + 0x8880u));
+    return (int)r;
+#endif
+}
+
 __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round)
 {
     B200_DYN_SMEM(dp_raw);
-    __shared__ int8_t s_mat[32];
+    __shared__ u32 s_rows[5 * 2];                          // matrix row of each target base, 8 bytes (5 used)
     u32 *he = (u32 *)dp_raw + threadIdx.x;                 // column j of this lane: he[j * DP_THREADS]
     const unsigned lane = threadIdx.x & 31;
     u32 *he_warp = (u32 *)dp_raw + (threadIdx.x & ~31u);
-    if (threadIdx.x < 25) s_mat[threadIdx.x] = P.opt.mat[threadIdx.x];
+    if (threadIdx.x < 10) {
+        u32 v = 0;
+        for (int k = 0; k < 4; ++k) {
+            const int col = (threadIdx.x & 1) * 4 + k;
+            if (col < 5) v |= (u32)(u8)P.opt.mat[(threadIdx.x >> 1) * 5 + col] << (8 * k);
+        }
+        s_rows[threadIdx.x] = v;
+    }
     __syncthreads();
     const DevIndex &ix = P.ix;
     const mem_opt_t &opt = P.opt;
@@ -202,6 +223,7 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
     const unsigned njobs = P.njobs[round];
     const i64 l_pac = ix.l_pac;
     u64 n_ksw = 0, n_cells = 0;
+    unsigned ncell32 = 0;                  // cells of the current job (flushed into n_cells when it ends)
 
     DpLane L;
     memset(&L, 0, sizeof(L));
@@ -209,26 +231,34 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
 
     for (;;) {
         // ---------------------------------------------------------------- hot slot: up to 8 cells of the current row
+        // The 8 H/E words are fetched first (independent LDS, the row is padded by 8 columns), the cells are then
+        // evaluated from registers; the substitution score comes from the target base's matrix row held in two
+        // registers (byte select with sign replication), so a cell has no memory latency on its dependency chain.
         if (active) {
+            u32 *p = he + L.j * DP_THREADS;
+            u32 w8[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) w8[u] = p[u * DP_THREADS];
+            const int rem = L.end - L.j;
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-                if (L.j < L.end) {
-                    u32 *p = he + L.j * DP_THREADS;
-                    const u32 wv = *p;
+                if (u < rem) {
+                    const u32 wv = w8[u];
+                    const int jj = L.j + u;
                     int M = (int)(wv & DP_HMASK);
                     const int e = (int)((wv >> 14) & DP_HMASK);
-                    const int sc = s_mat[L.tb5 + (int)(wv >> 28)];
+                    const int sc = dp_score(L.srow_lo, L.srow_hi, wv >> 28);
                     M = M ? M + sc : 0;                                                   // ksw.c:433
                     const int h = __vimax3_s32(M, e, L.f);                                // ksw.c:434-435
                     const int en = __viaddmax_s32_relu(e, -e_del, M - oe_del);            // ksw.c:439-442
-                    *p = (wv & DP_QMASK) | (u32)L.h1 | ((u32)en << 14);                   // ksw.c:432,442
-                    if (L.h1 | en) { L.last_nz = L.j; if (L.first_nz > L.j) L.first_nz = L.j; }
+                    p[u * DP_THREADS] = (wv & DP_QMASK) | (u32)L.h1 | ((u32)en << 14);    // ksw.c:432,442
+                    if (L.h1 | en) { L.last_nz = jj; if (L.first_nz > jj) L.first_nz = jj; }
                     L.h1 = h;
-                    if (h >= L.m) { L.m = h; L.mj = L.j; }                                // ksw.c:437-438 (last column on ties)
+                    if (h >= L.m) { L.m = h; L.mj = jj; }                                 // ksw.c:437-438 (last column on ties)
                     L.f = __viaddmax_s32_relu(L.f, -e_ins, M - oe_ins);                   // ksw.c:444-447
-                    ++L.j;
                 }
             }
+            if (rem > 0) L.j += rem < 8 ? rem : 8;
         }
         // ---------------------------------------------------------------- control slot
         bool ksw_fin = false;
@@ -262,14 +292,14 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
                     if (++L.i >= L.tlen) ksw_fin = true;
                     else {                                                                // next row, ksw.c:411-423
                         L.fpos += L.fstep;
-                        L.tb5 = dp_target_base(ix, L) * 5;
+                        { const int tb = dp_target_base(ix, L); L.srow_lo = s_rows[2 * tb]; L.srow_hi = s_rows[2 * tb + 1]; }
                         if (L.beg < L.i - L.w) L.beg = L.i - L.w;
                         if (L.end > L.i + L.w + 1) L.end = L.i + L.w + 1;
                         if (L.end > L.qlen) L.end = L.qlen;
                         L.h1 = 0;
                         if (L.beg == 0) { L.h1 = L.h0 - (o_del + e_del * (L.i + 1)); if (L.h1 < 0) L.h1 = 0; }
                         L.f = 0; L.m = 0; L.mj = -1; L.first_nz = 0x7fffffff; L.last_nz = -1; L.j = L.beg;
-                        if (L.end > L.beg) n_cells += (u64)(L.end - L.beg);
+                        if (L.end > L.beg) ncell32 += (unsigned)(L.end - L.beg);
                     }
                 }
             }
@@ -316,6 +346,7 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
                         J->w = J->w > aw ? J->w : aw;
                         J->score = score;
                         active = false;                                                   // job done
+                        n_cells += ncell32; ncell32 = 0;
                         continue;
                     }
                 }
@@ -325,6 +356,7 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
                 if (J->qbeg + J->slen == J->lq) {                                         // bwamem.c:778
                     J->qe = J->lq; J->re = J->rbeg + J->slen; J->score = L.a_score;
                     active = false;
+                    n_cells += ncell32; ncell32 = 0;
                     continue;
                 }
                 L.sc0 = L.a_score; L.prev = L.a_score;
@@ -355,12 +387,12 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
                 ++n_ksw;
                 if (L.tlen <= 0) { ksw_fin = true; continue; }                            // no rows: result is the initial state
                 L.pacw_tag = 0xffffffffu;
-                L.tb5 = dp_target_base(ix, L) * 5;
+                { const int tb = dp_target_base(ix, L); L.srow_lo = s_rows[2 * tb]; L.srow_hi = s_rows[2 * tb + 1]; }
                 if (L.end > L.w + 1) L.end = L.w + 1;                                     // row 0: beg = 0 >= -w
                 if (L.end > L.qlen) L.end = L.qlen;
                 L.h1 = L.h0 - (o_del + e_del); if (L.h1 < 0) L.h1 = 0;
                 L.f = 0; L.m = 0; L.mj = -1; L.first_nz = 0x7fffffff; L.last_nz = -1; L.j = 0;
-                if (L.end > 0) n_cells += (u64)L.end;
+                if (L.end > 0) ncell32 += (unsigned)L.end;
                 need_init = true;
             }
             break;

@@ -23,6 +23,25 @@ __device__ __forceinline__ Occ32Blk occ32_load(const uint4 *occ32, u64 blk)
     return b;
 }
 
+// Both sectors of one extension in ONE issue group: the four 128-bit loads are emitted back to back so that the
+// extension costs one memory round trip (ptxas otherwise sinks the second sector's loads below the first
+// sector's arithmetic, which serialises two round trips).  When bl == bk the second pair hits the sector in flight.
+__device__ __forceinline__ void occ32_load2(const uint4 *occ32, u64 bk, u64 bl, Occ32Blk &K, Occ32Blk &L)
+{
+    const uint4 *pk = occ32 + (bk << 1), *pl = occ32 + (bl << 1);
+#ifdef B200_EMU
+    K.cnt = pk[0]; K.pl = pk[1]; L.cnt = pl[0]; L.pl = pl[1];
+#else
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%16];\n\t"
+                 "ld.global.nc.v4.u32 {%4,%5,%6,%7}, [%16+16];\n\t"
+                 "ld.global.nc.v4.u32 {%8,%9,%10,%11}, [%17];\n\t"
+                 "ld.global.nc.v4.u32 {%12,%13,%14,%15}, [%17+16];"
+                 : "=r"(K.cnt.x), "=r"(K.cnt.y), "=r"(K.cnt.z), "=r"(K.cnt.w), "=r"(K.pl.x), "=r"(K.pl.y), "=r"(K.pl.z), "=r"(K.pl.w),
+                   "=r"(L.cnt.x), "=r"(L.cnt.y), "=r"(L.cnt.z), "=r"(L.cnt.w), "=r"(L.pl.x), "=r"(L.pl.y), "=r"(L.pl.z), "=r"(L.pl.w)
+                 : "l"(pk), "l"(pl));
+#endif
+}
+
 // (# of symbol c, # of symbols > c) among rows [block start, block start + off] of a block, plus checkpoint
 __device__ __forceinline__ void occ32_pair(const Occ32Blk &b, int off, int c, u32 &n_eq, u32 &n_gt)
 {
@@ -42,23 +61,32 @@ __device__ __forceinline__ void occ32_pair(const Occ32Blk &b, int off, int c, u3
 }
 
 // Child c of a bi-interval: ok[c] of bwt_extend (bwt.c:262-275).  PT = u32 when seq_len < 2^32 - 2, else u64.
-// *two_ref = 1 when the two interval ends fall into different 128-row blocks of the REFERENCE layout
-// (what bwt_2occ4 would have fetched; the algorithmic-traffic counter of the roofline).
+// Split in two so that a caller can issue the two sector requests of the NEXT extension at the bottom of its
+// loop and consume them at the top (the requests of all lanes are then in flight together and each extension
+// costs one memory round trip).  *two_ref = 1 when the two interval ends fall into different 128-row blocks of
+// the REFERENCE layout (what bwt_2occ4 would have fetched; the algorithmic-traffic counter of the roofline).
 template <class PT>
-__device__ __forceinline__ void occ32_child(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, int c,
-                                            PT &n0, PT &n1, PT &n2, int &two_ref)
+__device__ __forceinline__ void occ32_issue(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, Occ32Blk &Bk, Occ32Blk &Bl)
+{
+    const PT primary = (PT)ix.primary;
+    const PT a = is_back ? x0 : x1;
+    const PT k = a - 1, l = k + x2;                                   // bwt.c:265
+    const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary); // bwt.c:192-193
+    occ32_load2(ix.occ32, (u64)kp >> 6, (u64)lp >> 6, Bk, Bl);
+}
+
+template <class PT>
+__device__ __forceinline__ void occ32_finish(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, int c,
+                                             const Occ32Blk &Bk, const Occ32Blk &Bl, PT &n0, PT &n1, PT &n2, int &two_ref)
 {
     const PT primary = (PT)ix.primary;
     const PT a = is_back ? x0 : x1, b = is_back ? x1 : x0;
-    const PT k = a - 1, l = k + x2;                                   // bwt.c:265
-    const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary); // bwt.c:192-193
-    const u64 bk = (u64)kp >> 6, bl = (u64)lp >> 6;
-    Occ32Blk B = occ32_load(ix.occ32, bk);
+    const PT k = a - 1, l = k + x2;
+    const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary);
     u32 ek, gk, el, gl;
-    occ32_pair(B, (int)(kp & 63), c, ek, gk);
-    if (bl != bk) B = occ32_load(ix.occ32, bl);
-    occ32_pair(B, (int)(lp & 63), c, el, gl);
-    two_ref = (int)((bk >> 1) != (bl >> 1));
+    occ32_pair(Bk, (int)(kp & 63), c, ek, gk);
+    occ32_pair(Bl, (int)(lp & 63), c, el, gl);
+    two_ref = (int)(((u64)kp >> 7) != ((u64)lp >> 7));
     PT tk = ek, tl = el, sk = gk, sl = gl;
     if (sizeof(PT) == 8) {                                            // superblock bases (rows >= 2^32)
         const int s0 = (int)((u64)kp >> 32), s1 = (int)((u64)lp >> 32);
@@ -71,4 +99,13 @@ __device__ __forceinline__ void occ32_child(const DevIndex &ix, PT x0, PT x1, PT
     const PT nb = b + (PT)(a <= primary && a + x2 - 1 >= primary) + (sl - sk);   // bwt.c:271-274
     n0 = is_back ? na : nb;
     n1 = is_back ? nb : na;
+}
+
+template <class PT>
+__device__ __forceinline__ void occ32_child(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, int c,
+                                            PT &n0, PT &n1, PT &n2, int &two_ref)
+{
+    Occ32Blk Bk, Bl;
+    occ32_issue<PT>(ix, x0, x1, x2, is_back, Bk, Bl);
+    occ32_finish<PT>(ix, x0, x1, x2, is_back, c, Bk, Bl, n0, n1, n2, two_ref);
 }

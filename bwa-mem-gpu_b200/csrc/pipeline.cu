@@ -200,7 +200,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     if (ctx->d_arena.ensure((size_t)arena_cap * sizeof(mem_alnreg_t)) || ctx->d_reg_off.ensure((size_t)n * 8) ||
         ctx->d_reg_n.ensure((size_t)n * 4) || ctx->d_dst_off.ensure(((size_t)n + 1) * 8)) return -1;
     // round-based fast path (ext2.cu) when scores fit 14 bits and one H/E row per lane fits shared memory
-    const int he_cols = ctx->max_len + 2;
+    const int he_cols = ctx->max_len + 2 + 8;                                 // + 8: the DP hot slot prefetches 8 columns
     bool fast_ext = (i64)ctx->max_len * opt->a < 16384 && (size_t)he_cols * 64 * 4 <= 96 * 1024;
     for (int k = 0; k < 25; ++k) if (opt->mat[k] > opt->a) fast_ext = false;     // bound above assumes max(mat) == a
     if (ctx->ext_path == 1) fast_ext = false;

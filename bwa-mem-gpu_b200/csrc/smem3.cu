@@ -147,7 +147,60 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
         k0 = (PT)ix.L2[b0] + 1; kk2 = (PT)(ix.L2[(b0) + 1] - ix.L2[b0]); k1 = (PT)ix.L2[3 - (b0)] + 1;  \
     } while (0)
 
+    Occ32Blk Bk, Bl;                                                        // sectors of the pending extension
+    bool pending = false;
+    int is_back = 0, c = 0;
     for (;;) {
+      if (pending) {
+        // ------------------------------------------------------------ the single gather site: consume the sectors
+        PT n0, n1, n2; int two;
+        occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
+        ++n_ext; n_two += two;
+        // ------------------------------------------------------------ consume
+        bool adv = false;                                                   // forward phases: continue with the child
+        int restart = -1;                                                   // >= 0: start a new forward chain of this kind at x
+        if (st == S3_FWD) {                                                 // bwt.c:308-315
+            adv = true;
+            if (n2 != kk2) {
+                if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; adv = false; }
+                else {
+                    S3_PUSH(i);
+                    if (n2 < min_intv) { S3_START_BWD(); adv = false; }
+                }
+            }
+        } else if (st == S3_P3) {                                           // bwt.c:369-375
+            if (n2 < max_mem_intv && i - x >= min_seed_len) {
+                if (n2 > 0) s3_emit(out, n_out, P.cap_out, n0, n1, n2, x, i + 1);   // bwamem.c:174
+                x = i + 1; restart = S3_P3;
+            } else adv = true;
+        } else {                                                            // S3_BWD, bwt.c:331-341
+            if (n2 < min_intv) {
+                if (ncurr == 0 && i + 1 < last_start) {
+                    last_start = i + 1;
+                    if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
+                }
+            } else if (ncurr == 0 || n2 != last_x2) {
+                S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                    // ncurr <= j: slot already consumed
+                ++ncurr; last_x2 = n2;
+            }
+            if (++j == nprev) {                                             // bwt.c:343-344
+                if (ncurr == 0) {
+                    if (pass == 1) { x = ret; restart = S3_FWD; } else { ++k2; st = S3_TASK; i = -1; }
+                } else { nprev = ncurr; ncurr = 0; j = 0; --i; }
+            }
+            if (restart < 0 && st == S3_BWD) S3_LOAD_ENTRY(j);
+        }
+        if (adv) { k0 = n0; k1 = n1; kk2 = n2; ++i; }
+        if (restart >= 0) {                                                 // inline restart of a forward chain at x
+            u32 b0 = 4;
+            if (x < len) b0 = S3_QGET(x);
+            if (b0 < 4) {
+                S3_SET_INTV((int)b0);
+                i = x + 1; st = restart;
+                if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; }
+            } else { st = S3_TASK; i = -1; }                                // N or end of read: slow path decides
+        }
+      }
         // ------------------------------------------------------------ request: base at position i, or slow path
         u32 b = 4;
         if ((unsigned)i < (unsigned)len) b = S3_QGET(i);
@@ -235,58 +288,10 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
             if ((unsigned)i < (unsigned)len) b = S3_QGET(i);
         }
         if (r < 0) break;                                                   // no reads left for this lane
-
-        // ------------------------------------------------------------ the single gather site
-        const int is_back = st == S3_BWD;
-        const int c = is_back ? (int)b : 3 - (int)b;
-        PT n0, n1, n2; int two;
-        occ32_child<PT>(ix, k0, k1, kk2, is_back, c, n0, n1, n2, two);
-        ++n_ext; n_two += two;
-
-        // ------------------------------------------------------------ consume
-        bool adv = false;                                                   // forward phases: continue with the child
-        int restart = -1;                                                   // >= 0: start a new forward chain of this kind at x
-        if (st == S3_FWD) {                                                 // bwt.c:308-315
-            adv = true;
-            if (n2 != kk2) {
-                if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; adv = false; }
-                else {
-                    S3_PUSH(i);
-                    if (n2 < min_intv) { S3_START_BWD(); adv = false; }
-                }
-            }
-        } else if (st == S3_P3) {                                           // bwt.c:369-375
-            if (n2 < max_mem_intv && i - x >= min_seed_len) {
-                if (n2 > 0) s3_emit(out, n_out, P.cap_out, n0, n1, n2, x, i + 1);   // bwamem.c:174
-                x = i + 1; restart = S3_P3;
-            } else adv = true;
-        } else {                                                            // S3_BWD, bwt.c:331-341
-            if (n2 < min_intv) {
-                if (ncurr == 0 && i + 1 < last_start) {
-                    last_start = i + 1;
-                    if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
-                }
-            } else if (ncurr == 0 || n2 != last_x2) {
-                S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                    // ncurr <= j: slot already consumed
-                ++ncurr; last_x2 = n2;
-            }
-            if (++j == nprev) {                                             // bwt.c:343-344
-                if (ncurr == 0) {
-                    if (pass == 1) { x = ret; restart = S3_FWD; } else { ++k2; st = S3_TASK; i = -1; }
-                } else { nprev = ncurr; ncurr = 0; j = 0; --i; }
-            }
-            if (restart < 0 && st == S3_BWD) S3_LOAD_ENTRY(j);
-        }
-        if (adv) { k0 = n0; k1 = n1; kk2 = n2; ++i; }
-        if (restart >= 0) {                                                 // inline restart of a forward chain at x
-            u32 b0 = 4;
-            if (x < len) b0 = S3_QGET(x);
-            if (b0 < 4) {
-                S3_SET_INTV((int)b0);
-                i = x + 1; st = restart;
-                if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; }
-            } else { st = S3_TASK; i = -1; }                                // N or end of read: slow path decides
-        }
+        is_back = st == S3_BWD;
+        c = is_back ? (int)b : 3 - (int)b;
+        occ32_issue<PT>(ix, k0, k1, kk2, is_back, Bk, Bl);                  // requests in flight across the back-edge
+        pending = true;
     }
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
 }

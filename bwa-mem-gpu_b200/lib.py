@@ -19,7 +19,7 @@ PRODUCT_SO = os.path.join(HERE, "libbwamem_b200.so")
 IDX_FULL_SA = 0x1
 
 _SYMBOLS = [
-    "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
+    "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
@@ -122,6 +122,13 @@ class Context:
 
     def tune(self, key: str, value: int):
         self._chk(self.lib.b200_ctx_tune(self.h, key.encode(), C.c_int64(value)), "tune")
+
+    def microbench(self, kind: int, table_bytes: int = 0, blocks_per_sm: int = 8, iters: int = 2000, mlp: int = 1):
+        """(milliseconds, units): kind 0 random 32-B sector gathers, kind 1 DPX instructions."""
+        out = (C.c_double * 2)()
+        self._chk(self.lib.b200_microbench(self.h, C.c_int(kind), C.c_int64(table_bytes), C.c_int(blocks_per_sm),
+                                           C.c_int(iters), C.c_int(mlp), out), "microbench")
+        return out[0], out[1]
 
     def _chk(self, rc, what):
         if rc < 0:

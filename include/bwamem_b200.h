@@ -219,6 +219,11 @@ int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs
  * [9]=kernel launches */
 int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out /* 16 */);
 
+/* Roofline denominators measured on this device: kind 0 = dependent random 32-byte sector
+ * gathers over a table of table_bytes (`mlp` independent chains per lane), kind 1 = DPX instruction issue rate.
+ * out[0] = milliseconds, out[1] = sectors gathered / DPX instructions executed. */
+int b200_microbench(b200_ctx_t *ctx, int kind, int64_t table_bytes, int blocks_per_sm, int iters, int mlp, double *out);
+
 /* =====================================================================================
  * Drop-in scalar entry points: the reference's own names and signatures.  Each call runs the
  * device code on a batch of one (parity tests call these one problem at a time).  The device

@@ -237,6 +237,19 @@ inline unsigned __brev(unsigned x)
     return __builtin_bswap32(x);
 }
 template <class T> inline T __ldg(const T *p) { return *p; }
+// PRMT: byte select from {y:x}; selector nibble bit 3 = replicate the sign bit of the selected byte
+inline unsigned __byte_perm(unsigned x, unsigned y, unsigned s)
+{
+    const uint64_t v = (uint64_t)y << 32 | x;
+    unsigned r = 0;
+    for (int k = 0; k < 4; ++k) {
+        const unsigned sel = (s >> (4 * k)) & 0xf;
+        unsigned b = (unsigned)(v >> (8 * (sel & 7))) & 0xff;
+        if (sel & 8) b = (b & 0x80) ? 0xff : 0x00;
+        r |= b << (8 * k);
+    }
+    return r;
+}
 // DPX (emulated exactly; on sm_100a these are single instructions)
 inline int __vimax3_s32(int a, int b, int c) { return std::max(a, std::max(b, c)); }
 inline int __vimin3_s32(int a, int b, int c) { return std::min(a, std::min(b, c)); }
