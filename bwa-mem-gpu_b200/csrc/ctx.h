@@ -39,6 +39,9 @@ struct b200_ctx {
     int cap_intv = 0;                          // 0 = auto from read length
     int ext_path = 0;                          // 0 = auto, 1 = force the general warp-per-read kernel, 2 = force the round-based fast path
     int smem_path = 0;                         // 0 = auto (smem3 for short reads), 2 = smem2 kernel, 1 = general kernel only
+    int l2_persist = 0;                        // 1: pin the seeding index in persisting L2 (set before the index upload)
+    size_t l2_setaside = 0, l2_window = 0;
+    int smem_bps = 0;                          // > 0: cap on resident blocks per SM of the seeding kernel (experiments)
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
 
     // per-chunk intermediates

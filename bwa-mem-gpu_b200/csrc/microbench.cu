@@ -10,11 +10,11 @@ __global__ void __launch_bounds__(128) gather_bench_kernel(const uint4 *tab, u64
     u64 x0 = gtid * 0x9e3779b97f4a7c15ull + 12345, x1 = ~x0 * 0xbf58476d1ce4e5b9ull, x2 = x0 ^ 0x94d049bb133111ebull, x3 = x1 + 77;
     u32 acc = 0;
     for (int it = 0; it < iters; ++it) {
-        const uint4 *p0 = tab + ((x0 % n_sectors) << 1);
+        const uint4 *p0 = tab + (__umul64hi(x0, n_sectors) << 1);
         uint4 a0 = __ldg(p0), b0 = __ldg(p0 + 1), a1 = a0, b1 = b0, a2 = a0, b2 = b0, a3 = a0, b3 = b0;
-        if (mlp > 1) { const uint4 *p = tab + ((x1 % n_sectors) << 1); a1 = __ldg(p); b1 = __ldg(p + 1); }
-        if (mlp > 2) { const uint4 *p = tab + ((x2 % n_sectors) << 1); a2 = __ldg(p); b2 = __ldg(p + 1); }
-        if (mlp > 3) { const uint4 *p = tab + ((x3 % n_sectors) << 1); a3 = __ldg(p); b3 = __ldg(p + 1); }
+        if (mlp > 1) { const uint4 *p = tab + (__umul64hi(x1, n_sectors) << 1); a1 = __ldg(p); b1 = __ldg(p + 1); }
+        if (mlp > 2) { const uint4 *p = tab + (__umul64hi(x2, n_sectors) << 1); a2 = __ldg(p); b2 = __ldg(p + 1); }
+        if (mlp > 3) { const uint4 *p = tab + (__umul64hi(x3, n_sectors) << 1); a3 = __ldg(p); b3 = __ldg(p + 1); }
         x0 = x0 * 6364136223846793005ull + (a0.x ^ b0.w) + 1442695040888963407ull;
         x1 = x1 * 6364136223846793005ull + (a1.y ^ b1.z) + 1;
         x2 = x2 * 6364136223846793005ull + (a2.z ^ b2.y) + 3;

@@ -32,13 +32,13 @@ __device__ __forceinline__ void occ32_load2(const uint4 *occ32, u64 bk, u64 bl, 
 #ifdef B200_EMU
     K.cnt = pk[0]; K.pl = pk[1]; L.cnt = pl[0]; L.pl = pl[1];
 #else
-    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%16];\n\t"
-                 "ld.global.nc.v4.u32 {%4,%5,%6,%7}, [%16+16];\n\t"
-                 "ld.global.nc.v4.u32 {%8,%9,%10,%11}, [%17];\n\t"
-                 "ld.global.nc.v4.u32 {%12,%13,%14,%15}, [%17+16];"
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u64 p, %16, %17;\n\t"
+                 "ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%16];\n\t"
+                 "@p ld.global.nc.v8.u32 {%8,%9,%10,%11,%12,%13,%14,%15}, [%17];\n\t}"
                  : "=r"(K.cnt.x), "=r"(K.cnt.y), "=r"(K.cnt.z), "=r"(K.cnt.w), "=r"(K.pl.x), "=r"(K.pl.y), "=r"(K.pl.z), "=r"(K.pl.w),
                    "=r"(L.cnt.x), "=r"(L.cnt.y), "=r"(L.cnt.z), "=r"(L.cnt.w), "=r"(L.pl.x), "=r"(L.pl.y), "=r"(L.pl.z), "=r"(L.pl.w)
                  : "l"(pk), "l"(pl));
+    if (bk == bl) L = K;
 #endif
 }
 

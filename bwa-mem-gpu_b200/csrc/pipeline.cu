@@ -111,7 +111,8 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     SP.retry_n = ctl_u32(ctx, CTL_RETRY); SP.retry_ids = ctx->d_retry.as<i32>();
     if (use3) {
         const size_t smem = smem_fast3_bytes(wide, lcap3, pk_stride);
-        const int per_sm = std::max(1, std::min(8, (int)((224 * 1024) / (smem + 1024))));
+        int per_sm = std::max(1, std::min(8, (int)((224 * 1024) / (smem + 1024))));
+        if (ctx->smem_bps > 0) per_sm = std::min(per_sm, ctx->smem_bps);
         const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * per_sm));
         const int spill_cap = std::max(1, ctx->max_len + 1 - lcap3);
         if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;

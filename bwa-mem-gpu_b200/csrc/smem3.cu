@@ -53,9 +53,9 @@ template <> struct Ent<u64> {
 __device__ __forceinline__ void s3_emit(Intv *out, int &n_out, int cap_out, u64 x0, u64 x1, u64 x2, int start, int end)
 {
     if (n_out < cap_out) {
-        uint4 *q = (uint4 *)&out[n_out];
-        q[0] = make_uint4((u32)x0, (u32)(x0 >> 32), (u32)x1, (u32)(x1 >> 32));
-        q[1] = make_uint4((u32)x2, (u32)(x2 >> 32), (u32)end, (u32)start);
+        uint4 *q = (uint4 *)&out[n_out];                   // streaming stores: keep the index resident in L2
+        __stcs(q, make_uint4((u32)x0, (u32)(x0 >> 32), (u32)x1, (u32)(x1 >> 32)));
+        __stcs(q + 1, make_uint4((u32)x2, (u32)(x2 >> 32), (u32)end, (u32)start));
     }
     ++n_out;
 }
@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                     const uint4 *src = (const uint4 *)(P.pk + (size_t)r * P.pk_stride);
                     const int nq = (len + 31) >> 5;
                     for (int w = 0; w < nq; ++w) {
-                        const uint4 v = __ldg(src + w);
+                        const uint4 v = __ldcs(src + w);
                         Q[(4 * w) * S3_THREADS] = v.x; Q[(4 * w + 1) * S3_THREADS] = v.y;
                         Q[(4 * w + 2) * S3_THREADS] = v.z; Q[(4 * w + 3) * S3_THREADS] = v.w;
                     }

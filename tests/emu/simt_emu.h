@@ -224,6 +224,7 @@ inline unsigned __reduce_or_sync(unsigned mask, unsigned v)
 }
 
 // ------------------------------------------------------------------ integer intrinsics
+inline unsigned long long __umul64hi(unsigned long long a, unsigned long long b) { return (unsigned long long)(((unsigned __int128)a * b) >> 64); }
 inline int __popc(unsigned x) { return __builtin_popcount(x); }
 inline int __popcll(unsigned long long x) { return __builtin_popcountll(x); }
 inline int __clz(int x) { return x ? __builtin_clz((unsigned)x) : 32; }
@@ -237,6 +238,8 @@ inline unsigned __brev(unsigned x)
     return __builtin_bswap32(x);
 }
 template <class T> inline T __ldg(const T *p) { return *p; }
+template <class T> inline T __ldcs(const T *p) { return *p; }
+template <class T> inline void __stcs(T *p, T v) { *p = v; }
 // PRMT: byte select from {y:x}; selector nibble bit 3 = replicate the sign bit of the selected byte
 inline unsigned __byte_perm(unsigned x, unsigned y, unsigned s)
 {
