@@ -169,8 +169,11 @@ static std::vector<b200_ctx *> g_reg;
 b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac)
 {
     std::lock_guard<std::mutex> lk(g_reg_mu);
-    for (b200_ctx *c : g_reg) if (c->bwt_identity == bwt) return c;
-    b200_ctx *c = b200_ctx_create(0);
+    b200_ctx *c = nullptr;
+    for (b200_ctx *r : g_reg) if (r->bwt_identity == bwt) c = r;
+    if (c && (!pac || !c->stub_pac)) return c;
+    const bool fresh = c == nullptr;            // else: created by an FM-index primitive, now needs the real reference
+    if (fresh) c = b200_ctx_create(0);
     if (!c) { fprintf(stderr, "[b200] %s\n", b200_last_error()); exit(1); }
     // primitives that only need the FM-index may arrive without bns/pac: upload a 1-contig stub
     bntseq_t stub; bntann1_t ann; uint8_t zero = 0;
@@ -187,7 +190,8 @@ b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t 
     }
     if (rc) { fprintf(stderr, "[b200] %s\n", b200_last_error()); exit(1); }
     c->bwt_identity = bwt;
-    g_reg.push_back(c);
+    c->stub_pac = pac == nullptr;
+    if (fresh) g_reg.push_back(c);
     return c;
 }
 

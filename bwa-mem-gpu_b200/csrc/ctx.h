@@ -28,6 +28,7 @@ struct b200_ctx {
     DevIndex ix;
     DevBuf d_occ32, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
     const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
+    bool stub_pac = false;             // index uploaded by a bwt-only primitive (no bns / pac yet)
 
     // resident input batch
     DevBuf d_seq, d_off;

@@ -72,6 +72,27 @@ extern "C" int ksw_extend2(int qlen, const uint8_t *query, int tlen, const uint8
     return out[0];
 }
 
+// The query profile of the reference (kswq_t, ksw.c:50-56) is private to ksw.c; callers only pass the pointer back and
+// free() it.  Ours records the score width chosen at the first call, which is all that later calls depend on (ksw.c:350-353).
+struct _kswq_t { int qlen, size; };
+
+extern "C" kswr_t ksw_align2(int qlen, uint8_t *query, int tlen, uint8_t *target, int m, const int8_t *mat, int o_del,
+                             int e_del, int o_ins, int e_ins, int xtra, kswq_t **qry)
+{
+    if (m != 5) { fprintf(stderr, "[b200::ksw_align2] only the 5-letter nt4 alphabet is supported (m=%d)\n", m); exit(1); }
+    if (!g_ksw_ctx) { g_ksw_ctx = b200_ctx_create(0); if (!g_ksw_ctx) die_on(-1, "ksw_align2"); }
+    int size = (xtra & 0x10000) ? 1 : 2;                        // KSW_XBYTE, ksw.c:350
+    if (qry && *qry) size = (*qry)->size;
+    else if (qry) { *qry = (kswq_t *)malloc(sizeof(kswq_t)); (*qry)->qlen = qlen; (*qry)->size = size; }
+    int32_t ql = qlen, tl = tlen, xx = (xtra & ~0x10000) | (size == 1 ? 0x10000 : 0), out[7];
+    int64_t zero = 0;
+    die_on(b200_ksw_align2_batch(g_ksw_ctx, 1, &ql, &zero, query, &tl, &zero, target, mat, o_del, e_del, o_ins, e_ins, &xx, out),
+           "ksw_align2");
+    kswr_t r;
+    r.score = out[0]; r.te = out[1]; r.qe = out[2]; r.score2 = out[3]; r.te2 = out[4]; r.tb = out[5]; r.qb = out[6];
+    return r;
+}
+
 extern "C" mem_alnreg_v mem_align1_core(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                                         int l_seq, char *seq, void *buf)
 {

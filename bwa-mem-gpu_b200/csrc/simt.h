@@ -17,6 +17,7 @@
 #define B200_FULL_MASK 0xffffffffu
 typedef uint64_t u64;
 typedef int64_t i64;
+typedef uint16_t u16;
 typedef uint32_t u32;
 typedef int32_t i32;
 typedef uint8_t u8;

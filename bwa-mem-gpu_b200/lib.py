@@ -21,7 +21,7 @@ IDX_FULL_SA = 0x1
 _SYMBOLS = [
     "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
-    "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_align_batch",
+    "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host",
@@ -211,6 +211,16 @@ class Context:
             self.h, C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8), _p(tlen, C.c_int32),
             _p(toff, C.c_int64), _p(t, C.c_uint8), opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
             _p(w, C.c_int32), C.c_int(end_bonus), C.c_int(zdrop), _p(h0, C.c_int32), _p(out, C.c_int32)), "ksw_extend2")
+        return out
+
+    def ksw_align2(self, qlen, qoff, q, tlen, toff, t, opt: MemOpt, xtra):
+        n = len(qlen)
+        out = np.zeros((n, 7), dtype=np.int32)
+        xtra = np.ascontiguousarray(xtra, dtype=np.int32)
+        self._chk(self.lib.b200_ksw_align2_batch(
+            self.h, C.c_int64(n), _p(qlen, C.c_int32), _p(qoff, C.c_int64), _p(q, C.c_uint8), _p(tlen, C.c_int32),
+            _p(toff, C.c_int64), _p(t, C.c_uint8), opt.mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+            _p(xtra, C.c_int32), _p(out, C.c_int32)), "ksw_align2")
         return out
 
     # ---------------- stage seams

@@ -121,6 +121,10 @@ typedef struct {
 } bseq1_t;
 
 #define MEM_F_PE        0x2
+/* ksw.h:11-19 */
+struct _kswq_t;
+typedef struct _kswq_t kswq_t;
+typedef struct { int score; int te, qe; int score2, te2; int tb, qb; } kswr_t;
 #endif /* BWAMEM_B200_NO_TYPES */
 
 /* =====================================================================================
@@ -199,6 +203,12 @@ int b200_ksw_extend2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, cons
                            int o_del, int e_del, int o_ins, int e_ins, const int32_t *w, int end_bonus,
                            int zdrop, const int32_t *h0, int32_t *out);
 
+/* ksw_align2 (ksw.c:343) over an array of problems (striped u8 / i16 local SW incl. the KSW_XSTART reverse pass);
+ * xtra per problem as in ksw.h:33-36; out: 7 x int32 per problem = kswr_t {score, te, qe, score2, te2, tb, qb} */
+int b200_ksw_align2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
+                          const int32_t *tlen, const int64_t *toff, const uint8_t *t, const int8_t *mat,
+                          int o_del, int e_del, int o_ins, int e_ins, const int32_t *xtra, int32_t *out);
+
 /* mem_align1_core (bwamem.c:1061) for a batch = worker1 of mem_process_seqs (bwamem.c:1183):
  * seeding -> chaining -> filtering -> extension -> mem_sort_dedup_patch.  Reads may be ASCII or nt4.
  * out_regs holds cap records; read r's regions are the next out_n[r] records in read order.
@@ -250,6 +260,8 @@ int      bwt_smem1a(const bwt_t *bwt, int len, const uint8_t *q, int x, int min_
 int      ksw_extend2(int qlen, const uint8_t *query, int tlen, const uint8_t *target, int m, const int8_t *mat,
                      int o_del, int e_del, int o_ins, int e_ins, int w, int end_bonus, int zdrop, int h0,
                      int *qle, int *tle, int *gtle, int *gscore, int *max_off);                     /* ksw.h:108 */
+kswr_t   ksw_align2(int qlen, uint8_t *query, int tlen, uint8_t *target, int m, const int8_t *mat, int o_del, int e_del,
+                    int o_ins, int e_ins, int xtra, kswq_t **qry);                                   /* ksw.h:64 */
 mem_alnreg_v mem_align1_core(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                              int l_seq, char *seq, void *buf);                                      /* bwamem.c:1061 */
 #endif

@@ -112,3 +112,39 @@ def ragged_reads(name: str, seed: int = 17):
 
 def golden_path(name):
     return os.path.join(GOLDEN, name)
+
+
+KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
+
+
+def sw_problems(rng, n, maxq=160, maxt=420, sat=False):
+    """Local-alignment problems in the shape mem_matesw / mem_seed_sw produce (bwamem_pair.c:150-162, bwamem.c:640-672):
+    a target window holding zero, one or two diverged copies of (a piece of) the query."""
+    qs, ts = [], []
+    for _ in range(n):
+        lq = int(rng.integers(1, maxq))
+        q = rng.integers(0, 4, size=lq, dtype=np.uint8)
+        if rng.random() < 0.1 and lq > 3:
+            q[int(rng.integers(0, lq))] = 4
+        parts = [rng.integers(0, 4, size=int(rng.integers(0, maxt // 3)), dtype=np.uint8)]
+        for _c in range(int(rng.integers(0, 3))):
+            a, b = sorted(rng.integers(0, lq + 1, size=2))
+            piece = []
+            for x in q[a:b]:
+                r = rng.random()
+                if r < 0.05: piece.append(int(rng.integers(0, 4)))
+                elif r < 0.065: continue
+                elif r < 0.08: piece.extend([int(x) & 3, int(rng.integers(0, 4))])
+                else: piece.append(int(x) & 3 if x < 4 else 4)
+            parts.append(np.array(piece, dtype=np.uint8))
+            parts.append(rng.integers(0, 4, size=int(rng.integers(0, maxt // 4)), dtype=np.uint8))
+        t = np.concatenate(parts)[:maxt]
+        if sat and rng.random() < 0.3:                      # identical long pair: byte scores saturate at 255
+            q = rng.integers(0, 4, size=int(rng.integers(250, 300)), dtype=np.uint8); t = q.copy()
+        qs.append(q); ts.append(t)
+    ql = np.array([len(x) for x in qs], np.int32); tl = np.array([len(x) for x in ts], np.int32)
+    qoff = np.concatenate([[0], np.cumsum(ql)[:-1]]).astype(np.int64)
+    toff = np.concatenate([[0], np.cumsum(tl)[:-1]]).astype(np.int64)
+    q = np.ascontiguousarray(np.concatenate(qs + [np.zeros(1, np.uint8)]).astype(np.uint8))
+    t = np.ascontiguousarray(np.concatenate(ts + [np.zeros(1, np.uint8)]).astype(np.uint8))
+    return ql, qoff, q, tl, toff, t

@@ -73,6 +73,13 @@ def test_golden_ksw_extend2(backend):
 
 
 @pytest.mark.parametrize("backend", BACKENDS)
+def test_golden_ksw_align2(backend):
+    g, ctx = _load("ksw_align2.npz"), cm.context(backend, G)
+    args = [g[k] for k in ("ql", "qoff", "q", "tl", "toff", "t")]
+    assert np.array_equal(ctx.ksw_align2(*args, abi.default_opt(), g["xtra"]), g["out"])
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
 def test_golden_align(backend):
     ctx = cm.context(backend, G)
     opt = abi.default_opt()

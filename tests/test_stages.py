@@ -161,6 +161,37 @@ def test_ksw_extend2_random(backend):
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
+def test_ksw_align2_random(backend):
+    """ksw_align2 (ksw.c:343): all 7 kswr_t fields; byte and 16-bit score paths, 2nd-best threshold (KSW_XSUBO),
+    start coordinates (KSW_XSTART reverse pass with KSW_XSTOP), byte saturation at 255, empty targets."""
+    ctx = cm.context(backend, "tiny")
+    rl = cm.reflib()
+    rng = np.random.default_rng(11)
+    n = _sizes(backend, 300, 20000)
+    for (a, b, o, e) in [(1, 4, 6, 1), (2, 3, 4, 2), (1, 1, 1, 1)]:
+        opt = abi.default_opt()
+        opt.a, opt.b, opt.o_del, opt.o_ins, opt.e_del, opt.e_ins = a, b, o, o + 1, e, e
+        abi.fill_scmat(opt)
+        ql, qoff, q, tl, toff, t = cm.sw_problems(rng, n)
+        flags = rng.choice([0, cm.KSW_XSUBO, cm.KSW_XSTART, cm.KSW_XSUBO | cm.KSW_XSTART], size=n)
+        byte = np.where(ql * a < 250, rng.choice([0, cm.KSW_XBYTE], size=n), 0)      # bwamem_pair.c:153
+        xtra = (flags | byte | rng.integers(1, 40, size=n)).astype(np.int32)
+        exp = rl.ksw_align2(ql, qoff, q, tl, toff, t, opt, xtra)
+        got = ctx.ksw_align2(ql, qoff, q, tl, toff, t, opt, xtra)
+        bad = np.nonzero((exp != got).any(axis=1))[0]
+        assert len(bad) == 0, (bad[:5], xtra[bad[:5]], exp[bad[:5]], got[bad[:5]])
+    # byte scores running into saturation (no reverse pass: the reference reads H0[-1] there)
+    opt = abi.default_opt()
+    ql, qoff, q, tl, toff, t = cm.sw_problems(rng, max(n // 4, 50), maxq=300, sat=True)
+    xtra = np.full(len(ql), cm.KSW_XBYTE | cm.KSW_XSUBO | 19, np.int32)
+    exp = rl.ksw_align2(ql, qoff, q, tl, toff, t, opt, xtra)
+    got = ctx.ksw_align2(ql, qoff, q, tl, toff, t, opt, xtra)
+    assert (exp[:, 0] == 255).any()
+    assert np.array_equal(exp, got)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
 @pytest.mark.parametrize("gname", ["small", "rep"])
 def test_align_regs(backend, gname):
     """mem_align1_core (bwamem.c:1061) for a batch: all 88 bytes of every mem_alnreg_t."""
