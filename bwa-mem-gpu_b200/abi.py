@@ -67,6 +67,10 @@ ALNREG_DTYPE = np.dtype([
 ], align=True)
 assert ALNREG_DTYPE.itemsize == 88
 
+# mem_pestat_t (bwamem.h:59-63): int low, high, failed; double avg, std
+PESTAT_DTYPE = np.dtype([("low", "<i4"), ("high", "<i4"), ("failed", "<i4"), ("avg", "<f8"), ("std", "<f8")], align=True)
+assert PESTAT_DTYPE.itemsize == 32
+
 INTV_DTYPE = np.dtype([("x0", "<u8"), ("x1", "<u8"), ("x2", "<u8"), ("info", "<u8")])
 
 MEM_F_PE = 0x2

@@ -100,6 +100,7 @@ __device__ inline int patch_reg(const DevIndex &ix, const mem_opt_t &opt, const 
 {
     int w, score, q_s, r_s, ok;
     double r;
+    if (query == nullptr) return 0;                                       // bwamem.c:417 (callers without a query: mem_matesw)
     if (a->rb < ix.l_pac && b->rb >= ix.l_pac) return 0;
     if (a->qb >= b->qb || a->qe >= b->qe || a->re >= b->re) return 0;
     w = (int)((a->re - b->rb) - (a->qe - b->qb));

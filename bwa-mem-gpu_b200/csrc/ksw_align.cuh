@@ -149,21 +149,29 @@ __device__ inline KswAlnRes kswa_pass(int size, int qlen, QF qf, int tlen, TF tf
     return r;
 }
 
-// ksw_align2 (ksw.c:343-365).  q / t are plain byte arrays (nt4 codes); the reverse pass of KSW_XSTART reads the
-// reversed prefixes through index arithmetic instead of reversing the buffers in place (ksw.c:358,361).
+// ksw_align2 (ksw.c:343-365).  Query and target come through accessors (plain byte arrays, the reverse complement
+// of a read, bases decoded from the packed reference ...); the reverse pass of KSW_XSTART reads the reversed
+// prefixes through index arithmetic instead of reversing buffers in place (ksw.c:358,361).
 struct KswaFwd { const u8 *p; __device__ __forceinline__ int operator()(int i) const { return p[i]; } };
-struct KswaRevQ { const u8 *p; int last; __device__ __forceinline__ int operator()(int i) const { return p[last - i]; } };
-struct KswaRevT { const u8 *p; int te; __device__ __forceinline__ int operator()(int i) const { return i <= te ? p[te - i] : p[i]; } };
+template <class Q> struct KswaRevQ { Q q; int last; __device__ __forceinline__ int operator()(int i) const { return q(last - i); } };
+template <class T> struct KswaRevT { T t; int te; __device__ __forceinline__ int operator()(int i) const { return i <= te ? t(te - i) : t(i); } };
+
+template <class Q, class T>
+__device__ inline KswAlnRes kswa_align2_f(int qlen, Q query, int tlen, T target, const int8_t *mat, int o_del, int e_del,
+                                          int o_ins, int e_ins, int xtra, const KswaScratch &S, unsigned gmask, int glane, int *ovf)
+{
+    const int size = (xtra & KSWA_XBYTE) ? 1 : 2;
+    KswAlnRes r = kswa_pass(size, qlen, query, tlen, target, mat, o_del, e_del, o_ins, e_ins, xtra, S, gmask, glane, ovf);
+    if ((xtra & KSWA_XSTART) == 0 || ((xtra & KSWA_XSUBO) && r.score < (xtra & 0xffff))) return r;
+    const KswAlnRes rr = kswa_pass(size, r.qe + 1, KswaRevQ<Q>{query, r.qe}, tlen, KswaRevT<T>{target, r.te}, mat, o_del, e_del,
+                                   o_ins, e_ins, KSWA_XSTOP | r.score, S, gmask, glane, ovf);
+    if (r.score == rr.score) { r.tb = r.te - rr.te; r.qb = r.qe - rr.qe; }
+    return r;
+}
 
 __device__ inline KswAlnRes kswa_align2(int qlen, const u8 *query, int tlen, const u8 *target, const int8_t *mat, int o_del,
                                         int e_del, int o_ins, int e_ins, int xtra, const KswaScratch &S, unsigned gmask,
                                         int glane, int *ovf)
 {
-    const int size = (xtra & KSWA_XBYTE) ? 1 : 2;
-    KswAlnRes r = kswa_pass(size, qlen, KswaFwd{query}, tlen, KswaFwd{target}, mat, o_del, e_del, o_ins, e_ins, xtra, S, gmask, glane, ovf);
-    if ((xtra & KSWA_XSTART) == 0 || ((xtra & KSWA_XSUBO) && r.score < (xtra & 0xffff))) return r;
-    const KswAlnRes rr = kswa_pass(size, r.qe + 1, KswaRevQ{query, r.qe}, tlen, KswaRevT{target, r.te}, mat, o_del, e_del,
-                                   o_ins, e_ins, KSWA_XSTOP | r.score, S, gmask, glane, ovf);
-    if (r.score == rr.score) { r.tb = r.te - rr.te; r.qb = r.qe - rr.qe; }
-    return r;
+    return kswa_align2_f(qlen, KswaFwd{query}, tlen, KswaFwd{target}, mat, o_del, e_del, o_ins, e_ins, xtra, S, gmask, glane, ovf);
 }

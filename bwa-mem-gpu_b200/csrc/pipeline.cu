@@ -338,6 +338,22 @@ extern "C" int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_
     return ctx->total_regs;
 }
 
+// Replace the resident region lists (e.g. with lists produced elsewhere) for the stages that run after worker1.
+extern "C" int b200_batch_set_regs(b200_ctx_t *ctx, const mem_alnreg_t *regs, const int32_t *cnt)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    i64 tot = 0;
+    for (int i = 0; i < ctx->n_reads; ++i) tot += cnt[i];
+    if (ctx->d_final.ensure((size_t)(tot + 1) * sizeof(mem_alnreg_t)) || ctx->d_final_n.ensure((size_t)ctx->n_reads * 4 + 4)) return -1;
+    if (tot) B200_CHECK(cudaMemcpyAsync(ctx->d_final.p, regs, (size_t)tot * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, ctx->st));
+    if (ctx->n_reads) B200_CHECK(cudaMemcpyAsync(ctx->d_final_n.p, cnt, (size_t)ctx->n_reads * 4, cudaMemcpyHostToDevice, ctx->st));
+    if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, ctx->st)) return -1;      // reads as nt4 (idempotent)
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    ctx->total_regs = tot;
+    return 0;
+}
+
 extern "C" int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out)
 {
     if (!ctx) return -1;

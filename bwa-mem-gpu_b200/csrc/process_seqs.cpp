@@ -1,6 +1,7 @@
 // Drop-in mem_process_seqs (bwamem.h:69, bwamem.c:1215-1244): worker1 (mem_align1_core for every read,
-// bwamem.c:1183-1195) runs on the GPU through b200_align_batch; everything after it stays the REFERENCE's own
-// host code -- mem_pestat (bwamem_pair.c:72), worker2 = mem_mark_primary_se / mem_reg2sam / mem_sam_pe
+// bwamem.c:1183-1195) runs on the GPU through b200_align_batch, and so does the mate-rescue block of mem_sam_pe
+// (bwamem_pair.c:291-302, b200_batch_rescue); the rest stays the REFERENCE's own host code -- mem_pestat
+// (bwamem_pair.c:72), worker2 = mem_mark_primary_se / mem_reg2sam / mem_sam_pe with MEM_F_NO_RESCUE
 // (bwamem.c:1197-1213) -- which this library does not contain: those symbols are resolved from the host
 // program the library is linked into (weak references, or the global symbol scope when loaded dynamically).
 // Nothing here computes alignments on the CPU; if the host functions are missing the call fails loudly.
@@ -14,6 +15,7 @@
 #include "../../include/bwamem_b200.h"
 
 #define MEM_F_PRIMARY5_ 0x800        /* bwamem.h:47 */
+#define MEM_F_NO_RESCUE_ 0x20        /* bwa.h:78 */
 
 extern "C" {
 int  mem_mark_primary_se(const mem_opt_t *opt, int n, mem_alnreg_t *a, int64_t id) __attribute__((weak));
@@ -91,20 +93,42 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         exit(1);
     }
     mem_alnreg_v *rv = (mem_alnreg_v *)malloc((size_t)(n > 0 ? n : 1) * sizeof(mem_alnreg_v));
-    for (int64_t i = 0, k = 0; i < n; ++i) {
-        rv[i].n = rv[i].m = cnt[i];
-        rv[i].a = (mem_alnreg_t *)malloc((size_t)(cnt[i] > 0 ? cnt[i] : 1) * sizeof(mem_alnreg_t));
-        memcpy(rv[i].a, regs.data() + k, (size_t)cnt[i] * sizeof(mem_alnreg_t));
-        k += cnt[i];
+    auto fill_rv = [&](bool first) {
+        for (int64_t i = 0, k = 0; i < n; ++i) {
+            if (!first) free(rv[i].a);
+            rv[i].n = rv[i].m = cnt[i];
+            rv[i].a = (mem_alnreg_t *)malloc((size_t)(cnt[i] > 0 ? cnt[i] : 1) * sizeof(mem_alnreg_t));
+            memcpy(rv[i].a, regs.data() + k, (size_t)cnt[i] * sizeof(mem_alnreg_t));
+            k += cnt[i];
+        }
+    };
+    fill_rv(true);
+    for (int i = 0; i < n; ++i)
         for (int j = 0; j < seqs[i].l_seq; ++j) seqs[i].seq[j] = (char)nt4_of((uint8_t)seqs[i].seq[j]);   // bwamem.c:1067-1068
-    }
 
-    // ---- batch-level insert-size statistics and worker2: the reference's own host code
+    // ---- batch-level insert-size statistics (the reference's own host code), then mate rescue on the device
     mem_pestat_t pes[4];
+    mem_opt_t opt2 = *opt;
     if (pe) {
         if (pes0) memcpy(pes, pes0, 4 * sizeof(mem_pestat_t));        // bwamem.c:1237
         else f_pestat(opt, bns->l_pac, n, rv, pes);                   // bwamem.c:1238
+        if (!(opt->flag & MEM_F_NO_RESCUE_)) {                        // bwamem_pair.c:291-302 for every pair
+            if (b200_batch_rescue(g_ps_ctx, opt, pes, nullptr, nullptr)) {
+                fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
+                exit(1);
+            }
+            for (;;) {
+                int64_t got = b200_batch_download(g_ps_ctx, (int64_t)regs.size(), regs.data(), cnt.data());
+                if (got >= 0) break;
+                if (-got > (int64_t)regs.size()) { regs.resize((size_t)-got); continue; }
+                fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
+                exit(1);
+            }
+            fill_rv(false);
+            opt2.flag |= MEM_F_NO_RESCUE_;                            // worker2 must not repeat it
+        }
     }
+    opt = &opt2;
     const int n_units = pe ? n >> 1 : n;
     int n_threads = opt->n_threads > 0 ? opt->n_threads : 1;
     if (n_threads > n_units) n_threads = n_units > 0 ? n_units : 1;

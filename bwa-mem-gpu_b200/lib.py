@@ -22,7 +22,7 @@ _SYMBOLS = [
     "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
-    "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters",
+    "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host",
     "b200_process_seqs_set_ctx", "b200_mem_process_seqs", "mem_process_seqs",
@@ -279,6 +279,17 @@ class Context:
         if tot < 0:
             return None, int(-tot)
         return out[:tot], cnt[:n_reads]
+
+    def batch_set_regs(self, regs, cnt):
+        regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        self._chk(self.lib.b200_batch_set_regs(self.h, C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32)), "batch_set_regs")
+
+    def batch_rescue(self, opt: MemOpt, pes):
+        """pes: 4 x mem_pestat_t as a numpy array of PESTAT_DTYPE.  Returns (ksw_align2 calls, DP cells, device ms)."""
+        pes = np.ascontiguousarray(pes)
+        st = (C.c_int64 * 2)(); ms = C.c_float(0)
+        self._chk(self.lib.b200_batch_rescue(self.h, C.byref(opt), C.c_void_p(pes.ctypes.data), st, C.byref(ms)), "batch_rescue")
+        return int(st[0]), int(st[1]), float(ms.value)
 
     def counters(self):
         out = np.zeros(16, dtype=np.uint64)

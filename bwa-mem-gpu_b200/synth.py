@@ -143,9 +143,11 @@ def simulate_long_reads(contigs, n_reads: int, min_len: int = 1000, max_len: int
 
 
 def simulate_pairs(contigs, n_pairs: int, read_len: int = 150, ins_mean: float = 500.0, ins_sd: float = 50.0,
-                   sub_rate: float = 0.01, damaged_frac: float = 0.05, seed: int = 1003):
-    """Config-3 style FR pairs, interleaved (2*n_pairs, read_len); a damaged_frac of pairs have one
-    mate with 30 % substitutions over a random 100-bp window so that mate rescue actually runs."""
+                   sub_rate: float = 0.01, damaged_frac: float = 0.05, seed: int = 1003, damage: str = "window"):
+    """Config-3 style FR pairs, interleaved (2*n_pairs, read_len); a damaged_frac of pairs have one damaged mate.
+    damage="window": 30 % substitutions over a random 100-bp window (such a mate usually still
+    seeds from its clean part, so few rescues run).  damage="periodic": one substitution every 14 bases, i.e. no exact
+    match of min_seed_len = 19 survives: the mate gets no region at all and can only be placed by mem_matesw."""
     rng = np.random.default_rng(seed)
     lens = np.array([len(c) for c in contigs], dtype=np.int64)
     cat = np.concatenate(contigs)
@@ -172,6 +174,10 @@ def simulate_pairs(contigs, n_pairs: int, read_len: int = 150, ins_mean: float =
     dmg = np.nonzero(rng.random(n_pairs) < damaged_frac)[0]
     for p in dmg:
         r = 2 * p + int(rng.integers(0, 2))
+        if damage == "periodic":
+            ph = int(rng.integers(0, 14))
+            reads[r, ph::14] = (reads[r, ph::14] + rng.integers(1, 4, size=len(reads[r, ph::14]))) % 4
+            continue
         w0 = int(rng.integers(0, read_len - 100 + 1))
         m = rng.random(100) < 0.30
         seg = reads[r, w0:w0 + 100]

@@ -223,6 +223,14 @@ int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, con
 int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *seqs, const int64_t *off);
 int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stage_ms);
 int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n);
+/* Paired-end stage on the resident batch (reads interleaved, mates at 2i / 2i+1): the mate-rescue block of
+ * mem_sam_pe (bwamem_pair.c:291-302 around mem_matesw, :137-206, ksw_align2 + mem_sort_dedup_patch) for every pair,
+ * given the batch's insert-size statistics pes[4] (mem_pestat, bwamem_pair.c:72, computed by the host program).
+ * The resident region lists are replaced by the rescued ones (fetch with b200_batch_download); the host then calls
+ * mem_sam_pe with MEM_F_NO_RESCUE set.  stats (may be NULL): [0]=ksw_align2 calls [1]=their DP cells; ms (may be
+ * NULL): device time.  b200_batch_set_regs() loads region lists produced elsewhere into the resident batch. */
+int b200_batch_rescue(b200_ctx_t *ctx, const mem_opt_t *opt, const mem_pestat_t *pes, int64_t *stats, float *ms);
+int b200_batch_set_regs(b200_ctx_t *ctx, const mem_alnreg_t *regs, const int32_t *cnt);
 /* work counters of the last b200_batch_run (for the roofline arithmetic):
  * [0]=bwt_extend calls [1]=of which touched two Occ blocks [2]=SA lookups [3]=LF steps walked
  * [4]=ksw_extend2 calls [5]=DP cells (sum over rows of end-beg) [6]=seeds [7]=chains kept [8]=regions

@@ -368,6 +368,66 @@ int64_t ref_process_seqs(void *p, const void *opt_, int64_t n_processed, int n, 
 	return tot <= cap ? tot : -tot;
 }
 
+/* ---------------------------------------------------------------- paired-end: pestat and the mate-rescue loop */
+
+extern int mem_matesw(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, const mem_pestat_t pes[4],
+                      const mem_alnreg_t *a, int l_ms, const uint8_t *ms, mem_alnreg_v *ma);
+
+static mem_alnreg_v *regs_unflatten(int n_reads, const void *regs, const int32_t *cnt)
+{
+	mem_alnreg_v *v = calloc(n_reads > 0 ? n_reads : 1, sizeof(mem_alnreg_v));
+	const mem_alnreg_t *r = (const mem_alnreg_t*)regs; int i;
+	for (i = 0; i < n_reads; ++i) {
+		v[i].n = v[i].m = cnt[i];
+		v[i].a = malloc((cnt[i] > 0 ? cnt[i] : 1) * sizeof(mem_alnreg_t));
+		memcpy(v[i].a, r, cnt[i] * sizeof(mem_alnreg_t)); r += cnt[i];
+	}
+	return v;
+}
+
+/* mem_pestat (bwamem_pair.c:72) over flat region lists; pes_out = 4 x mem_pestat_t */
+void ref_pestat(void *p, const void *opt_, int n_reads, const void *regs, const int32_t *cnt, void *pes_out)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; int i;
+	mem_alnreg_v *v = regs_unflatten(n_reads, regs, cnt);
+	mem_pestat((const mem_opt_t*)opt_, idx->bns->l_pac, n_reads, v, (mem_pestat_t*)pes_out);
+	for (i = 0; i < n_reads; ++i) free(v[i].a);
+	free(v);
+}
+
+/* The rescue block of mem_sam_pe (bwamem_pair.c:291-302), verbatim control flow around the reference's
+ * mem_matesw, for every pair.  seqs: nt4 codes.  Returns total regions or -(needed); *n_sw = sum of mem_matesw returns. */
+int64_t ref_mate_rescue(void *p, const void *opt_, const void *pes_, int n_reads, const uint8_t *seqs, const int64_t *off,
+                        const void *regs, const int32_t *cnt, int64_t cap, void *out_regs, int32_t *out_n, int64_t *n_sw)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	const mem_pestat_t *pes = (const mem_pestat_t*)pes_;
+	mem_alnreg_v *v = regs_unflatten(n_reads, regs, cnt);
+	int64_t tot = 0, nsw = 0; int pr, i, j;
+	for (pr = 0; pr + 1 < n_reads; pr += 2) {
+		mem_alnreg_v *a = &v[pr], b[2];
+		kv_init(b[0]); kv_init(b[1]);
+		for (i = 0; i < 2; ++i)
+			for (j = 0; j < a[i].n; ++j)
+				if (a[i].a[j].score >= a[i].a[0].score - opt->pen_unpaired)
+					kv_push(mem_alnreg_t, b[i], a[i].a[j]);
+		for (i = 0; i < 2; ++i)
+			for (j = 0; j < b[i].n && j < opt->max_matesw; ++j)
+				nsw += mem_matesw(opt, idx->bns, idx->pac, pes, &b[i].a[j], (int)(off[pr + !i + 1] - off[pr + !i]),
+				                  seqs + off[pr + !i], &a[!i]);
+		free(b[0].a); free(b[1].a);
+	}
+	for (i = 0; i < n_reads; ++i) tot += v[i].n;
+	if (tot <= cap) {
+		mem_alnreg_t *o = (mem_alnreg_t*)out_regs;
+		for (i = 0; i < n_reads; ++i) { memcpy(o, v[i].a, v[i].n * sizeof(mem_alnreg_t)); o += v[i].n; }
+	}
+	for (i = 0; i < n_reads; ++i) { out_n[i] = v[i].n; free(v[i].a); }
+	free(v);
+	if (n_sw) *n_sw = nsw;
+	return tot <= cap ? tot : -tot;
+}
+
 void ref_set_verbose(int v) { bwa_verbose = v; }
 
 /* ---------------------------------------------------------------- index from in-memory arrays

@@ -148,3 +148,7 @@ def sw_problems(rng, n, maxq=160, maxt=420, sat=False):
     q = np.ascontiguousarray(np.concatenate(qs + [np.zeros(1, np.uint8)]).astype(np.uint8))
     t = np.ascontiguousarray(np.concatenate(ts + [np.zeros(1, np.uint8)]).astype(np.uint8))
     return ql, qoff, q, tl, toff, t
+
+
+def reflib_pestat(idx, opt, regs, cnt):
+    return idx.pestat(opt, regs, cnt)

@@ -229,6 +229,31 @@ class RefIndex:
         assert tot >= 0
         return out[:tot].copy(), cnt
 
+    def pestat(self, opt: MemOpt, regs, cnt):
+        """mem_pestat (bwamem_pair.c:72) -> 4 x PESTAT_DTYPE"""
+        from bwa_mem_gpu_b200.abi import PESTAT_DTYPE
+        pes = np.zeros(4, dtype=PESTAT_DTYPE)
+        regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        self.lib.ref_pestat(self.h, C.byref(opt), C.c_int(len(cnt)), C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32),
+                            C.c_void_p(pes.ctypes.data))
+        return pes
+
+    def mate_rescue(self, opt: MemOpt, pes, seqs, off, regs, cnt):
+        """The rescue block of mem_sam_pe (bwamem_pair.c:291-302) for every pair -> (regs, counts, n_sw)."""
+        n = len(off) - 1
+        regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        pes = np.ascontiguousarray(pes)
+        cap = len(regs) + 8 * n + 64
+        out = np.zeros(cap, dtype=ALNREG_DTYPE)
+        ocnt = np.zeros(max(n, 1), dtype=np.int32)
+        nsw = C.c_int64(0)
+        self.lib.ref_mate_rescue.restype = C.c_int64
+        tot = self.lib.ref_mate_rescue(self.h, C.byref(opt), C.c_void_p(pes.ctypes.data), C.c_int(n), _p(seqs, C.c_uint8),
+                                       _p(off, C.c_int64), C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32), C.c_int64(cap),
+                                       C.c_void_p(out.ctypes.data), _p(ocnt, C.c_int32), C.byref(nsw))
+        assert tot >= 0
+        return out[:tot].copy(), ocnt[:n], nsw.value
+
     def process_seqs(self, opt: MemOpt, seqs, off, names=None, quals=None, n_processed=0, pes0=None):
         n = len(off) - 1
         if names is None:

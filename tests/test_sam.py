@@ -62,15 +62,17 @@ def test_sam_single_end(backend, gname):
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
-def test_sam_paired_end(backend):
-    """Interleaved pairs (MEM_F_PE): batch-level mem_pestat + mem_sam_pe on the host over device-computed regions."""
+@pytest.mark.parametrize("damage", ["window", "periodic"])
+def test_sam_paired_end(backend, damage):
+    """Interleaved pairs (MEM_F_PE): batch-level mem_pestat on the host, mate rescue on the device, mem_sam_pe (with
+    MEM_F_NO_RESCUE) on the host; "periodic" damage leaves mates that only mem_matesw can place."""
     gname = "small"
     idx = cm.ref_index(gname)
     opt = abi.default_opt()
     opt.flag |= 0x2
     opt.n_threads = 4
     npairs = 300 if backend == "emu" else 8000
-    reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=81, damaged_frac=0.1)
+    reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=81, damaged_frac=0.1, damage=damage)
     seqs = np.ascontiguousarray(reads.reshape(-1))
     off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
     names = [f"p{i // 2}" for i in range(2 * npairs)]

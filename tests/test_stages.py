@@ -281,3 +281,41 @@ def test_align_general_extension_kernel(backend):
     r2, n2 = ctx.align(opt, seqs, off)
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
     assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_mate_rescue(backend, gname):
+    """The mate-rescue block of mem_sam_pe (bwamem_pair.c:291-302; mem_matesw :137-206) for every pair of a batch with
+    damaged mates: all 88 bytes of every region after rescue, and the number of ksw_align2 calls."""
+    from bwa_mem_gpu_b200 import synth
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    opt.flag |= abi.MEM_F_PE
+    npairs = _sizes(backend, 250, 20000)
+    reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=19, damaged_frac=0.3, damage="periodic")
+    seqs = np.ascontiguousarray(reads.reshape(-1))
+    off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
+    regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
+    pes = cm.reflib_pestat(idx, opt, regs, cnt)
+    assert not pes["failed"][1]                                   # FR is usable
+    e_regs, e_cnt, e_sw = idx.mate_rescue(opt, pes, seqs, off, regs, cnt)
+    assert e_sw > npairs // 20                                    # the case really exercises ksw_align2
+    ctx.batch_upload(seqs, off)
+    ctx.batch_set_regs(regs, cnt)
+    n_sw, cells, _ = ctx.batch_rescue(opt, pes)
+    g_regs, g_cnt = ctx.batch_download(2 * npairs, len(e_regs) + 64)
+    assert n_sw == e_sw and cells > 0
+    assert np.array_equal(g_cnt, e_cnt)
+    assert g_regs.tobytes() == e_regs.tobytes()
+    # all four orientations usable and a wide window: several SW per anchor, insertions in the middle of the list
+    pes2 = pes.copy()
+    pes2["failed"] = 0
+    pes2["low"], pes2["high"] = 1, 900
+    e_regs, e_cnt, e_sw = idx.mate_rescue(opt, pes2, seqs, off, regs, cnt)
+    ctx.batch_set_regs(regs, cnt)
+    n_sw, _, _ = ctx.batch_rescue(opt, pes2)
+    g_regs, g_cnt = ctx.batch_download(2 * npairs, len(e_regs) + 64)
+    assert n_sw == e_sw
+    assert np.array_equal(g_cnt, e_cnt) and g_regs.tobytes() == e_regs.tobytes()
