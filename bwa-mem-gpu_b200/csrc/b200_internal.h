@@ -33,7 +33,7 @@ struct ChainRec {        // one kept chain after mem_chain_flt
 
 enum {                   // work / traffic counters (u64 each)
     CNT_EXTEND = 0, CNT_TWO_BLOCK, CNT_SA, CNT_LF, CNT_KSW, CNT_CELLS, CNT_SEEDS, CNT_CHAINS, CNT_REGS,
-    CNT_LAUNCH, CNT_N = 16
+    CNT_LAUNCH, CNT_SEEDSW, CNT_SEEDSW_CELLS, CNT_N = 16
 };
 
 // ---- stage parameter blocks (passed by value to the kernels) ---------------------------------
@@ -77,6 +77,17 @@ struct ChainParams {
     const i64 *chn_off, *cseed_off;
     ChainRec *chains; Seed *cseeds;
     int *overflow;
+};
+
+struct SeedSwParams {                            // mem_flt_chained_seeds over the long reads of a chunk
+    DevIndex ix;
+    mem_opt_t opt;
+    const u8 *seq; const i64 *off; int n_reads;
+    ChainRec *chains; const i64 *chn_off; const i32 *chn_n; Seed *cseeds;
+    const i32 *min_hsp;                          // per read: min_HSP_score (bwamem.c:608)
+    const i32 *long_reads; int n_long;           // reads that pass the length test (bwamem.c:609)
+    int slen_cap;
+    unsigned *work_counter; u64 *stats; int *overflow;
 };
 
 struct ExtParams {
@@ -151,6 +162,7 @@ int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,
                        int n_reads, mem_alnreg_t *dst, cudaStream_t st);
+int launch_seed_sw(const SeedSwParams &P, int n_sms, cudaStream_t st);
 int launch_exclusive_scan(const i32 *in, i64 *out /* n+1 */, int n, i64 *tmp, cudaStream_t st);
 int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl, cudaStream_t st);
 int launch_extend_batch(const DevIndex &ix, i64 n, const u64 *ik, int is_back, u64 *ok, cudaStream_t st);

@@ -3,6 +3,7 @@
 // buffers; results are compacted in read order.  Replaces mem_align_GPU / miniBatchMain
 // (cuda/bwamem_GPU.cu:3457, cuda/minibatch_process.cpp:188) and worker1 of mem_process_seqs
 // (bwamem.c:1183-1195, 1232).
+#include <math.h>
 #include "ctx.h"
 #include <string.h>
 #include <stdlib.h>
@@ -60,6 +61,7 @@ struct StageTimer {
 
 // stop_after: 1 = SMEM intervals, 2 = seeds, 3 = chains (opt stage in chain_stage), 5 = everything
 static int g_chain_stage = 1;
+#define SSW_MAX_Q 200                                    // mem_seed_sw only aligns windows shorter than MEM_SHORT_LEN
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms)
 {
@@ -188,6 +190,37 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     CP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
     if (launch_chain(CP, 1, st)) return -1;
     ++launches;
+    // ---- K3b: mem_flt_chained_seeds (bwamem.c:605-622) for the reads long enough to need it
+    if (stop_after != 3 || g_chain_stage >= 2) {
+        // min_l and min_HSP_score depend on the read length only; log() is evaluated on the host like the reference does
+        std::vector<i32> by_len((size_t)ctx->max_len + 1, -2), mh((size_t)n), lr;
+        for (int r = 0; r < n; ++r) {
+            const int l_query = (int)(ctx->h_off[r0 + r + 1] - ctx->h_off[r0 + r]);
+            if (by_len[l_query] == -2) {                                 // -1: too short for the filter (bwamem.c:609)
+                const double min_l = opt->min_chain_weight ? 1.1f * opt->min_chain_weight : 5.5f * log((double)l_query);
+                by_len[l_query] = (l_query == 0 || min_l > 0.05f * l_query) ? -1 : (int)(opt->a * min_l + .499);
+            }
+            mh[r] = by_len[l_query];
+            if (by_len[l_query] >= 0) lr.push_back(r);
+        }
+        if (!lr.empty()) {
+            if (ctx->d_pa.ensure((size_t)n * 4) || ctx->d_pb.ensure(lr.size() * 4)) return -1;
+            B200_CHECK(cudaMemcpyAsync(ctx->d_pa.p, mh.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            B200_CHECK(cudaMemcpyAsync(ctx->d_pb.p, lr.data(), lr.size() * 4, cudaMemcpyHostToDevice, st));
+            if (ctl_zero(ctx, CTL_WORK)) return -1;
+            SeedSwParams SP;
+            memset(&SP, 0, sizeof(SP));
+            SP.ix = ctx->ix; SP.opt = *opt; SP.seq = ctx->d_seq.as<u8>(); SP.off = d_off; SP.n_reads = n;
+            SP.chains = ctx->d_chains.as<ChainRec>(); SP.chn_off = ctx->d_seed_off.as<i64>(); SP.chn_n = ctx->d_chn_n.as<i32>();
+            SP.cseeds = ctx->d_cseeds.as<Seed>(); SP.min_hsp = ctx->d_pa.as<i32>();
+            SP.long_reads = ctx->d_pb.as<i32>(); SP.n_long = (int)lr.size();
+            SP.slen_cap = (SSW_MAX_Q + 7) / 8 + 1;
+            SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = (u64 *)ctl_u64(ctx, CTL_STATS) + CNT_SEEDSW; SP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
+            if (launch_seed_sw(SP, ctx->n_sms, st)) return -1;
+            B200_CHECK(cudaStreamSynchronize(st));                       // mh / lr are stack-owned host buffers
+            ++launches;
+        }
+    }
     tm.mark(st);
     if (stop_after == 3) {
         if (ctl_read(ctx, CTL_OVF2, 1, &ovf)) return -1;

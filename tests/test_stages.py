@@ -319,3 +319,49 @@ def test_mate_rescue(backend, gname):
     g_regs, g_cnt = ctx.batch_download(2 * npairs, len(e_regs) + 64)
     assert n_sw == e_sw
     assert np.array_equal(g_cnt, e_cnt) and g_regs.tobytes() == e_regs.tobytes()
+
+
+def _long_reads(gname, n, seed, lo=800, hi=3000, sub=0.06, indel=0.01):
+    """Long noisy reads: seeds are short, so mem_flt_chained_seeds (l_query >~ 735) has real work."""
+    from bwa_mem_gpu_b200 import synth
+    rng = np.random.default_rng(seed)
+    contigs = cm.genome(gname)
+    seqs, off = [], [0]
+    for i in range(n):
+        l = int(rng.integers(lo, hi))
+        r, _ = synth.simulate_reads(contigs, 1, read_len=l, seed=seed * 1000 + i, sub_rate=sub, indel_rate=indel)
+        s = r.reshape(-1)
+        if i % 7 == 3:                                     # chimeric: second half from elsewhere
+            r2, _ = synth.simulate_reads(contigs, 1, read_len=l, seed=seed * 1000 + i + 500000, sub_rate=sub, indel_rate=indel)
+            s = np.concatenate([s[: l // 2], r2.reshape(-1)[l // 2:]])
+        seqs.append(s); off.append(off[-1] + len(s))
+    return np.ascontiguousarray(np.concatenate(seqs).astype(np.uint8)), np.array(off, dtype=np.int64)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_flt_chained_seeds_long_reads(backend, gname):
+    """mem_flt_chained_seeds / mem_seed_sw (bwamem.c:605-622, 578-603): surviving seeds and their SW scores."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = _long_reads(gname, _sizes(backend, 24, 600), seed=3)
+    a1 = idx.chains(opt, seqs, off, stage=1, cap_chn_per_read=512, cap_seed_per_read=16384)
+    a = idx.chains(opt, seqs, off, stage=2, cap_chn_per_read=512, cap_seed_per_read=16384)
+    b = ctx.chains(opt, seqs, off, stage=2, cap_chn_per_read=512, cap_seed_per_read=16384)
+    assert len(a[2]) < len(a1[2])                          # the filter really removed seeds
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_align_long_reads(backend):
+    """mem_align1_core on 0.8-3 kbp noisy reads (seed SW filter + wide-band extension + region patching)."""
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    opt = abi.default_opt()
+    seqs, off = _long_reads("small", _sizes(backend, 16, 400), seed=5)
+    r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
+    r1, n1 = ctx.align(opt, seqs, off)
+    assert np.array_equal(n0, n1)
+    assert r0.tobytes() == r1.tobytes()
