@@ -12,6 +12,8 @@
 #include <thread>
 #include <vector>
 #include <atomic>
+#include <functional>
+#include <string>
 #include "../../include/bwamem_b200.h"
 
 #define MEM_F_PRIMARY5_ 0x800        /* bwamem.h:47 */
@@ -51,10 +53,43 @@ static inline uint8_t nt4_of(uint8_t c)
     return c == '-' ? 5 : 4;
 }
 
-static b200_ctx_t *g_ps_ctx = nullptr;
+// One context per device; a batch is cut into contiguous blocks of reads (whole pairs), one per context, each driven
+// by its own host thread.  Nothing is exchanged between devices: the only batch-level quantity, mem_pestat, is computed
+// on the host over all blocks (as the reference does over all reads) and handed to every block's rescue stage.
+static std::vector<b200_ctx_t *> g_ps_ctxs;
 static const bwt_t *g_ps_bwt = nullptr;
+static int g_ps_want_devices = 1;
 
-extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctx = ctx; g_ps_bwt = nullptr; }
+extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctxs.assign(1, ctx); g_ps_bwt = nullptr; }
+extern "C" void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs) { g_ps_ctxs.assign(ctxs, ctxs + n); g_ps_bwt = nullptr; }
+extern "C" void b200_process_seqs_use_devices(int n_devices) { g_ps_want_devices = n_devices > 0 ? n_devices : 1; }
+
+struct Shard {
+    b200_ctx_t *ctx; int r0, n;
+    std::vector<mem_alnreg_t> regs; std::vector<int32_t> cnt;
+    std::string err;
+};
+
+static void shard_download(Shard &sh)
+{
+    for (;;) {
+        int64_t got = b200_batch_download(sh.ctx, (int64_t)sh.regs.size(), sh.regs.data(), sh.cnt.data());
+        if (got >= 0) return;
+        if (-got > (int64_t)sh.regs.size()) { sh.regs.resize((size_t)-got); continue; }
+        sh.err = b200_last_error();
+        return;
+    }
+}
+
+static void run_shards(std::vector<Shard> &shards, const std::function<void(Shard &)> &fn)
+{
+    std::vector<std::thread> th;
+    for (size_t d = 1; d < shards.size(); ++d) th.emplace_back([&, d]() { fn(shards[d]); });
+    fn(shards[0]);
+    for (auto &t : th) t.join();
+    for (auto &sh : shards)
+        if (!sh.err.empty()) { fprintf(stderr, "[b200::mem_process_seqs] %s\n", sh.err.c_str()); exit(1); }
+}
 
 extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                                       int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
@@ -65,42 +100,50 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
     sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
     pestat_fn f_pestat = (pe && !pes0) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
 
-    if (!g_ps_ctx || (g_ps_bwt && g_ps_bwt != bwt)) {                 // lazy context from the index identity
-        g_ps_ctx = b200_ctx_create(0);
-        if (!g_ps_ctx || b200_index_upload(g_ps_ctx, bwt, bns, pac, B200_IDX_FULL_SA)) {
-            fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
-            exit(1);
+    if (g_ps_ctxs.empty() || (g_ps_bwt && g_ps_bwt != bwt)) {         // lazy contexts from the index identity
+        g_ps_ctxs.clear();
+        for (int d = 0; d < g_ps_want_devices; ++d) {
+            b200_ctx_t *c = b200_ctx_create(d);
+            if (!c || b200_index_upload(c, bwt, bns, pac, B200_IDX_FULL_SA)) {
+                fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
+                exit(1);
+            }
+            g_ps_ctxs.push_back(c);
         }
         g_ps_bwt = bwt;
     }
 
-    // ---- worker1 on the device
+    // ---- worker1 on the device(s)
     std::vector<int64_t> off((size_t)n + 1);
     int64_t tot = 0;
     for (int i = 0; i < n; ++i) { off[i] = tot; tot += seqs[i].l_seq; }
     off[n] = tot;
     std::vector<uint8_t> flat((size_t)tot + 1);
     for (int i = 0; i < n; ++i) memcpy(flat.data() + off[i], seqs[i].seq, (size_t)seqs[i].l_seq);
-    std::vector<int32_t> cnt((size_t)n + 1);
-    std::vector<mem_alnreg_t> regs;
-    int64_t cap = 2 * (int64_t)n + 64;
-    for (;;) {
-        regs.resize((size_t)cap);
-        int64_t got = b200_align_batch(g_ps_ctx, opt, n, flat.data(), off.data(), cap, regs.data(), cnt.data());
-        if (got >= 0) break;
-        if (-got > cap) { cap = -got; continue; }
-        fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
-        exit(1);
+    const int G = (int)g_ps_ctxs.size();
+    std::vector<Shard> shards((size_t)G);
+    for (int d = 0; d < G; ++d) {
+        int lo = (int)((int64_t)n * d / G), hi = (int)((int64_t)n * (d + 1) / G);
+        if (pe) { lo &= ~1; hi = d == G - 1 ? n : hi & ~1; }          // mates stay together
+        shards[d].ctx = g_ps_ctxs[d]; shards[d].r0 = lo; shards[d].n = hi - lo;
     }
+    run_shards(shards, [&](Shard &sh) {
+        sh.cnt.assign((size_t)sh.n + 1, 0);
+        sh.regs.resize((size_t)(2 * (int64_t)sh.n + 64));
+        if (b200_batch_upload(sh.ctx, sh.n, flat.data(), off.data() + sh.r0) || b200_batch_run(sh.ctx, opt, nullptr)) { sh.err = b200_last_error(); return; }
+        shard_download(sh);
+    });
     mem_alnreg_v *rv = (mem_alnreg_v *)malloc((size_t)(n > 0 ? n : 1) * sizeof(mem_alnreg_v));
     auto fill_rv = [&](bool first) {
-        for (int64_t i = 0, k = 0; i < n; ++i) {
-            if (!first) free(rv[i].a);
-            rv[i].n = rv[i].m = cnt[i];
-            rv[i].a = (mem_alnreg_t *)malloc((size_t)(cnt[i] > 0 ? cnt[i] : 1) * sizeof(mem_alnreg_t));
-            memcpy(rv[i].a, regs.data() + k, (size_t)cnt[i] * sizeof(mem_alnreg_t));
-            k += cnt[i];
-        }
+        for (auto &sh : shards)
+            for (int64_t i = 0, k = 0; i < sh.n; ++i) {
+                mem_alnreg_v &v = rv[sh.r0 + i];
+                if (!first) free(v.a);
+                v.n = v.m = sh.cnt[i];
+                v.a = (mem_alnreg_t *)malloc((size_t)(sh.cnt[i] > 0 ? sh.cnt[i] : 1) * sizeof(mem_alnreg_t));
+                memcpy(v.a, sh.regs.data() + k, (size_t)sh.cnt[i] * sizeof(mem_alnreg_t));
+                k += sh.cnt[i];
+            }
     };
     fill_rv(true);
     for (int i = 0; i < n; ++i)
@@ -113,17 +156,10 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         if (pes0) memcpy(pes, pes0, 4 * sizeof(mem_pestat_t));        // bwamem.c:1237
         else f_pestat(opt, bns->l_pac, n, rv, pes);                   // bwamem.c:1238
         if (!(opt->flag & MEM_F_NO_RESCUE_)) {                        // bwamem_pair.c:291-302 for every pair
-            if (b200_batch_rescue(g_ps_ctx, opt, pes, nullptr, nullptr)) {
-                fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
-                exit(1);
-            }
-            for (;;) {
-                int64_t got = b200_batch_download(g_ps_ctx, (int64_t)regs.size(), regs.data(), cnt.data());
-                if (got >= 0) break;
-                if (-got > (int64_t)regs.size()) { regs.resize((size_t)-got); continue; }
-                fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error());
-                exit(1);
-            }
+            run_shards(shards, [&](Shard &sh) {
+                if (b200_batch_rescue(sh.ctx, opt, pes, nullptr, nullptr)) { sh.err = b200_last_error(); return; }
+                shard_download(sh);
+            });
             fill_rv(false);
             opt2.flag |= MEM_F_NO_RESCUE_;                            // worker2 must not repeat it
         }

@@ -253,6 +253,11 @@ int b200_microbench(b200_ctx_t *ctx, int kind, int64_t table_bytes, int blocks_p
  * b200_process_seqs_set_ctx() selects an existing context (index already uploaded); otherwise one is created on
  * device 0 from (bwt, bns, pac) at the first call. */
 void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
+/* Several devices in one host process: the batch is cut into contiguous blocks of reads (whole pairs), one per
+ * context, each driven by its own host thread; results are put back in input order.  Either hand over contexts that
+ * already hold the index, or ask for contexts on devices 0..n-1 to be created at the first call. */
+void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs);
+void b200_process_seqs_use_devices(int n_devices);
 void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                            int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
 

@@ -10,7 +10,7 @@ import pytest
 
 import common as cm
 import refapi
-from bwa_mem_gpu_b200 import abi, synth
+from bwa_mem_gpu_b200 import abi, synth, lib as L
 
 BACKENDS = [pytest.param("emu", id="emu"), pytest.param("cuda", id="cuda", marks=pytest.mark.gpu)]
 needs_ref = pytest.mark.skipif(not cm.have_ref(), reason="oracle/_ref not built")
@@ -22,7 +22,7 @@ class BSeq1(C.Structure):          # bseq1_t, bwa.h:56-63
                 ("l_name", C.c_int8), ("l_comment", C.c_int8), ("l_qual", C.c_int16)]
 
 
-def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None):
+def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards=1):
     idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
     C.CDLL(refapi.REF_SO, mode=os.RTLD_GLOBAL)          # the "host program": the reference's worker2 functions
     lib = ctx.lib
@@ -36,7 +36,17 @@ def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None):
         keep.append((s, nm))
         arr[i].l_seq = int(off[i + 1] - off[i]); arr[i].id = i
         arr[i].name = nm; arr[i].comment = None; arr[i].seq = C.cast(s, C.POINTER(C.c_char)); arr[i].qual = None
-    lib.b200_process_seqs_set_ctx(ctx.h)
+    if n_shards == 1:
+        lib.b200_process_seqs_set_ctx(ctx.h)
+    else:                                                   # several contexts (here: all on device 0), one block of reads each
+        extra = []
+        for _ in range(n_shards - 1):
+            c = L.Context(0, lib)
+            c.upload_host_index(ctx._host_index)
+            extra.append(c)
+        keep.append(extra)
+        hs = (C.c_void_p * n_shards)(ctx.h, *[c.h for c in extra])
+        lib.b200_process_seqs_set_ctxs(n_shards, hs)
     lib.b200_mem_process_seqs(C.byref(opt), C.c_void_p(idx.bwt_struct()), C.c_void_p(idx.bns_struct()),
                               C.c_void_p(idx.pac().ctypes.data), C.c_int64(n_processed), C.c_int(n), arr, None)
     out = b"".join(C.string_at(arr[i].sam) for i in range(n))
@@ -80,3 +90,28 @@ def test_sam_paired_end(backend, damage):
     got = _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names)
     assert got == exp
     assert exp.count(b"\n") >= 2 * npairs
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("pe", [0, 1])
+def test_sam_sharded_over_contexts(backend, pe):
+    """One batch cut into 3 contiguous blocks (whole pairs) on 3 contexts: SAM identical to the reference's, i.e. to
+    the unsharded run; the PE case needs the batch-level mem_pestat over all blocks before each block's rescue."""
+    gname = "small"
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    opt.n_threads = 4
+    if pe:
+        opt.flag |= 0x2
+        npairs = 301 if backend == "emu" else 6001
+        reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=83, damaged_frac=0.1, damage="periodic")
+        seqs = np.ascontiguousarray(reads.reshape(-1))
+        off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
+        names = [f"p{i // 2}" for i in range(2 * npairs)]
+    else:
+        seqs, off = cm.reads_for(gname, 401 if backend == "emu" else 20001, seed=73, indel=0.004, sub=0.015)
+        names = None
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=64)
+    got = _our_sam(backend, gname, opt, seqs, off, n_processed=64, names=names, n_shards=3)
+    assert got == exp
