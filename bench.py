@@ -110,6 +110,22 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def measured_traffic(kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json:
+    dram__bytes_read.sum + dram__bytes_write.sum, one launch = one 2^20-read chunk), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    t = json.load(open(p)).get(kernel)
+    return None if t is None else float(t["dram_bytes_per_launch"])
+
+
+def microbench_ceilings():
+    """Random 32-B-sector gather rates and the DPX issue rate measured on this pool (profiles/microbench.json)."""
+    p = os.path.join(ROOT, "profiles", "microbench.json")
+    return json.load(open(p)) if os.path.exists(p) else None
+
+
 def cpu_reference(a, hidx, seqs, off, n_sample, threads):
     """The reference's CPU implementation of the same path (mem_align1_core over kt_for), oracle/_ref."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -243,9 +259,13 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
-        alg_bytes = 64.0 * (cnt["extend"] + cnt["two_block"])                 # per batch (counters are per last run)
+        # dominant kernel: the SMEM seeding kernel, launched once per chunk of 2^20 reads; bytes and time per launch
+        n_launch = max(1, -(-a.reads // (1 << 20)))
+        alg_bytes = 64.0 * (cnt["extend"] + cnt["two_block"]) / n_launch      # counters are per batch_run
         smem_ms = stage[1] / a.steps
-        achieved = alg_bytes / (smem_ms * 1e-3) / 1e9 if smem_ms > 0 else 0.0
+        achieved = alg_bytes / (smem_ms / n_launch * 1e-3) / 1e9 if smem_ms > 0 else 0.0
+        mb = microbench_ceilings()
+        ext_ms = stage[4] / a.steps
         out = {
             "metric": METRIC, "value": world * a.reads / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": dev_ms_max, "higher_is_better": True,
@@ -262,12 +282,21 @@ def main():
             "clocks": clocks,
             "stage_ms": {k: float(v) / a.steps for k, v in zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], stage)},
             "counters": cnt,
-            "roofline": {"bound": "hbm", "kernel": "smem_collect_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes": alg_bytes,
-                         "note": "64 B x Occ blocks touched by bwt_extend (1 or 2 per call), summed over the batch"},
-            "extension": {"gcups": cnt["cells"] / (stage[4] / a.steps * 1e-3) / 1e9 if stage[4] > 0 else None,
-                          "cells": cnt["cells"], "ksw_calls": cnt["ksw"]},
+            "roofline": {"bound": "hbm", "kernel": "smem_fast3_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic("smem_fast3_kernel"),
+                         "peak_source": peak_src, "algorithmic_bytes": alg_bytes, "launches_per_step": n_launch,
+                         "ms_per_launch": smem_ms / n_launch,
+                         "note": "algorithmic bytes = 64 B x Occ blocks touched by bwt_extend (1 or 2 per call, "
+                                 "SURVEY.md 8d) per launch (one chunk of 2^20 reads); the kernel itself reads one 32-B "
+                                 "sector per Occ block from its own index layout, so DRAM traffic is below that"},
+            "extension": {"gcups": cnt["cells"] / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None,
+                          "cells": cnt["cells"], "ksw_calls": cnt["ksw"], "dpx_ops_per_cell": 5,
+                          "dpx_peak_gcups": (mb["dpx_tops"] * 1e3 / 5) if mb and "dpx_tops" in mb else None,
+                          "frac_of_dpx_peak": (cnt["cells"] / (ext_ms * 1e-3) / 1e9) / (mb["dpx_tops"] * 1e3 / 5)
+                                              if mb and "dpx_tops" in mb and ext_ms > 0 else None},
+            "gather_ceiling": ({"sectors_per_s_l2": mb.get("gather_l2_gsectors"), "sectors_per_s_dram": mb.get("gather_dram_gsectors"),
+                                "achieved_gsectors": (cnt["extend"] + cnt["two_block"]) / (smem_ms * 1e-3) / 1e9 if smem_ms > 0 else None}
+                               if mb else None),
             "smem_lookups_per_sec": cnt["extend"] / (smem_ms * 1e-3) if smem_ms > 0 else None,
         }
         if not a.no_cpu_baseline:

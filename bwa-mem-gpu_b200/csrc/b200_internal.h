@@ -33,7 +33,7 @@ struct ChainRec {        // one kept chain after mem_chain_flt
 
 enum {                   // work / traffic counters (u64 each)
     CNT_EXTEND = 0, CNT_TWO_BLOCK, CNT_SA, CNT_LF, CNT_KSW, CNT_CELLS, CNT_SEEDS, CNT_CHAINS, CNT_REGS,
-    CNT_LAUNCH, CNT_SEEDSW, CNT_SEEDSW_CELLS, CNT_N = 16
+    CNT_LAUNCH, CNT_SEEDSW, CNT_SEEDSW_CELLS, CNT_BIN0, CNT_BIN1, CNT_BIN2, CNT_N = 16
 };
 
 // ---- stage parameter blocks (passed by value to the kernels) ---------------------------------
@@ -123,9 +123,13 @@ struct Ext2Params {
     mem_alnreg_t *regs;              // per read at chn_off[r], capacity = the read's seed count
     u64 *srt;                        // per chain at its seed_off
     ExtRead *rstate;
-    ExtJob *jobs[2];
-    unsigned *njobs;                 // per round
-    int he_cols;                     // shared-memory columns per lane in the DP kernel (max query side + 1)
+    // Jobs are binned by the longer of their two query flanks so that the DP kernel of a bin sizes its shared-memory
+    // rows for that bin only (short flanks = many resident warps).  Bins 0 and 2 share one array (bin 0 grows up from
+    // slot 0, bin 2 down from the last slot), bin 1 has its own; both double-buffered by round parity.
+    ExtJob *jobs[2], *jobs_mid[2];
+    int jobs_cap;                    // slots per array (>= reads in the chunk: at most one job per read and round)
+    int bin_max[2];                  // longest flank of bin 0 / bin 1
+    unsigned *njobs;                 // per round: 8 counters: [0..2] jobs emitted per bin, [4..6] jobs taken by the DP kernel
     i32 *eh; int eh_cap;             // finish kernel scratch (mem_patch_reg's global alignment)
     i64 *reg_off; i32 *reg_n;
     unsigned *work_counter;
@@ -157,7 +161,7 @@ int launch_sa_locate(const SeedParams &p, cudaStream_t st);
 int launch_chain(const ChainParams &p, int emit, cudaStream_t st);
 int launch_extend(const ExtParams &p, int grid, int block, cudaStream_t st);
 int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t st);
-int launch_ext2_dp(const Ext2Params &p, int round, int grid, cudaStream_t st);
+int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st);
 int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,

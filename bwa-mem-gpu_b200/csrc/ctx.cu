@@ -53,6 +53,9 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
     else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
+    else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;
+    else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
+    else if (!strcmp(key, "ext_bps")) ctx->ext_bps = (int)value;
     else if (!strcmp(key, "l2_persist")) ctx->l2_persist = (int)value;
     else { b200_set_error("unknown tunable '%s'", key); return -1; }
     return 0;

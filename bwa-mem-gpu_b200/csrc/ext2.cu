@@ -28,6 +28,12 @@
 #define DP_HMASK 0x3fffu
 #define DP_QMASK 0x70000000u
 
+__device__ __forceinline__ ExtJob *job_slot(const Ext2Params &P, int parity, int bin, unsigned slot)
+{
+    if (bin == 1) return P.jobs_mid[parity] + slot;
+    return bin == 0 ? P.jobs[parity] + slot : P.jobs[parity] + (P.jobs_cap - 1 - (int)slot);
+}
+
 // ------------------------------------------------------------------------------------------------ planning
 __device__ __forceinline__ int clamp_band(const mem_opt_t &opt, int qlen, int w, int end_bonus)
 {   // ksw.c:399-407 with max = max(mat)
@@ -44,12 +50,17 @@ __device__ __forceinline__ int clamp_band(const mem_opt_t &opt, int qlen, int w,
 __global__ void __launch_bounds__(128) ext_plan_kernel(Ext2Params P, int round)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const ExtJob *jprev = P.jobs[(round + 1) & 1];
-    ExtJob *jcur = P.jobs[round & 1];
     int r;
     const ExtJob *done = nullptr;
     if (round == 0) { if (t >= P.n_reads) return; r = t; }
-    else { if ((unsigned)t >= P.njobs[round - 1]) return; done = &jprev[t]; r = done->read; }
+    else {
+        const unsigned *nj = P.njobs + 8 * (round - 1);
+        unsigned u = (unsigned)t;
+        int bin = 0;
+        if (u >= nj[0]) { u -= nj[0]; bin = 2; if (u >= nj[2]) { u -= nj[2]; bin = 1; if (u >= nj[1]) return; } }
+        done = job_slot(P, (round + 1) & 1, bin, u);
+        r = done->read;
+    }
     const mem_opt_t &opt = P.opt;
     const DevIndex &ix = P.ix;
     const i64 l_pac = ix.l_pac;
@@ -144,15 +155,17 @@ __global__ void __launch_bounds__(128) ext_plan_kernel(Ext2Params P, int round)
                 if (i == c.n) { srt[k] = 0; --er.k; continue; }
             }
             // extend this seed: one job
-            const unsigned slot = atomicAdd(&P.njobs[round], 1u);
+            const int ql = s.qbeg, qr = l_query - (s.qbeg + s.len);
+            const int flank = ql > qr ? ql : qr;
+            const int bin = flank <= P.bin_max[0] ? 0 : flank <= P.bin_max[1] ? 1 : 2;
+            const unsigned slot = atomicAdd(&P.njobs[8 * round + bin], 1u);
             ExtJob j;
             j.rbeg = s.rbeg; j.rmax0 = er.rmax0; j.rmax1 = er.rmax1;
             j.read = r; j.qbeg = s.qbeg; j.slen = s.len; j.lq = l_query;
-            const int ql = s.qbeg, qr = l_query - (s.qbeg + s.len);
             j.wl0 = clamp_band(opt, ql, opt.w, opt.pen_clip5); j.wl1 = clamp_band(opt, ql, opt.w << 1, opt.pen_clip5);
             j.wr0 = clamp_band(opt, qr, opt.w, opt.pen_clip3); j.wr1 = clamp_band(opt, qr, opt.w << 1, opt.pen_clip3);
             j.rb = j.re = 0; j.qb = j.qe = j.score = j.truesc = j.w = j.pad = 0;
-            jcur[slot] = j;
+            *job_slot(P, round & 1, bin, slot) = j;
             emitted = true;
             break;
         }
@@ -199,7 +212,7 @@ __device__ __forceinline__ int dp_score(u32 lo, u32 hi, u32 q)
 #endif
 }
 
-__global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round)
+__global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round, int bin)
 {
     B200_DYN_SMEM(dp_raw);
     __shared__ u32 s_rows[5 * 2];                          // matrix row of each target base, 8 bytes (5 used)
@@ -219,8 +232,8 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
     const mem_opt_t &opt = P.opt;
     const int o_del = opt.o_del, e_del = opt.e_del, o_ins = opt.o_ins, e_ins = opt.e_ins;
     const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins, zdrop = opt.zdrop;
-    ExtJob *jobs = P.jobs[round & 1];
-    const unsigned njobs = P.njobs[round];
+    const unsigned njobs = P.njobs[8 * round + bin];
+    unsigned *work_counter = P.njobs + 8 * round + 4 + bin;
     const i64 l_pac = ix.l_pac;
     u64 n_ksw = 0, n_cells = 0;
     unsigned ncell32 = 0;                  // cells of the current job (flushed into n_cells when it ends)
@@ -308,9 +321,9 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
         while ((active && ksw_fin) || (!active && !exhausted)) {
             int next_side = -1, next_t = 0;
             if (!active) {                                                                // fetch a job
-                const unsigned slot = atomicAdd(P.work_counter, 1u);
+                const unsigned slot = atomicAdd(work_counter, 1u);
                 if (slot >= njobs) { exhausted = true; break; }
-                L.job = &jobs[slot];
+                L.job = job_slot(P, round & 1, bin, slot);
                 active = true;
                 L.a_score = -1;
                 if (L.job->qbeg) { next_side = 0; next_t = 0; L.prev = -1; }
@@ -455,13 +468,13 @@ int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t
     B200_CHECK(cudaGetLastError());
     return 0;
 }
-int launch_ext2_dp(const Ext2Params &p, int round, int grid, cudaStream_t st)
+int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st)
 {
-    const size_t smem = (size_t)p.he_cols * DP_THREADS * 4;
+    const size_t smem = (size_t)he_cols * DP_THREADS * 4;
 #ifndef B200_EMU
     B200_CHECK(cudaFuncSetAttribute(ext_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
-    B200_LAUNCH(ext_dp_kernel, grid, DP_THREADS, smem, st, p, round);
+    B200_LAUNCH(ext_dp_kernel, grid, DP_THREADS, smem, st, p, round, bin);
     B200_CHECK(cudaGetLastError());
     return 0;
 }

@@ -234,7 +234,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     if (ctx->d_arena.ensure((size_t)arena_cap * sizeof(mem_alnreg_t)) || ctx->d_reg_off.ensure((size_t)n * 8) ||
         ctx->d_reg_n.ensure((size_t)n * 4) || ctx->d_dst_off.ensure(((size_t)n + 1) * 8)) return -1;
     // round-based fast path (ext2.cu) when scores fit 14 bits and one H/E row per lane fits shared memory
-    const int he_cols = ctx->max_len + 2 + 8;                                 // + 8: the DP hot slot prefetches 8 columns
+    const int he_cols = ctx->max_len + 2 + 8;                                 // widest bin; + 8: the DP hot slot prefetches 8 columns
     bool fast_ext = (i64)ctx->max_len * opt->a < 16384 && (size_t)he_cols * 64 * 4 <= 96 * 1024;
     for (int k = 0; k < 25; ++k) if (opt->mat[k] > opt->a) fast_ext = false;     // bound above assumes max(mat) == a
     if (ctx->ext_path == 1) fast_ext = false;
@@ -245,9 +245,10 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         const int fin_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * 2));
         const int eh_cap = ctx->max_len + 2;
         if (ctx->d_jobs0.ensure((size_t)n * sizeof(ExtJob)) || ctx->d_jobs1.ensure((size_t)n * sizeof(ExtJob)) ||
-            ctx->d_rstate.ensure((size_t)n * sizeof(ExtRead)) || ctx->d_njobs.ensure((size_t)MAX_ROUNDS * 4) ||
+            ctx->d_jobs2.ensure((size_t)n * sizeof(ExtJob)) || ctx->d_jobs3.ensure((size_t)n * sizeof(ExtJob)) ||
+            ctx->d_rstate.ensure((size_t)n * sizeof(ExtRead)) || ctx->d_njobs.ensure((size_t)MAX_ROUNDS * 32) ||
             ctx->d_srt.ensure((size_t)(tot_seeds + 1) * 8) || ctx->d_eh.ensure((size_t)fin_blocks * 128 * 2 * eh_cap * 4)) return -1;
-        B200_CHECK(cudaMemsetAsync(ctx->d_njobs.p, 0, (size_t)MAX_ROUNDS * 4, st));
+        B200_CHECK(cudaMemsetAsync(ctx->d_njobs.p, 0, (size_t)MAX_ROUNDS * 32, st));
         Ext2Params XP;
         memset(&XP, 0, sizeof(XP));
         XP.ix = ctx->ix; XP.opt = *opt; XP.seq = ctx->d_seq.as<u8>(); XP.off = d_off; XP.n_reads = n;
@@ -256,25 +257,34 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         XP.regs = ctx->d_arena.as<mem_alnreg_t>(); XP.srt = ctx->d_srt.as<u64>();
         XP.rstate = ctx->d_rstate.as<ExtRead>();
         XP.jobs[0] = ctx->d_jobs0.as<ExtJob>(); XP.jobs[1] = ctx->d_jobs1.as<ExtJob>();
+        XP.jobs_mid[0] = ctx->d_jobs2.as<ExtJob>(); XP.jobs_mid[1] = ctx->d_jobs3.as<ExtJob>();
+        XP.jobs_cap = n;
+        // flank-length bins: the DP kernel of a bin holds flank + 1 columns (+ 8 for the hot slot's prefetch) per lane
+        const int bin_flank[3] = { ctx->ext_bin0 > 0 ? ctx->ext_bin0 : 32, ctx->ext_bin1 > 0 ? ctx->ext_bin1 : 64, ctx->max_len };
+        XP.bin_max[0] = std::min(bin_flank[0], ctx->max_len); XP.bin_max[1] = std::min(std::max(bin_flank[1], XP.bin_max[0]), ctx->max_len);
         XP.njobs = ctx->d_njobs.as<unsigned>();
-        XP.he_cols = he_cols; XP.eh = ctx->d_eh.as<i32>(); XP.eh_cap = eh_cap;
+        XP.eh = ctx->d_eh.as<i32>(); XP.eh_cap = eh_cap;
         XP.reg_off = reg_off_ptr; XP.reg_n = reg_n_ptr;
         XP.work_counter = ctl_u32(ctx, CTL_WORK); XP.stats = ctl_u64(ctx, CTL_STATS);
-        const int dp_per_sm = std::max(1, std::min(8, (int)((200 * 1024) / ((size_t)he_cols * 64 * 4))));
         int threads = n;
         for (int round = 0; ; ++round) {
             if (round >= MAX_ROUNDS) { b200_set_error("extension: more than %d rounds", MAX_ROUNDS); return -2; }
             if (launch_ext2_plan(XP, round, threads, st)) return -1;
             ++launches;
-            unsigned nj = 0;
-            B200_CHECK(cudaMemcpyAsync(&nj, XP.njobs + round, 4, cudaMemcpyDeviceToHost, st));
+            unsigned nj[3] = { 0, 0, 0 };
+            B200_CHECK(cudaMemcpyAsync(nj, XP.njobs + 8 * round, 12, cudaMemcpyDeviceToHost, st));
             B200_CHECK(cudaStreamSynchronize(st));
-            if (nj == 0) break;
-            if (ctl_zero(ctx, CTL_WORK)) return -1;
-            const int grid = std::max(1, std::min((int)((nj + 63) / 64), ctx->n_sms * dp_per_sm));
-            if (launch_ext2_dp(XP, round, grid, st)) return -1;
-            ++launches;
-            threads = (int)nj;
+            if (nj[0] + nj[1] + nj[2] == 0) break;
+            for (int b = 0; b < 3; ++b) {
+                if (nj[b] == 0) continue;
+                const int cols = (b == 2 ? ctx->max_len : XP.bin_max[b]) + 2 + 8;
+                const int dp_per_sm = std::max(1, std::min(ctx->ext_bps > 0 ? ctx->ext_bps : 16, (int)((200 * 1024) / ((size_t)cols * 64 * 4))));
+                const int grid = std::max(1, std::min((int)((nj[b] + 63) / 64), ctx->n_sms * dp_per_sm));
+                if (launch_ext2_dp(XP, round, b, cols, grid, st)) return -1;
+                ++launches;
+                ctx->stats[CNT_BIN0 + b] += nj[b];
+            }
+            threads = (int)(nj[0] + nj[1] + nj[2]);
         }
         if (ctl_zero(ctx, CTL_WORK)) return -1;
         if (launch_ext2_finish(XP, fin_blocks, st)) return -1;

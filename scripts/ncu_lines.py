@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Per-CUDA-source-line instruction / sample shares for one kernel of an .ncu-rep, by joining the SASS page of the
 report with the line table of the cubin inside the built .so (same build!).
-usage: scripts/ncu_lines.py <report.ncu-rep> <kernel-name-regex> <mangled-function-substring> <cubin stem> [top]"""
+usage: scripts/ncu_lines.py <report.ncu-rep> <kernel-name-regex> <mangled-function-substring> <cubin stem> [top] [section]
+(section: which of the matching launches, 0-based)"""
 import collections, csv, os, re, subprocess, sys, tempfile
 
 rep, kre, fsub, stem = sys.argv[1:5]
@@ -33,7 +34,10 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-n
 rows = list(csv.reader(out.split("\n")))
 h = rows[1]
 I = h.index
-data = [r for r in rows[2:] if len(r) > 10]
+sect = int(sys.argv[6]) if len(sys.argv) > 6 else 0
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"] + [len(rows)]
+print(f"{len(starts) - 1} sections in the report page; using section {sect}")
+data = [r for r in rows[starts[sect] + 2: starts[sect + 1]] if len(r) > 10]
 if len(data) != len(seq):
     print(f"warning: {len(data)} SASS rows in report vs {len(seq)} in cubin (different build?)")
 agg = collections.defaultdict(lambda: [0, 0, 0])
