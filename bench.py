@@ -157,7 +157,7 @@ def main():
         if rank != 0:
             return
         from bwa_mem_gpu_b200 import lib as L
-        n_sample = a.cpu_sample or min(a.reads, max(20000, 4000 * cores))
+        n_sample = a.cpu_sample or min(a.reads, max(20000, 150000 * cores))
         contigs, seqs, off, _ = build_inputs(a, 0)
         hidx = L.HostIndex(contigs)          # host-side index construction only (no device work)
         vals = []
@@ -300,7 +300,7 @@ def main():
             "smem_lookups_per_sec": cnt["extend"] / (smem_ms * 1e-3) if smem_ms > 0 else None,
         }
         if not a.no_cpu_baseline:
-            n_sample = a.cpu_sample or min(a.reads, max(20000, 4000 * cores))
+            n_sample = a.cpu_sample or min(a.reads, max(20000, 150000 * cores))
             cb = cpu_reference(a, hidx, seqs, off, n_sample, cores)
             if cb is not None:
                 out["cpu_baseline"] = cb
