@@ -33,7 +33,7 @@ struct ChainRec {        // one kept chain after mem_chain_flt
 
 enum {                   // work / traffic counters (u64 each)
     CNT_EXTEND = 0, CNT_TWO_BLOCK, CNT_SA, CNT_LF, CNT_KSW, CNT_CELLS, CNT_SEEDS, CNT_CHAINS, CNT_REGS,
-    CNT_LAUNCH, CNT_SEEDSW, CNT_SEEDSW_CELLS, CNT_BIN0, CNT_BIN1, CNT_BIN2, CNT_N = 16
+    CNT_LAUNCH, CNT_SEEDSW, CNT_SEEDSW_CELLS, CNT_BIN0, CNT_BIN1, CNT_BIN2, CNT_DP8, CNT_N = 16
 };
 
 // ---- stage parameter blocks (passed by value to the kernels) ---------------------------------
@@ -162,6 +162,8 @@ int launch_chain(const ChainParams &p, int emit, cudaStream_t st);
 int launch_extend(const ExtParams &p, int grid, int block, cudaStream_t st);
 int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t st);
 int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st);
+size_t ext2_dp8_smem(int n_groups);
+int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, cudaStream_t st);
 int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,

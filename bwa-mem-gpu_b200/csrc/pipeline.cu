@@ -238,6 +238,8 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     bool fast_ext = (i64)ctx->max_len * opt->a < 16384 && (size_t)he_cols * 64 * 4 <= 96 * 1024;
     for (int k = 0; k < 25; ++k) if (opt->mat[k] > opt->a) fast_ext = false;     // bound above assumes max(mat) == a
     if (ctx->ext_path == 1) fast_ext = false;
+    // byte-score DP kernel: every H / E / F of a read is at most l_query * a (ksw.c:399: h0 + qlen * max(mat))
+    const bool dp8 = fast_ext && ctx->ext_path != 2 && (i64)ctx->max_len * opt->a <= 255 && opt->a <= 63;
     i32 *reg_n_ptr = ctx->d_reg_n.as<i32>();
     i64 *reg_off_ptr = ctx->d_reg_off.as<i64>();
     if (fast_ext) {
@@ -277,7 +279,18 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
             if (nj[0] + nj[1] + nj[2] == 0) break;
             for (int b = 0; b < 3; ++b) {
                 if (nj[b] == 0) continue;
-                const int cols = (b == 2 ? ctx->max_len : XP.bin_max[b]) + 2 + 8;
+                const int flank = b == 2 ? ctx->max_len : XP.bin_max[b];
+                if (dp8) {                                                   // byte scores, two columns per instruction (ext3.cu)
+                    const int n_groups = (flank >> 3) + 1;                   // columns 0 .. flank
+                    const int dp_per_sm = std::max(1, std::min(ctx->ext_bps > 0 ? ctx->ext_bps : 16, (int)((200 * 1024) / (ext2_dp8_smem(n_groups) + 1024))));
+                    const int grid = std::max(1, std::min((int)((nj[b] + 63) / 64), ctx->n_sms * dp_per_sm));
+                    if (launch_ext2_dp8(XP, round, b, n_groups, grid, st)) return -1;
+                    ++launches;
+                    ctx->stats[CNT_BIN0 + b] += nj[b];
+                    ctx->stats[CNT_DP8] += nj[b];
+                    continue;
+                }
+                const int cols = flank + 2 + 8;
                 const int dp_per_sm = std::max(1, std::min(ctx->ext_bps > 0 ? ctx->ext_bps : 16, (int)((200 * 1024) / ((size_t)cols * 64 * 4))));
                 const int grid = std::max(1, std::min((int)((nj[b] + 63) / 64), ctx->n_sms * dp_per_sm));
                 if (launch_ext2_dp(XP, round, b, cols, grid, st)) return -1;

@@ -295,5 +295,5 @@ class Context:
         out = np.zeros(16, dtype=np.uint64)
         self.lib.b200_batch_counters(self.h, _p(out, C.c_uint64))
         names = ["extend", "two_block", "sa", "lf_steps", "ksw", "cells", "seeds", "chains", "regs", "launches",
-                 "seed_sw", "seed_sw_cells", "ext_bin0", "ext_bin1", "ext_bin2"]
+                 "seed_sw", "seed_sw_cells", "ext_bin0", "ext_bin1", "ext_bin2", "dp8_jobs"]
         return {k: int(out[i]) for i, k in enumerate(names)}

@@ -260,6 +260,37 @@ inline int __vimax3_s32_relu(int a, int b, int c) { return std::max(0, std::max(
 inline int __vimax_s32_relu(int a, int b) { return std::max(0, std::max(a, b)); }
 inline int __viaddmax_s32(int a, int b, int c) { return std::max(a + b, c); }
 inline int __viaddmax_s32_relu(int a, int b, int c) { return std::max(0, std::max(a + b, c)); }
+// 16x2 DPX / video SIMD (per-half, wrap-around add like the hardware)
+namespace emu {
+inline int16_t lo16(unsigned x) { return (int16_t)(x & 0xffffu); }
+inline int16_t hi16(unsigned x) { return (int16_t)(x >> 16); }
+inline unsigned pk16(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
+inline int16_t wrap16(int v) { return (int16_t)(uint16_t)(unsigned)v; }
+}
+inline unsigned __vadd2(unsigned a, unsigned b) { return emu::pk16(emu::lo16(a) + emu::lo16(b), emu::hi16(a) + emu::hi16(b)); }
+inline unsigned __viaddmax_s16x2(unsigned a, unsigned b, unsigned c)
+{ return emu::pk16(std::max<int>(emu::wrap16(emu::lo16(a) + emu::lo16(b)), emu::lo16(c)), std::max<int>(emu::wrap16(emu::hi16(a) + emu::hi16(b)), emu::hi16(c))); }
+inline unsigned __viaddmin_s16x2(unsigned a, unsigned b, unsigned c)
+{ return emu::pk16(std::min<int>(emu::wrap16(emu::lo16(a) + emu::lo16(b)), emu::lo16(c)), std::min<int>(emu::wrap16(emu::hi16(a) + emu::hi16(b)), emu::hi16(c))); }
+inline unsigned __viaddmax_s16x2_relu(unsigned a, unsigned b, unsigned c)
+{ return emu::pk16(std::max<int>(0, std::max<int>(emu::wrap16(emu::lo16(a) + emu::lo16(b)), emu::lo16(c))), std::max<int>(0, std::max<int>(emu::wrap16(emu::hi16(a) + emu::hi16(b)), emu::hi16(c)))); }
+inline unsigned __vimax3_s16x2(unsigned a, unsigned b, unsigned c)
+{ return emu::pk16(std::max<int>(emu::lo16(a), std::max<int>(emu::lo16(b), emu::lo16(c))), std::max<int>(emu::hi16(a), std::max<int>(emu::hi16(b), emu::hi16(c)))); }
+inline unsigned __vmaxu2(unsigned a, unsigned b)
+{ return emu::pk16(std::max<unsigned>(a & 0xffffu, b & 0xffffu), std::max<unsigned>(a >> 16, b >> 16)); }
+// prmt.b32 default mode: selector nibble bit 3 = replicate the sign bit of the selected byte
+inline unsigned emu_prmt(unsigned a, unsigned b, unsigned s)
+{
+    const uint64_t v = (uint64_t)b << 32 | a;
+    unsigned r = 0;
+    for (int k = 0; k < 4; ++k) {
+        const unsigned n = (s >> (4 * k)) & 0xf;
+        unsigned byte = (unsigned)(v >> (8 * (n & 7))) & 0xff;
+        if (n & 8) byte = (byte & 0x80) ? 0xff : 0x00;
+        r |= byte << (8 * k);
+    }
+    return r;
+}
 inline int __viaddmin_s32(int a, int b, int c) { return std::min(a + b, c); }
 
 // ------------------------------------------------------------------ atomics
