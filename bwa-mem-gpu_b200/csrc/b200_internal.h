@@ -155,6 +155,8 @@ int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cuda
 size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
+int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st);
+size_t kmer_tab_entries(int kmax);
 int launch_seed_count(const SeedParams &p, cudaStream_t st);
 int launch_seed_fill(const SeedParams &p, cudaStream_t st);
 int launch_sa_locate(const SeedParams &p, cudaStream_t st);

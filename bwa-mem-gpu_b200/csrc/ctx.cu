@@ -53,6 +53,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
     else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
+    else if (!strcmp(key, "kmer_k")) ctx->kmer_k = (int)value;               // before the index upload
     else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
     else if (!strcmp(key, "ext_bps")) ctx->ext_bps = (int)value;
@@ -66,7 +67,7 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
-    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
                        &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,
@@ -121,6 +122,14 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
         if (ctx->d_occ32.ensure((size_t)n_blk * 32)) return -1;
         if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
         ix.occ32 = ctx->d_occ32.as<uint4>();
+        ix.kmer_tab = nullptr; ix.kmer_k = 0;
+        if (ctx->kmer_k > 0) {                                       // k-mer interval table (kmer_tab.cu)
+            const bool wide = seq_len >= 0xfffffff0ull;      // same rule as the seeding kernel template (pipeline.cu)
+            const int kk = ctx->kmer_k > 12 ? 12 : ctx->kmer_k;
+            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide ? 32 : 16))) return -1;
+            if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
+            ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;
+        }
 #ifndef B200_EMU
         {   // optional (tunable l2_persist=1, before the upload): persisting-L2 window over the seeding index.
             // Measured on B200: seeding -2 %, but the other stages lose L2 and the batch gets slower, so it is off.

@@ -27,6 +27,10 @@ struct DevIndex {
     // re-laid Occ index for the seeding kernel (built once on the device, see occ32.cuh)
     const uint4 *occ32;      // 2 x uint4 per 64-row block
     u64 sb_cnt[8][4];        // counts at the start of each 2^32-row superblock (rows < 2^35)
+    // bi-intervals of all strings of length 1..kmer_k (see kmer_tab.cuh); 0 = no table
+    const uint4 *kmer_tab;   // entry of string W (length k): kmer_tab[(kmer_off[k] + W) * quads], quads = 1 (u32) / 2 (u64)
+    int kmer_k;
+    u32 kmer_off[14];
 };
 
 struct Intv { u64 x0, x1, x2, info; };   // == bwtintv_t (bwt.h:62)

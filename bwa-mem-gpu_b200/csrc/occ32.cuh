@@ -75,6 +75,17 @@ __device__ __forceinline__ void occ32_issue(const DevIndex &ix, PT x0, PT x1, PT
     occ32_load2(ix.occ32, (u64)kp >> 6, (u64)lp >> 6, Bk, Bl);
 }
 
+// 1 when the reference's bwt_2occ4 (bwt.c:189-220) would have read two 128-row blocks for this extension
+template <class PT>
+__device__ __forceinline__ int occ32_two_ref(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back)
+{
+    const PT primary = (PT)ix.primary;
+    const PT a = is_back ? x0 : x1;
+    const PT k = a - 1, l = k + x2;
+    const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary);
+    return (int)(((u64)kp >> 7) != ((u64)lp >> 7));
+}
+
 template <class PT>
 __device__ __forceinline__ void occ32_finish(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, int c,
                                              const Occ32Blk &Bk, const Occ32Blk &Bl, PT &n0, PT &n1, PT &n2, int &two_ref)

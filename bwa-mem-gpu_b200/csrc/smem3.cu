@@ -111,6 +111,14 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     int i = -1, sx = 0, nfw = 0, base = 0, nprev = 0, ncurr = 0, j = 0, last_start = 0, ret = 0;
     PT min_intv = 1, k0 = 0, k1 = 0, kk2 = 0, last_x2 = 0;              // (k0,k1,kk2): the interval to extend next
     u32 pend = 0;
+    // k-mer table (kmer_tab.cu): strings of up to KT bases are answered by one table load instead of two index sectors.
+    // wf / flen: code and length of the current forward chain; wst: its first KT bases, left-aligned; wb: the KT bases
+    // that start at the backward sweep's position i + 1, left-aligned (first base most significant everywhere).
+    const int KT = ix.kmer_k;
+    const uint4 *const ktab = ix.kmer_tab;
+    u32 wf = 0, wst = 0, wb = 0;
+    int flen = 0;
+    bool ptab = false;
 
 #define S3_QGET(pos) ((Q[((pos) >> 3) * S3_THREADS] >> (((pos) & 7) << 2)) & 7u)
 #define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
@@ -139,12 +147,13 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
 #define S3_START_BWD()                                                                                  \
     do {                                                                                                \
         ret = i; base = nfw - 1; nprev = nfw; ncurr = 0; j = 0; i = sx - 1; last_start = 0x7fffffff;    \
-        st = S3_BWD;                                                                                    \
+        st = S3_BWD; wb = wst;                                                                          \
         S3_LOAD_ENTRY(0);                                                                               \
     } while (0)
 #define S3_SET_INTV(b0)                                                                                 \
     do {                                                                                                \
         k0 = (PT)ix.L2[b0] + 1; kk2 = (PT)(ix.L2[(b0) + 1] - ix.L2[b0]); k1 = (PT)ix.L2[3 - (b0)] + 1;  \
+        wf = (u32)(b0); flen = 1; wst = KT > 0 ? (u32)(b0) << (2 * KT - 2) : 0u;                        \
     } while (0)
 
     Occ32Blk Bk, Bl;                                                        // sectors of the pending extension
@@ -154,7 +163,11 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
       if (pending) {
         // ------------------------------------------------------------ the single gather site: consume the sectors
         PT n0, n1, n2; int two;
-        occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
+        if (ptab) {                                                         // table entry: the child's bi-interval itself
+            if (sizeof(PT) == 4) { n0 = (PT)Bk.cnt.x; n1 = (PT)Bk.cnt.y; n2 = (PT)Bk.cnt.z; }
+            else { n0 = (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x); n1 = (PT)((u64)Bk.cnt.w << 32 | Bk.cnt.z); n2 = (PT)((u64)Bk.pl.y << 32 | Bk.pl.x); }
+            two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
+        } else occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
         ++n_ext; n_two += two;
         // ------------------------------------------------------------ consume
         bool adv = false;                                                   // forward phases: continue with the child
@@ -186,11 +199,18 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
             if (++j == nprev) {                                             // bwt.c:343-344
                 if (ncurr == 0) {
                     if (pass == 1) { x = ret; restart = S3_FWD; } else { ++k2; st = S3_TASK; i = -1; }
-                } else { nprev = ncurr; ncurr = 0; j = 0; --i; }
+                } else {                                                    // next backward position: base c joins the window
+                    nprev = ncurr; ncurr = 0; j = 0; --i;
+                    if (KT > 0) wb = ((u32)c << (2 * KT - 2)) | (wb >> 2);
+                }
             }
             if (restart < 0 && st == S3_BWD) S3_LOAD_ENTRY(j);
         }
-        if (adv) { k0 = n0; k1 = n1; kk2 = n2; ++i; }
+        if (adv) {
+            k0 = n0; k1 = n1; kk2 = n2; ++i;
+            wf = (wf << 2) | (u32)(3 - c); ++flen;                          // forward phases extend with base 3 - c
+            if (flen <= KT) wst = wf << (2 * (KT - flen));
+        }
         if (restart >= 0) {                                                 // inline restart of a forward chain at x
             u32 b0 = 4;
             if (x < len) b0 = S3_QGET(x);
@@ -290,7 +310,16 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
         if (r < 0) break;                                                   // no reads left for this lane
         is_back = st == S3_BWD;
         c = is_back ? (int)b : 3 - (int)b;
-        occ32_issue<PT>(ix, k0, k1, kk2, is_back, Bk, Bl);                  // requests in flight across the back-edge
+        {
+            const int cur = is_back ? (int)pend - (i + 1) : flen;           // length of the string whose interval is extended
+            ptab = cur < KT;
+            if (ptab) {                                                     // child = string of cur + 1 <= KT bases: table
+                const u32 wn = is_back ? (b << (2 * cur)) | (cur ? wb >> (2 * (KT - cur)) : 0u) : (wf << 2) | b;
+                const uint4 *e = ktab + (size_t)(ix.kmer_off[cur + 1] + wn) * EQ;
+                Bk.cnt = __ldg(e);
+                if (EQ == 2) Bk.pl = __ldg(e + 1);
+            } else occ32_issue<PT>(ix, k0, k1, kk2, is_back, Bk, Bl);       // requests in flight across the back-edge
+        }
         pending = true;
     }
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
