@@ -52,7 +52,6 @@ struct SmemParams {
     unsigned *retry_n; i32 *retry_ids; int use_retry;
     // smem3.cu: 4-bit packed reads (pk_stride words per read) and the per-thread spill area (spill_cap entries)
     const u32 *pk; int pk_stride; int spill_cap;
-    int use_uq;                                  // unique-run shortcut (needs ix.sa_full* and ix.isa_full*)
 };
 
 struct SeedParams {
@@ -156,7 +155,6 @@ int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cuda
 size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
-int launch_build_isa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st);
 int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st);
 size_t kmer_tab_entries(int kmax);
 int launch_seed_count(const SeedParams &p, cudaStream_t st);

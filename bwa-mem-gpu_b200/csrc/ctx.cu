@@ -54,7 +54,6 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
     else if (!strcmp(key, "kmer_k")) ctx->kmer_k = (int)value;               // before the index upload
-    else if (!strcmp(key, "smem_uq")) ctx->smem_uq = (int)value;             // 0 before the index upload: no inverse SA; 0 later: shortcut off
     else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
     else if (!strcmp(key, "ext_bps")) ctx->ext_bps = (int)value;
@@ -68,7 +67,7 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
-    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_isa, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
                        &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,
@@ -157,12 +156,6 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
         if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
         if (launch_build_full_sa(ix, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
         if (narrow) ix.sa_full32 = ctx->d_sa_full.as<u32>(); else ix.sa_full64 = ctx->d_sa_full.as<u64>();
-        ix.isa_full32 = nullptr; ix.isa_full64 = nullptr;
-        if (ctx->smem_uq) {                                          // inverse SA for the unique-run shortcut of the seeding kernel
-            if (ctx->d_isa.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
-            if (launch_build_isa(ix, narrow ? ctx->d_isa.as<u32>() : nullptr, narrow ? nullptr : ctx->d_isa.as<u64>(), ctx->st)) return -1;
-            if (narrow) ix.isa_full32 = ctx->d_isa.as<u32>(); else ix.isa_full64 = ctx->d_isa.as<u64>();
-        }
     }
     B200_CHECK(cudaStreamSynchronize(ctx->st));
     ctx->has_index = true;

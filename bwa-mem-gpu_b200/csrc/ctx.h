@@ -26,7 +26,7 @@ struct b200_ctx {
     cudaStream_t st = nullptr;
     bool has_index = false;
     DevIndex ix;
-    DevBuf d_occ32, d_kmer, d_isa, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_jobs2, d_jobs3, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
+    DevBuf d_occ32, d_kmer, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_jobs2, d_jobs3, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
     const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
     bool stub_pac = false;             // index uploaded by a bwt-only primitive (no bns / pac yet)
 
@@ -44,7 +44,6 @@ struct b200_ctx {
     size_t l2_setaside = 0, l2_window = 0;
     int ext_bin0 = 0, ext_bin1 = 0;            // > 0: flank-length limits of extension bins 0 / 1 (default 32 / 64)
     int ext_bps = 0;                           // > 0: cap on resident blocks per SM of the extension DP kernel
-    int smem_uq = 1;                           // unique-run shortcut of the seeding kernel (needs the full SA + inverse SA)
     int kmer_k = 10;                           // longest string in the k-mer interval table (0 = none); set before the index upload
     int smem_bps = 0;                          // > 0: cap on resident blocks per SM of the seeding kernel (experiments)
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel

@@ -18,8 +18,6 @@ struct DevIndex {
     int sa_intv;
     const u32 *sa_full32;    // optional full SA (seq_len+1 entries) when seq_len < 2^32
     const u64 *sa_full64;    // optional full SA otherwise
-    const u32 *isa_full32;   // optional inverse SA (text position -> row), same widths; enables the unique-run shortcut
-    const u64 *isa_full64;
     const u8 *pac;           // 2-bit packed forward reference
     i64 l_pac;
     int n_seqs;

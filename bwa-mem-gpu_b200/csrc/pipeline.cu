@@ -119,7 +119,6 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         const int spill_cap = std::max(1, ctx->max_len + 1 - lcap3);
         if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;
         SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
-        SP.use_uq = ctx->smem_uq && (ctx->ix.isa_full32 || ctx->ix.isa_full64) && (ctx->ix.sa_full32 || ctx->ix.sa_full64);
         SP.lists = (Intv *)ctx->d_spill.p;
         if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, st)) return -1;
         ++launches;

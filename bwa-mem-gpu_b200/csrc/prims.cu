@@ -98,23 +98,6 @@ int launch_sa_batch(const DevIndex &ix, i64 n, const u64 *k, u64 *out, int use_f
     B200_CHECK(cudaGetLastError());
     return 0;
 }
-// inverse of the full SA: isa[SA[k]] = k for rows 1..seq_len (row 0 is the sentinel suffix)
-__global__ void build_isa_kernel(DevIndex ix, u32 *out32, u64 *out64)
-{
-    u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x + 1;
-    const u64 stride = (u64)gridDim.x * blockDim.x;
-    for (; k <= ix.seq_len; k += stride) {
-        if (out32) out32[ix.sa_full32[k]] = (u32)k; else out64[ix.sa_full64[k]] = k;
-    }
-}
-int launch_build_isa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st)
-{
-    u64 n = ix.seq_len + 1;
-    int grid = (int)((n + 255) / 256 < 148 * 32 ? (n + 255) / 256 : 148 * 32);
-    B200_LAUNCH(build_isa_kernel, grid, 256, 0, st, ix, out32, out64);
-    B200_CHECK(cudaGetLastError());
-    return 0;
-}
 int launch_build_full_sa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st)
 {
     u64 n = ix.seq_len + 1;

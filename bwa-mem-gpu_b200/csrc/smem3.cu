@@ -118,18 +118,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     const uint4 *const ktab = ix.kmer_tab;
     u32 wf = 0, wst = 0, wb = 0;
     int flen = 0;
-    int pkind = 0;                                                      // what the pending load is: 0 sectors, 1 table, 2 SA, 3 pac word, 4 inverse SA
-    // Unique-run shortcut.  While an interval has size 1 the string occurs once in the (forward + reverse-complement)
-    // text T, at q = SA[x0]; whether one more base extends it is decided by T itself, and the interval after m such
-    // steps differs only in the coordinate that LF-maps: x1 = ISA[|T| - q - len] going forward, x0 = ISA[q - m] going
-    // backward (rows of a single suffix never split).  So a run of size-1 steps -- most of a forward sweep and of
-    // the backward sweep of its longest entry -- costs one SA load, one pac word per 16 bases and one ISA load.
-    // uq: 0 off, 1 SA requested, 2 comparing, 3 ISA requested; uq_q = q; tpos = next text position to compare.
-    const bool UQ = P.use_uq != 0;
-    int uq = 0, uq_m = 0;
-    bool uq_done = false;
-    i64 uq_q = 0, tpos = 0;
-    const i64 tlen2 = (i64)ix.seq_len;
+    bool ptab = false;
 
 #define S3_QGET(pos) ((Q[((pos) >> 3) * S3_THREADS] >> (((pos) & 7) << 2)) & 7u)
 #define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
@@ -173,45 +162,8 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     for (;;) {
       if (pending) {
         // ------------------------------------------------------------ the single gather site: consume the sectors
-        if (pkind >= 2) {
-            // -------------------------------------------------------- unique run: SA value, pac word or ISA value arrived
-            const bool bw = st == S3_BWD;
-            if (pkind == 2) {                                               // q = SA[x0]
-                uq_q = sizeof(PT) == 4 ? (i64)Bk.cnt.x : (i64)((u64)Bk.cnt.y << 32 | Bk.cnt.x);
-                tpos = bw ? uq_q - 1 : uq_q + flen;
-                uq_m = 0; uq = 2;
-                if (tpos < 0 || tpos >= tlen2) { uq = 0; uq_done = true; }
-            } else if (pkind == 3) {                                        // compare against the 16 bases of this pac word
-                const u32 w = Bk.cnt.x;
-                const i64 tag = (i64)Bk.cnt.y;
-                bool more = false;
-                for (;;) {
-                    if ((unsigned)i >= (unsigned)len || tpos < 0 || tpos >= tlen2) break;
-                    const u32 bq = S3_QGET(i);
-                    if (bq > 3) break;
-                    const i64 f = tpos >= ix.l_pac ? (ix.l_pac << 1) - 1 - tpos : tpos;
-                    if ((f >> 4) != tag) { more = true; break; }
-                    const int fi = (int)f;
-                    u32 tb = (w >> ((((fi >> 2) & 3) << 3) + ((~fi & 3) << 1))) & 3u;
-                    if (tpos >= ix.l_pac) tb = 3u - tb;
-                    if (tb != bq) break;
-                    ++uq_m;
-                    if (bw) { --i; --tpos; if (KT > 0) wb = (bq << (2 * KT - 2)) | (wb >> 2); }
-                    else { ++i; ++tpos; wf = (wf << 2) | bq; ++flen; if (flen <= KT) wst = wf << (2 * (KT - flen)); }
-                }
-                if (!more) {
-                    if (uq_m > 0) uq = 3; else { uq = 0; uq_done = true; }
-                }
-            } else {                                                        // the coordinate that moved
-                const PT v = sizeof(PT) == 4 ? (PT)Bk.cnt.x : (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x);
-                if (bw) k0 = v; else k1 = v;
-                n_ext += (u64)uq_m;
-                uq = 0; uq_done = true;
-            }
-        } else {
         PT n0, n1, n2; int two;
-        uq_done = false;
-        if (pkind == 1) {                                                         // table entry: the child's bi-interval itself
+        if (ptab) {                                                         // table entry: the child's bi-interval itself
             if (sizeof(PT) == 4) { n0 = (PT)Bk.cnt.x; n1 = (PT)Bk.cnt.y; n2 = (PT)Bk.cnt.z; }
             else { n0 = (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x); n1 = (PT)((u64)Bk.cnt.w << 32 | Bk.cnt.z); n2 = (PT)((u64)Bk.pl.y << 32 | Bk.pl.x); }
             two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
@@ -268,12 +220,10 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                 if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; }
             } else { st = S3_TASK; i = -1; }                                // N or end of read: slow path decides
         }
-        }
       }
         // ------------------------------------------------------------ request: base at position i, or slow path
         u32 b = 4;
         if ((unsigned)i < (unsigned)len) b = S3_QGET(i);
-        if (uq) b = 0;                                                      // a unique run is in flight: no slow path now
         while (b > 3) {
             if (st == S3_FWD) {                                             // read end or N: bwt.c:316-318, 321
                 if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; continue; }
@@ -359,29 +309,11 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
         }
         if (r < 0) break;                                                   // no reads left for this lane
         is_back = st == S3_BWD;
-        if (UQ && uq == 0 && !uq_done && kk2 == 1 && (is_back ? nprev == 1 : (st == S3_FWD && min_intv == 1))) uq = 1;
-        if (uq) {                                                           // unique run: SA, pac word or inverse SA
-            pkind = uq + 1;
-            if (uq == 1) {
-                if (sizeof(PT) == 4) Bk.cnt.x = __ldg(ix.sa_full32 + k0);
-                else { const u64 v = __ldg(ix.sa_full64 + k0); Bk.cnt.x = (u32)v; Bk.cnt.y = (u32)(v >> 32); }
-            } else if (uq == 2) {
-                const i64 f = tpos >= ix.l_pac ? (ix.l_pac << 1) - 1 - tpos : tpos;
-                Bk.cnt.x = __ldg((const u32 *)ix.pac + (f >> 4));
-                Bk.cnt.y = (u32)(f >> 4);
-            } else {
-                const i64 ip = is_back ? uq_q - uq_m : tlen2 - uq_q - flen;
-                if (sizeof(PT) == 4) Bk.cnt.x = __ldg(ix.isa_full32 + ip);
-                else { const u64 v = __ldg(ix.isa_full64 + ip); Bk.cnt.x = (u32)v; Bk.cnt.y = (u32)(v >> 32); }
-            }
-            pending = true;
-            continue;
-        }
         c = is_back ? (int)b : 3 - (int)b;
         {
             const int cur = is_back ? (int)pend - (i + 1) : flen;           // length of the string whose interval is extended
-            pkind = cur < KT ? 1 : 0;
-            if (pkind) {                                                     // child = string of cur + 1 <= KT bases: table
+            ptab = cur < KT;
+            if (ptab) {                                                     // child = string of cur + 1 <= KT bases: table
                 const u32 wn = is_back ? (b << (2 * cur)) | (cur ? wb >> (2 * (KT - cur)) : 0u) : (wf << 2) | b;
                 const uint4 *e = ktab + (size_t)(ix.kmer_off[cur + 1] + wn) * EQ;
                 Bk.cnt = __ldg(e);
