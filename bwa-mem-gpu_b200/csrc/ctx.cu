@@ -53,6 +53,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
     else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
+    else if (!strcmp(key, "force_wide")) ctx->force_wide = (int)value;       // before the index upload
     else if (!strcmp(key, "kmer_k")) ctx->kmer_k = (int)value;               // before the index upload
     else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
@@ -124,7 +125,7 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
         ix.occ32 = ctx->d_occ32.as<uint4>();
         ix.kmer_tab = nullptr; ix.kmer_k = 0;
         if (ctx->kmer_k > 0) {                                       // k-mer interval table (kmer_tab.cu)
-            const bool wide = seq_len >= 0xfffffff0ull;      // same rule as the seeding kernel template (pipeline.cu)
+            const bool wide = seq_len >= 0xfffffff0ull || ctx->force_wide;      // same rule as the seeding kernel template (pipeline.cu)
             const int kk = ctx->kmer_k > 12 ? 12 : ctx->kmer_k;
             if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide ? 32 : 16))) return -1;
             if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;

@@ -44,7 +44,8 @@ struct b200_ctx {
     size_t l2_setaside = 0, l2_window = 0;
     int ext_bin0 = 0, ext_bin1 = 0;            // > 0: flank-length limits of extension bins 0 / 1 (default 32 / 64)
     int ext_bps = 0;                           // > 0: cap on resident blocks per SM of the extension DP kernel
-    int kmer_k = 10;                           // longest string in the k-mer interval table (0 = none); set before the index upload
+    int force_wide = 0;                        // 1: run the 64-bit-position templates even when seq_len < 2^32 (tests); set before the index upload
+    int kmer_k = 9;                            // longest string in the k-mer interval table (0 = none); set before the index upload
     int smem_bps = 0;                          // > 0: cap on resident blocks per SM of the seeding kernel (experiments)
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
 

@@ -77,7 +77,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     tm.mark(st);
     // ---- K1 setup: which seeding kernel
     const int cap_intv = auto_cap_intv(ctx, opt);
-    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull;
+    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull || ctx->force_wide;
     const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
     int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 12;
     lcap3 = lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);

@@ -365,3 +365,28 @@ def test_align_long_reads(backend):
     r1, n1 = ctx.align(opt, seqs, off)
     assert np.array_equal(n0, n1)
     assert r0.tobytes() == r1.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("tune", [{"force_wide": 1}, {"force_wide": 1, "kmer_k": 0}, {"kmer_k": 0}, {"kmer_k": 6}, {"kmer_k": 12}])
+def test_seeding_variants(backend, tune):
+    """The 64-bit-position templates of the seeding kernel (used when the doubled text reaches 2^32 rows) forced on a
+    small genome, and k-mer interval tables of other depths: intervals and regions unchanged."""
+    from bwa_mem_gpu_b200 import lib as L
+    gname = "rep"
+    lib = cm.backend_lib(backend)
+    ctx = L.Context(0, lib)
+    for k, v in tune.items():
+        ctx.tune(k, v)
+    ctx.upload_host_index(cm.context(backend, gname)._host_index)
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 300, 20000), seed=57, indel=0.004, n_rate=0.002)
+    a = idx.collect_intv(opt, seqs, off)
+    b = ctx.collect_intv(opt, seqs, off)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
+    r1, n1 = ctx.align(opt, seqs, off)
+    assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
