@@ -276,8 +276,8 @@ def main():
                        "wall_ms_per_step": wall_ms_max, "index_build_s": t_index, "index_upload_s": t_upload,
                        "read_sim_s": t_reads},
             "e2e": {"value": world * a.reads / (e2e_ms_max * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(len(seqs) + off.nbytes),
-                    "d2h_bytes_per_step": int(tot * abi.ALNREG_DTYPE.itemsize + 4 * a.reads)},
+                    "h2d_bytes_per_step": world * int(len(seqs) + off.nbytes),          # all ranks (each copies its own block)
+                    "d2h_bytes_per_step": world * int(tot * abi.ALNREG_DTYPE.itemsize + 4 * a.reads)},
             "gpu_launches": int(cnt["launches"]) * a.steps,
             "clocks": clocks,
             "stage_ms": {k: float(v) / a.steps for k, v in zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], stage)},
@@ -288,7 +288,8 @@ def main():
                          "ms_per_launch": smem_ms / n_launch,
                          "note": "algorithmic bytes = 64 B x Occ blocks touched by bwt_extend (1 or 2 per call, "
                                  "SURVEY.md 8d) per launch (one chunk of 2^20 reads); the kernel itself reads one 32-B "
-                                 "sector per Occ block from its own index layout, so DRAM traffic is below that"},
+                                 "sector per Occ block from its own index layout and answers calls on strings of <= 9 bases from a "
+                                 "k-mer interval table, so DRAM traffic is below that"},
             "extension": {"gcups": cnt["cells"] / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None,
                           "cells": cnt["cells"], "ksw_calls": cnt["ksw"], "dpx_ops_per_cell": 5,
                           "dpx_peak_gcups": (mb["dpx_tops"] * 1e3 / 5) if mb and "dpx_tops" in mb else None,
