@@ -52,6 +52,9 @@ struct SmemParams {
     unsigned *retry_n; i32 *retry_ids; int use_retry;
     // smem3.cu: 4-bit packed reads (pk_stride words per read) and the per-thread spill area (spill_cap entries)
     const u32 *pk; int pk_stride; int spill_cap;
+    // third seeding pass (bwamem.c:167-182) in its own kernel: its intervals go to the END of the read's output slots
+    // (out3_n of them, growing downwards); the main kernel then skips the pass and merges them before its final sort
+    i32 *out3_n; int split_p3;
 };
 
 struct SeedParams {
@@ -154,6 +157,7 @@ int launch_smem_fast(const SmemParams &p, int grid, int wide, cudaStream_t st);
 int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st);
 size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st);
+int launch_smem_p3(const SmemParams &p, int n_sms, int wide, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
 int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st);
 size_t kmer_tab_entries(int kmax);

@@ -53,6 +53,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
     else if (!strcmp(key, "smem_path")) ctx->smem_path = (int)value;
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
+    else if (!strcmp(key, "split_p3")) ctx->split_p3 = (int)value;
     else if (!strcmp(key, "force_wide")) ctx->force_wide = (int)value;       // before the index upload
     else if (!strcmp(key, "kmer_k")) ctx->kmer_k = (int)value;               // before the index upload
     else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;

@@ -120,6 +120,13 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;
         SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
         SP.lists = (Intv *)ctx->d_spill.p;
+        if (ctx->split_p3 && opt->max_mem_intv > 0) {                        // pass 3 first: uniform forward-only lanes
+            SP.split_p3 = 1; SP.out3_n = ctx->d_retry.as<i32>();
+            SP.work_counter = ctl_u32(ctx, CTL_WORK2);
+            if (launch_smem_p3(SP, ctx->n_sms, wide ? 1 : 0, st)) return -1;
+            SP.work_counter = ctl_u32(ctx, CTL_WORK);
+            ++launches;
+        }
         if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, st)) return -1;
         ++launches;
     } else if (ctx->smem_path != 1) {

@@ -90,7 +90,7 @@ __global__ void pack4_kernel(u8 *seq, const i64 *off, int n_reads, u32 *pk, int 
     }
 }
 
-template <class PT, int LCAP>
+template <class PT, int LCAP, bool SPLIT>                                   // SPLIT: pass 3 ran in smem_p3_kernel
 __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(s3_raw);
@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                     if (n2 < min_intv) { S3_START_BWD(); adv = false; }
                 }
             }
-        } else if (st == S3_P3) {                                           // bwt.c:369-375
+        } else if (!SPLIT && st == S3_P3) {                                 // bwt.c:369-375
             if (n2 < max_mem_intv && i - x >= min_seed_len) {
                 if (n2 > 0) s3_emit(out, n_out, P.cap_out, n0, n1, n2, x, i + 1);   // bwamem.c:174
                 x = i + 1; restart = S3_P3;
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                 if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
                 if (pass == 1) x = ret; else ++k2;
                 st = S3_TASK; i = -1;
-            } else if (st == S3_P3) {                                       // bwt.c:366-378
+            } else if (!SPLIT && st == S3_P3) {                             // bwt.c:366-378
                 if (i >= len) { st = S3_FIN; i = -1; }
                 else { x = i + 1; st = S3_TASK; i = -1; }
             } else if (st == S3_TASK) {
@@ -251,8 +251,11 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                         sx = (s0 + e0) >> 1; min_intv = (PT)sz + 1; found = true;
                         break;
                     }
-                    if (!found) { pass = 3; x = 0; continue; }
-                } else {                                                    // bwamem.c:167-182
+                    if (!found) {
+                        if (SPLIT) { st = S3_FIN; continue; }
+                        pass = 3; x = 0; continue;
+                    }
+                } else if (!SPLIT) {                                        // bwamem.c:167-182
                     if (max_mem_intv == 0) { st = S3_FIN; continue; }
                     while (x < len && S3_QGET(x) > 3) ++x;
                     if (x >= len) { st = S3_FIN; continue; }
@@ -270,6 +273,18 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
             } else {                                                        // S3_FIN: finish this read, take the next
                 if (r >= 0) {
                     int n = n_out;
+                    if (SPLIT && len >= min_seed_len) {                // append the third pass's intervals (stored at the end)
+                        const int n3 = P.out3_n[r];
+                        if (n + n3 > P.cap_out) { atomicMax(P.overflow, n + n3); n = n > P.cap_out ? P.cap_out : n; }
+                        else {
+                            for (int a = 0; a < n3; ++a) {
+                                const uint4 *src = (const uint4 *)&out[P.cap_out - 1 - a];
+                                const uint4 v0 = src[0], v1 = src[1];
+                                ((uint4 *)&out[n + a])[0] = v0; ((uint4 *)&out[n + a])[1] = v1;
+                            }
+                            n += n3;
+                        }
+                    }
                     if (n > P.cap_out) { atomicMax(P.overflow, n); n = P.cap_out; }
                     for (int a = 1; a < n; ++a) {                           // sort by info (bwamem.c:184)
                         const uint4 v0 = ((uint4 *)&out[a])[0], v1 = ((uint4 *)&out[a])[1];
@@ -325,6 +340,114 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
 }
 
+// Third seeding pass on its own (bwamem.c:167-182 around bwt_seed_strategy1, bwt.c:358-379): forward-only sweeps that
+// restart right after every seed, so every lane runs the same short loop -- no lists, no backward phase.  One read per
+// lane (persistent), requests issued at the bottom of the loop and consumed at the top like in the main kernel.
+template <class PT>
+__global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
+{
+    B200_DYN_SMEM(p3_raw);
+    constexpr int EQ = Ent<PT>::kQuads;
+    u32 *Q = (u32 *)p3_raw + threadIdx.x;                                   // word w: Q[w * S3_THREADS]
+    const DevIndex &ix = P.ix;
+    const int min_seed_len = P.min_seed_len;
+    const PT max_mem_intv = (PT)P.max_mem_intv;
+    const int KT = ix.kmer_k;
+    const uint4 *const ktab = ix.kmer_tab;
+    u64 n_ext = 0, n_two = 0;
+    Intv *out = nullptr;
+    int len = 0, r = -1, n_out = 0, x = 0, i = 0, flen = 0, c = 0;
+    PT k0 = 0, k1 = 0, kk2 = 0;
+    u32 wf = 0;
+    Occ32Blk Bk, Bl;
+    bool pending = false, ptab = false;
+    for (;;) {
+        if (pending) {
+            PT n0, n1, n2; int two;
+            if (ptab) {
+                if (sizeof(PT) == 4) { n0 = (PT)Bk.cnt.x; n1 = (PT)Bk.cnt.y; n2 = (PT)Bk.cnt.z; }
+                else { n0 = (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x); n1 = (PT)((u64)Bk.cnt.w << 32 | Bk.cnt.z); n2 = (PT)((u64)Bk.pl.y << 32 | Bk.pl.x); }
+                two = occ32_two_ref<PT>(ix, k0, k1, kk2, 0);
+            } else occ32_finish<PT>(ix, k0, k1, kk2, 0, c, Bk, Bl, n0, n1, n2, two);
+            ++n_ext; n_two += two;
+            if (n2 < max_mem_intv && i - x >= min_seed_len) {               // bwt.c:369-373
+                if (n2 > 0) {                                               // bwamem.c:174
+                    if (n_out < P.cap_out) {
+                        uint4 *q = (uint4 *)&out[P.cap_out - 1 - n_out];
+                        __stcs(q, make_uint4((u32)n0, (u32)((u64)n0 >> 32), (u32)n1, (u32)((u64)n1 >> 32)));
+                        __stcs(q + 1, make_uint4((u32)n2, (u32)((u64)n2 >> 32), (u32)(i + 1), (u32)x));
+                    }
+                    ++n_out;
+                }
+                x = i + 1; flen = 0;                                        // next sweep starts after the seed
+            } else { k0 = n0; k1 = n1; kk2 = n2; wf = (wf << 2) | (u32)(3 - c); ++flen; ++i; }
+            pending = false;
+        }
+        // ---- next request: continue the sweep, start a new one, or take the next read
+        u32 b = 4;
+        for (;;) {
+            if (flen > 0) {                                                 // inside a sweep: base at i
+                if (i < len) { b = S3_QGET(i); if (b < 4) break; x = i + 1; flen = 0; continue; }   // N: bwt.c:376
+                x = len; flen = 0; continue;                                // read end: bwt.c:378
+            }
+            while (x < len && S3_QGET(x) > 3) ++x;                          // bwamem.c:169-181
+            if (r >= 0 && x < len) {
+                const int b0 = (int)S3_QGET(x);
+                k0 = (PT)ix.L2[b0] + 1; kk2 = (PT)(ix.L2[b0 + 1] - ix.L2[b0]); k1 = (PT)ix.L2[3 - b0] + 1;   // bwt_set_intv
+                wf = (u32)b0; flen = 1; i = x + 1;
+                continue;
+            }
+            if (r >= 0) {
+                if (n_out > P.cap_out) { atomicMax(P.overflow, n_out); n_out = P.cap_out; }
+                P.out3_n[r] = n_out;
+            }
+            const unsigned nr = atomicAdd(P.work_counter, 1u);
+            if (nr >= (unsigned)P.n_reads) { r = -1; break; }
+            r = (int)nr;
+            len = (int)(P.off[r + 1] - P.off[r]);
+            out = P.out + (size_t)r * P.cap_out;
+            n_out = 0; x = 0; flen = 0;
+            if (len < min_seed_len) { x = len; continue; }                  // bwamem.c:267: no seeding at all
+            const uint4 *src = (const uint4 *)(P.pk + (size_t)r * P.pk_stride);
+            const int nq = (len + 31) >> 5;
+            for (int w = 0; w < nq; ++w) {
+                const uint4 v = __ldcs(src + w);
+                Q[(4 * w) * S3_THREADS] = v.x; Q[(4 * w + 1) * S3_THREADS] = v.y;
+                Q[(4 * w + 2) * S3_THREADS] = v.z; Q[(4 * w + 3) * S3_THREADS] = v.w;
+            }
+        }
+        if (r < 0) break;
+        c = 3 - (int)b;
+        ptab = flen < KT;
+        if (ptab) {
+            const uint4 *e = ktab + (size_t)(ix.kmer_off[flen + 1] + ((wf << 2) | b)) * EQ;
+            Bk.cnt = __ldg(e);
+            if (EQ == 2) Bk.pl = __ldg(e + 1);
+        } else occ32_issue<PT>(ix, k0, k1, kk2, 0, Bk, Bl);
+        pending = true;
+    }
+    if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
+}
+
+int launch_smem_p3(const SmemParams &p, int n_sms, int wide, cudaStream_t st)
+{
+    const size_t smem = (size_t)p.pk_stride * 4 * S3_THREADS;
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute(smem_p3_kernel<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute(smem_p3_kernel<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    int occ = 0;                                                            // resident blocks per SM (registers + shared memory)
+    if (wide) B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smem_p3_kernel<u64>, S3_THREADS, smem));
+    else B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smem_p3_kernel<u32>, S3_THREADS, smem));
+    if (occ > 0) per_sm = std::min(per_sm, occ);
+#endif
+    const int grid = std::max(1, std::min((p.n_reads + S3_THREADS - 1) / S3_THREADS, n_sms * per_sm));
+    if (wide) B200_LAUNCH(smem_p3_kernel<u64>, grid, S3_THREADS, smem, st, p);
+    else B200_LAUNCH(smem_p3_kernel<u32>, grid, S3_THREADS, smem, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
 int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st)
 {
     if (n_reads <= 0) return 0;
@@ -338,15 +461,21 @@ size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)
     return (size_t)lcap * (wide ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
 }
 
+template <class PT, int LCAP, bool SPLIT>
+static int launch_fast3_ts(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
+{
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute(smem_fast3_kernel<PT, LCAP, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+#endif
+    B200_LAUNCH((smem_fast3_kernel<PT, LCAP, SPLIT>), grid, S3_THREADS, smem, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
 template <class PT, int LCAP>
 static int launch_fast3_t(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
 {
-#ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute(smem_fast3_kernel<PT, LCAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-#endif
-    B200_LAUNCH((smem_fast3_kernel<PT, LCAP>), grid, S3_THREADS, smem, st, p);
-    B200_CHECK(cudaGetLastError());
-    return 0;
+    return p.split_p3 ? launch_fast3_ts<PT, LCAP, true>(p, grid, smem, st) : launch_fast3_ts<PT, LCAP, false>(p, grid, smem, st);
 }
 
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st)
