@@ -44,11 +44,20 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables (b200_ctx_tune)")
-    return ap.parse_args()
+    ap.add_argument("--index", default="auto", choices=["auto", "host", "device"],
+                    help="index construction: host SA-IS builder or the device builder (b200_index_build_device); auto = device")
+    ap.add_argument("--human", action="store_true",
+                    help="BASELINE.json configs[3] reference: 24 contigs totalling 3.1 Gbp (device-built index; 64-bit positions)")
+    ap.add_argument("--check", type=int, default=20000,
+                    help="reads of the step's batch whose mem_alnreg_t records are compared with the reference CPU code (0 = none)")
+    a = ap.parse_args()
+    if a.human:
+        a.contigs, a.contig_len = 24, 129_166_667
+    return a
 
 
 def workload_name(a):
-    return (f"synthetic {a.contigs}x{a.contig_len / 1e6:g} Mbp reference (seed 20261104), "
+    return (f"synthetic {a.contigs}x{a.contig_len / 1e6:.6g} Mbp reference (seed 20261104), "
             f"{a.reads / 1e6:g}M x {a.read_len} bp single-end reads per GPU, 1% sub + 0.015%/bp indel")
 
 
@@ -97,10 +106,31 @@ def build_inputs(a, rank):
     from bwa_mem_gpu_b200 import synth
     contigs = synth.make_genome([a.contig_len] * a.contigs)
     t0 = time.time()
-    reads, _ = synth.simulate_reads(contigs, a.reads, read_len=a.read_len, seed=1002 + 7919 * rank)
+    reads, truth = synth.simulate_reads(contigs, a.reads, read_len=a.read_len, seed=1002 + 7919 * rank)
     seqs = np.ascontiguousarray(reads.reshape(-1))
     off = np.arange(0, a.reads + 1, dtype=np.int64) * a.read_len
+    build_inputs.truth = truth
     return contigs, seqs, off, time.time() - t0
+
+
+def truth_check(a, contigs, truth, regs, cnt):
+    """Size-independent property: a read drawn from a known place must come back there.  Fraction of reads whose
+    best region (first record) lies on the true strand within 20 bp of the true start."""
+    lens = np.array([len(c) for c in contigs], dtype=np.int64)
+    l_pac = int(lens.sum())
+    starts_c = np.concatenate([[0], np.cumsum(lens)])[:-1]
+    n = len(cnt)
+    first = np.concatenate([[0], np.cumsum(cnt.astype(np.int64))])[:-1]
+    has = cnt > 0
+    r = regs[first[has]]
+    gpos = (starts_c[truth["contig"]] + truth["pos"])[:n][has]
+    rev = truth["rev"][:n][has]
+    on_rev = r["rb"] >= l_pac
+    fwd_start = np.where(on_rev, 2 * l_pac - r["re"], r["rb"])                  # forward-strand start of the aligned part
+    clip = np.where(on_rev, a.read_len - r["qe"], r["qb"])                       # read bases before it on the forward strand
+    ok = (on_rev == rev) & (np.abs(fwd_start - clip - gpos) <= 20)
+    return {"reads": int(n), "with_region": int(has.sum()), "best_region_at_true_locus": int(ok.sum()),
+            "frac": float(ok.sum()) / max(1, n)}
 
 
 def peaks():
@@ -134,7 +164,7 @@ def microbench_ceilings():
     return json.load(open(p)) if os.path.exists(p) else None
 
 
-def cpu_reference(a, hidx, seqs, off, n_sample, threads):
+def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None):
     """The reference's CPU implementation of the same path (mem_align1_core over kt_for), oracle/_ref."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refapi
@@ -149,9 +179,15 @@ def cpu_reference(a, hidx, seqs, off, n_sample, threads):
     t0 = time.time()
     _, cnt = idx.align(opt, seqs, sub_off, n_threads=threads, count_only=True)
     dt = time.time() - t0
-    return {"value": n_sample / dt, "unit": UNIT, "cores": threads, "kind": "reference",
-            "sample": f"first {n_sample} reads of the step's batch, mem_align1_core via kt_for, {dt:.2f} s",
-            "regions": int(cnt.sum())}
+    out = {"value": n_sample / dt, "unit": UNIT, "cores": threads, "kind": "reference",
+           "sample": f"first {n_sample} reads of the step's batch, mem_align1_core via kt_for, {dt:.2f} s",
+           "regions": int(cnt.sum())}
+    if check is not None:                                  # parity on a sample: all 88 bytes of every record
+        n_chk, dev_regs, dev_cnt = check
+        r0, c0 = idx.align(opt, seqs, off[: n_chk + 1], n_threads=threads, cap_per_read=64)
+        same = bool(np.array_equal(c0, dev_cnt[:n_chk])) and r0.tobytes() == dev_regs[: int(c0.sum())].tobytes()
+        out["parity_sample"] = {"reads": int(n_chk), "regions": int(c0.sum()), "identical_to_reference": same}
+    return out
 
 
 def main():
@@ -205,16 +241,20 @@ def main():
 
     t_setup = time.time()
     contigs, seqs, off, t_reads = build_inputs(a, rank)
-    t0 = time.time()
-    hidx = L.HostIndex(contigs)
-    t_index = time.time() - t0
     ctx = L.Context(local_rank)
     for kv in filter(None, a.tune.split(",")):
         k, v = kv.split("=")
         ctx.tune(k, int(v))
     t0 = time.time()
-    ctx.upload_host_index(hidx)
-    t_upload = time.time() - t0
+    if a.index == "host":
+        hidx = L.HostIndex(contigs)
+        t_index = time.time() - t0
+        t0 = time.time()
+        ctx.upload_host_index(hidx)
+        t_upload = time.time() - t0
+    else:                                           # suffix sort, BWT, Occ blocks and SA on the device (index_dev.cu)
+        hidx = ctx.build_index_device(contigs)
+        t_index, t_upload = time.time() - t0, 0.0
     opt = abi.default_opt()
 
     # ---------------- device-resident timing ("value")
@@ -282,8 +322,8 @@ def main():
             "config": {"workload": workload_name(a), "path": "mem_align1_core batch (reads -> mem_alnreg_t)",
                        "l2": "inputs + intermediates per step are GBs (>> 126 MB L2); no explicit flush",
                        "sharding": "reads sharded per rank, FM-index replicated, no collective on the data path",
-                       "wall_ms_per_step": wall_ms_max, "index_build_s": t_index, "index_upload_s": t_upload,
-                       "read_sim_s": t_reads},
+                       "wall_ms_per_step": wall_ms_max, "index": "host SA-IS + upload" if a.index == "host" else "built on the device",
+                       "index_build_s": t_index, "index_upload_s": t_upload, "seq_len": hidx.seq_len, "read_sim_s": t_reads},
             "e2e": {"value": world * a.reads / (e2e_ms_max * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": world * int(len(seqs) + off.nbytes),          # all ranks (each copies its own block)
                     "d2h_bytes_per_step": world * int(tot * abi.ALNREG_DTYPE.itemsize + 4 * a.reads)},
@@ -312,9 +352,19 @@ def main():
         }
         if not a.no_cpu_baseline:
             n_sample = a.cpu_sample or min(a.reads, max(20000, 150000 * cores))
-            cb = cpu_reference(a, hidx, seqs, off, n_sample, cores)
+            chk = None
+            if a.check > 0:
+                n_chk = min(a.check, a.reads)
+                dev_cnt = pin_n.numpy()[:n_chk].copy()
+                dev_regs = np.frombuffer(pin_out.numpy()[: int(dev_cnt.sum()) * abi.ALNREG_DTYPE.itemsize].tobytes(), dtype=abi.ALNREG_DTYPE)
+                chk = (n_chk, dev_regs, dev_cnt)
+            cb = cpu_reference(a, hidx, seqs, off, n_sample, cores, chk)
             if cb is not None:
+                out["parity_sample"] = cb.pop("parity_sample", None)
                 out["cpu_baseline"] = cb
+        all_cnt = pin_n.numpy()[: a.reads]
+        all_regs = np.frombuffer(pin_out.numpy()[: int(all_cnt.astype(np.int64).sum()) * abi.ALNREG_DTYPE.itemsize], dtype=abi.ALNREG_DTYPE)
+        out["truth_check"] = truth_check(a, contigs, build_inputs.truth, all_regs, all_cnt)
         print(json.dumps(out))
     if world > 1:
         dist.barrier()

@@ -60,6 +60,8 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
     else if (!strcmp(key, "ext_bps")) ctx->ext_bps = (int)value;
     else if (!strcmp(key, "l2_persist")) ctx->l2_persist = (int)value;
+    else if (!strcmp(key, "idx_group_cap")) ctx->idx_group_cap = value > ((i64)1 << 30) ? ((i64)1 << 30) : value;   // before b200_index_build_device
+    else if (!strcmp(key, "idx_tie_cap")) ctx->idx_tie_cap = value;
     else { b200_set_error("unknown tunable '%s'", key); return -1; }
     return 0;
 }
@@ -78,6 +80,57 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     for (DevBuf *b : bufs) b->release();
     cudaStreamDestroy(ctx->st);
     delete ctx;
+}
+
+// Derived device structures of an index whose reference-layout arrays are resident (uploaded or built on the device):
+// occ32 re-layout, k-mer interval table, and the full suffix array unless it is there already.
+int b200_index_finish(b200_ctx *ctx, int flags)
+{
+    DevIndex &ix = ctx->ix;
+    const u64 seq_len = ix.seq_len;
+    {   // occ32 re-layout for the seeding kernel (occ32.cuh); superblock bases already in ix.sb_cnt
+        const u64 n_blk = (seq_len >> 6) + 2;
+        if (ctx->d_bwt.bytes < ((n_blk + 1) / 2) * 64) { b200_set_error("internal: bwt padding too small"); return -1; }
+        if (ctx->d_occ32.ensure((size_t)n_blk * 32)) return -1;
+        if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
+        ix.occ32 = ctx->d_occ32.as<uint4>();
+        ix.kmer_tab = nullptr; ix.kmer_k = 0;
+        if (ctx->kmer_k > 0) {                                       // k-mer interval table (kmer_tab.cu)
+            const bool wide = seq_len >= 0xfffffff0ull || ctx->force_wide;      // same rule as the seeding kernel template (pipeline.cu)
+            const int kk = ctx->kmer_k > 12 ? 12 : ctx->kmer_k;
+            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide ? 32 : 16))) return -1;
+            if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
+            ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;
+        }
+#ifndef B200_EMU
+        {   // optional (tunable l2_persist=1, before the upload): persisting-L2 window over the seeding index.
+            // Measured on B200: seeding -2 %, but the other stages lose L2 and the batch gets slower, so it is off.
+            cudaDeviceProp prop;
+            if (cudaGetDeviceProperties(&prop, ctx->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0 && ctx->l2_persist) {
+                const size_t setaside = (size_t)prop.persistingL2CacheMaxSize;
+                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside);
+                cudaStreamAttrValue av;
+                memset(&av, 0, sizeof(av));
+                size_t win = std::min<size_t>((size_t)n_blk * 32, (size_t)prop.accessPolicyMaxWindowSize);
+                av.accessPolicyWindow.base_ptr = ctx->d_occ32.p;
+                av.accessPolicyWindow.num_bytes = win;
+                av.accessPolicyWindow.hitRatio = win <= setaside ? 1.0f : (float)((double)setaside / (double)win);
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                if (cudaStreamSetAttribute(ctx->st, cudaStreamAttributeAccessPolicyWindow, &av) != cudaSuccess) cudaGetLastError();
+                ctx->l2_setaside = setaside; ctx->l2_window = win;
+            }
+        }
+#endif
+    }
+    if ((flags & B200_IDX_FULL_SA) && !ix.sa_full32 && !ix.sa_full64) {
+        const bool narrow = seq_len < 0xffffffffull;
+        if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
+        if (launch_build_full_sa(ix, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
+        if (narrow) ix.sa_full32 = ctx->d_sa_full.as<u32>(); else ix.sa_full64 = ctx->d_sa_full.as<u64>();
+    }
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    return 0;
 }
 
 extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_size, uint64_t primary,
@@ -111,54 +164,15 @@ extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint6
     ix.sa = ctx->d_sa.as<u64>(); ix.n_sa = n_sa; ix.sa_intv = sa_intv;
     ix.pac = ctx->d_pac.as<u8>(); ix.l_pac = l_pac; ix.n_seqs = n_seqs;
     ix.ann_off = ctx->d_ann_off.as<i64>(); ix.ann_len = ctx->d_ann_len.as<i32>(); ix.ann_alt = ctx->d_ann_alt.as<i32>();
-    {   // occ32 re-layout for the seeding kernel (occ32.cuh); superblock bases read from the host checkpoints
-        if (seq_len >> 35) { b200_set_error("seq_len >= 2^35 not supported by the occ32 layout"); return -1; }
-        for (int s = 0; s < 8; ++s)
-            for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = 0;
-        for (u64 s = 1; (s << 32) < seq_len; ++s) {
-            const uint32_t *blk = bwt + (((s << 32) >> 7) << 4);
-            for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = (u64)blk[2 * c] | (u64)blk[2 * c + 1] << 32;
-        }
-        const u64 n_blk = (seq_len >> 6) + 2;
-        if (bwt_bytes < ((n_blk + 1) / 2) * 64) { b200_set_error("internal: bwt padding too small"); return -1; }
-        if (ctx->d_occ32.ensure((size_t)n_blk * 32)) return -1;
-        if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
-        ix.occ32 = ctx->d_occ32.as<uint4>();
-        ix.kmer_tab = nullptr; ix.kmer_k = 0;
-        if (ctx->kmer_k > 0) {                                       // k-mer interval table (kmer_tab.cu)
-            const bool wide = seq_len >= 0xfffffff0ull || ctx->force_wide;      // same rule as the seeding kernel template (pipeline.cu)
-            const int kk = ctx->kmer_k > 12 ? 12 : ctx->kmer_k;
-            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide ? 32 : 16))) return -1;
-            if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
-            ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;
-        }
-#ifndef B200_EMU
-        {   // optional (tunable l2_persist=1, before the upload): persisting-L2 window over the seeding index.
-            // Measured on B200: seeding -2 %, but the other stages lose L2 and the batch gets slower, so it is off.
-            cudaDeviceProp prop;
-            if (cudaGetDeviceProperties(&prop, ctx->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0 && ctx->l2_persist) {
-                const size_t setaside = (size_t)prop.persistingL2CacheMaxSize;
-                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside);
-                cudaStreamAttrValue av;
-                memset(&av, 0, sizeof(av));
-                size_t win = std::min<size_t>((size_t)n_blk * 32, (size_t)prop.accessPolicyMaxWindowSize);
-                av.accessPolicyWindow.base_ptr = ctx->d_occ32.p;
-                av.accessPolicyWindow.num_bytes = win;
-                av.accessPolicyWindow.hitRatio = win <= setaside ? 1.0f : (float)((double)setaside / (double)win);
-                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-                if (cudaStreamSetAttribute(ctx->st, cudaStreamAttributeAccessPolicyWindow, &av) != cudaSuccess) cudaGetLastError();
-                ctx->l2_setaside = setaside; ctx->l2_window = win;
-            }
-        }
-#endif
+    for (int s = 0; s < 8; ++s)                                      // superblock bases from the host checkpoints
+        for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = 0;
+    if (seq_len >> 35) { b200_set_error("seq_len >= 2^35 not supported by the occ32 layout"); return -1; }
+    for (u64 s = 1; (s << 32) < seq_len; ++s) {
+        const uint32_t *blk = bwt + (((s << 32) >> 7) << 4);
+        for (int c = 0; c < 4; ++c) ix.sb_cnt[s][c] = (u64)blk[2 * c] | (u64)blk[2 * c + 1] << 32;
     }
-    if (flags & B200_IDX_FULL_SA) {
-        const bool narrow = seq_len < 0xffffffffull;
-        if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
-        if (launch_build_full_sa(ix, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
-        if (narrow) ix.sa_full32 = ctx->d_sa_full.as<u32>(); else ix.sa_full64 = ctx->d_sa_full.as<u64>();
-    }
+    ctx->idx_bwt_size = bwt_size;
+    if (b200_index_finish(ctx, flags)) return -1;
     B200_CHECK(cudaStreamSynchronize(ctx->st));
     ctx->has_index = true;
     return 0;

@@ -49,6 +49,9 @@ struct b200_ctx {
     int kmer_k = 9;                            // longest string in the k-mer interval table (0 = none); set before the index upload
     int smem_bps = 0;                          // > 0: cap on resident blocks per SM of the seeding kernel (experiments)
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
+    i64 idx_group_cap = 0, idx_tie_cap = 0;    // device index builder (index_dev.cu): suffixes per sort group / colliding suffixes per group (0 = default)
+    u64 idx_bwt_size = 0;                      // words of the reference-layout BWT held in d_bwt
+    int idx_groups = 0; i64 idx_ties = 0;      // what the last device index build did
 
     // per-chunk intermediates
     DevBuf d_intv, d_intv_n, d_lists, d_seed_n, d_seed_off, d_l_rep, d_seeds, d_cseeds, d_chains, d_chn_n,
@@ -66,4 +69,5 @@ struct b200_ctx {
 enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_RETRY = 5, CTL_WORK2 = 6, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
+int b200_index_finish(b200_ctx *ctx, int flags);
 b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac);

@@ -24,7 +24,7 @@ _SYMBOLS = [
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
-    "b200_hostidx_pac", "b200_index_upload_host",
+    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -105,6 +105,74 @@ class B200Error(RuntimeError):
     pass
 
 
+def pack_pac(contigs):
+    """2-bit forward reference in the layout of the reference's .pac (bntseq.c:230: base i in byte i>>2, bits (~i&3)*2)."""
+    l_pac = int(sum(len(c) for c in contigs))
+    pac = np.zeros(l_pac // 4 + 1, dtype=np.uint8)
+    pos = 0
+    for c in contigs:                                    # contig by contig: no second copy of a 3.1 Gbp genome
+        c = np.asarray(c, dtype=np.uint8)
+        if c.size and int(c.max()) > 3:
+            raise B200Error("bases must be nt4 codes 0..3")
+        head = (-pos) % 4                                # bases completing the current byte
+        for k in range(min(head, len(c))):
+            i = pos + k
+            pac[i >> 2] |= np.uint8(int(c[k]) << ((~i & 3) << 1))
+        body = c[head:]
+        nb = len(body) // 4
+        if nb:
+            q = body[: nb * 4].reshape(nb, 4)
+            b0 = (pos + head) >> 2
+            pac[b0: b0 + nb] = (q[:, 0] << 6) | (q[:, 1] << 4) | (q[:, 2] << 2) | q[:, 3]
+        for k in range(nb * 4, len(body)):
+            i = pos + head + k
+            pac[i >> 2] |= np.uint8(int(body[k]) << ((~i & 3) << 1))
+        pos += len(c)
+    return pac, l_pac
+
+
+class DeviceBuiltIndex:
+    """Host-side view of an index built on the device by Context.build_index_device (same attributes as HostIndex)."""
+
+    def __init__(self, ctx: "Context", contigs, names=None):
+        self.ctx = ctx
+        self._pac, self.l_pac = pack_pac(contigs)
+        lens = np.array([len(c) for c in contigs], dtype=np.int64)
+        self.ann_off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+        self.ann_len = lens.astype(np.int32)
+        self.ann_alt = np.zeros(len(contigs), dtype=np.int32)
+        self.names = names or [f"chr{i + 1}" for i in range(len(contigs))]
+        self._bwt = self._sa = None
+
+    def _fill_info(self):
+        info = self.ctx.index_info()
+        self.primary = int(info[0])
+        self.L2 = [int(x) for x in info[1:6]]
+        self.seq_len, self.bwt_size, self.n_sa, self.sa_intv = int(info[6]), int(info[7]), int(info[8]), int(info[9])
+        self.sort_groups, self.host_ordered = int(info[11]), int(info[12])
+
+    def _download(self):
+        if self._bwt is None:
+            self._bwt = np.zeros(self.bwt_size, dtype=np.uint32)
+            self._sa = np.zeros(self.n_sa, dtype=np.uint64)
+            self.ctx._chk(self.ctx.lib.b200_index_download(self.ctx.h, _p(self._bwt, C.c_uint32), _p(self._sa, C.c_uint64)),
+                          "index_download")
+
+    def bwt_words(self):
+        self._download()
+        return self._bwt
+
+    def sa(self):
+        self._download()
+        return self._sa
+
+    def pac(self):
+        return self._pac
+
+    def close(self):
+        self._bwt = self._sa = None
+
+
 class Context:
     """One GPU: device index + batch pipeline (mirrors process_data_t / transferIndex of the reference)."""
 
@@ -160,6 +228,21 @@ class Context:
         self._chk(self.lib.b200_index_upload_host(self.h, hidx.h, C.c_int(len(hidx.ann_off)), _p(hidx.ann_off, C.c_int64),
                                                   _p(hidx.ann_len, C.c_int32), _p(hidx.ann_alt, C.c_int32),
                                                   C.c_int(flags)), "index_upload_host")
+
+    def build_index_device(self, contigs, flags=IDX_FULL_SA, names=None):
+        """Index the genome ON the device (b200_index_build_device) and leave it resident.  Returns a DeviceBuiltIndex
+        with the attributes of HostIndex (arrays are downloaded on demand)."""
+        d = DeviceBuiltIndex(self, contigs, names)
+        self._chk(self.lib.b200_index_build_device(
+            self.h, _p(d._pac, C.c_uint8), C.c_int64(d.l_pac), C.c_int(len(d.ann_off)), _p(d.ann_off, C.c_int64),
+            _p(d.ann_len, C.c_int32), _p(d.ann_alt, C.c_int32), C.c_int(flags)), "index_build_device")
+        d._fill_info()
+        return d
+
+    def index_info(self):
+        info = np.zeros(13, dtype=np.uint64)
+        self._chk(self.lib.b200_index_info(self.h, C.c_void_p(info.ctypes.data)), "index_info")
+        return info
 
     # ---------------- primitives
     def occ4(self, k):

@@ -164,6 +164,21 @@ const uint8_t  *b200_hostidx_pac(const b200_hostidx_t *h);
 int b200_index_upload_host(b200_ctx_t *ctx, const b200_hostidx_t *h, int n_seqs, const int64_t *ann_offset,
                            const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
 
+/* Device-side index construction (csrc/index_dev.cu): the arrays of bwa_idx_build (bwtindex.c:253-323; BWT of
+ * forward + reverse complement bwtindex.c:63-126, Occ checkpoints :149-172, sampled SA bwt.c:62-84) computed on the
+ * GPU from the 2-bit forward reference `pac` (bntseq.c:230 layout, l_pac/4+1 bytes) and left resident, ready for
+ * alignment -- seconds instead of hours for a 3.1 Gbp text.  Suffixes are sorted by their first 32 bases in key-range
+ * groups; suffixes colliding on all 32 bases are ordered on the host, at most "idx_tie_cap" (tunable) per group, else
+ * the call fails (repeat-saturated texts: use b200_hostidx_build or `bwa index`).
+ * b200_index_info: [0]=primary [1..5]=L2 [6]=seq_len [7]=bwt_size [8]=n_sa [9]=sa_intv [10]=l_pac
+ *                  [11]=sort groups [12]=suffixes ordered on the host (0 for an uploaded index).
+ * b200_index_download copies the reference-layout arrays (bwt_t.bwt: bwt_size words; bwt_t.sa: n_sa values) of the
+ * resident index to the host, e.g. to fill a bwt_t for the host side of mem_process_seqs; either pointer may be NULL. */
+int b200_index_build_device(b200_ctx_t *ctx, const uint8_t *pac, int64_t l_pac, int n_seqs, const int64_t *ann_offset,
+                            const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
+int b200_index_info(b200_ctx_t *ctx, uint64_t *info /* 13 */);
+int b200_index_download(b200_ctx_t *ctx, uint32_t *bwt, uint64_t *sa);
+
 /* =====================================================================================
  * Batched device entry points (arrays of problems; host buffers in, host buffers out).
  * All return 0 on success, <0 on error (message in b200_last_error()); a capacity overflow
