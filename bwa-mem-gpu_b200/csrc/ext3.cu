@@ -100,6 +100,11 @@ __device__ __forceinline__ unsigned d8_nz8(const uint4 w)
     return m;
 }
 
+// ROWSYNC: a lane runs all column groups of its row before the warp meets in the control slot, so the per-row
+// bookkeeping executes once per row for (nearly) all 32 lanes instead of once per 8-column slot for the few lanes that
+// happen to finish a row in that slot; lanes with shorter rows idle until the longest row of the warp is done (jobs are
+// binned by flank length, which bounds that).  ROWSYNC = false is the one-slot-per-iteration state machine.
+template <bool ROWSYNC>
 __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int round, int bin, int n_groups)
 {
     B200_DYN_SMEM(d8_raw);
@@ -143,7 +148,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
 
     for (;;) {
         // ---------------------------------------------------------------- hot slot: one group of 8 columns
-        if (active && L.g <= L.gend) {
+        for (bool first = true; active && L.g <= L.gend && (ROWSYNC || first); first = false) {
             const int c0 = L.g << 3;
             uint4 *hp = HE + L.g * D8_THREADS;
             const uint4 w = *hp;
@@ -161,6 +166,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
             *hp = o;
             ++L.g;
         }
+        if (ROWSYNC) __syncwarp();
         // ---------------------------------------------------------------- control slot
         bool ksw_fin = false;
         if (active && L.g > L.gend) {                                                     // row i finished
@@ -358,13 +364,15 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
 
 size_t ext2_dp8_smem(int n_groups) { return (size_t)n_groups * D8_THREADS * (16 + 8); }
 
-int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, cudaStream_t st)
+int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, cudaStream_t st)
 {
     const size_t smem = ext2_dp8_smem(n_groups);
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
-    B200_LAUNCH(ext_dp8_kernel, grid, D8_THREADS, smem, st, p, round, bin, n_groups);
+    if (rowsync) B200_LAUNCH(ext_dp8_kernel<true>, grid, D8_THREADS, smem, st, p, round, bin, n_groups);
+    else B200_LAUNCH(ext_dp8_kernel<false>, grid, D8_THREADS, smem, st, p, round, bin, n_groups);
     B200_CHECK(cudaGetLastError());
     return 0;
 }

@@ -279,8 +279,14 @@ def test_align_general_extension_kernel(backend):
     finally:
         ctx.tune("ext_path", 0)
     r2, n2 = ctx.align(opt, seqs, off)
+    ctx.tune("ext_rowsync", 0)                       # byte-score kernel as a one-slot-per-iteration state machine
+    try:
+        r3, n3 = ctx.align(opt, seqs, off)
+    finally:
+        ctx.tune("ext_rowsync", 1)
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
     assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
+    assert np.array_equal(n0, n3) and r0.tobytes() == r3.tobytes()
 
 
 @needs_ref
