@@ -114,7 +114,7 @@ struct ExtJob {          // one seed extension: both sides + band retries (bwame
     i32 read, qbeg, slen, lq;        // read, seed on the query, query length
     i32 wl0, wl1, wr0, wr1;          // bands of the two tries per side, already clamped like ksw.c:399-407
     i64 rb, re;                      // results
-    i32 qb, qe, score, truesc, w, pad;
+    i32 qb, qe, score, truesc, w, key;   // key: (left flank / 8) << 5 | (right flank / 8), the order jobs are handed to the DP lanes in
 };
 struct ExtRead { i32 ci, k, nav, pad; i64 rmax0, rmax1; };   // per-read cursor between rounds
 struct Ext2Params {
@@ -133,6 +133,7 @@ struct Ext2Params {
     int jobs_cap;                    // slots per array (>= reads in the chunk: at most one job per read and round)
     int bin_max[2];                  // longest flank of bin 0 / bin 1
     unsigned *njobs;                 // per round: 8 counters: [0..2] jobs emitted per bin, [4..6] jobs taken by the DP kernel
+    u32 *perm; u32 *sort_cnt;        // optional: per bin (b * jobs_cap) the job slots ordered by key, longest flanks first; 3 x 1024 counters
     i32 *eh; int eh_cap;             // finish kernel scratch (mem_patch_reg's global alignment)
     i64 *reg_off; i32 *reg_n;
     unsigned *work_counter;
@@ -170,6 +171,7 @@ int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t
 int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st);
 size_t ext2_dp8_smem(int n_groups);
 int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, cudaStream_t st);
+int launch_ext2_sort(const Ext2Params &p, int round, int n_jobs, int n_sms, cudaStream_t st);
 int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,

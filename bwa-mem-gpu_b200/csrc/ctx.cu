@@ -60,6 +60,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
     else if (!strcmp(key, "ext_bps")) ctx->ext_bps = (int)value;
     else if (!strcmp(key, "ext_rowsync")) ctx->ext_rowsync = (int)value;
+    else if (!strcmp(key, "ext_sort")) ctx->ext_sort = (int)value;
     else if (!strcmp(key, "l2_persist")) ctx->l2_persist = (int)value;
     else if (!strcmp(key, "idx_group_cap")) ctx->idx_group_cap = value > ((i64)1 << 30) ? ((i64)1 << 30) : value;   // before b200_index_build_device
     else if (!strcmp(key, "idx_tie_cap")) ctx->idx_tie_cap = value;
@@ -72,7 +73,7 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
-    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
+    DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_jobs2, &ctx->d_jobs3, &ctx->d_jsort, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
                        &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,

@@ -26,7 +26,7 @@ struct b200_ctx {
     cudaStream_t st = nullptr;
     bool has_index = false;
     DevIndex ix;
-    DevBuf d_occ32, d_kmer, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_jobs2, d_jobs3, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
+    DevBuf d_occ32, d_kmer, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_jobs2, d_jobs3, d_jsort, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;
     const void *bwt_identity = nullptr;       // host bwt_t* this index was uploaded from (drop-in registry)
     bool stub_pac = false;             // index uploaded by a bwt-only primitive (no bns / pac yet)
 
@@ -44,6 +44,7 @@ struct b200_ctx {
     size_t l2_setaside = 0, l2_window = 0;
     int ext_bin0 = 0, ext_bin1 = 0;            // > 0: flank-length limits of extension bins 0 / 1 (default 32 / 64)
     int ext_bps = 0;                           // > 0: cap on resident blocks per SM of the extension DP kernel
+    int ext_sort = 1;                          // byte-score extension kernel: jobs handed out ordered by flank shape (ext3.cu)
     int ext_rowsync = 1;                       // byte-score extension kernel: a lane finishes its row before the warp's control slot (ext3.cu)
     int split_p3 = 1;                          // third seeding pass in its own kernel (smem_p3_kernel) ahead of the main one
     int force_wide = 0;                        // 1: run the 64-bit-position templates even when seq_len < 2^32 (tests); set before the index upload

@@ -164,7 +164,8 @@ __global__ void __launch_bounds__(128) ext_plan_kernel(Ext2Params P, int round)
             j.read = r; j.qbeg = s.qbeg; j.slen = s.len; j.lq = l_query;
             j.wl0 = clamp_band(opt, ql, opt.w, opt.pen_clip5); j.wl1 = clamp_band(opt, ql, opt.w << 1, opt.pen_clip5);
             j.wr0 = clamp_band(opt, qr, opt.w, opt.pen_clip3); j.wr1 = clamp_band(opt, qr, opt.w << 1, opt.pen_clip3);
-            j.rb = j.re = 0; j.qb = j.qe = j.score = j.truesc = j.w = j.pad = 0;
+            j.rb = j.re = 0; j.qb = j.qe = j.score = j.truesc = j.w = 0;
+            j.key = ((ql >> 3) > 31 ? 31 : (ql >> 3)) << 5 | ((qr >> 3) > 31 ? 31 : (qr >> 3));
             *job_slot(P, round & 1, bin, slot) = j;
             emitted = true;
             break;

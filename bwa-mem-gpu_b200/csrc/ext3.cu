@@ -67,10 +67,11 @@ struct D8Const { u32 ne_del2, noe_del2, noe_ins2, ne_ins2, ne_ins_hi; };
 
 // two columns (j, j+1): w = their H/E bytes [h_j, e_j, h_j+1, e_j+1], im / sm = input / store masks, qsel = prmt selector
 // of the two substitution scores, col2 = (j, j+1)
+template <bool MASKED>
 __device__ __forceinline__ u32 d8_pair(u32 w, u32 im, u32 sm, u32 qsel, u32 col2, const D8Lane &L, const D8Const &K,
                                        u32 &fc, u32 &hc, u32 &key)
 {
-    const u32 wm = w & im;
+    const u32 wm = MASKED ? w & im : w;
     const u32 H2 = d8_prmt(wm, 0u, 0x4240u), E2 = d8_prmt(wm, 0u, 0x4341u);
     const u32 sc2 = d8_prmt(L.srow_lo, L.srow_hi, qsel);
     const u32 Mp = __viaddmin_s16x2(H2, sc2, H2 << 6);                                  // ksw.c:433
@@ -80,11 +81,11 @@ __device__ __forceinline__ u32 d8_pair(u32 w, u32 im, u32 sm, u32 qsel, u32 col2
     const u32 F2 = __viaddmax_s16x2(A, K.ne_ins_hi, T2 << 16);                          // (F_j, F_j+1), ksw.c:445-447
     fc = __viaddmax_s16x2(F2, K.ne_ins2, T2);                                           // high half: F_j+2
     const u32 h2 = __vimax3_s16x2(Mp, E2, F2);                                          // ksw.c:434-435
-    key = __vmaxu2(key, ((h2 << 8) + col2) & im);                                       // ksw.c:437-438
+    key = __vmaxu2(key, MASKED ? ((h2 << 8) + col2) & im : (h2 << 8) + col2);           // ksw.c:437-438
     const u32 Hs2 = d8_prmt(hc, h2, 0x5432u);                                           // (H(i,j-1), H(i,j)), ksw.c:432
     hc = h2;
     const u32 nw = en2 * 256u + Hs2;
-    return (nw & sm) | (w & ~sm);
+    return MASKED ? (nw & sm) | (w & ~sm) : nw;
 }
 
 // bit c set when column c of the 16-byte group word holds a non-zero h or e
@@ -153,16 +154,29 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
             uint4 *hp = HE + L.g * D8_THREADS;
             const uint4 w = *hp;
             const uint2 q = QS[L.g * D8_THREADS];
-            int lo = L.beg - c0; lo = lo < 0 ? 0 : lo;
-            int hi = L.end - c0, hs = hi + 1;
-            hi = hi > 8 ? 8 : hi; hs = hs > 8 ? 8 : hs;
-            const uint4 plo = s_pref[lo], phi = s_pref[hi], phs = s_pref[hs];
             const u32 cb = (u32)c0 * 0x10001u + 0x00010000u;
             uint4 o;
-            o.x = d8_pair(w.x, phi.x & ~plo.x, phs.x & ~plo.x, q.x, cb, L, K, L.fc, L.hc, L.key);
-            o.y = d8_pair(w.y, phi.y & ~plo.y, phs.y & ~plo.y, q.x >> 16, cb + 0x00020002u, L, K, L.fc, L.hc, L.key);
-            o.z = d8_pair(w.z, phi.z & ~plo.z, phs.z & ~plo.z, q.y, cb + 0x00040004u, L, K, L.fc, L.hc, L.key);
-            o.w = d8_pair(w.w, phi.w & ~plo.w, phs.w & ~plo.w, q.y >> 16, cb + 0x00060006u, L, K, L.fc, L.hc, L.key);
+            // a group wholly inside [beg, end) needs no masks; the warp takes the unmasked path only when that holds for every
+            // lane still in its row (both paths give the same values for such a group)
+            bool edge = L.beg > c0 || L.end < c0 + 8;
+#ifndef B200_EMU
+            if (ROWSYNC) edge = __any_sync(__activemask(), edge);
+#endif
+            if (edge) {
+                int lo = L.beg - c0; lo = lo < 0 ? 0 : lo;
+                int hi = L.end - c0, hs = hi + 1;
+                hi = hi > 8 ? 8 : hi; hs = hs > 8 ? 8 : hs;
+                const uint4 plo = s_pref[lo], phi = s_pref[hi], phs = s_pref[hs];
+                o.x = d8_pair<true>(w.x, phi.x & ~plo.x, phs.x & ~plo.x, q.x, cb, L, K, L.fc, L.hc, L.key);
+                o.y = d8_pair<true>(w.y, phi.y & ~plo.y, phs.y & ~plo.y, q.x >> 16, cb + 0x00020002u, L, K, L.fc, L.hc, L.key);
+                o.z = d8_pair<true>(w.z, phi.z & ~plo.z, phs.z & ~plo.z, q.y, cb + 0x00040004u, L, K, L.fc, L.hc, L.key);
+                o.w = d8_pair<true>(w.w, phi.w & ~plo.w, phs.w & ~plo.w, q.y >> 16, cb + 0x00060006u, L, K, L.fc, L.hc, L.key);
+            } else {
+                o.x = d8_pair<false>(w.x, 0u, 0u, q.x, cb, L, K, L.fc, L.hc, L.key);
+                o.y = d8_pair<false>(w.y, 0u, 0u, q.x >> 16, cb + 0x00020002u, L, K, L.fc, L.hc, L.key);
+                o.z = d8_pair<false>(w.z, 0u, 0u, q.y, cb + 0x00040004u, L, K, L.fc, L.hc, L.key);
+                o.w = d8_pair<false>(w.w, 0u, 0u, q.y >> 16, cb + 0x00060006u, L, K, L.fc, L.hc, L.key);
+            }
             *hp = o;
             ++L.g;
         }
@@ -239,7 +253,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
             if (!active) {                                                                // fetch a job
                 const unsigned slot = atomicAdd(work_counter, 1u);
                 if (slot >= njobs) { exhausted = true; break; }
-                L.job = d8_job_slot(P, round & 1, bin, slot);
+                L.job = d8_job_slot(P, round & 1, bin, P.perm ? P.perm[(size_t)bin * P.jobs_cap + slot] : slot);
                 active = true;
                 L.a_score = -1;
                 if (L.job->qbeg) { next_side = 0; next_t = 0; L.prev = -1; }
@@ -360,6 +374,56 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
         atomicAdd(&P.stats[CNT_KSW], (unsigned long long)n_ksw);
         atomicAdd(&P.stats[CNT_CELLS], (unsigned long long)n_cells);
     }
+}
+
+// ---- job order: counting sort of every bin's job slots by ExtJob::key, descending (longest flanks first, so the tail of a
+// launch is short work), so that the lanes of a warp hold extensions of the same shape and run their rows in step
+#define JS_KEYS 1024
+__device__ __forceinline__ bool js_locate(const Ext2Params &P, int round, unsigned t, int &bin, unsigned &slot)
+{
+    const unsigned *nj = P.njobs + 8 * round;
+    bin = 0; slot = t;
+    if (slot >= nj[0]) { slot -= nj[0]; bin = 2; if (slot >= nj[2]) { slot -= nj[2]; bin = 1; if (slot >= nj[1]) return false; } }
+    return true;
+}
+__global__ void job_hist_kernel(Ext2Params P, int round, int n_jobs)
+{
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    int bin; unsigned slot;
+    if ((int)t >= n_jobs || !js_locate(P, round, t, bin, slot)) return;
+    atomicAdd(&P.sort_cnt[bin * JS_KEYS + (d8_job_slot(P, round & 1, bin, slot)->key & (JS_KEYS - 1))], 1u);
+}
+__global__ void job_scan_kernel(Ext2Params P)                // one block of 3 warps: counts -> first position of each key
+{
+    const int bin = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    u32 *c = P.sort_cnt + bin * JS_KEYS;
+    unsigned run = 0;
+    for (int base = JS_KEYS - 32; base >= 0; base -= 32) {   // descending keys; 32 keys per step, lane 0 takes the highest
+        const int k = base + 31 - lane;
+        const unsigned v = c[k];
+        unsigned inc = v;
+        for (int d = 1; d < 32; d <<= 1) { const unsigned o = __shfl_up_sync(B200_FULL_MASK, inc, d); if (lane >= d) inc += o; }
+        c[k] = run + inc - v;
+        run += __shfl_sync(B200_FULL_MASK, inc, 31);
+    }
+}
+__global__ void job_scatter_kernel(Ext2Params P, int round, int n_jobs)
+{
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    int bin; unsigned slot;
+    if ((int)t >= n_jobs || !js_locate(P, round, t, bin, slot)) return;
+    const unsigned pos = atomicAdd(&P.sort_cnt[bin * JS_KEYS + (d8_job_slot(P, round & 1, bin, slot)->key & (JS_KEYS - 1))], 1u);
+    P.perm[(size_t)bin * P.jobs_cap + pos] = slot;
+}
+int launch_ext2_sort(const Ext2Params &p, int round, int n_jobs, int n_sms, cudaStream_t st)
+{
+    B200_CHECK(cudaMemsetAsync(p.sort_cnt, 0, 3 * JS_KEYS * 4, st));
+    B200_LAUNCH(job_hist_kernel, (n_jobs + 255) / 256, 256, 0, st, p, round, n_jobs);
+    B200_LAUNCH(job_scan_kernel, 1, 96, 0, st, p);
+    B200_LAUNCH(job_scatter_kernel, (n_jobs + 255) / 256, 256, 0, st, p, round, n_jobs);
+    B200_CHECK(cudaGetLastError());
+    (void)n_sms;
+    return 0;
 }
 
 size_t ext2_dp8_smem(int n_groups) { return (size_t)n_groups * D8_THREADS * (16 + 8); }

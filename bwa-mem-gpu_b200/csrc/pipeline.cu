@@ -256,6 +256,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         if (ctx->d_jobs0.ensure((size_t)n * sizeof(ExtJob)) || ctx->d_jobs1.ensure((size_t)n * sizeof(ExtJob)) ||
             ctx->d_jobs2.ensure((size_t)n * sizeof(ExtJob)) || ctx->d_jobs3.ensure((size_t)n * sizeof(ExtJob)) ||
             ctx->d_rstate.ensure((size_t)n * sizeof(ExtRead)) || ctx->d_njobs.ensure((size_t)MAX_ROUNDS * 32) ||
+            ctx->d_jsort.ensure(((size_t)3 * n + 3 * 1024) * 4) ||
             ctx->d_srt.ensure((size_t)(tot_seeds + 1) * 8) || ctx->d_eh.ensure((size_t)fin_blocks * 128 * 2 * eh_cap * 4)) return -1;
         B200_CHECK(cudaMemsetAsync(ctx->d_njobs.p, 0, (size_t)MAX_ROUNDS * 32, st));
         Ext2Params XP;
@@ -272,6 +273,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         const int bin_flank[3] = { ctx->ext_bin0 > 0 ? ctx->ext_bin0 : 32, ctx->ext_bin1 > 0 ? ctx->ext_bin1 : 64, ctx->max_len };
         XP.bin_max[0] = std::min(bin_flank[0], ctx->max_len); XP.bin_max[1] = std::min(std::max(bin_flank[1], XP.bin_max[0]), ctx->max_len);
         XP.njobs = ctx->d_njobs.as<unsigned>();
+        if (dp8 && ctx->ext_sort) { XP.perm = ctx->d_jsort.as<u32>(); XP.sort_cnt = XP.perm + (size_t)3 * n; }
         XP.eh = ctx->d_eh.as<i32>(); XP.eh_cap = eh_cap;
         XP.reg_off = reg_off_ptr; XP.reg_n = reg_n_ptr;
         XP.work_counter = ctl_u32(ctx, CTL_WORK); XP.stats = ctl_u64(ctx, CTL_STATS);
@@ -284,6 +286,10 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
             B200_CHECK(cudaMemcpyAsync(nj, XP.njobs + 8 * round, 12, cudaMemcpyDeviceToHost, st));
             B200_CHECK(cudaStreamSynchronize(st));
             if (nj[0] + nj[1] + nj[2] == 0) break;
+            if (XP.perm) {                                                   // hand jobs out by shape (ext3.cu)
+                if (launch_ext2_sort(XP, round, (int)(nj[0] + nj[1] + nj[2]), ctx->n_sms, st)) return -1;
+                launches += 3;
+            }
             for (int b = 0; b < 3; ++b) {
                 if (nj[b] == 0) continue;
                 const int flank = b == 2 ? ctx->max_len : XP.bin_max[b];
