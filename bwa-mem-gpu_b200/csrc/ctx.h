@@ -44,6 +44,7 @@ struct b200_ctx {
     size_t l2_setaside = 0, l2_window = 0;
     int ext_bin0 = 0, ext_bin1 = 0;            // > 0: flank-length limits of extension bins 0 / 1 (default 32 / 64)
     int ext_bps = 0;                           // > 0: cap on resident blocks per SM of the extension DP kernel
+    int ext_phased = 1;                        // byte-score extension kernel: warp-wide phases (left sides, retries, right sides, next jobs)
     int ext_sort = 1;                          // byte-score extension kernel: jobs handed out ordered by flank shape (ext3.cu)
     int ext_rowsync = 1;                       // byte-score extension kernel: a lane finishes its row before the warp's control slot (ext3.cu)
     int split_p3 = 1;                          // third seeding pass in its own kernel (smem_p3_kernel) ahead of the main one

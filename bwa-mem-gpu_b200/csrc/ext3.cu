@@ -105,8 +105,12 @@ __device__ __forceinline__ unsigned d8_nz8(const uint4 w)
 // bookkeeping executes once per row for (nearly) all 32 lanes instead of once per 8-column slot for the few lanes that
 // happen to finish a row in that slot; lanes with shorter rows idle until the longest row of the warp is done (jobs are
 // binned by flank length, which bounds that).  ROWSYNC = false is the one-slot-per-iteration state machine.
+// `phased` (with ROWSYNC): the warp moves through its jobs in phases -- left sides, left band retries, right sides, right
+// retries, next 32 jobs -- a lane whose next DP belongs to a later phase parks until no lane is mid-DP.  Together with the
+// job order (same flank shape next to each other) the rows a warp executes in one step then have the same number of
+// column groups, instead of a short left flank in one lane waiting for a long right flank in another.
 template <bool ROWSYNC>
-__global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int round, int bin, int n_groups)
+__global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int round, int bin, int n_groups, int phased)
 {
     B200_DYN_SMEM(d8_raw);
     __shared__ u32 s_rows[5 * 2];                          // matrix row of each target base, 8 bytes (5 used)
@@ -145,11 +149,11 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
 
     D8Lane L;
     memset(&L, 0, sizeof(L));
-    bool active = false, exhausted = false, need_init = false;
+    bool active = false, exhausted = false, need_init = false, parked = false;
 
     for (;;) {
         // ---------------------------------------------------------------- hot slot: one group of 8 columns
-        for (bool first = true; active && L.g <= L.gend && (ROWSYNC || first); first = false) {
+        for (bool first = true; active && !parked && L.g <= L.gend && (ROWSYNC || first); first = false) {
             const int c0 = L.g << 3;
             uint4 *hp = HE + L.g * D8_THREADS;
             const uint4 w = *hp;
@@ -183,7 +187,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
         if (ROWSYNC) __syncwarp();
         // ---------------------------------------------------------------- control slot
         bool ksw_fin = false;
-        if (active && L.g > L.gend) {                                                     // row i finished
+        if (active && !parked && L.g > L.gend) {                                          // row i finished
             int m = 0, mj = -1, h1 = L.h1i;
             if (L.beg < L.end) {
                 const u32 klo = L.key & 0xffffu, khi = L.key >> 16;
@@ -248,7 +252,8 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
             }
         }
         // job / side / retry transitions; loops only when a DP has no rows (tlen <= 0)
-        while ((active && ksw_fin) || (!active && !exhausted)) {
+        const bool may_fetch = !phased || !__any_sync(B200_FULL_MASK, active);              // phased: the warp takes 32 jobs at a time
+        while ((active && ksw_fin) || (!active && !exhausted && may_fetch)) {
             int next_side = -1, next_t = 0;
             if (!active) {                                                                // fetch a job
                 const unsigned slot = atomicAdd(work_counter, 1u);
@@ -366,6 +371,14 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
                 ((u8 *)(qs_src + (j >> 3) * D8_THREADS))[j & 7] = (u8)(qv * 0x11u + 0x80u);
             }
         }
+        if (phased) {                                                                       // open the gate for the earliest waiting phase
+            if (need_init) parked = true;
+            if (!__any_sync(B200_FULL_MASK, active && !parked)) {
+                const int ph = parked ? L.side * 2 + L.t : 99;
+                const int pmin = __reduce_min_sync(B200_FULL_MASK, ph);
+                if (ph == pmin) parked = false;
+            }
+        }
         need_init = false;
         __syncwarp();
         if (__all_sync(B200_FULL_MASK, exhausted && !active)) break;
@@ -428,15 +441,15 @@ int launch_ext2_sort(const Ext2Params &p, int round, int n_jobs, int n_sms, cuda
 
 size_t ext2_dp8_smem(int n_groups) { return (size_t)n_groups * D8_THREADS * (16 + 8); }
 
-int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, cudaStream_t st)
+int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, int phased, cudaStream_t st)
 {
     const size_t smem = ext2_dp8_smem(n_groups);
 #ifndef B200_EMU
     B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
-    if (rowsync) B200_LAUNCH(ext_dp8_kernel<true>, grid, D8_THREADS, smem, st, p, round, bin, n_groups);
-    else B200_LAUNCH(ext_dp8_kernel<false>, grid, D8_THREADS, smem, st, p, round, bin, n_groups);
+    if (rowsync) B200_LAUNCH(ext_dp8_kernel<true>, grid, D8_THREADS, smem, st, p, round, bin, n_groups, phased);
+    else B200_LAUNCH(ext_dp8_kernel<false>, grid, D8_THREADS, smem, st, p, round, bin, n_groups, 0);
     B200_CHECK(cudaGetLastError());
     return 0;
 }

@@ -297,7 +297,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
                     const int n_groups = (flank >> 3) + 1;                   // columns 0 .. flank
                     const int dp_per_sm = std::max(1, std::min(ctx->ext_bps > 0 ? ctx->ext_bps : 16, (int)((200 * 1024) / (ext2_dp8_smem(n_groups) + 1024))));
                     const int grid = std::max(1, std::min((int)((nj[b] + 63) / 64), ctx->n_sms * dp_per_sm));
-                    if (launch_ext2_dp8(XP, round, b, n_groups, grid, ctx->ext_rowsync, st)) return -1;
+                    if (launch_ext2_dp8(XP, round, b, n_groups, grid, ctx->ext_rowsync, ctx->ext_phased, st)) return -1;
                     ++launches;
                     ctx->stats[CNT_BIN0 + b] += nj[b];
                     ctx->stats[CNT_DP8] += nj[b];

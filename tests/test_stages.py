@@ -284,6 +284,13 @@ def test_align_general_extension_kernel(backend):
         r3, n3 = ctx.align(opt, seqs, off)
     finally:
         ctx.tune("ext_rowsync", 1)
+    for key in ("ext_phased", "ext_sort"):           # without warp-wide phases / without the job order
+        ctx.tune(key, 0)
+        try:
+            r4, n4 = ctx.align(opt, seqs, off)
+        finally:
+            ctx.tune(key, 1)
+        assert np.array_equal(n0, n4) and r0.tobytes() == r4.tobytes()
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
     assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
     assert np.array_equal(n0, n3) and r0.tobytes() == r3.tobytes()
