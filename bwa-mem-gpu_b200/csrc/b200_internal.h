@@ -157,8 +157,8 @@ int launch_smem_single(const SmemParams &p, int grid, int block, cudaStream_t st
 int launch_smem_fast(const SmemParams &p, int grid, int wide, cudaStream_t st);
 int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st);
 size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
-int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st);
-int launch_smem_p3(const SmemParams &p, int n_sms, int wide, cudaStream_t st);
+int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, int qglob, cudaStream_t st);
+int launch_smem_p3(const SmemParams &p, int n_sms, int wide, int qglob, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
 int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st);
 size_t kmer_tab_entries(int kmax);

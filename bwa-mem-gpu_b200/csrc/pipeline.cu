@@ -81,7 +81,10 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
     int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 12;
     lcap3 = lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);
-    const bool use3 = ctx->smem_path == 0 && smem_fast3_bytes(wide, lcap3, pk_stride) <= 100 * 1024;
+    // reads too long to stage in shared memory keep their 4-bit codes in global memory (smem_path 3 forces that variant)
+    const bool qglob = ctx->smem_path == 3 || (ctx->smem_path == 0 && smem_fast3_bytes(wide, lcap3, pk_stride) > 100 * 1024);
+    if (qglob) lcap3 = 16;
+    const bool use3 = ctx->smem_path == 0 || ctx->smem_path == 3;
     // ---- K0: ASCII -> nt4 (idempotent on already-packed input) [+ 4-bit packed copy for the seeding kernel]
     if (use3) {
         if (ctx->d_pk.ensure((size_t)n * pk_stride * 4 + 64)) return -1;
@@ -112,22 +115,26 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
     SP.retry_n = ctl_u32(ctx, CTL_RETRY); SP.retry_ids = ctx->d_retry.as<i32>();
     if (use3) {
-        const size_t smem = smem_fast3_bytes(wide, lcap3, pk_stride);
+        const size_t smem = smem_fast3_bytes(wide, lcap3, qglob ? 0 : pk_stride);
         int per_sm = std::max(1, std::min(8, (int)((224 * 1024) / (smem + 1024))));
         if (ctx->smem_bps > 0) per_sm = std::min(per_sm, ctx->smem_bps);
-        const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * per_sm));
+        int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * per_sm));
         const int spill_cap = std::max(1, ctx->max_len + 1 - lcap3);
+        {   // keep the per-lane spill areas of long reads under ~8 GB
+            const size_t per_block = (size_t)128 * spill_cap * (wide ? 32 : 16);
+            fast_blocks = (int)std::max<size_t>(1, std::min<size_t>(fast_blocks, ((size_t)8 << 30) / per_block));
+        }
         if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;
         SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
         SP.lists = (Intv *)ctx->d_spill.p;
         if (ctx->split_p3 && opt->max_mem_intv > 0) {                        // pass 3 first: uniform forward-only lanes
             SP.split_p3 = 1; SP.out3_n = ctx->d_retry.as<i32>();
             SP.work_counter = ctl_u32(ctx, CTL_WORK2);
-            if (launch_smem_p3(SP, ctx->n_sms, wide ? 1 : 0, st)) return -1;
+            if (launch_smem_p3(SP, ctx->n_sms, wide ? 1 : 0, qglob ? 1 : 0, st)) return -1;
             SP.work_counter = ctl_u32(ctx, CTL_WORK);
             ++launches;
         }
-        if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, st)) return -1;
+        if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, qglob ? 1 : 0, st)) return -1;
         ++launches;
     } else if (ctx->smem_path != 1) {
         const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);

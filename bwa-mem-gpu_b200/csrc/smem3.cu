@@ -90,7 +90,9 @@ __global__ void pack4_kernel(u8 *seq, const i64 *off, int n_reads, u32 *pk, int 
     }
 }
 
-template <class PT, int LCAP, bool SPLIT>                                   // SPLIT: pass 3 ran in smem_p3_kernel
+// QGLOB: the read is too long to stage in shared memory (long reads): its 4-bit codes are fetched from the packed
+// copy in global memory instead (consecutive positions of a lane share a 32-byte sector, so these are L1 hits).
+template <class PT, int LCAP, bool SPLIT, bool QGLOB>                       // SPLIT: pass 3 ran in smem_p3_kernel
 __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(s3_raw);
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     constexpr int EQ = E::kQuads;
     uint4 *L = (uint4 *)s3_raw + threadIdx.x;                            // slot s: L[s * EQ * S3_THREADS]
     u32 *Q = (u32 *)((uint4 *)s3_raw + LCAP * EQ * S3_THREADS) + threadIdx.x;   // word w: Q[w * S3_THREADS]
+    const u32 *Qg = P.pk;                                                // QGLOB: packed codes of the current read
     const size_t gtid = (size_t)blockIdx.x * S3_THREADS + threadIdx.x;
     uint4 *SP = (uint4 *)P.lists + gtid * (size_t)P.spill_cap * EQ;      // spilled entry e: SP[e * EQ]
     const DevIndex &ix = P.ix;
@@ -120,7 +123,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
     int flen = 0;
     bool ptab = false;
 
-#define S3_QGET(pos) ((Q[((pos) >> 3) * S3_THREADS] >> (((pos) & 7) << 2)) & 7u)
+#define S3_QGET(pos) (((QGLOB ? __ldg(Qg + ((pos) >> 3)) : Q[((pos) >> 3) * S3_THREADS]) >> (((pos) & 7) << 2)) & 7u)
 #define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
 #define S3_PUSH(endv)                                                                                   \
     do {                                                                                                \
@@ -307,7 +310,8 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
                 out = P.out + (size_t)r * P.cap_out;
                 n_out = 0; i = -1;
                 if (len < min_seed_len) continue;                           // bwamem.c:267 (FIN again -> out_n = 0)
-                {                                                           // stage the packed read
+                if (QGLOB) Qg = P.pk + (size_t)r * P.pk_stride;
+                else {                                                      // stage the packed read
                     const uint4 *src = (const uint4 *)(P.pk + (size_t)r * P.pk_stride);
                     const int nq = (len + 31) >> 5;
                     for (int w = 0; w < nq; ++w) {
@@ -343,12 +347,13 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
 // Third seeding pass on its own (bwamem.c:167-182 around bwt_seed_strategy1, bwt.c:358-379): forward-only sweeps that
 // restart right after every seed, so every lane runs the same short loop -- no lists, no backward phase.  One read per
 // lane (persistent), requests issued at the bottom of the loop and consumed at the top like in the main kernel.
-template <class PT>
+template <class PT, bool QGLOB>
 __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(p3_raw);
     constexpr int EQ = Ent<PT>::kQuads;
     u32 *Q = (u32 *)p3_raw + threadIdx.x;                                   // word w: Q[w * S3_THREADS]
+    const u32 *Qg = P.pk;
     const DevIndex &ix = P.ix;
     const int min_seed_len = P.min_seed_len;
     const PT max_mem_intv = (PT)P.max_mem_intv;
@@ -408,6 +413,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
             out = P.out + (size_t)r * P.cap_out;
             n_out = 0; x = 0; flen = 0;
             if (len < min_seed_len) { x = len; continue; }                  // bwamem.c:267: no seeding at all
+            if (QGLOB) { Qg = P.pk + (size_t)r * P.pk_stride; continue; }
             const uint4 *src = (const uint4 *)(P.pk + (size_t)r * P.pk_stride);
             const int nq = (len + 31) >> 5;
             for (int w = 0; w < nq; ++w) {
@@ -429,23 +435,27 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
 }
 
-int launch_smem_p3(const SmemParams &p, int n_sms, int wide, cudaStream_t st)
+template <class PT, bool QGLOB>
+static int launch_p3_t(const SmemParams &p, int n_sms, cudaStream_t st)
 {
-    const size_t smem = (size_t)p.pk_stride * 4 * S3_THREADS;
+    const size_t smem = QGLOB ? 0 : (size_t)p.pk_stride * 4 * S3_THREADS;
     int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute(smem_p3_kernel<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    B200_CHECK(cudaFuncSetAttribute(smem_p3_kernel<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((smem_p3_kernel<PT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     int occ = 0;                                                            // resident blocks per SM (registers + shared memory)
-    if (wide) B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smem_p3_kernel<u64>, S3_THREADS, smem));
-    else B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, smem_p3_kernel<u32>, S3_THREADS, smem));
+    B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (smem_p3_kernel<PT, QGLOB>), S3_THREADS, smem));
     if (occ > 0) per_sm = std::min(per_sm, occ);
 #endif
     const int grid = std::max(1, std::min((p.n_reads + S3_THREADS - 1) / S3_THREADS, n_sms * per_sm));
-    if (wide) B200_LAUNCH(smem_p3_kernel<u64>, grid, S3_THREADS, smem, st, p);
-    else B200_LAUNCH(smem_p3_kernel<u32>, grid, S3_THREADS, smem, st, p);
+    B200_LAUNCH((smem_p3_kernel<PT, QGLOB>), grid, S3_THREADS, smem, st, p);
     B200_CHECK(cudaGetLastError());
     return 0;
+}
+
+int launch_smem_p3(const SmemParams &p, int n_sms, int wide, int qglob, cudaStream_t st)
+{
+    if (qglob) return wide ? launch_p3_t<u64, true>(p, n_sms, st) : launch_p3_t<u32, true>(p, n_sms, st);
+    return wide ? launch_p3_t<u64, false>(p, n_sms, st) : launch_p3_t<u32, false>(p, n_sms, st);
 }
 
 int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st)
@@ -456,18 +466,18 @@ int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cuda
     return 0;
 }
 
-size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)
+size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)             // pk_stride = 0: read not staged (QGLOB)
 {
     return (size_t)lcap * (wide ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
 }
 
-template <class PT, int LCAP, bool SPLIT>
+template <class PT, int LCAP, bool SPLIT, bool QGLOB>
 static int launch_fast3_ts(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
 {
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute(smem_fast3_kernel<PT, LCAP, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((smem_fast3_kernel<PT, LCAP, SPLIT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
 #endif
-    B200_LAUNCH((smem_fast3_kernel<PT, LCAP, SPLIT>), grid, S3_THREADS, smem, st, p);
+    B200_LAUNCH((smem_fast3_kernel<PT, LCAP, SPLIT, QGLOB>), grid, S3_THREADS, smem, st, p);
     B200_CHECK(cudaGetLastError());
     return 0;
 }
@@ -475,11 +485,16 @@ static int launch_fast3_ts(const SmemParams &p, int grid, size_t smem, cudaStrea
 template <class PT, int LCAP>
 static int launch_fast3_t(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
 {
-    return p.split_p3 ? launch_fast3_ts<PT, LCAP, true>(p, grid, smem, st) : launch_fast3_ts<PT, LCAP, false>(p, grid, smem, st);
+    return p.split_p3 ? launch_fast3_ts<PT, LCAP, true, false>(p, grid, smem, st) : launch_fast3_ts<PT, LCAP, false, false>(p, grid, smem, st);
 }
 
-int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, cudaStream_t st)
+int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, int qglob, cudaStream_t st)
 {
+    if (qglob) {                                                            // long reads: lcap 16, read in global memory
+        const size_t smem = smem_fast3_bytes(wide, 16, 0);
+        if (wide) return p.split_p3 ? launch_fast3_ts<u64, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<u64, 16, false, true>(p, grid, smem, st);
+        return p.split_p3 ? launch_fast3_ts<u32, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<u32, 16, false, true>(p, grid, smem, st);
+    }
     const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
     if (wide) {
         if (lcap == 8) return launch_fast3_t<u64, 8>(p, grid, smem, st);

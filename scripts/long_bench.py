@@ -17,6 +17,8 @@ def main():
     ap.add_argument("--check", type=int, default=300)
     ap.add_argument("--contigs", type=int, default=4)
     ap.add_argument("--contig-len", type=int, default=25_000_000)
+    ap.add_argument("--chunk", type=int, default=4096, help="reads per pipeline chunk")
+    ap.add_argument("--tune", default="", help="comma-separated key=value context tunables")
     a = ap.parse_args()
     contigs = synth.make_genome([a.contig_len] * a.contigs)
     rng = np.random.default_rng(5)
@@ -32,7 +34,10 @@ def main():
     off = np.concatenate([[0], np.cumsum([len(s) for _, s in seqs])]).astype(np.int64)
     hidx = L.HostIndex(contigs)
     ctx = L.Context(0)
-    ctx.tune("chunk_reads", 4096)
+    ctx.tune("chunk_reads", a.chunk)
+    for kv in filter(None, a.tune.split(",")):
+        k, v = kv.split("=")
+        ctx.tune(k, int(v))
     ctx.upload_host_index(hidx)
     opt = abi.default_opt()
     ctx.batch_upload(flat, off)
@@ -41,7 +46,7 @@ def main():
     ms = ctx.batch_run(opt, want_stage_ms=True)
     wall = time.time() - t0
     cnt = ctx.counters()
-    res = {"reads": a.reads, "bases": int(off[-1]), "device_ms": ms[5], "wall_s": wall,
+    res = {"chunk_reads": a.chunk, "tune": a.tune, "reads": a.reads, "bases": int(off[-1]), "device_ms": ms[5], "wall_s": wall,
            "stage_ms": dict(zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], ms)),
            "reads_per_s": a.reads / (ms[5] * 1e-3), "mbases_per_s": off[-1] / (ms[5] * 1e-3) / 1e6,
            "ksw_extend2_gcups": cnt["cells"] / (ms[4] * 1e-3) / 1e9, "counters": cnt}

@@ -382,10 +382,12 @@ def test_align_long_reads(backend):
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("tune", [{"force_wide": 1}, {"force_wide": 1, "kmer_k": 0}, {"kmer_k": 0}, {"kmer_k": 6}, {"kmer_k": 12}])
+@pytest.mark.parametrize("tune", [{"force_wide": 1}, {"force_wide": 1, "kmer_k": 0}, {"kmer_k": 0}, {"kmer_k": 6}, {"kmer_k": 12},
+                                  {"smem_path": 3}, {"smem_path": 3, "force_wide": 1}, {"smem_path": 3, "split_p3": 0}])
 def test_seeding_variants(backend, tune):
     """The 64-bit-position templates of the seeding kernel (used when the doubled text reaches 2^32 rows) forced on a
-    small genome, and k-mer interval tables of other depths: intervals and regions unchanged."""
+    small genome, k-mer interval tables of other depths, and the long-read variant that fetches the read's codes from
+    global memory (smem_path 3): intervals and regions unchanged."""
     from bwa_mem_gpu_b200 import lib as L
     gname = "rep"
     lib = cm.backend_lib(backend)
