@@ -177,6 +177,9 @@ int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t 
 int launch_gather_regs(const mem_alnreg_t *src, const i64 *src_off, const i32 *n, const i64 *dst_off,
                        int n_reads, mem_alnreg_t *dst, cudaStream_t st);
 int launch_seed_sw(const SeedSwParams &P, int n_sms, cudaStream_t st);
+struct SswJob;
+bool seed_sw2_supported(const mem_opt_t *opt);
+int launch_seed_sw2(const SeedSwParams &P, SswJob *jobs, i64 n_seeds_total, i32 *score_out, unsigned *n_jobs, int n_sms, cudaStream_t st);
 int launch_exclusive_scan(const i32 *in, i64 *out /* n+1 */, int n, i64 *tmp, cudaStream_t st);
 int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 *ck, u64 *cl, cudaStream_t st);
 int launch_extend_batch(const DevIndex &ix, i64 n, const u64 *ik, int is_back, u64 *ok, cudaStream_t st);

@@ -47,7 +47,7 @@ extern "C" b200_ctx_t *b200_ctx_create(int device)
 extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
 {
     if (!ctx || !key) { b200_set_error("null argument"); return -1; }
-    if (!strcmp(key, "chunk_reads")) { if (value < 1) value = 1; ctx->chunk_reads = (int)value; }
+    if (!strcmp(key, "chunk_reads")) { if (value < 1) value = 1; ctx->chunk_reads = (int)value; ctx->chunk_user = true; }
     else if (!strcmp(key, "smem_lcap")) ctx->smem_lcap = (int)value;
     else if (!strcmp(key, "cap_intv")) ctx->cap_intv = (int)value;
     else if (!strcmp(key, "ext_path")) ctx->ext_path = (int)value;
@@ -62,6 +62,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_rowsync")) ctx->ext_rowsync = (int)value;
     else if (!strcmp(key, "ext_sort")) ctx->ext_sort = (int)value;
     else if (!strcmp(key, "ext_phased")) ctx->ext_phased = (int)value;
+    else if (!strcmp(key, "ssw_path")) ctx->ssw_path = (int)value;
     else if (!strcmp(key, "l2_persist")) ctx->l2_persist = (int)value;
     else if (!strcmp(key, "idx_group_cap")) ctx->idx_group_cap = value > ((i64)1 << 30) ? ((i64)1 << 30) : value;   // before b200_index_build_device
     else if (!strcmp(key, "idx_tie_cap")) ctx->idx_tie_cap = value;

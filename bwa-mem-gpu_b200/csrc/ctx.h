@@ -36,7 +36,7 @@ struct b200_ctx {
     std::vector<i64> h_off;
 
     // tunables
-    int chunk_reads = 1 << 20;
+    int chunk_reads = 1 << 20; bool chunk_user = false;   // reads per pipeline chunk (tunable; unset: scaled down for long reads, pipeline.cu)
     int cap_intv = 0;                          // 0 = auto from read length
     int ext_path = 0;                          // 0 = auto, 1 = force the general warp-per-read kernel, 2 = force the round-based fast path
     int smem_path = 0;                         // 0 = auto (smem3 for short reads), 2 = smem2 kernel, 1 = general kernel only
@@ -44,6 +44,7 @@ struct b200_ctx {
     size_t l2_setaside = 0, l2_window = 0;
     int ext_bin0 = 0, ext_bin1 = 0;            // > 0: flank-length limits of extension bins 0 / 1 (default 32 / 64)
     int ext_bps = 0;                           // > 0: cap on resident blocks per SM of the extension DP kernel
+    int ssw_path = 0;                          // mem_seed_sw: 0 = one alignment per lane (seedsw2.cu), 1 = lane-group restatement of the striped code (seedsw.cu)
     int ext_phased = 1;                        // byte-score extension kernel: warp-wide phases (left sides, retries, right sides, next jobs)
     int ext_sort = 1;                          // byte-score extension kernel: jobs handed out ordered by flank shape (ext3.cu)
     int ext_rowsync = 1;                       // byte-score extension kernel: a lane finishes its row before the warp's control slot (ext3.cu)

@@ -230,9 +230,15 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
             SP.long_reads = ctx->d_pb.as<i32>(); SP.n_long = (int)lr.size();
             SP.slen_cap = (SSW_MAX_Q + 7) / 8 + 1;
             SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = (u64 *)ctl_u64(ctx, CTL_STATS) + CNT_SEEDSW; SP.overflow = (int *)ctl_u32(ctx, CTL_OVF2);
-            if (launch_seed_sw(SP, ctx->n_sms, st)) return -1;
+            if (ctx->ssw_path != 1 && seed_sw2_supported(opt)) {            // one Smith-Waterman per lane (seedsw2.cu)
+                if (ctx->d_pc.ensure((size_t)(tot_seeds + 1) * 32) || ctx->d_pd.ensure((size_t)(tot_seeds + 1) * 4)) return -1;
+                if (launch_seed_sw2(SP, (SswJob *)ctx->d_pc.p, tot_seeds, ctx->d_pd.as<i32>(), ctl_u32(ctx, 7), ctx->n_sms, st)) return -1;
+                launches += 3;
+            } else {                                                         // lane-group restatement of the striped code (seedsw.cu)
+                if (launch_seed_sw(SP, ctx->n_sms, st)) return -1;
+                ++launches;
+            }
             B200_CHECK(cudaStreamSynchronize(st));                       // mh / lr are stack-owned host buffers
-            ++launches;
         }
     }
     tm.mark(st);
@@ -379,6 +385,15 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     return 0;
 }
 
+// Reads per pipeline chunk: the tunable when it was set, else 2^20 reads but at most ~2^30 bases (long reads: the
+// per-read interval / list buffers grow with the read length, while the lane-per-read kernels want >= 10^5 reads in flight)
+static int eff_chunk(const b200_ctx *ctx)
+{
+    if (ctx->chunk_user) return ctx->chunk_reads;
+    const i64 by_bases = ((i64)1 << 30) / std::max(1, ctx->max_len);
+    return (int)std::max<i64>(4096, std::min<i64>(ctx->chunk_reads, by_bases));
+}
+
 extern "C" int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stage_ms)
 {
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
@@ -389,8 +404,9 @@ extern "C" int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stag
     if (ctx->d_final_n.ensure((size_t)ctx->n_reads * 4 + 4)) return -1;
     cudaEvent_t ea = nullptr, eb = nullptr;               // device-side bracket of the whole batch on the launching stream
     if (stage_ms) { cudaEventCreate(&ea); cudaEventCreate(&eb); cudaEventRecord(ea, ctx->st); }
-    for (int r0 = 0; r0 < ctx->n_reads; r0 += ctx->chunk_reads) {
-        int n = std::min(ctx->chunk_reads, ctx->n_reads - r0);
+    const int chunk = eff_chunk(ctx);
+    for (int r0 = 0; r0 < ctx->n_reads; r0 += chunk) {
+        int n = std::min(chunk, ctx->n_reads - r0);
         int rc = b200_run_chunk(ctx, opt, r0, n, 5, stage_ms);
         if (rc) return rc;
     }
@@ -454,8 +470,9 @@ extern "C" int64_t b200_collect_intv_batch(b200_ctx_t *ctx, const mem_opt_t *opt
     if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
     i64 tot = 0;
     std::vector<Intv> tmp;
-    for (int r0 = 0; r0 < n_reads; r0 += ctx->chunk_reads) {
-        int n = std::min(ctx->chunk_reads, n_reads - r0);
+    const int chunk = eff_chunk(ctx);
+    for (int r0 = 0; r0 < n_reads; r0 += chunk) {
+        int n = std::min(chunk, n_reads - r0);
         int rc = b200_run_chunk(ctx, opt, r0, n, 1, nullptr);
         if (rc) return rc;
         const int cap_intv = auto_cap_intv(ctx, opt);
@@ -481,8 +498,9 @@ extern "C" int b200_chain_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int stage
     if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
     i64 nc = 0, ns = 0;
     g_chain_stage = stage;
-    for (int r0 = 0; r0 < n_reads; r0 += ctx->chunk_reads) {
-        int n = std::min(ctx->chunk_reads, n_reads - r0);
+    const int chunk = eff_chunk(ctx);
+    for (int r0 = 0; r0 < n_reads; r0 += chunk) {
+        int n = std::min(chunk, n_reads - r0);
         int rc = b200_run_chunk(ctx, opt, r0, n, 3, nullptr);
         if (rc) { g_chain_stage = 1; return rc; }
         std::vector<i64> soff((size_t)n + 1);

@@ -17,7 +17,7 @@ def main():
     ap.add_argument("--check", type=int, default=300)
     ap.add_argument("--contigs", type=int, default=4)
     ap.add_argument("--contig-len", type=int, default=25_000_000)
-    ap.add_argument("--chunk", type=int, default=4096, help="reads per pipeline chunk")
+    ap.add_argument("--chunk", type=int, default=0, help="reads per pipeline chunk (0 = the library's own choice)")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables")
     a = ap.parse_args()
     contigs = synth.make_genome([a.contig_len] * a.contigs)
@@ -32,13 +32,13 @@ def main():
     seqs.sort(key=lambda t: t[0])
     flat = np.ascontiguousarray(np.concatenate([s for _, s in seqs]).astype(np.uint8))
     off = np.concatenate([[0], np.cumsum([len(s) for _, s in seqs])]).astype(np.int64)
-    hidx = L.HostIndex(contigs)
     ctx = L.Context(0)
-    ctx.tune("chunk_reads", a.chunk)
+    if a.chunk > 0:
+        ctx.tune("chunk_reads", a.chunk)
     for kv in filter(None, a.tune.split(",")):
         k, v = kv.split("=")
         ctx.tune(k, int(v))
-    ctx.upload_host_index(hidx)
+    hidx = ctx.build_index_device(contigs)
     opt = abi.default_opt()
     ctx.batch_upload(flat, off)
     ctx.batch_run(opt)

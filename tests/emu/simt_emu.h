@@ -132,6 +132,7 @@ struct int4 { int x, y, z, w; };
 struct int2 { int x, y; };
 struct ulonglong2 { unsigned long long x, y; };
 inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
+inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 inline int4 make_int4(int x, int y, int z, int w) { return int4{x, y, z, w}; }
 inline int2 make_int2(int x, int y) { return int2{x, y}; }
 inline ulonglong2 make_ulonglong2(unsigned long long x, unsigned long long y) { return ulonglong2{x, y}; }
@@ -276,6 +277,10 @@ inline unsigned __viaddmax_s16x2_relu(unsigned a, unsigned b, unsigned c)
 { return emu::pk16(std::max<int>(0, std::max<int>(emu::wrap16(emu::lo16(a) + emu::lo16(b)), emu::lo16(c))), std::max<int>(0, std::max<int>(emu::wrap16(emu::hi16(a) + emu::hi16(b)), emu::hi16(c)))); }
 inline unsigned __vimax3_s16x2(unsigned a, unsigned b, unsigned c)
 { return emu::pk16(std::max<int>(emu::lo16(a), std::max<int>(emu::lo16(b), emu::lo16(c))), std::max<int>(emu::hi16(a), std::max<int>(emu::hi16(b), emu::hi16(c)))); }
+inline unsigned __vimax3_s16x2_relu(unsigned a, unsigned b, unsigned c)
+{ return emu::pk16(std::max<int>(0, std::max<int>(emu::lo16(a), std::max<int>(emu::lo16(b), emu::lo16(c)))), std::max<int>(0, std::max<int>(emu::hi16(a), std::max<int>(emu::hi16(b), emu::hi16(c))))); }
+inline unsigned __vmaxs2(unsigned a, unsigned b)
+{ return emu::pk16(std::max<int>(emu::lo16(a), emu::lo16(b)), std::max<int>(emu::hi16(a), emu::hi16(b))); }
 inline unsigned __vmaxu2(unsigned a, unsigned b)
 { return emu::pk16(std::max<unsigned>(a & 0xffffu, b & 0xffffu), std::max<unsigned>(a >> 16, b >> 16)); }
 // prmt.b32 default mode: selector nibble bit 3 = replicate the sign bit of the selected byte

@@ -354,17 +354,29 @@ def _long_reads(gname, n, seed, lo=800, hi=3000, sub=0.06, indel=0.01):
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
 @pytest.mark.parametrize("gname", ["small", "rep"])
-def test_flt_chained_seeds_long_reads(backend, gname):
-    """mem_flt_chained_seeds / mem_seed_sw (bwamem.c:605-622, 578-603): surviving seeds and their SW scores."""
+@pytest.mark.parametrize("scoring", ["default", "ont"])
+def test_flt_chained_seeds_long_reads(backend, gname, scoring):
+    """mem_flt_chained_seeds / mem_seed_sw (bwamem.c:605-622, 578-603): surviving seeds and their SW scores, from the
+    one-alignment-per-lane kernel (seedsw2.cu, default) and from the lane-group restatement of the striped code."""
     idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
     opt = abi.default_opt()
+    if scoring == "ont":                                   # cheap mismatches, cheap and unequal gap costs (in the spirit of -x ont2d)
+        opt.a, opt.b, opt.o_del, opt.o_ins, opt.e_del, opt.e_ins = 2, 3, 2, 7, 1, 2
+        opt.min_seed_len = 14
+        abi.fill_scmat(opt)
     seqs, off = _long_reads(gname, _sizes(backend, 24, 600), seed=3)
     a1 = idx.chains(opt, seqs, off, stage=1, cap_chn_per_read=512, cap_seed_per_read=16384)
     a = idx.chains(opt, seqs, off, stage=2, cap_chn_per_read=512, cap_seed_per_read=16384)
     b = ctx.chains(opt, seqs, off, stage=2, cap_chn_per_read=512, cap_seed_per_read=16384)
-    assert len(a[2]) < len(a1[2])                          # the filter really removed seeds
-    for x, y in zip(a, b):
-        assert np.array_equal(x, y)
+    ctx.tune("ssw_path", 1)
+    try:
+        c = ctx.chains(opt, seqs, off, stage=2, cap_chn_per_read=512, cap_seed_per_read=16384)
+    finally:
+        ctx.tune("ssw_path", 0)
+    if scoring == "default":
+        assert len(a[2]) < len(a1[2])                      # the filter really removed seeds
+    for x, y, z in zip(a, b, c):
+        assert np.array_equal(x, y) and np.array_equal(x, z)
 
 
 @needs_ref
