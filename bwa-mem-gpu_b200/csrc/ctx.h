@@ -24,6 +24,7 @@ struct b200_ctx {
     int device = 0;
     int n_sms = 148;
     cudaStream_t st = nullptr;
+    cudaStream_t st_h2d = nullptr, st_d2h = nullptr;    // copy streams of b200_align_batch (created on first use)
     bool has_index = false;
     DevIndex ix;
     DevBuf d_occ32, d_kmer, d_retry, d_pk, d_spill, d_jobs0, d_jobs1, d_jobs2, d_jobs3, d_jsort, d_rstate, d_njobs, d_bwt, d_sa, d_sa_full, d_pac, d_ann_off, d_ann_len, d_ann_alt;

@@ -363,6 +363,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
             if (nb.ensure(need * 2)) return -1;
             if (ctx->total_regs) B200_CHECK(cudaMemcpyAsync(nb.p, ctx->d_final.p, (size_t)ctx->total_regs * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st));
             B200_CHECK(cudaStreamSynchronize(st));
+            if (ctx->st_d2h) B200_CHECK(cudaStreamSynchronize(ctx->st_d2h));   // b200_align_batch: earlier chunks may still be on their way out
             ctx->d_final.release();
             ctx->d_final = nb;
         }
@@ -453,13 +454,66 @@ extern "C" int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out)
     return 0;
 }
 
+// Host buffers in, host buffers out, with the copies overlapped with the kernels: the reads of chunk k+1.. travel on
+// their own stream while chunk k computes (the compute stream waits on a per-chunk event), and each chunk's records go
+// back on a third stream as soon as its read-ordered gather is done.  With pinned host buffers only the first chunk's
+// upload and the last chunk's download are exposed; pageable buffers make the same calls behave synchronously.
 extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
                                     const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
 {
-    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
-    int rc = b200_batch_run(ctx, opt, nullptr);
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    B200_CHECK(cudaSetDevice(ctx->device));
+    if (!ctx->st_h2d) {
+        B200_CHECK(cudaStreamCreateWithFlags(&ctx->st_h2d, cudaStreamNonBlocking));
+        B200_CHECK(cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking));
+    }
+    const i64 base = n_reads ? off[0] : 0, nbytes = n_reads ? off[n_reads] - base : 0;
+    ctx->h_off.resize((size_t)n_reads + 1);
+    int mx = 0;
+    for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
+    for (int i = 0; i < n_reads; ++i) mx = std::max<int>(mx, (int)(off[i + 1] - off[i]));
+    if (ctx->d_seq.ensure((size_t)nbytes + 64) || ctx->d_off.ensure(((size_t)n_reads + 1) * 8) ||
+        ctx->d_final_n.ensure((size_t)n_reads * 4 + 4)) return -1;
+    ctx->n_reads = n_reads; ctx->n_bytes = nbytes; ctx->max_len = mx;
+    ctx->total_regs = 0;
+    memset(ctx->stats, 0, sizeof(ctx->stats));
+    B200_CHECK(cudaMemcpyAsync(ctx->d_off.p, ctx->h_off.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, ctx->st));
+    const int chunk = eff_chunk(ctx);
+    const int n_chunks = n_reads ? (n_reads + chunk - 1) / chunk : 0;
+    std::vector<cudaEvent_t> up((size_t)n_chunks, nullptr);
+    int rc = 0;
+    for (int k = 0; k < n_chunks && !rc; ++k) {                                        // all uploads queued up front, one event per chunk
+        const int r0 = k * chunk, n = std::min(chunk, n_reads - r0);
+        const i64 b0 = ctx->h_off[r0], b1 = ctx->h_off[r0 + n];
+        if (cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming) != cudaSuccess) { b200_set_error("cudaEventCreate failed"); rc = -1; break; }
+        if (b1 > b0 && cudaMemcpyAsync(ctx->d_seq.as<u8>() + b0, seqs + base + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, ctx->st_h2d) != cudaSuccess) {
+            b200_set_error("read upload failed"); rc = -1; break;
+        }
+        cudaEventRecord(up[k], ctx->st_h2d);
+    }
+    i64 copied = 0;                                                                     // records already on their way to the host
+    for (int k = 0; k < n_chunks && !rc; ++k) {
+        const int r0 = k * chunk, n = std::min(chunk, n_reads - r0);
+        cudaStreamWaitEvent(ctx->st, up[k], 0);
+        const i64 before = ctx->total_regs;
+        rc = b200_run_chunk(ctx, opt, r0, n, 5, nullptr);                               // returns with the chunk's gather finished
+        if (rc) break;
+        if (out_n) cudaMemcpyAsync(out_n + r0, ctx->d_final_n.as<i32>() + r0, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->st_d2h);
+        if (ctx->total_regs <= cap && ctx->total_regs > before) {
+            cudaMemcpyAsync(out_regs + before, ctx->d_final.as<mem_alnreg_t>() + before, (size_t)(ctx->total_regs - before) * sizeof(mem_alnreg_t),
+                            cudaMemcpyDeviceToHost, ctx->st_d2h);
+            copied = ctx->total_regs;
+        }
+    }
+    cudaStreamSynchronize(ctx->st_h2d);
+    cudaError_t e = cudaStreamSynchronize(ctx->st_d2h);
+    cudaStreamSynchronize(ctx->st);
+    for (cudaEvent_t ev : up) if (ev) cudaEventDestroy(ev);
     if (rc) return rc;
-    return b200_batch_download(ctx, cap, out_regs, out_n);
+    if (e != cudaSuccess) { b200_set_error("result download failed: %s", cudaGetErrorString(e)); return -1; }
+    if (ctx->total_regs > cap) return -ctx->total_regs;
+    (void)copied;
+    return ctx->total_regs;
 }
 
 // ---- stage seams (parity tests) -----------------------------------------------------------------
