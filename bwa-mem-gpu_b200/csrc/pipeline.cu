@@ -32,8 +32,14 @@ extern "C" int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *se
     const i64 base = n_reads ? off[0] : 0, nbytes = n_reads ? off[n_reads] - base : 0;
     ctx->h_off.resize((size_t)n_reads + 1);
     int mx = 0;
-    for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
-    for (int i = 0; i < n_reads; ++i) mx = std::max<int>(mx, (int)(off[i + 1] - off[i]));
+    if (n_reads && base == 0) memcpy(ctx->h_off.data(), off, ((size_t)n_reads + 1) * 8);
+    else for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
+    {
+        i64 m = 0;
+        const i64 *h = ctx->h_off.data();
+        for (int i = 0; i < n_reads; ++i) { const i64 d = h[i + 1] - h[i]; m = d > m ? d : m; }
+        mx = (int)m;
+    }
     if (ctx->d_seq.ensure((size_t)nbytes + 64) || ctx->d_off.ensure(((size_t)n_reads + 1) * 8)) return -1;
     if (nbytes) B200_CHECK(cudaMemcpyAsync(ctx->d_seq.p, seqs + base, (size_t)nbytes, cudaMemcpyHostToDevice, ctx->st));
     B200_CHECK(cudaMemcpyAsync(ctx->d_off.p, ctx->h_off.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, ctx->st));
@@ -207,13 +213,20 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     // ---- K3b: mem_flt_chained_seeds (bwamem.c:605-622) for the reads long enough to need it
     if (stop_after != 3 || g_chain_stage >= 2) {
         // min_l and min_HSP_score depend on the read length only; log() is evaluated on the host like the reference does
-        std::vector<i32> by_len((size_t)ctx->max_len + 1, -2), mh((size_t)n), lr;
-        for (int r = 0; r < n; ++r) {
+        std::vector<i32> by_len((size_t)ctx->max_len + 1, -2), mh, lr;
+        auto hsp_of = [&](int l_query) -> int {                          // -1: too short for the filter (bwamem.c:609)
+            const double min_l = opt->min_chain_weight ? 1.1f * opt->min_chain_weight : 5.5f * log((double)l_query);
+            return (l_query == 0 || min_l > 0.05f * l_query) ? -1 : (int)(opt->a * min_l + .499);
+        };
+        // min_l - 0.05 l is concave in l (a constant or 5.5 ln l, minus a line): when it is positive at both ends of
+        // [min_seed_len, max_len] it is positive for every read that can carry a seed (bwamem.c:267), i.e. no read of the
+        // chunk reaches the filter, and the per-read pass below (10^6 host iterations per chunk) is skipped
+        const int l_lo = std::max(1, std::min(opt->min_seed_len, ctx->max_len));
+        const bool none_long = ctx->max_len < 1 || (hsp_of(ctx->max_len) < 0 && hsp_of(l_lo) < 0);
+        if (!none_long) mh.resize((size_t)n);
+        for (int r = 0; r < n && !none_long; ++r) {
             const int l_query = (int)(ctx->h_off[r0 + r + 1] - ctx->h_off[r0 + r]);
-            if (by_len[l_query] == -2) {                                 // -1: too short for the filter (bwamem.c:609)
-                const double min_l = opt->min_chain_weight ? 1.1f * opt->min_chain_weight : 5.5f * log((double)l_query);
-                by_len[l_query] = (l_query == 0 || min_l > 0.05f * l_query) ? -1 : (int)(opt->a * min_l + .499);
-            }
+            if (by_len[l_query] == -2) by_len[l_query] = hsp_of(l_query);
             mh[r] = by_len[l_query];
             if (by_len[l_query] >= 0) lr.push_back(r);
         }
@@ -470,8 +483,14 @@ extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n
     const i64 base = n_reads ? off[0] : 0, nbytes = n_reads ? off[n_reads] - base : 0;
     ctx->h_off.resize((size_t)n_reads + 1);
     int mx = 0;
-    for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
-    for (int i = 0; i < n_reads; ++i) mx = std::max<int>(mx, (int)(off[i + 1] - off[i]));
+    if (n_reads && base == 0) memcpy(ctx->h_off.data(), off, ((size_t)n_reads + 1) * 8);
+    else for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
+    {
+        i64 m = 0;
+        const i64 *h = ctx->h_off.data();
+        for (int i = 0; i < n_reads; ++i) { const i64 d = h[i + 1] - h[i]; m = d > m ? d : m; }
+        mx = (int)m;
+    }
     if (ctx->d_seq.ensure((size_t)nbytes + 64) || ctx->d_off.ensure(((size_t)n_reads + 1) * 8) ||
         ctx->d_final_n.ensure((size_t)n_reads * 4 + 4)) return -1;
     ctx->n_reads = n_reads; ctx->n_bytes = nbytes; ctx->max_len = mx;
