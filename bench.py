@@ -281,11 +281,13 @@ def main():
     cap = int(regs_total * 1.1) + 1024
     pin_out = torch.empty(cap * abi.ALNREG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     pin_n = torch.empty(a.reads, dtype=torch.int32).pin_memory()
+    pin_off = torch.empty(a.reads + 1, dtype=torch.int64).pin_memory()
+    pin_off.numpy()[:] = off
     import ctypes as C
 
     def e2e_step():
         tot = ctx.lib.b200_align_batch(ctx.h, C.byref(opt), C.c_int(a.reads), C.c_void_p(pin_seq.data_ptr()),
-                                       off.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(cap),
+                                       C.c_void_p(pin_off.data_ptr()), C.c_int64(cap),
                                        C.c_void_p(pin_out.data_ptr()), C.c_void_p(pin_n.data_ptr()))
         if tot < 0:
             raise SystemExit(f"b200_align_batch failed: {ctx.lib.b200_last_error().decode()} ({tot})")

@@ -35,6 +35,7 @@ struct b200_ctx {
     DevBuf d_seq, d_off;
     int n_reads = 0; i64 n_bytes = 0; int max_len = 0;
     std::vector<i64> h_off;
+    const i64 *hoff = nullptr;                 // host view of the batch's read offsets (h_off, or the caller's array during b200_align_batch)
 
     // tunables
     int chunk_reads = 1 << 20; bool chunk_user = false;   // reads per pipeline chunk (tunable; unset: scaled down for long reads, pipeline.cu)

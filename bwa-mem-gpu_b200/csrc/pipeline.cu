@@ -46,6 +46,7 @@ extern "C" int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *se
     B200_CHECK(cudaStreamSynchronize(ctx->st));
     ctx->n_reads = n_reads; ctx->n_bytes = nbytes; ctx->max_len = mx;
     ctx->total_regs = 0;
+    ctx->hoff = ctx->h_off.data();
     return 0;
 }
 
@@ -73,7 +74,8 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
 {
     cudaStream_t st = ctx->st;
     const i64 *d_off = ctx->d_off.as<i64>() + r0;
-    const i64 byte0 = ctx->h_off[r0], nbytes = ctx->h_off[r0 + n] - byte0;
+    if (!ctx->hoff) { b200_set_error("no resident batch (b200_batch_upload first)"); return -1; }
+    const i64 byte0 = ctx->hoff[r0], nbytes = ctx->hoff[r0 + n] - byte0;
     (void)nbytes;
     StageTimer tm; tm.init(stage_ms != nullptr);
     if (ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
@@ -95,7 +97,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     if (use3) {
         if (ctx->d_pk.ensure((size_t)n * pk_stride * 4 + 64)) return -1;
         if (launch_pack4(ctx->d_seq.as<u8>(), d_off, n, ctx->d_pk.as<u32>(), pk_stride, st)) return -1;
-    } else if (launch_pack_reads(ctx->d_seq.as<u8>() + byte0, ctx->h_off[r0 + n] - byte0, st)) return -1;
+    } else if (launch_pack_reads(ctx->d_seq.as<u8>() + byte0, ctx->hoff[r0 + n] - byte0, st)) return -1;
     ++launches;
     tm.mark(st);
 
@@ -225,7 +227,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         const bool none_long = ctx->max_len < 1 || (hsp_of(ctx->max_len) < 0 && hsp_of(l_lo) < 0);
         if (!none_long) mh.resize((size_t)n);
         for (int r = 0; r < n && !none_long; ++r) {
-            const int l_query = (int)(ctx->h_off[r0 + r + 1] - ctx->h_off[r0 + r]);
+            const int l_query = (int)(ctx->hoff[r0 + r + 1] - ctx->hoff[r0 + r]);
             if (by_len[l_query] == -2) by_len[l_query] = hsp_of(l_query);
             mh[r] = by_len[l_query];
             if (by_len[l_query] >= 0) lr.push_back(r);
@@ -481,13 +483,16 @@ extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n
         B200_CHECK(cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking));
     }
     const i64 base = n_reads ? off[0] : 0, nbytes = n_reads ? off[n_reads] - base : 0;
-    ctx->h_off.resize((size_t)n_reads + 1);
+    if (n_reads && base == 0) { ctx->h_off.clear(); ctx->hoff = off; }                  // offsets read in place for the duration of the call
+    else {
+        ctx->h_off.resize((size_t)n_reads + 1);
+        for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
+        ctx->hoff = ctx->h_off.data();
+    }
     int mx = 0;
-    if (n_reads && base == 0) memcpy(ctx->h_off.data(), off, ((size_t)n_reads + 1) * 8);
-    else for (int i = 0; i <= n_reads; ++i) ctx->h_off[i] = n_reads ? off[i] - base : 0;
     {
         i64 m = 0;
-        const i64 *h = ctx->h_off.data();
+        const i64 *h = ctx->hoff;
         for (int i = 0; i < n_reads; ++i) { const i64 d = h[i + 1] - h[i]; m = d > m ? d : m; }
         mx = (int)m;
     }
@@ -496,15 +501,15 @@ extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n
     ctx->n_reads = n_reads; ctx->n_bytes = nbytes; ctx->max_len = mx;
     ctx->total_regs = 0;
     memset(ctx->stats, 0, sizeof(ctx->stats));
-    B200_CHECK(cudaMemcpyAsync(ctx->d_off.p, ctx->h_off.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, ctx->st));
     const int chunk = eff_chunk(ctx);
     const int n_chunks = n_reads ? (n_reads + chunk - 1) / chunk : 0;
     std::vector<cudaEvent_t> up((size_t)n_chunks, nullptr);
     int rc = 0;
     for (int k = 0; k < n_chunks && !rc; ++k) {                                        // all uploads queued up front, one event per chunk
         const int r0 = k * chunk, n = std::min(chunk, n_reads - r0);
-        const i64 b0 = ctx->h_off[r0], b1 = ctx->h_off[r0 + n];
+        const i64 b0 = ctx->hoff[r0], b1 = ctx->hoff[r0 + n];
         if (cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming) != cudaSuccess) { b200_set_error("cudaEventCreate failed"); rc = -1; break; }
+        cudaMemcpyAsync(ctx->d_off.as<i64>() + r0, ctx->hoff + r0, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, ctx->st_h2d);
         if (b1 > b0 && cudaMemcpyAsync(ctx->d_seq.as<u8>() + b0, seqs + base + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, ctx->st_h2d) != cudaSuccess) {
             b200_set_error("read upload failed"); rc = -1; break;
         }
@@ -528,6 +533,7 @@ extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n
     cudaError_t e = cudaStreamSynchronize(ctx->st_d2h);
     cudaStreamSynchronize(ctx->st);
     for (cudaEvent_t ev : up) if (ev) cudaEventDestroy(ev);
+    if (ctx->hoff == off) ctx->hoff = nullptr;                                          // the caller's array is not ours to keep
     if (rc) return rc;
     if (e != cudaSuccess) { b200_set_error("result download failed: %s", cudaGetErrorString(e)); return -1; }
     if (ctx->total_regs > cap) return -ctx->total_regs;
