@@ -336,7 +336,8 @@ def main():
             "stage_ms": {k: float(v) / a.steps for k, v in zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], stage)},
             "counters": cnt,
             "roofline": {"bound": "hbm", "kernel": SEED_KERNELS, "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(SEED_KERNELS),
+                         "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": measured_traffic(SEED_KERNELS) if (a.contigs, a.contig_len, a.read_len) == (4, 25_000_000, 150) else None,
                          "peak_source": peak_src, "algorithmic_bytes": alg_bytes, "launches_per_step": n_launch,
                          "ms_per_launch": smem_ms / n_launch,
                          "note": "algorithmic bytes = 64 B x Occ blocks touched by bwt_extend (1 or 2 per call, "
