@@ -89,10 +89,12 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
     int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 12;
     lcap3 = lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);
-    // reads too long to stage in shared memory keep their 4-bit codes in global memory (smem_path 3 forces that variant)
-    const bool qglob = ctx->smem_path == 3 || (ctx->smem_path == 0 && smem_fast3_bytes(wide, lcap3, pk_stride) > 100 * 1024);
+    // reads too long to stage in shared memory: smem_fast_kernel (smem2.cu) by default -- measured faster on 1-10 kbp reads
+    // (575 vs 758 ms per 200 k reads) -- or, with smem_path 3, the fast3 kernels fetching the read's 4-bit codes from global memory
+    const bool fits3 = smem_fast3_bytes(wide, lcap3, pk_stride) <= 100 * 1024;
+    const bool qglob = ctx->smem_path == 3;
     if (qglob) lcap3 = 16;
-    const bool use3 = ctx->smem_path == 0 || ctx->smem_path == 3;
+    const bool use3 = (ctx->smem_path == 0 && fits3) || qglob;
     // ---- K0: ASCII -> nt4 (idempotent on already-packed input) [+ 4-bit packed copy for the seeding kernel]
     if (use3) {
         if (ctx->d_pk.ensure((size_t)n * pk_stride * 4 + 64)) return -1;
