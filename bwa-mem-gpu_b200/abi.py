@@ -71,6 +71,12 @@ assert ALNREG_DTYPE.itemsize == 88
 PESTAT_DTYPE = np.dtype([("low", "<i4"), ("high", "<i4"), ("failed", "<i4"), ("avg", "<f8"), ("std", "<f8")], align=True)
 assert PESTAT_DTYPE.itemsize == 32
 
+# b200_aln_t (include/bwamem_b200.h): mem_aln_t without the floating-point fields
+ALN_DTYPE = np.dtype([("pos", "<i8"), ("rid", "<i4"), ("flag", "<i4"), ("is_rev", "<i4"), ("is_alt", "<i4"),
+                      ("n_cigar", "<i4"), ("NM", "<i4"), ("score", "<i4"), ("sub", "<i4"), ("alt_sc", "<i4"), ("l_md", "<i4"),
+                      ("cigar_off", "<i8"), ("md_off", "<i8")], align=True)
+assert ALN_DTYPE.itemsize == 64
+
 INTV_DTYPE = np.dtype([("x0", "<u8"), ("x1", "<u8"), ("x2", "<u8"), ("info", "<u8")])
 
 MEM_F_PE = 0x2

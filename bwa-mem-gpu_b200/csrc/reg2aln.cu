@@ -1,0 +1,345 @@
+// mem_reg2aln (bwamem.c:1099-1169) on the device -- for every region of a batch the final
+// position, CIGAR, NM and MD: infer_bw (bwamem.c:799-806), the band-doubling loop around bwa_gen_cigar2 (bwa.c:261-347),
+// ksw_global2 with its traceback matrix (ksw.c:504-606), the squeeze of leading / trailing deletions, soft clips,
+// bns_depos / bns_pos2rid.  MAPQ (mem_approx_mapq_se, double arithmetic with log) stays with the caller.
+//
+// One region per lane (persistent lanes, atomic work counter).  The H/E row and the traceback bytes live in a
+// lane-private global scratch (L1/L2-resident at the batch sizes used: <= 100 KB per lane for 150-bp reads); CIGAR
+// words and MD characters go to fixed-stride slots of a per-chunk arena and are compacted by a scan + gather, so only
+// the bytes that exist travel back to the host.  The traceback reproduces the reference's direction bits (ties: M over
+// E over F, `>=` for H, `>` for continuing a gap), so CIGARs are identical, not just equivalent.
+#include "ctx.h"
+#include "extend_common.cuh"
+
+struct R2AParams {
+    DevIndex ix; mem_opt_t opt;
+    const u8 *seq; const i64 *off;
+    const mem_alnreg_t *regs; const i32 *reg_read; int n_regs;
+    b200_aln_t *aln;
+    u32 *cig; int cig_stride; char *md; int md_stride;
+    i32 *he; int he_cap;                 // per lane: 2 * he_cap ints
+    u8 *z; i64 z_cap;                    // per lane: traceback bytes
+    unsigned *work_counter; int *overflow;
+};
+
+#define R2A_MINUS_INF (-0x40000000)
+
+__device__ __forceinline__ int r2a_infer_bw(int l1, int l2, int score, int a, int q, int r)       // bwamem.c:799-806
+{
+    if (l1 == l2 && l1 * a - score < (q + r - a) << 1) return 0;
+    int w = (int)((double)((l1 < l2 ? l1 : l2) * a - score - q) / r + 2.);
+    const int d = l1 > l2 ? l1 - l2 : l2 - l1;
+    if (w < d) w = d;
+    return w;
+}
+
+struct R2AMd {                           // kstring appends of bwa_gen_cigar2 (kputw / kputc)
+    char *s; int l, cap; int *ovf;
+    __device__ __forceinline__ void putc_(char c) { if (l < cap) s[l] = c; else *ovf = 1; ++l; }
+    __device__ inline void putw(int v)
+    {
+        char buf[12]; int n = 0;
+        unsigned x = v < 0 ? (unsigned)-v : (unsigned)v;
+        do { buf[n++] = (char)('0' + x % 10); x /= 10; } while (x);
+        if (v < 0) putc_('-');
+        while (n) putc_(buf[--n]);
+    }
+};
+
+__device__ __forceinline__ void r2a_push(u32 *cigar, int &n_cigar, int cap, int op, int len, int *ovf)   // push_cigar, ksw.c:492-502
+{
+    if (n_cigar == 0 || op != (int)(cigar[(n_cigar - 1 < cap ? n_cigar - 1 : cap - 1)] & 0xf)) {
+        if (n_cigar < cap) cigar[n_cigar] = (u32)len << 4 | (u32)op; else *ovf = 1;
+        ++n_cigar;
+    } else if (n_cigar - 1 < cap) cigar[n_cigar - 1] += (u32)len << 4;
+}
+
+// ksw_global2 (ksw.c:504-606) with traceback; returns the score, CIGAR (already reversed into reading order) in cigar[]
+template <class QF, class TF>
+__device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins,
+                                  int w, i32 *H, i32 *E, u8 *z, i64 z_cap, u32 *cigar, int cig_cap, int &n_cigar, int *ovf)
+{
+    const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins;
+    const int n_col = qlen < 2 * w + 1 ? qlen : 2 * w + 1;
+    n_cigar = 0;
+    if ((i64)n_col * tlen > z_cap) { *ovf = 2; return R2A_MINUS_INF; }
+    int j;
+    H[0] = 0; E[0] = R2A_MINUS_INF;
+    for (j = 1; j <= qlen && j <= w; ++j) { H[j] = -(o_ins + e_ins * j); E[j] = R2A_MINUS_INF; }
+    for (; j <= qlen; ++j) H[j] = E[j] = R2A_MINUS_INF;
+    for (int i = 0; i < tlen; ++i) {
+        int f = R2A_MINUS_INF, t;
+        const int8_t *mrow = mat + tf(i) * 5;
+        const int beg = i > w ? i - w : 0;
+        const int end = i + w + 1 < qlen ? i + w + 1 : qlen;
+        int h1 = beg == 0 ? -(o_del + e_del * (i + 1)) : R2A_MINUS_INF;
+        u8 *zi = z + (i64)i * n_col;
+        for (j = beg; j < end; ++j) {
+            int m = H[j], e = E[j], h;
+            u8 d;
+            H[j] = h1;
+            m += mrow[qf(j)];
+            d = m >= e ? 0 : 1;
+            h = m >= e ? m : e;
+            d = h >= f ? d : 2;
+            h = h >= f ? h : f;
+            h1 = h;
+            t = m - oe_del;
+            e -= e_del;
+            d |= e > t ? 1 << 2 : 0;
+            e = e > t ? e : t;
+            E[j] = e;
+            t = m - oe_ins;
+            f -= e_ins;
+            d |= f > t ? 2 << 4 : 0;
+            f = f > t ? f : t;
+            zi[j - beg] = d;
+        }
+        H[end] = h1; E[end] = R2A_MINUS_INF;
+    }
+    const int score = H[qlen];
+    {   // backtrack (ksw.c:587-602)
+        int which = 0;
+        int i = tlen - 1, k = (i + w + 1 < qlen ? i + w + 1 : qlen) - 1;
+        while (i >= 0 && k >= 0) {
+            which = z[(i64)i * n_col + (k - (i > w ? i - w : 0))] >> (which << 1) & 3;
+            if (which == 0) { r2a_push(cigar, n_cigar, cig_cap, 0, 1, ovf); --i; --k; }
+            else if (which == 1) { r2a_push(cigar, n_cigar, cig_cap, 2, 1, ovf); --i; }
+            else { r2a_push(cigar, n_cigar, cig_cap, 1, 1, ovf); --k; }
+        }
+        if (i >= 0) r2a_push(cigar, n_cigar, cig_cap, 2, i + 1, ovf);
+        if (k >= 0) r2a_push(cigar, n_cigar, cig_cap, 1, k + 1, ovf);
+        const int nc = n_cigar < cig_cap ? n_cigar : cig_cap;
+        for (int a = 0; a < nc >> 1; ++a) { const u32 tmp = cigar[a]; cigar[a] = cigar[nc - 1 - a]; cigar[nc - 1 - a] = tmp; }
+    }
+    return score;
+}
+
+// bwa_gen_cigar2 (bwa.c:261-347): CIGAR + score + NM + MD of query[0, l_query) against text [rb, re)
+template <class QF, class TF>
+__device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int w_, int l_query, QF qf, i64 rb, i64 rlen, TF tf, bool rev,
+                                      i32 *H, i32 *E, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf)
+{
+    const mem_opt_t &opt = P.opt;
+    if (l_query == rlen && w_ == 0) {                                          // no gap; no need to do DP
+        if (P.cig_stride > 0) cigar[0] = (u32)l_query << 4;
+        n_cigar = 1;
+        score = 0;
+        for (int i = 0; i < l_query; ++i) score += mat[tf(i) * 5 + qf(i)];
+    } else {
+        int max_ins = (int)((double)(((l_query + 1) >> 1) * mat[0] - opt.o_ins) / opt.e_ins + 1.);
+        int max_del = (int)((double)(((l_query + 1) >> 1) * mat[0] - opt.o_del) / opt.e_del + 1.);
+        int max_gap = max_ins > max_del ? max_ins : max_del;
+        max_gap = max_gap > 1 ? max_gap : 1;
+        const int dl = (int)rlen > l_query ? (int)rlen - l_query : l_query - (int)rlen;
+        int w = (max_gap + dl + 1) >> 1;
+        w = w < w_ ? w : w_;
+        const int min_w = dl + 3;
+        w = w > min_w ? w : min_w;
+        score = r2a_global2(l_query, qf, (int)rlen, tf, mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins, w, H, E, z, P.z_cap,
+                            cigar, P.cig_stride, n_cigar, ovf);
+    }
+    {   // NM and MD (bwa.c:311-338)
+        int x = 0, y = 0, u = 0, n_mm = 0, n_gap = 0;
+        const int nc = n_cigar < P.cig_stride ? n_cigar : P.cig_stride;
+        md.l = 0;
+        for (int k = 0; k < nc; ++k) {
+            const int op = (int)(cigar[k] & 0xf), len = (int)(cigar[k] >> 4);
+            if (op == 0) {
+                for (int i = 0; i < len; ++i) {
+                    const int rc = tf(y + i);
+                    if (qf(x + i) != rc) { md.putw(u); md.putc_((rev ? "TGCAN" : "ACGTN")[rc]); ++n_mm; u = 0; }
+                    else ++u;
+                }
+                x += len; y += len;
+            } else if (op == 2) {
+                if (k > 0 && k < n_cigar - 1) {
+                    md.putw(u); md.putc_('^');
+                    for (int i = 0; i < len; ++i) md.putc_((rev ? "TGCAN" : "ACGTN")[tf(y + i)]);
+                    u = 0; n_gap += len;
+                }
+                y += len;
+            } else if (op == 1) { x += len; n_gap += len; }
+        }
+        md.putw(u);
+        NM = n_mm + n_gap;
+    }
+}
+
+__global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
+{
+    __shared__ int8_t s_mat[25];
+    if (threadIdx.x < 25) s_mat[threadIdx.x] = P.opt.mat[threadIdx.x];
+    __syncthreads();
+    const size_t lane_id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    i32 *H = P.he + lane_id * 2 * (size_t)P.he_cap, *E = H + P.he_cap;
+    u8 *z = P.z + lane_id * (size_t)P.z_cap;
+    const mem_opt_t &opt = P.opt;
+    const DevIndex &ix = P.ix;
+    const i64 l_pac = ix.l_pac;
+    int ovf = 0;
+    for (;;) {
+        const unsigned g = atomicAdd(P.work_counter, 1u);
+        if (g >= (unsigned)P.n_regs) break;
+        const mem_alnreg_t ar = P.regs[g];
+        const int r = P.reg_read[g];
+        const u8 *query = P.seq + P.off[r];
+        const int l_seq = (int)(P.off[r + 1] - P.off[r]);
+        u32 *cigar = P.cig + (size_t)g * P.cig_stride;
+        R2AMd md; md.s = P.md + (size_t)g * P.md_stride; md.l = 0; md.cap = P.md_stride; md.ovf = &ovf;
+        b200_aln_t a;
+        memset(&a, 0, sizeof(a));
+        if (ar.rb < 0 || ar.re < 0) { a.rid = -1; a.pos = -1; a.flag = 0x4; P.aln[g] = a; continue; }   // unmapped record
+        const int qb = ar.qb, qe = ar.qe;
+        const i64 rb = ar.rb, re = ar.re;
+        if (ar.secondary >= 0) a.flag |= 0x100;
+        int tmp = r2a_infer_bw(qe - qb, (int)(re - rb), ar.truesc, opt.a, opt.o_del, opt.e_del);
+        int w2 = r2a_infer_bw(qe - qb, (int)(re - rb), ar.truesc, opt.a, opt.o_ins, opt.e_ins);
+        w2 = w2 > tmp ? w2 : tmp;
+        if (w2 > opt.w) w2 = w2 < ar.w ? w2 : ar.w;
+        int n_cigar = 0, NM = -1, score = 0, last_sc = -(1 << 30), it = 0;
+        const int lq = qe - qb;
+        const i64 rlen = re - rb;
+        const bool ok = lq > 0 && rb < re && !(rb < l_pac && re > l_pac);      // bwa.c:272
+        const bool rev = rb >= l_pac;
+        do {
+            w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
+            n_cigar = 0; NM = -1;
+            if (ok) {
+                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, z, cigar, n_cigar, score, NM, md, &ovf);
+                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, z, cigar, n_cigar, score, NM, md, &ovf);
+            }
+            if (score == last_sc || w2 == opt.w << 2) break;
+            last_sc = score;
+            w2 <<= 1;
+        } while (++it < 3 && score < ar.truesc - opt.a);
+        a.NM = NM;
+        int is_rev;
+        i64 pos = dev_depos(ix, rb < l_pac ? rb : re - 1, &is_rev);
+        a.is_rev = is_rev;
+        const int cap = P.cig_stride;
+        if (n_cigar > 0 && n_cigar <= cap) {                                       // squeeze out leading or trailing deletions
+            if ((cigar[0] & 0xf) == 2) {
+                pos += cigar[0] >> 4;
+                --n_cigar;
+                for (int k = 0; k < n_cigar; ++k) cigar[k] = cigar[k + 1];
+            } else if ((cigar[n_cigar - 1] & 0xf) == 2) --n_cigar;
+        }
+        if (qb != 0 || qe != l_seq) {                                              // add clipping to CIGAR
+            const int clip5 = is_rev ? l_seq - qe : qb, clip3 = is_rev ? qb : l_seq - qe;
+            if (n_cigar + 2 > cap) ovf = 1;
+            else {
+                if (clip5) { for (int k = n_cigar; k > 0; --k) cigar[k] = cigar[k - 1]; cigar[0] = (u32)clip5 << 4 | 3; ++n_cigar; }
+                if (clip3) cigar[n_cigar++] = (u32)clip3 << 4 | 3;
+            }
+        }
+        a.n_cigar = n_cigar; a.l_md = md.l;
+        a.rid = dev_pos2rid(ix, pos);
+        a.pos = pos - (a.rid >= 0 ? ix.ann_off[a.rid] : 0);
+        a.score = ar.score; a.sub = ar.sub > ar.csub ? ar.sub : ar.csub;
+        a.is_alt = ar.is_alt; a.alt_sc = ar.alt_sc;
+        P.aln[g] = a;
+    }
+    if (ovf) atomicMax(P.overflow, ovf);
+}
+
+// ---- compaction of the fixed-stride arena into the output pools
+__global__ void r2a_lengths_kernel(const b200_aln_t *aln, int n, i32 *n_cig, i32 *l_md)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    n_cig[g] = aln[g].n_cigar; l_md[g] = aln[g].l_md;
+}
+__global__ void r2a_gather_kernel(b200_aln_t *aln, int n, const u32 *cig, int cig_stride, const char *md, int md_stride,
+                                  const i64 *cig_off, const i64 *md_off, u32 *cig_out, char *md_out, i64 cig_base, i64 md_base)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const int nc = aln[g].n_cigar, lm = aln[g].l_md;
+    const u32 *cs = cig + (size_t)g * cig_stride;
+    const char *ms = md + (size_t)g * md_stride;
+    for (int k = 0; k < nc && k < cig_stride; ++k) cig_out[cig_off[g] + k] = cs[k];
+    for (int k = 0; k < lm && k < md_stride; ++k) md_out[md_off[g] + k] = ms[k];
+    aln[g].cigar_off = cig_base + cig_off[g];
+    aln[g].md_off = md_base + md_off[g];
+}
+
+extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
+                                      const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
+                                      uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2])
+{
+    if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
+    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    cudaStream_t st = ctx->st;
+    if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
+    i64 n_regs = 0;
+    for (int r = 0; r < n_reads; ++r) n_regs += cnt[r];
+    if (totals) totals[0] = totals[1] = 0;
+    if (n_regs == 0) return 0;
+    if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
+    std::vector<i32> reg_read((size_t)n_regs);
+    {
+        i64 g = 0;
+        for (int r = 0; r < n_reads; ++r) for (int k = 0; k < cnt[r]; ++k) reg_read[g++] = r;
+    }
+    const int max_len = std::max(1, ctx->max_len);
+    const int w4 = (opt->w << 2) + 64;
+    const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = max_len + 2;
+    const i64 z_cap = (i64)std::min(max_len, 2 * w4 + 1) * ((i64)max_len + w4);
+    const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
+    const int chunk = (int)std::max<i64>(1024, std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
+    const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
+    const i64 lanes_fit = std::max<i64>(64, ((i64)12 << 30) / (i64)per_lane);
+    const int grid_max = (int)std::max<i64>(1, std::min<i64>((i64)ctx->n_sms * 8, lanes_fit / 64));
+    DevBuf d_regs, d_rr, d_aln, d_cig, d_md, d_he, d_z, d_nc, d_lm, d_co, d_mo, d_tmp, d_pool_c, d_pool_m;
+    struct Cleanup { DevBuf *b[14]; ~Cleanup() { for (DevBuf *x : b) x->release(); } }
+        cl{{&d_regs, &d_rr, &d_aln, &d_cig, &d_md, &d_he, &d_z, &d_nc, &d_lm, &d_co, &d_mo, &d_tmp, &d_pool_c, &d_pool_m}};
+    if (d_regs.ensure((size_t)chunk * sizeof(mem_alnreg_t)) || d_rr.ensure((size_t)chunk * 4) || d_aln.ensure((size_t)chunk * sizeof(b200_aln_t)) ||
+        d_cig.ensure((size_t)chunk * cig_stride * 4) || d_md.ensure((size_t)chunk * md_stride) ||
+        d_he.ensure((size_t)grid_max * 64 * he_cap * 8) || d_z.ensure((size_t)grid_max * 64 * (size_t)z_cap) ||
+        d_nc.ensure((size_t)chunk * 4) || d_lm.ensure((size_t)chunk * 4) || d_co.ensure(((size_t)chunk + 1) * 8) ||
+        d_mo.ensure(((size_t)chunk + 1) * 8) || d_tmp.ensure(((size_t)chunk / 1024 + 2) * 8) ||
+        d_pool_c.ensure((size_t)chunk * cig_stride * 4) || d_pool_m.ensure((size_t)chunk * md_stride) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
+    i64 cig_total = 0, md_total = 0;
+    bool fits = true;
+    for (i64 g0 = 0; g0 < n_regs; g0 += chunk) {
+        const int n = (int)std::min<i64>(chunk, n_regs - g0);
+        B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
+        B200_CHECK(cudaMemcpyAsync(d_rr.p, reg_read.data() + g0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        B200_CHECK(cudaMemsetAsync(ctx->d_ctl.p, 0, CTL_SLOTS * 8, st));
+        R2AParams P;
+        memset(&P, 0, sizeof(P));
+        P.ix = ctx->ix; P.opt = *opt; P.seq = ctx->d_seq.as<u8>(); P.off = ctx->d_off.as<i64>();
+        P.regs = d_regs.as<mem_alnreg_t>(); P.reg_read = d_rr.as<i32>(); P.n_regs = n;
+        P.aln = d_aln.as<b200_aln_t>(); P.cig = d_cig.as<u32>(); P.cig_stride = cig_stride; P.md = d_md.as<char>(); P.md_stride = md_stride;
+        P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
+        P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
+        const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
+        B200_LAUNCH(reg2aln_kernel, grid, 64, 0, st, P);
+        B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
+        B200_CHECK(cudaGetLastError());
+        if (launch_exclusive_scan(d_nc.as<i32>(), d_co.as<i64>(), n, d_tmp.as<i64>(), st)) return -1;
+        if (launch_exclusive_scan(d_lm.as<i32>(), d_mo.as<i64>(), n, d_tmp.as<i64>(), st)) return -1;
+        B200_LAUNCH(r2a_gather_kernel, (n + 255) / 256, 256, 0, st, d_aln.as<b200_aln_t>(), n, (const u32 *)d_cig.p, cig_stride,
+                    (const char *)d_md.p, md_stride, (const i64 *)d_co.p, (const i64 *)d_mo.p, d_pool_c.as<u32>(), d_pool_m.as<char>(),
+                    cig_total, md_total);
+        B200_CHECK(cudaGetLastError());
+        i64 nc = 0, nm = 0; u64 ovf = 0;
+        B200_CHECK(cudaMemcpyAsync(&nc, d_co.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
+        B200_CHECK(cudaMemcpyAsync(&nm, d_mo.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
+        B200_CHECK(cudaMemcpyAsync(&ovf, ctx->d_ctl.as<u64>() + CTL_OVF2, 8, cudaMemcpyDeviceToHost, st));
+        B200_CHECK(cudaStreamSynchronize(st));
+        if ((int)ovf) { b200_set_error("reg2aln: per-region %s capacity exceeded", (int)ovf == 2 ? "traceback" : "CIGAR/MD"); return -1; }
+        B200_CHECK(cudaMemcpyAsync(out_aln + g0, d_aln.p, (size_t)n * sizeof(b200_aln_t), cudaMemcpyDeviceToHost, st));
+        if (cig_total + nc > cap_cigar || md_total + nm > cap_md) fits = false;
+        if (fits) {
+            if (nc) B200_CHECK(cudaMemcpyAsync(out_cigar + cig_total, d_pool_c.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, st));
+            if (nm) B200_CHECK(cudaMemcpyAsync(out_md + md_total, d_pool_m.p, (size_t)nm, cudaMemcpyDeviceToHost, st));
+        }
+        B200_CHECK(cudaStreamSynchronize(st));
+        cig_total += nc; md_total += nm;
+    }
+    if (totals) { totals[0] = cig_total; totals[1] = md_total; }
+    if (!fits) { b200_set_error("reg2aln: output pools too small (need %lld CIGAR words, %lld MD bytes)", (long long)cig_total, (long long)md_total); return -2; }
+    return n_regs;
+}

@@ -11,7 +11,7 @@ import os
 
 import numpy as np
 
-from .abi import ALNREG_DTYPE, INTV_DTYPE, MemOpt
+from .abi import ALN_DTYPE, ALNREG_DTYPE, INTV_DTYPE, MemOpt
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 PRODUCT_SO = os.path.join(HERE, "libbwamem_b200.so")
@@ -24,7 +24,7 @@ _SYMBOLS = [
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
-    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download",
+    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -51,6 +51,7 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_collect_intv_batch.restype = C.c_int64
     lib.b200_align_batch.restype = C.c_int64
     lib.b200_batch_download.restype = C.c_int64
+    lib.b200_reg2aln_batch.restype = C.c_int64
     lib.b200_hostidx_build.restype = C.c_void_p
     lib.b200_hostidx_build.argtypes = [C.c_void_p, C.c_int64]
     lib.b200_hostidx_free.argtypes = [C.c_void_p]
@@ -345,6 +346,24 @@ class Context:
                 cap = int(-tot)
                 continue
             self._chk(tot, "align")
+
+    def reg2aln(self, opt: MemOpt, seqs, off, regs, cnt):
+        """mem_reg2aln for every region: (b200_aln_t records, CIGAR words, MD bytes)."""
+        n = len(off) - 1
+        regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        aln = np.zeros(max(1, len(regs)), dtype=ALN_DTYPE)
+        tot = (C.c_int64 * 2)()
+        cap_c, cap_m = 8 * len(regs) + 64, 24 * len(regs) + 64
+        while True:
+            cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
+            rc = self.lib.b200_reg2aln_batch(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                             C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32), C.c_void_p(aln.ctypes.data),
+                                             C.c_int64(cap_c), _p(cig, C.c_uint32), C.c_int64(cap_m), C.c_void_p(md.ctypes.data), tot)
+            if rc == -2:
+                cap_c, cap_m = int(tot[0]) + 64, int(tot[1]) + 64
+                continue
+            self._chk(rc, "reg2aln")
+            return aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
 
     def batch_upload(self, seqs, off):
         n = len(off) - 1

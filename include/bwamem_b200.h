@@ -179,6 +179,21 @@ int b200_index_build_device(b200_ctx_t *ctx, const uint8_t *pac, int64_t l_pac, 
 int b200_index_info(b200_ctx_t *ctx, uint64_t *info /* 13 */);
 int b200_index_download(b200_ctx_t *ctx, uint32_t *bwt, uint64_t *sa);
 
+/* mem_reg2aln (bwamem.c:1099-1169; bwa_gen_cigar2 bwa.c:261-347, ksw_global2 ksw.c:504-606) for every region of a batch:
+ * the fields of mem_aln_t that do not need floating point (mapq = mem_approx_mapq_se stays with the caller).
+ * cigar words are bwa's (len<<4 | op, op in "MIDSH"); MD strings are not 0-terminated (l_md characters each). */
+typedef struct {
+	int64_t pos;                 /* 0-based on contig rid; -1 = unmapped */
+	int32_t rid, flag, is_rev, is_alt;
+	int32_t n_cigar, NM, score, sub, alt_sc, l_md;
+	int64_t cigar_off, md_off;   /* into the cigar / MD pools of the call */
+} b200_aln_t;
+/* regs / cnt: the regions of each read in order (as b200_align_batch returns them, after the caller's primary marking).
+ * Returns the number of regions; -2 when a pool is too small (totals[0..1] = CIGAR words / MD bytes needed). */
+int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
+                           const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
+                           uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2]);
+
 /* =====================================================================================
  * Batched device entry points (arrays of problems; host buffers in, host buffers out).
  * All return 0 on success, <0 on error (message in b200_last_error()); a capacity overflow

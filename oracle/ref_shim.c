@@ -465,3 +465,35 @@ void ref_index_release_wrapped(void *p)
 	for (i = 0; i < idx->bns->n_seqs; ++i) { free(idx->bns->anns[i].name); free(idx->bns->anns[i].anno); }
 	free(idx->bns->anns); free(idx->bns); free(idx->bwt); free(idx);
 }
+
+/* ---------------------------------------------------------------- mem_reg2aln (bwamem.c:1099-1169) for every region of a batch.
+ * aln: per region 8 x int64: pos, rid, is_rev, n_cigar, NM, score, sub, l_md (MD length without the terminating 0);
+ * cigar / md: concatenated over the regions in order.  Returns the number of regions, or -1 when a pool is too small
+ * (totals[0..1] = words / bytes needed). */
+int64_t ref_reg2aln(void *p, const void *opt_, int n_reads, const uint8_t *seqs, const int64_t *off, const void *regs_,
+                    const int32_t *cnt, int64_t *aln, int64_t cap_cigar, uint32_t *cigar, int64_t cap_md, char *md, int64_t *totals)
+{
+	bwaidx_t *idx = (bwaidx_t*)p;
+	const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	const mem_alnreg_t *regs = (const mem_alnreg_t*)regs_;
+	int64_t g = 0, nc = 0, nm = 0;
+	int r, k, ovf = 0;
+	for (r = 0; r < n_reads; ++r) {
+		int l = (int)(off[r + 1] - off[r]);
+		for (k = 0; k < cnt[r]; ++k, ++g) {
+			mem_aln_t a = mem_reg2aln(opt, idx->bns, idx->pac, l, (const char*)(seqs + off[r]), &regs[g]);
+			int l_md = a.cigar ? (int)strlen((char*)(a.cigar + a.n_cigar)) : 0;
+			int64_t *o = aln + 8 * g;
+			o[0] = a.pos; o[1] = a.rid; o[2] = a.is_rev; o[3] = a.n_cigar; o[4] = a.NM; o[5] = a.score; o[6] = a.sub; o[7] = l_md;
+			if (nc + a.n_cigar > cap_cigar || nm + l_md > cap_md) ovf = 1;
+			if (!ovf) {
+				if (a.n_cigar) memcpy(cigar + nc, a.cigar, (size_t)a.n_cigar * 4);
+				if (l_md) memcpy(md + nm, (char*)(a.cigar + a.n_cigar), (size_t)l_md);
+			}
+			nc += a.n_cigar; nm += l_md;
+			free(a.cigar);
+		}
+	}
+	totals[0] = nc; totals[1] = nm;
+	return ovf ? -1 : g;
+}

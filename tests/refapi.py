@@ -229,6 +229,24 @@ class RefIndex:
         assert tot >= 0
         return out[:tot].copy(), cnt
 
+    def reg2aln(self, opt: MemOpt, seqs, off, regs, cnt):
+        """mem_reg2aln (bwamem.c:1099) for every region -> (n x 8 int64: pos rid is_rev n_cigar NM score sub l_md, cigar, md)."""
+        n = len(off) - 1
+        regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        aln = np.zeros((max(1, len(regs)), 8), dtype=np.int64)
+        tot = (C.c_int64 * 2)()
+        cap_c, cap_m = 8 * len(regs) + 64, 24 * len(regs) + 64
+        self.lib.ref_reg2aln.restype = C.c_int64
+        while True:
+            cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
+            rc = self.lib.ref_reg2aln(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                      C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32), C.c_void_p(aln.ctypes.data),
+                                      C.c_int64(cap_c), _p(cig, C.c_uint32), C.c_int64(cap_m), C.c_void_p(md.ctypes.data), tot)
+            if rc < 0:
+                cap_c, cap_m = int(tot[0]) + 64, int(tot[1]) + 64
+                continue
+            return aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
+
     def pestat(self, opt: MemOpt, regs, cnt):
         """mem_pestat (bwamem_pair.c:72) -> 4 x PESTAT_DTYPE"""
         from bwa_mem_gpu_b200.abi import PESTAT_DTYPE

@@ -417,3 +417,47 @@ def test_seeding_variants(backend, tune):
     r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
     r1, n1 = ctx.align(opt, seqs, off)
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
+
+
+def _check_reg2aln(idx, ctx, opt, seqs, off):
+    regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
+    a0, c0, m0 = idx.reg2aln(opt, seqs, off, regs, cnt)
+    a1, c1, m1 = ctx.reg2aln(opt, seqs, off, regs, cnt)
+    assert len(a0) == len(a1) == len(regs)
+    for k, name in enumerate(["pos", "rid", "is_rev", "n_cigar", "NM", "score", "sub", "l_md"]):
+        assert np.array_equal(a0[:, k], a1[name].astype(np.int64)), name
+    assert np.array_equal(c0, c1)                          # CIGAR words in order = identical CIGARs (n_cigar matched above)
+    assert m0.tobytes() == m1.tobytes()                    # MD strings
+    assert np.array_equal(a1["cigar_off"], np.concatenate([[0], np.cumsum(a1["n_cigar"])[:-1]]))
+    assert np.array_equal(a1["md_off"], np.concatenate([[0], np.cumsum(a1["l_md"])[:-1]]))
+    return a1, c1
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep"])
+def test_reg2aln(backend, gname):
+    """mem_reg2aln (bwamem.c:1099-1169): position, CIGAR, NM and MD of every region -- short reads with indels, ragged
+    reads (clips, reverse strand, chimeric), non-default scoring."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 250, 20000), seed=77, sub=0.02, indel=0.01)
+    a, c = _check_reg2aln(idx, ctx, opt, seqs, off)
+    ops = c & 0xf
+    assert (ops == 1).any() and (ops == 2).any() and (ops == 3).any()      # insertions, deletions and clips occurred
+    assert a["is_rev"].any() and not a["is_rev"].all()
+    seqs, off = cm.ragged_reads(gname)
+    _check_reg2aln(idx, ctx, opt, seqs, off)
+    opt2 = abi.default_opt()
+    opt2.a, opt2.b, opt2.o_del, opt2.o_ins, opt2.e_del, opt2.e_ins = 2, 3, 2, 7, 1, 2
+    abi.fill_scmat(opt2)
+    seqs, off = cm.reads_for(gname, _sizes(backend, 120, 5000), seed=78, sub=0.03, indel=0.01)
+    _check_reg2aln(idx, ctx, opt2, seqs, off)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_reg2aln_long_reads(backend):
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    seqs, off = _long_reads("small", _sizes(backend, 6, 200), seed=9)
+    _check_reg2aln(idx, ctx, abi.default_opt(), seqs, off)
