@@ -291,9 +291,10 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
     const i64 lanes_fit = std::max<i64>(64, ((i64)12 << 30) / (i64)per_lane);
     const int grid_max = (int)std::max<i64>(1, std::min<i64>((i64)ctx->n_sms * 8, lanes_fit / 64));
-    DevBuf d_regs, d_rr, d_aln, d_cig, d_md, d_he, d_z, d_nc, d_lm, d_co, d_mo, d_tmp, d_pool_c, d_pool_m;
-    struct Cleanup { DevBuf *b[14]; ~Cleanup() { for (DevBuf *x : b) x->release(); } }
-        cl{{&d_regs, &d_rr, &d_aln, &d_cig, &d_md, &d_he, &d_z, &d_nc, &d_lm, &d_co, &d_mo, &d_tmp, &d_pool_c, &d_pool_m}};
+    // grow-only buffers kept in the context: a second call of the same shape allocates nothing
+    DevBuf &d_regs = ctx->d_r2a[0], &d_rr = ctx->d_r2a[1], &d_aln = ctx->d_r2a[2], &d_cig = ctx->d_r2a[3], &d_md = ctx->d_r2a[4],
+           &d_he = ctx->d_r2a[5], &d_z = ctx->d_r2a[6], &d_nc = ctx->d_r2a[7], &d_lm = ctx->d_r2a[8], &d_co = ctx->d_r2a[9],
+           &d_mo = ctx->d_r2a[10], &d_tmp = ctx->d_r2a[11], &d_pool_c = ctx->d_r2a[12], &d_pool_m = ctx->d_r2a[13];
     if (d_regs.ensure((size_t)chunk * sizeof(mem_alnreg_t)) || d_rr.ensure((size_t)chunk * 4) || d_aln.ensure((size_t)chunk * sizeof(b200_aln_t)) ||
         d_cig.ensure((size_t)chunk * cig_stride * 4) || d_md.ensure((size_t)chunk * md_stride) ||
         d_he.ensure((size_t)grid_max * 64 * he_cap * 8) || d_z.ensure((size_t)grid_max * 64 * (size_t)z_cap) ||

