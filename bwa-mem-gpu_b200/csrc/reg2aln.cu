@@ -20,6 +20,9 @@ struct R2AParams {
     i32 *he; int he_cap;                 // per lane: 2 * he_cap ints
     u8 *z; i64 z_cap;                    // per lane: traceback bytes
     unsigned *work_counter; int *overflow;
+    // two passes: pass 0 finishes the regions that need no DP (equal lengths, inferred band 0) and lists the others;
+    // pass 1 runs the listed regions, so that the lanes of a warp are all inside ksw_global2 together
+    i32 *dp_list; unsigned *dp_n; int pass;
 };
 
 #define R2A_MINUS_INF (-0x40000000)
@@ -179,8 +182,9 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
     const i64 l_pac = ix.l_pac;
     int ovf = 0;
     for (;;) {
-        const unsigned g = atomicAdd(P.work_counter, 1u);
-        if (g >= (unsigned)P.n_regs) break;
+        unsigned g = atomicAdd(P.work_counter, 1u);
+        if (P.pass == 1) { if (g >= *P.dp_n) break; g = (unsigned)P.dp_list[g]; }
+        else if (g >= (unsigned)P.n_regs) break;
         const mem_alnreg_t ar = P.regs[g];
         const int r = P.reg_read[g];
         const u8 *query = P.seq + P.off[r];
@@ -202,6 +206,10 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
         const i64 rlen = re - rb;
         const bool ok = lq > 0 && rb < re && !(rb < l_pac && re > l_pac);      // bwa.c:272
         const bool rev = rb >= l_pac;
+        if (P.pass == 0 && ok && !(lq == rlen && (w2 < opt.w << 2 ? w2 : opt.w << 2) == 0)) {   // needs ksw_global2: second pass
+            P.dp_list[atomicAdd(P.dp_n, 1u)] = (i32)g;
+            continue;
+        }
         do {
             w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
             n_cigar = 0; NM = -1;
@@ -315,7 +323,10 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         P.aln = d_aln.as<b200_aln_t>(); P.cig = d_cig.as<u32>(); P.cig_stride = cig_stride; P.md = d_md.as<char>(); P.md_stride = md_stride;
         P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
+        P.dp_list = d_nc.as<i32>(); P.dp_n = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY); P.pass = 0;      // d_nc is free until the lengths kernel
         const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
+        B200_LAUNCH(reg2aln_kernel, grid, 64, 0, st, P);
+        P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);
         B200_LAUNCH(reg2aln_kernel, grid, 64, 0, st, P);
         B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
         B200_CHECK(cudaGetLastError());
