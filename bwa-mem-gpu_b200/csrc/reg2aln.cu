@@ -23,6 +23,7 @@ struct R2AParams {
     // two passes: pass 0 finishes the regions that need no DP (equal lengths, inferred band 0) and lists the others;
     // pass 1 runs the listed regions, so that the lanes of a warp are all inside ksw_global2 together
     i32 *dp_list; unsigned *dp_n; int pass;
+    int he_smem;                         // H / E rows in shared memory (2 * he_cap * 64 ints per block)
 };
 
 #define R2A_MINUS_INF (-0x40000000)
@@ -57,55 +58,66 @@ __device__ __forceinline__ void r2a_push(u32 *cigar, int &n_cigar, int cap, int 
     } else if (n_cigar - 1 < cap) cigar[n_cigar - 1] += (u32)len << 4;
 }
 
-// ksw_global2 (ksw.c:504-606) with traceback; returns the score, CIGAR (already reversed into reading order) in cigar[]
+// ksw_global2 (ksw.c:504-606) with traceback; returns the score, CIGAR (already reversed into reading order) in cigar[].
+// H / E: entry j at H[j * hs] (hs = 1: lane-private global scratch; hs = block size: interleaved shared memory).
+// The traceback matrix keeps the reference's three direction fields as 4 bits per cell (h: 2 bits, "E continues", "F
+// continues"), eight cells per 32-bit word, rows padded to whole words: one store per eight cells instead of one per cell.
 template <class QF, class TF>
 __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins,
-                                  int w, i32 *H, i32 *E, u8 *z, i64 z_cap, u32 *cigar, int cig_cap, int &n_cigar, int *ovf)
+                                  int w, i32 *H, i32 *E, int hs, u8 *z, i64 z_cap, u32 *cigar, int cig_cap, int &n_cigar, int *ovf)
 {
     const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins;
     const int n_col = qlen < 2 * w + 1 ? qlen : 2 * w + 1;
+    const int row_words = (n_col + 7) >> 3;
+    u32 *zw = (u32 *)z;
     n_cigar = 0;
-    if ((i64)n_col * tlen > z_cap) { *ovf = 2; return R2A_MINUS_INF; }
+    if ((i64)row_words * 4 * tlen > z_cap) { *ovf = 2; return R2A_MINUS_INF; }
     int j;
     H[0] = 0; E[0] = R2A_MINUS_INF;
-    for (j = 1; j <= qlen && j <= w; ++j) { H[j] = -(o_ins + e_ins * j); E[j] = R2A_MINUS_INF; }
-    for (; j <= qlen; ++j) H[j] = E[j] = R2A_MINUS_INF;
+    for (j = 1; j <= qlen && j <= w; ++j) { H[j * hs] = -(o_ins + e_ins * j); E[j * hs] = R2A_MINUS_INF; }
+    for (; j <= qlen; ++j) H[j * hs] = E[j * hs] = R2A_MINUS_INF;
     for (int i = 0; i < tlen; ++i) {
         int f = R2A_MINUS_INF, t;
         const int8_t *mrow = mat + tf(i) * 5;
         const int beg = i > w ? i - w : 0;
         const int end = i + w + 1 < qlen ? i + w + 1 : qlen;
         int h1 = beg == 0 ? -(o_del + e_del * (i + 1)) : R2A_MINUS_INF;
-        u8 *zi = z + (i64)i * n_col;
+        u32 *zi = zw + (i64)i * row_words;
+        u32 acc = 0;
         for (j = beg; j < end; ++j) {
-            int m = H[j], e = E[j], h;
-            u8 d;
-            H[j] = h1;
+            int m = H[j * hs], e = E[j * hs], h;
+            u32 d;
+            H[j * hs] = h1;
             m += mrow[qf(j)];
-            d = m >= e ? 0 : 1;
+            d = m >= e ? 0u : 1u;
             h = m >= e ? m : e;
-            d = h >= f ? d : 2;
+            d = h >= f ? d : 2u;
             h = h >= f ? h : f;
             h1 = h;
             t = m - oe_del;
             e -= e_del;
-            d |= e > t ? 1 << 2 : 0;
+            d |= e > t ? 4u : 0u;
             e = e > t ? e : t;
-            E[j] = e;
+            E[j * hs] = e;
             t = m - oe_ins;
             f -= e_ins;
-            d |= f > t ? 2 << 4 : 0;
+            d |= f > t ? 8u : 0u;
             f = f > t ? f : t;
-            zi[j - beg] = d;
+            const int c = j - beg;
+            acc |= d << ((c & 7) << 2);
+            if ((c & 7) == 7) { zi[c >> 3] = acc; acc = 0; }
         }
-        H[end] = h1; E[end] = R2A_MINUS_INF;
+        if ((end - beg) & 7) zi[(end - beg) >> 3] = acc;
+        H[end * hs] = h1; E[end * hs] = R2A_MINUS_INF;
     }
-    const int score = H[qlen];
+    const int score = H[qlen * hs];
     {   // backtrack (ksw.c:587-602)
         int which = 0;
         int i = tlen - 1, k = (i + w + 1 < qlen ? i + w + 1 : qlen) - 1;
         while (i >= 0 && k >= 0) {
-            which = z[(i64)i * n_col + (k - (i > w ? i - w : 0))] >> (which << 1) & 3;
+            const int c = k - (i > w ? i - w : 0);
+            const u32 d = zw[(i64)i * row_words + (c >> 3)] >> ((c & 7) << 2) & 0xfu;
+            which = which == 0 ? (int)(d & 3u) : which == 1 ? (int)(d >> 2 & 1u) : (int)(d >> 3 & 1u) << 1;
             if (which == 0) { r2a_push(cigar, n_cigar, cig_cap, 0, 1, ovf); --i; --k; }
             else if (which == 1) { r2a_push(cigar, n_cigar, cig_cap, 2, 1, ovf); --i; }
             else { r2a_push(cigar, n_cigar, cig_cap, 1, 1, ovf); --k; }
@@ -121,7 +133,7 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
 // bwa_gen_cigar2 (bwa.c:261-347): CIGAR + score + NM + MD of query[0, l_query) against text [rb, re)
 template <class QF, class TF>
 __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int w_, int l_query, QF qf, i64 rb, i64 rlen, TF tf, bool rev,
-                                      i32 *H, i32 *E, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf)
+                                      i32 *H, i32 *E, int hs, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf)
 {
     const mem_opt_t &opt = P.opt;
     if (l_query == rlen && w_ == 0) {                                          // no gap; no need to do DP
@@ -139,7 +151,7 @@ __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int
         w = w < w_ ? w : w_;
         const int min_w = dl + 3;
         w = w > min_w ? w : min_w;
-        score = r2a_global2(l_query, qf, (int)rlen, tf, mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins, w, H, E, z, P.z_cap,
+        score = r2a_global2(l_query, qf, (int)rlen, tf, mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins, w, H, E, hs, z, P.z_cap,
                             cigar, P.cig_stride, n_cigar, ovf);
     }
     {   // NM and MD (bwa.c:311-338)
@@ -174,8 +186,11 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
     __shared__ int8_t s_mat[25];
     if (threadIdx.x < 25) s_mat[threadIdx.x] = P.opt.mat[threadIdx.x];
     __syncthreads();
+    B200_DYN_SMEM(r2a_raw);
     const size_t lane_id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     i32 *H = P.he + lane_id * 2 * (size_t)P.he_cap, *E = H + P.he_cap;
+    int hs = 1;
+    if (P.he_smem) { H = (i32 *)r2a_raw + threadIdx.x; E = H + (size_t)P.he_cap * 64; hs = 64; }    // [column][lane], conflict-free
     u8 *z = P.z + lane_id * (size_t)P.z_cap;
     const mem_opt_t &opt = P.opt;
     const DevIndex &ix = P.ix;
@@ -214,8 +229,8 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
             w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
             n_cigar = 0; NM = -1;
             if (ok) {
-                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, z, cigar, n_cigar, score, NM, md, &ovf);
-                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, z, cigar, n_cigar, score, NM, md, &ovf);
+                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf);
+                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf);
             }
             if (score == last_sc || w2 == opt.w << 2) break;
             last_sc = score;
@@ -293,7 +308,7 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
     const int max_len = std::max(1, ctx->max_len);
     const int w4 = (opt->w << 2) + 64;
     const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = max_len + 2;
-    const i64 z_cap = (i64)std::min(max_len, 2 * w4 + 1) * ((i64)max_len + w4);
+    const i64 z_cap = (((i64)(std::min(max_len, 2 * w4 + 1) + 7) / 8 * 4) * ((i64)max_len + w4) + 15) / 16 * 16;   // 4 bits per cell, rows padded to words
     const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
     const int chunk = (int)std::max<i64>(1024, std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
@@ -325,9 +340,15 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
         P.dp_list = d_nc.as<i32>(); P.dp_n = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY); P.pass = 0;      // d_nc is free until the lengths kernel
         const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
-        B200_LAUNCH(reg2aln_kernel, grid, 64, 0, st, P);
+        const size_t he_bytes = (size_t)2 * he_cap * 64 * 4;
+        P.he_smem = he_bytes <= 100 * 1024 ? 1 : 0;
+        const size_t smem = P.he_smem ? he_bytes : 0;
+#ifndef B200_EMU
+        B200_CHECK(cudaFuncSetAttribute(reg2aln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#endif
+        B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
         P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);
-        B200_LAUNCH(reg2aln_kernel, grid, 64, 0, st, P);
+        B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
         B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
         B200_CHECK(cudaGetLastError());
         if (launch_exclusive_scan(d_nc.as<i32>(), d_co.as<i64>(), n, d_tmp.as<i64>(), st)) return -1;
