@@ -461,3 +461,32 @@ def test_reg2aln_long_reads(backend):
     idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
     seqs, off = _long_reads("small", _sizes(backend, 6, 200), seed=9)
     _check_reg2aln(idx, ctx, abi.default_opt(), seqs, off)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_align_batch_pipeline_edges(backend):
+    """b200_align_batch (uploads / chunks / downloads overlapped): many small chunks, offsets that do not start at 0, an
+    output capacity that is too small (-needed, nothing truncated silently), an empty batch."""
+    import ctypes as C
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    opt = abi.default_opt()
+    n = _sizes(backend, 300, 20000)
+    seqs, off = cm.reads_for("small", n, seed=4)
+    r0, n0 = idx.align(opt, seqs, off, n_threads=8, cap_per_read=256)
+    ctx.tune("chunk_reads", max(64, n // 7))
+    try:
+        r1, n1 = ctx.align(opt, seqs, off)
+        r2, n2 = ctx.align(opt, seqs, off[n // 3:].copy())
+        out = np.zeros(5, dtype=abi.ALNREG_DTYPE); cnt = np.zeros(n, dtype=np.int32)
+        tot = ctx.lib.b200_align_batch(ctx.h, C.byref(opt), C.c_int(n), seqs.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                       off.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(5), C.c_void_p(out.ctypes.data),
+                                       cnt.ctypes.data_as(C.POINTER(C.c_int32)))
+        r3, n3 = ctx.align(opt, seqs, off[:1].copy())
+    finally:
+        ctx.tune("chunk_reads", 1 << 20)
+    assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
+    k = int(n0[: n // 3].sum())
+    assert np.array_equal(n0[n // 3:], n2) and r0[k:].tobytes() == r2.tobytes()
+    assert tot == -len(r0) and np.array_equal(cnt, n0)
+    assert len(r3) == 0 and len(n3) == 0
