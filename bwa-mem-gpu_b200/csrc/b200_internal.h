@@ -168,7 +168,7 @@ int launch_sa_locate(const SeedParams &p, cudaStream_t st);
 int launch_chain(const ChainParams &p, int emit, cudaStream_t st);
 int launch_extend(const ExtParams &p, int grid, int block, cudaStream_t st);
 int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t st);
-int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st);
+int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, int rowsync, int phased, cudaStream_t st);
 size_t ext2_dp8_smem(int n_groups);
 int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, int phased, cudaStream_t st);
 int launch_ext2_sort(const Ext2Params &p, int round, int n_jobs, int n_sms, cudaStream_t st);

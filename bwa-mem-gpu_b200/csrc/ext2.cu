@@ -213,7 +213,9 @@ __device__ __forceinline__ int dp_score(u32 lo, u32 hi, u32 q)
 #endif
 }
 
-__global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round, int bin)
+// rowsync / phased: the scheduling of ext3.cu (a lane finishes its row before the warp's control slot; warp-wide phases over
+// 32 shape-ordered jobs), here as run-time flags.
+__global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int round, int bin, int rowsync, int phased)
 {
     B200_DYN_SMEM(dp_raw);
     __shared__ u32 s_rows[5 * 2];                          // matrix row of each target base, 8 bytes (5 used)
@@ -241,14 +243,14 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
 
     DpLane L;
     memset(&L, 0, sizeof(L));
-    bool active = false, exhausted = false, need_init = false;
+    bool active = false, exhausted = false, need_init = false, parked = false;
 
     for (;;) {
         // ---------------------------------------------------------------- hot slot: up to 8 cells of the current row
         // The 8 H/E words are fetched first (independent LDS, the row is padded by 8 columns), the cells are then
         // evaluated from registers; the substitution score comes from the target base's matrix row held in two
         // registers (byte select with sign replication), so a cell has no memory latency on its dependency chain.
-        if (active) {
+        for (bool first = true; active && !parked && (rowsync ? L.j < L.end : first); first = false) {
             u32 *p = he + L.j * DP_THREADS;
             u32 w8[8];
 #pragma unroll
@@ -274,9 +276,10 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
             }
             if (rem > 0) L.j += rem < 8 ? rem : 8;
         }
+        if (rowsync) __syncwarp();
         // ---------------------------------------------------------------- control slot
         bool ksw_fin = false;
-        if (active && L.j >= L.end) {                                                     // row i finished
+        if (active && !parked && L.j >= L.end) {                                          // row i finished
             const int jexit = L.beg < L.end ? L.end : L.beg;
             u32 *p = he + L.end * DP_THREADS;
             *p = (*p & DP_QMASK) | (u32)L.h1;                                             // ksw.c:449
@@ -319,12 +322,13 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
             }
         }
         // job / side / retry transitions; loops only when a DP has no rows (tlen <= 0)
-        while ((active && ksw_fin) || (!active && !exhausted)) {
+        const bool may_fetch = !phased || !__any_sync(B200_FULL_MASK, active);              // phased: the warp takes 32 jobs at a time
+        while ((active && ksw_fin) || (!active && !exhausted && may_fetch)) {
             int next_side = -1, next_t = 0;
             if (!active) {                                                                // fetch a job
                 const unsigned slot = atomicAdd(work_counter, 1u);
                 if (slot >= njobs) { exhausted = true; break; }
-                L.job = job_slot(P, round & 1, bin, slot);
+                L.job = job_slot(P, round & 1, bin, P.perm ? P.perm[(size_t)bin * P.jobs_cap + slot] : slot);
                 active = true;
                 L.a_score = -1;
                 if (L.job->qbeg) { next_side = 0; next_t = 0; L.prev = -1; }
@@ -434,6 +438,14 @@ __global__ void __launch_bounds__(DP_THREADS) ext_dp_kernel(Ext2Params P, int ro
                 col[j * DP_THREADS] = (u32)v | (qv << 28);
             }
         }
+        if (phased) {                                                                       // open the gate for the earliest waiting phase
+            if (need_init) parked = true;
+            if (!__any_sync(B200_FULL_MASK, active && !parked)) {
+                const int ph = parked ? L.side * 2 + L.t : 99;
+                const int pmin = __reduce_min_sync(B200_FULL_MASK, ph);
+                if (ph == pmin) parked = false;
+            }
+        }
         need_init = false;
         __syncwarp();
         if (__all_sync(B200_FULL_MASK, exhausted && !active)) break;
@@ -469,13 +481,13 @@ int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t
     B200_CHECK(cudaGetLastError());
     return 0;
 }
-int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, cudaStream_t st)
+int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, int rowsync, int phased, cudaStream_t st)
 {
     const size_t smem = (size_t)he_cols * DP_THREADS * 4;
 #ifndef B200_EMU
     B200_CHECK(cudaFuncSetAttribute(ext_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
-    B200_LAUNCH(ext_dp_kernel, grid, DP_THREADS, smem, st, p, round, bin);
+    B200_LAUNCH(ext_dp_kernel, grid, DP_THREADS, smem, st, p, round, bin, rowsync, rowsync ? phased : 0);
     B200_CHECK(cudaGetLastError());
     return 0;
 }

@@ -303,7 +303,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
         const int bin_flank[3] = { ctx->ext_bin0 > 0 ? ctx->ext_bin0 : 32, ctx->ext_bin1 > 0 ? ctx->ext_bin1 : 64, ctx->max_len };
         XP.bin_max[0] = std::min(bin_flank[0], ctx->max_len); XP.bin_max[1] = std::min(std::max(bin_flank[1], XP.bin_max[0]), ctx->max_len);
         XP.njobs = ctx->d_njobs.as<unsigned>();
-        if (dp8 && ctx->ext_sort) { XP.perm = ctx->d_jsort.as<u32>(); XP.sort_cnt = XP.perm + (size_t)3 * n; }
+        if (ctx->ext_sort) { XP.perm = ctx->d_jsort.as<u32>(); XP.sort_cnt = XP.perm + (size_t)3 * n; }
         XP.eh = ctx->d_eh.as<i32>(); XP.eh_cap = eh_cap;
         XP.reg_off = reg_off_ptr; XP.reg_n = reg_n_ptr;
         XP.work_counter = ctl_u32(ctx, CTL_WORK); XP.stats = ctl_u64(ctx, CTL_STATS);
@@ -336,7 +336,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
                 const int cols = flank + 2 + 8;
                 const int dp_per_sm = std::max(1, std::min(ctx->ext_bps > 0 ? ctx->ext_bps : 16, (int)((200 * 1024) / ((size_t)cols * 64 * 4))));
                 const int grid = std::max(1, std::min((int)((nj[b] + 63) / 64), ctx->n_sms * dp_per_sm));
-                if (launch_ext2_dp(XP, round, b, cols, grid, st)) return -1;
+                if (launch_ext2_dp(XP, round, b, cols, grid, ctx->ext_rowsync, ctx->ext_phased, st)) return -1;
                 ++launches;
                 ctx->stats[CNT_BIN0 + b] += nj[b];
             }

@@ -284,6 +284,19 @@ def test_align_general_extension_kernel(backend):
         r3, n3 = ctx.align(opt, seqs, off)
     finally:
         ctx.tune("ext_rowsync", 1)
+    ctx.tune("ext_path", 2)                          # the 32-bit-score round kernel (ext_dp_kernel), each scheduling variant
+    try:
+        for tune in ({}, {"ext_rowsync": 0}, {"ext_phased": 0}, {"ext_sort": 0}):
+            for k, v in tune.items():
+                ctx.tune(k, v)
+            try:
+                r5, n5 = ctx.align(opt, seqs, off)
+            finally:
+                for k in tune:
+                    ctx.tune(k, 1)
+            assert np.array_equal(n0, n5) and r0.tobytes() == r5.tobytes(), tune
+    finally:
+        ctx.tune("ext_path", 0)
     for key in ("ext_phased", "ext_sort"):           # without warp-wide phases / without the job order
         ctx.tune(key, 0)
         try:
