@@ -76,6 +76,7 @@ ALN_DTYPE = np.dtype([("pos", "<i8"), ("rid", "<i4"), ("flag", "<i4"), ("is_rev"
                       ("n_cigar", "<i4"), ("NM", "<i4"), ("score", "<i4"), ("sub", "<i4"), ("alt_sc", "<i4"), ("l_md", "<i4"),
                       ("cigar_off", "<i8"), ("md_off", "<i8")], align=True)
 assert ALN_DTYPE.itemsize == 64
+SEL_DTYPE = np.dtype([("kind", "<i4"), ("mapq", "<i4"), ("xa_of", "<i4"), ("flag", "<i4")])      # b200_sel_t
 
 INTV_DTYPE = np.dtype([("x0", "<u8"), ("x1", "<u8"), ("x2", "<u8"), ("info", "<u8")])
 

@@ -67,7 +67,8 @@ struct b200_ctx {
     DevBuf d_final, d_final_n;
     i64 total_regs = 0;
     unsigned long long stats[CNT_N] = {0};
-    DevBuf d_r2a[14];                          // b200_reg2aln_batch (reg2aln.cu)
+    DevBuf d_r2a[17];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
+    int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
     // scratch for the primitive batches
     DevBuf d_pa, d_pb, d_pc, d_pd, d_pe, d_pf, d_pg, d_ph;
 };

@@ -10,6 +10,8 @@
 // E over F, `>=` for H, `>` for continuing a gap), so CIGARs are identical, not just equivalent.
 #include "ctx.h"
 #include "extend_common.cuh"
+#include "finalize.cuh"
+#include <cmath>
 
 struct R2AParams {
     DevIndex ix; mem_opt_t opt;
@@ -24,6 +26,7 @@ struct R2AParams {
     // pass 1 runs the listed regions, so that the lanes of a warp are all inside ksw_global2 together
     i32 *dp_list; unsigned *dp_n; int pass;
     int he_smem;                         // H / E rows in shared memory (2 * he_cap * 64 ints per block)
+    const b200_sel_t *sel;               // b200_reg2sam_se_batch: which regions reach the SAM (null: all)
 };
 
 #define R2A_MINUS_INF (-0x40000000)
@@ -208,6 +211,7 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
         R2AMd md; md.s = P.md + (size_t)g * P.md_stride; md.l = 0; md.cap = P.md_stride; md.ovf = &ovf;
         b200_aln_t a;
         memset(&a, 0, sizeof(a));
+        if (P.sel && P.sel[g].kind == 0) { a.rid = -1; a.pos = -1; P.aln[g] = a; continue; }        // not in the SAM
         if (ar.rb < 0 || ar.re < 0) { a.rid = -1; a.pos = -1; a.flag = 0x4; P.aln[g] = a; continue; }   // unmapped record
         const int qb = ar.qb, qe = ar.qe;
         const i64 rb = ar.rb, re = ar.re;
@@ -261,6 +265,10 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
         a.pos = pos - (a.rid >= 0 ? ix.ann_off[a.rid] : 0);
         a.score = ar.score; a.sub = ar.sub > ar.csub ? ar.sub : ar.csub;
         a.is_alt = ar.is_alt; a.alt_sc = ar.alt_sc;
+        if (P.sel) {                                                               // mem_reg2sam, bwamem.c:1035-1038
+            a.flag |= P.sel[g].flag;
+            if (ar.secondary >= 0) a.sub = -1;
+        }
         P.aln[g] = a;
     }
     if (ovf) atomicMax(P.overflow, ovf);
@@ -287,16 +295,21 @@ __global__ void r2a_gather_kernel(b200_aln_t *aln, int n, const u32 *cig, int ci
     aln[g].md_off = md_base + md_off[g];
 }
 
-extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
-                                      const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
-                                      uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2])
+// regs_out / out_sel non-null: the worker2 steps of finalize.cuh run first on each chunk (chunks then hold whole reads)
+static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
+                            const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
+                            uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2],
+                            mem_alnreg_t *regs_out, b200_sel_t *out_sel, int64_t n_processed)
 {
+    const bool finalize = out_sel != nullptr;
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
     if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
     cudaStream_t st = ctx->st;
     if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
-    i64 n_regs = 0;
-    for (int r = 0; r < n_reads; ++r) n_regs += cnt[r];
+    std::vector<i64> roff((size_t)n_reads + 1, 0);
+    int max_cnt = 0;
+    for (int r = 0; r < n_reads; ++r) { roff[r + 1] = roff[r] + cnt[r]; max_cnt = std::max(max_cnt, (int)cnt[r]); }
+    const i64 n_regs = roff[n_reads];
     if (totals) totals[0] = totals[1] = 0;
     if (n_regs == 0) return 0;
     if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
@@ -310,7 +323,7 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
     const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = max_len + 2;
     const i64 z_cap = (((i64)(std::min(max_len, 2 * w4 + 1) + 7) / 8 * 4) * ((i64)max_len + w4) + 15) / 16 * 16;   // 4 bits per cell, rows padded to words
     const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
-    const int chunk = (int)std::max<i64>(1024, std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
+    const int chunk = (int)std::max<i64>(std::max(1024, max_cnt), std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
     const i64 lanes_fit = std::max<i64>(64, ((i64)12 << 30) / (i64)per_lane);
     const int grid_max = (int)std::max<i64>(1, std::min<i64>((i64)ctx->n_sms * 8, lanes_fit / 64));
@@ -324,10 +337,29 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         d_nc.ensure((size_t)chunk * 4) || d_lm.ensure((size_t)chunk * 4) || d_co.ensure(((size_t)chunk + 1) * 8) ||
         d_mo.ensure(((size_t)chunk + 1) * 8) || d_tmp.ensure(((size_t)chunk / 1024 + 2) * 8) ||
         d_pool_c.ensure((size_t)chunk * cig_stride * 4) || d_pool_m.ensure((size_t)chunk * md_stride) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
+    DevBuf &d_roff = ctx->d_r2a[14], &d_sel = ctx->d_r2a[15], &d_log = ctx->d_r2a[16];
+    if (finalize) {
+        if (d_roff.ensure(((size_t)n_reads + 1) * 8) || d_sel.ensure((size_t)chunk * sizeof(b200_sel_t))) return -1;
+        B200_CHECK(cudaMemcpyAsync(d_roff.p, roff.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
+        const int want = 4 * max_len + 65536;                  // log(l), l <= max(qe - qb, re - rb); the kernel checks the bound
+        if (ctx->log_cap < want) {
+            std::vector<double> tab((size_t)want);
+            for (int i = 0; i < want; ++i) tab[i] = std::log((double)i);                             // the host's libm, as mem_approx_mapq_se
+            if (d_log.ensure((size_t)want * 8)) return -1;
+            B200_CHECK(cudaMemcpyAsync(d_log.p, tab.data(), (size_t)want * 8, cudaMemcpyHostToDevice, st));
+            B200_CHECK(cudaStreamSynchronize(st));
+            ctx->log_cap = want;
+        }
+    }
     i64 cig_total = 0, md_total = 0;
     bool fits = true;
-    for (i64 g0 = 0; g0 < n_regs; g0 += chunk) {
-        const int n = (int)std::min<i64>(chunk, n_regs - g0);
+    int r_lo = 0;
+    for (i64 g0 = 0; g0 < n_regs;) {
+        int n = (int)std::min<i64>(chunk, n_regs - g0), r_hi = r_lo;
+        if (finalize) {
+            while (r_hi < n_reads && roff[r_hi + 1] - g0 <= chunk) ++r_hi;
+            n = (int)(roff[r_hi] - g0);
+        }
         B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
         B200_CHECK(cudaMemcpyAsync(d_rr.p, reg_read.data() + g0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
         B200_CHECK(cudaMemsetAsync(ctx->d_ctl.p, 0, CTL_SLOTS * 8, st));
@@ -339,6 +371,16 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
         P.dp_list = d_nc.as<i32>(); P.dp_n = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY); P.pass = 0;      // d_nc is free until the lengths kernel
+        if (finalize) {
+            FinParams F;
+            memset(&F, 0, sizeof(F));
+            F.opt = *opt; F.regs = d_regs.as<mem_alnreg_t>(); F.roff = d_roff.as<i64>(); F.g0 = g0; F.r0 = r_lo; F.n_reads = r_hi - r_lo;
+            F.id0 = n_processed; F.sel = d_sel.as<b200_sel_t>(); F.logtab = d_log.as<double>(); F.log_cap = ctx->log_cap;
+            F.overflow = P.overflow;
+            const int fgrid = std::max(1, std::min(ctx->n_sms * 8, (F.n_reads + 127) / 128));
+            B200_LAUNCH(finalize_se_kernel, fgrid, 128, 0, st, F);
+            P.sel = d_sel.as<b200_sel_t>();
+        }
         const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
         const size_t he_bytes = (size_t)2 * he_cap * 64 * 4;
         P.he_smem = he_bytes <= 100 * 1024 ? 1 : 0;
@@ -362,8 +404,15 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         B200_CHECK(cudaMemcpyAsync(&nm, d_mo.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
         B200_CHECK(cudaMemcpyAsync(&ovf, ctx->d_ctl.as<u64>() + CTL_OVF2, 8, cudaMemcpyDeviceToHost, st));
         B200_CHECK(cudaStreamSynchronize(st));
-        if ((int)ovf) { b200_set_error("reg2aln: per-region %s capacity exceeded", (int)ovf == 2 ? "traceback" : "CIGAR/MD"); return -1; }
+        if ((int)ovf) {
+            b200_set_error("reg2aln: per-region %s capacity exceeded", (int)ovf == 3 ? "log table" : (int)ovf == 2 ? "traceback" : "CIGAR/MD");
+            return -1;
+        }
         B200_CHECK(cudaMemcpyAsync(out_aln + g0, d_aln.p, (size_t)n * sizeof(b200_aln_t), cudaMemcpyDeviceToHost, st));
+        if (finalize) {
+            B200_CHECK(cudaMemcpyAsync(out_sel + g0, d_sel.p, (size_t)n * sizeof(b200_sel_t), cudaMemcpyDeviceToHost, st));
+            if (regs_out) B200_CHECK(cudaMemcpyAsync(regs_out + g0, d_regs.p, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyDeviceToHost, st));
+        }
         if (cig_total + nc > cap_cigar || md_total + nm > cap_md) fits = false;
         if (fits) {
             if (nc) B200_CHECK(cudaMemcpyAsync(out_cigar + cig_total, d_pool_c.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, st));
@@ -371,8 +420,25 @@ extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int
         }
         B200_CHECK(cudaStreamSynchronize(st));
         cig_total += nc; md_total += nm;
+        g0 += n; r_lo = r_hi;
     }
     if (totals) { totals[0] = cig_total; totals[1] = md_total; }
     if (!fits) { b200_set_error("reg2aln: output pools too small (need %lld CIGAR words, %lld MD bytes)", (long long)cig_total, (long long)md_total); return -2; }
     return n_regs;
+}
+
+extern "C" int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
+                                      const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
+                                      uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2])
+{
+    return reg2aln_impl(ctx, opt, n_reads, seqs, off, regs, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, nullptr, nullptr, 0);
+}
+
+extern "C" int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, int64_t n_processed, const uint8_t *seqs,
+                                         const int64_t *off, mem_alnreg_t *regs, const int32_t *cnt, b200_sel_t *out_sel,
+                                         b200_aln_t *out_aln, int64_t cap_cigar, uint32_t *out_cigar, int64_t cap_md, char *out_md,
+                                         int64_t totals[2])
+{
+    if (!out_sel || !regs) { b200_set_error("b200_reg2sam_se_batch: regs and out_sel are required"); return -1; }
+    return reg2aln_impl(ctx, opt, n_reads, seqs, off, regs, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, regs, out_sel, n_processed);
 }

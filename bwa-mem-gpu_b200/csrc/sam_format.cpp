@@ -1,0 +1,210 @@
+// SAM text of single-end reads from the arrays b200_reg2sam_se_batch returns: mem_aln2sam (bwamem.c:832-956) with
+// add_cigar (:819-830), the unmapped record of mem_reg2sam (:1043-1047) and the XA strings of mem_gen_alt
+// (bwamem_extra.c:143-161).  Host code: this is string formatting, done by a pool of threads over blocks of reads;
+// every number in the text was computed on the device.
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <thread>
+#include <vector>
+#include <algorithm>
+#include "../../include/bwamem_b200.h"
+
+#define SF_SOFTCLIP 0x200      /* MEM_F_SOFTCLIP, bwa.h:80 */
+#define SF_REF_HDR 0x100       /* MEM_F_REF_HDR,  bwa.h:79 */
+#define SF_XB 0x2000           /* MEM_F_XB,       bwa.h:84 */
+
+namespace {
+
+inline void put_int(std::string &s, long long v)        // kputw / kputl
+{
+    char buf[24]; int n = 0;
+    unsigned long long x = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+    do { buf[n++] = (char)('0' + x % 10); x /= 10; } while (x);
+    if (v < 0) s.push_back('-');
+    while (n) s.push_back(buf[--n]);
+}
+
+inline int code_of(uint8_t c)                            // reads may be given as nt4 codes or as letters
+{
+    if (c < 4) return c;
+    switch (c & 0xdf) { case 'A': return 0; case 'C': return 1; case 'G': return 2; case 'T': return 3; }
+    return 4;
+}
+
+struct Rec { const b200_aln_t *a; const uint32_t *cig; const char *md; int mapq; };
+
+void put_cigar(std::string &s, const mem_opt_t *opt, const Rec &p, int which)        // add_cigar
+{
+    if (!p.a->n_cigar) { s.push_back('*'); return; }
+    for (int i = 0; i < p.a->n_cigar; ++i) {
+        int c = (int)(p.cig[i] & 0xf);
+        if (!(opt->flag & SF_SOFTCLIP) && !p.a->is_alt && (c == 3 || c == 4)) c = which ? 4 : 3;
+        put_int(s, p.cig[i] >> 4); s.push_back("MIDSH"[c]);
+    }
+}
+
+struct Job {
+    const mem_opt_t *opt; const char *const *ann_names; const char *const *ann_annos;
+    const char *const *names; const char *const *comments; const uint8_t *seqs; const uint8_t *quals; const int64_t *off;
+    const int64_t *roff; const b200_sel_t *sel; const b200_aln_t *aln; const uint32_t *cigar; const char *md; const char *rg;
+};
+
+void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &list, int which, const std::string *xa)
+{
+    const mem_opt_t *opt = J.opt;
+    static const b200_aln_t unmapped = { -1, -1, 0x4, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 };
+    const Rec none = { &unmapped, nullptr, nullptr, 0 };
+    const Rec &p = list.empty() ? none : list[which];
+    const b200_aln_t &a = *p.a;
+    const int l_seq = (int)(J.off[r + 1] - J.off[r]);
+    const uint8_t *seq = J.seqs + J.off[r], *qual = J.quals ? J.quals + J.off[r] : nullptr;
+    int flag = a.flag;
+    if (a.rid < 0) flag |= 0x4;
+    if (a.is_rev) flag |= 0x10;
+    s += J.names[r]; s.push_back('\t');
+    put_int(s, (flag & 0xffff) | (flag & 0x10000 ? 0x100 : 0)); s.push_back('\t');
+    if (a.rid >= 0) {
+        s += J.ann_names[a.rid]; s.push_back('\t');
+        put_int(s, a.pos + 1); s.push_back('\t');
+        put_int(s, p.mapq); s.push_back('\t');
+        put_cigar(s, opt, p, which);
+    } else s += "*\t0\t0\t*";
+    s.push_back('\t');
+    s += "*\t0\t0";                                      // single-end: no mate
+    s.push_back('\t');
+    if (flag & 0x100) s += "*\t*";
+    else {
+        int qb = 0, qe = l_seq;
+        if (a.n_cigar && which && !(opt->flag & SF_SOFTCLIP) && !a.is_alt) {
+            const int c0 = (int)(p.cig[0] & 0xf), c1 = (int)(p.cig[a.n_cigar - 1] & 0xf);
+            if (!a.is_rev) {
+                if (c0 == 4 || c0 == 3) qb += (int)(p.cig[0] >> 4);
+                if (c1 == 4 || c1 == 3) qe -= (int)(p.cig[a.n_cigar - 1] >> 4);
+            } else {
+                if (c0 == 4 || c0 == 3) qe -= (int)(p.cig[0] >> 4);
+                if (c1 == 4 || c1 == 3) qb += (int)(p.cig[a.n_cigar - 1] >> 4);
+            }
+        }
+        if (!a.is_rev) {
+            for (int i = qb; i < qe; ++i) s.push_back("ACGTN"[code_of(seq[i])]);
+            s.push_back('\t');
+            if (qual) s.append((const char *)qual + qb, (size_t)std::max(0, qe - qb)); else s.push_back('*');
+        } else {
+            for (int i = qe - 1; i >= qb; --i) s.push_back("TGCAN"[code_of(seq[i])]);
+            s.push_back('\t');
+            if (qual) for (int i = qe - 1; i >= qb; --i) s.push_back((char)qual[i]); else s.push_back('*');
+        }
+    }
+    if (a.n_cigar) {
+        s += "\tNM:i:"; put_int(s, a.NM);
+        s += "\tMD:Z:"; s.append(p.md, (size_t)a.l_md);
+    }
+    if (a.score >= 0) { s += "\tAS:i:"; put_int(s, a.score); }
+    if (a.sub >= 0) { s += "\tXS:i:"; put_int(s, a.sub); }
+    if (J.rg && J.rg[0]) { s += "\tRG:Z:"; s += J.rg; }
+    if (!(flag & 0x100)) {
+        const int n = (int)list.size();
+        int i;
+        for (i = 0; i < n; ++i) if (i != which && !(list[i].a->flag & 0x100)) break;
+        if (i < n) {
+            s += "\tSA:Z:";
+            for (i = 0; i < n; ++i) {
+                const Rec &q = list[i];
+                if (i == which || (q.a->flag & 0x100)) continue;
+                s += J.ann_names[q.a->rid]; s.push_back(',');
+                put_int(s, q.a->pos + 1); s.push_back(',');
+                s.push_back("+-"[q.a->is_rev]); s.push_back(',');
+                for (int k = 0; k < q.a->n_cigar; ++k) { put_int(s, q.cig[k] >> 4); s.push_back("MIDSH"[q.cig[k] & 0xf]); }
+                s.push_back(','); put_int(s, q.mapq);
+                s.push_back(','); put_int(s, q.a->NM);
+                s.push_back(';');
+            }
+        }
+        if (a.alt_sc > 0) { char buf[48]; snprintf(buf, sizeof(buf), "\tpa:f:%.3f", (double)a.score / a.alt_sc); s += buf; }
+    }
+    if (xa && !xa->empty()) { s += (opt->flag & SF_XB) ? "\tXB:Z:" : "\tXA:Z:"; s += *xa; }
+    if (J.comments && J.comments[r]) { s.push_back('\t'); s += J.comments[r]; }
+    if ((opt->flag & SF_REF_HDR) && a.rid >= 0 && J.ann_annos && J.ann_annos[a.rid] && J.ann_annos[a.rid][0]) {
+        s += "\tXR:Z:";
+        const size_t t = s.size();
+        s += J.ann_annos[a.rid];
+        for (size_t i = t; i < s.size(); ++i) if (s[i] == '\t') s[i] = ' ';
+    }
+    s.push_back('\n');
+}
+
+void one_read(std::string &s, const Job &J, int r)
+{
+    const int64_t g0 = J.roff[r];
+    const int n = (int)(J.roff[r + 1] - g0);
+    std::vector<Rec> list;
+    std::vector<int> reg_of;
+    for (int k = 0; k < n; ++k)
+        if (J.sel[g0 + k].kind & 1) {
+            const b200_aln_t *a = J.aln + g0 + k;
+            list.push_back(Rec{ a, J.cigar + a->cigar_off, J.md + a->md_off, J.sel[g0 + k].mapq });
+            reg_of.push_back(k);
+        }
+    if (list.empty()) { one_record(s, J, r, list, 0, nullptr); return; }
+    std::vector<std::string> xa(list.size());
+    for (int i = 0; i < n; ++i) {                        // mem_gen_alt: entries appended in region order
+        const b200_sel_t &e = J.sel[g0 + i];
+        if (!(e.kind & 2)) continue;
+        const auto it = std::find(reg_of.begin(), reg_of.end(), e.xa_of);
+        if (it == reg_of.end()) continue;                // its record is not printed
+        std::string &x = xa[(size_t)(it - reg_of.begin())];
+        const b200_aln_t &t = J.aln[g0 + i];
+        const uint32_t *cg = J.cigar + t.cigar_off;
+        x += J.ann_names[t.rid]; x.push_back(','); x.push_back("+-"[t.is_rev]); put_int(x, t.pos + 1); x.push_back(',');
+        for (int k = 0; k < t.n_cigar; ++k) { put_int(x, cg[k] >> 4); x.push_back("MIDSHN"[cg[k] & 0xf]); }
+        x.push_back(','); put_int(x, t.NM);
+        if (J.opt->flag & SF_XB) { x.push_back(','); put_int(x, t.score); }
+        x.push_back(';');
+    }
+    for (int w = 0; w < (int)list.size(); ++w) one_record(s, J, r, list, w, &xa[w]);
+}
+
+}  // namespace
+
+extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos, int n_reads,
+                                      const char *const *names, const char *const *comments, const uint8_t *seqs,
+                                      const uint8_t *quals, const int64_t *off, const int32_t *cnt, const b200_sel_t *sel,
+                                      const b200_aln_t *aln, const uint32_t *cigar, const char *md, const char *rg_id,
+                                      int n_threads, int64_t cap, char *sam, int64_t *sam_off)
+{
+    std::vector<int64_t> roff((size_t)n_reads + 1, 0);
+    for (int r = 0; r < n_reads; ++r) roff[r + 1] = roff[r] + cnt[r];
+    const Job J = { opt, ann_names, ann_annos, names, comments, seqs, quals, off, roff.data(), sel, aln, cigar, md, rg_id };
+    const int nt = std::max(1, std::min(n_threads, std::max(1, n_reads / 256)));
+    std::vector<std::string> part((size_t)nt);
+    std::vector<std::vector<int64_t>> lens((size_t)nt);
+    auto work = [&](int t) {
+        const int lo = (int)((int64_t)n_reads * t / nt), hi = (int)((int64_t)n_reads * (t + 1) / nt);
+        std::string &s = part[t];
+        s.reserve((size_t)(hi - lo) * 400);
+        lens[t].reserve((size_t)(hi - lo));
+        for (int r = lo; r < hi; ++r) {
+            const size_t before = s.size();
+            one_read(s, J, r);
+            lens[t].push_back((int64_t)(s.size() - before));
+        }
+    };
+    if (nt == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t) th.emplace_back(work, t);
+        for (auto &x : th) x.join();
+    }
+    int64_t total = 0;
+    for (auto &s : part) total += (int64_t)s.size();
+    if (sam_off) {
+        int64_t o = 0; int r = 0;
+        for (int t = 0; t < nt; ++t) for (int64_t l : lens[t]) { sam_off[r++] = o; o += l; }
+        sam_off[n_reads] = o;
+    }
+    if (total > cap) return -total;
+    int64_t o = 0;
+    for (auto &s : part) { memcpy(sam + o, s.data(), s.size()); o += (int64_t)s.size(); }
+    return total;
+}

@@ -24,7 +24,7 @@ _SYMBOLS = [
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
-    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch",
+    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -52,6 +52,8 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_align_batch.restype = C.c_int64
     lib.b200_batch_download.restype = C.c_int64
     lib.b200_reg2aln_batch.restype = C.c_int64
+    lib.b200_reg2sam_se_batch.restype = C.c_int64
+    lib.b200_sam_se_format.restype = C.c_int64
     lib.b200_hostidx_build.restype = C.c_void_p
     lib.b200_hostidx_build.argtypes = [C.c_void_p, C.c_int64]
     lib.b200_hostidx_free.argtypes = [C.c_void_p]
@@ -364,6 +366,54 @@ class Context:
                 continue
             self._chk(rc, "reg2aln")
             return aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
+
+    def reg2sam_se(self, opt: MemOpt, seqs, off, regs, cnt, n_processed=0):
+        """worker2's single-end half before the SAM text (b200_reg2sam_se_batch): primary marking, record selection, MAPQ,
+        XA choice and mem_reg2aln -> (regions as updated, b200_sel_t, b200_aln_t, CIGAR words, MD bytes)."""
+        from .abi import SEL_DTYPE
+        n = len(off) - 1
+        regs0 = np.array(regs, dtype=ALNREG_DTYPE, copy=True); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        regs = regs0.copy()
+        aln = np.zeros(max(1, len(regs)), dtype=ALN_DTYPE)
+        sel = np.zeros(max(1, len(regs)), dtype=SEL_DTYPE)
+        tot = (C.c_int64 * 2)()
+        cap_c, cap_m = 8 * len(regs) + 64, 24 * len(regs) + 64
+        while True:
+            cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
+            regs[...] = regs0
+            rc = self.lib.b200_reg2sam_se_batch(self.h, C.byref(opt), C.c_int(n), C.c_int64(n_processed), _p(seqs, C.c_uint8),
+                                                _p(off, C.c_int64), C.c_void_p(regs.ctypes.data), _p(cnt, C.c_int32),
+                                                C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data), C.c_int64(cap_c),
+                                                _p(cig, C.c_uint32), C.c_int64(cap_m), C.c_void_p(md.ctypes.data), tot)
+            if rc == -2:
+                cap_c, cap_m = int(tot[0]) + 64, int(tot[1]) + 64
+                continue
+            self._chk(rc, "reg2sam_se")
+            return regs[:rc], sel[:rc], aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
+
+    def sam_se(self, opt: MemOpt, ann_names, names, seqs, off, cnt, sel, aln, cig, md, quals=None, comments=None, rg_id=None,
+               n_threads=8):
+        """b200_sam_se_format: SAM text (bytes) and the n + 1 offsets of the reads' records."""
+        n = len(off) - 1
+        cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        sel = np.ascontiguousarray(sel); aln = np.ascontiguousarray(aln)
+        cig = np.ascontiguousarray(cig, dtype=np.uint32); md = np.ascontiguousarray(md, dtype=np.uint8)
+        a_names = (C.c_char_p * max(1, len(ann_names)))(*[s.encode() for s in ann_names])
+        r_names = (C.c_char_p * max(1, n))(*[s.encode() for s in names])
+        r_comm = None if comments is None else (C.c_char_p * max(1, n))(*[None if s is None else s.encode() for s in comments])
+        soff = np.zeros(n + 1, dtype=np.int64)
+        cap = 1 << 16
+        while True:
+            sam = np.zeros(cap, dtype=np.uint8)
+            rc = self.lib.b200_sam_se_format(C.byref(opt), a_names, None, C.c_int(n), r_names, r_comm, _p(seqs, C.c_uint8),
+                                             None if quals is None else _p(quals, C.c_uint8), _p(off, C.c_int64), _p(cnt, C.c_int32),
+                                             C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data), _p(cig, C.c_uint32),
+                                             C.c_void_p(md.ctypes.data), None if rg_id is None else rg_id.encode(), C.c_int(n_threads),
+                                             C.c_int64(cap), C.c_void_p(sam.ctypes.data), _p(soff, C.c_int64))
+            if rc < 0:
+                cap = int(-rc) + 64
+                continue
+            return sam[:rc].tobytes(), soff
 
     def batch_upload(self, seqs, off):
         n = len(off) - 1

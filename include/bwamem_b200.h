@@ -194,6 +194,39 @@ int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, c
                            const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
                            uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2]);
 
+/* The single-end half of worker2 (bwamem.c:1195-1205) up to, not including, the SAM text: for every read
+ * mem_mark_primary_se (bwamem.c:529-565, tie-break hash_64(n_processed + read index + i)), mem_reorder_primary5
+ * (:988-1010, with MEM_F_PRIMARY5), then mem_reg2sam's walk (:1024-1042) -- which regions become SAM records, their
+ * supplementary flag, MAPQ (mem_approx_mapq_se :962-986, capped by the first record's unless MEM_F_KEEP_SUPP_MAPQ) --
+ * mem_gen_alt's choice of XA entries (bwamem_extra.c:116-170) and mem_reg2aln for every region that reaches the SAM.
+ * regs is updated in place to the reference's order and fields (hash, sub, sub_n, alt_sc, secondary, secondary_all).
+ * out_sel[g] / out_aln[g] describe region g of the updated array:
+ *   kind   bit 0: a SAM record of its own, in this order; bit 1: an XA entry of the record of region xa_of of the
+ *          same read, appended in this order; 0: the region does not reach the SAM (out_aln[g] is empty).
+ *   mapq   final MAPQ of the record;  flag  0x800 / 0x10000 for supplementary records (also OR-ed into out_aln.flag).
+ * out_aln[g].sub is -1 for secondary records as in mem_reg2sam.  A read none of whose regions has kind bit 0 gets the
+ * unmapped record (mem_reg2aln with ar = 0: rid -1, pos -1, flag 0x4), which needs no device work: b200_sam_se_format
+ * writes it.  Return value and pools as b200_reg2aln_batch. */
+typedef struct { int32_t kind, mapq, xa_of, flag; } b200_sel_t;
+int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, int64_t n_processed, const uint8_t *seqs,
+                              const int64_t *off, mem_alnreg_t *regs, const int32_t *cnt, b200_sel_t *out_sel,
+                              b200_aln_t *out_aln, int64_t cap_cigar, uint32_t *out_cigar, int64_t cap_md, char *out_md,
+                              int64_t totals[2]);
+
+/* SAM text of single-end reads from what b200_reg2sam_se_batch returned: mem_aln2sam (bwamem.c:832-956) with add_cigar
+ * (:819-830; hard clips for supplementary records unless MEM_F_SOFTCLIP), the unmapped record of mem_reg2sam
+ * (:1043-1047), SA and pa tags, the XA / XB strings of mem_gen_alt (bwamem_extra.c:143-161), RG (bwa_rg_id), the FASTQ
+ * comment and XR (MEM_F_REF_HDR).  Host code (string formatting by n_threads threads over blocks of reads).
+ * ann_names[rid] = bntann1_t.name, ann_annos (may be NULL) = bntann1_t.anno; names[r] = bseq1_t.name; comments (may be
+ * NULL, entries may be NULL); seqs as given to the aligner (letters or nt4 codes), quals (may be NULL) with the same
+ * offsets.  Returns the number of bytes written to sam (no terminating 0), or -(needed) when cap is too small;
+ * sam_off (may be NULL): n_reads + 1 offsets of the reads' records. */
+int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos, int n_reads,
+                           const char *const *names, const char *const *comments, const uint8_t *seqs, const uint8_t *quals,
+                           const int64_t *off, const int32_t *cnt, const b200_sel_t *sel, const b200_aln_t *aln,
+                           const uint32_t *cigar, const char *md, const char *rg_id, int n_threads, int64_t cap, char *sam,
+                           int64_t *sam_off);
+
 /* =====================================================================================
  * Batched device entry points (arrays of problems; host buffers in, host buffers out).
  * All return 0 on success, <0 on error (message in b200_last_error()); a capacity overflow

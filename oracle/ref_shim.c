@@ -497,3 +497,48 @@ int64_t ref_reg2aln(void *p, const void *opt_, int n_reads, const uint8_t *seqs,
 	totals[0] = nc; totals[1] = nm;
 	return ovf ? -1 : g;
 }
+
+/* (8) worker2, single-end (bwamem.c:1195-1205): mem_mark_primary_se [+ mem_reorder_primary5 with MEM_F_PRIMARY5] on each
+ * read's regions -- written back in place -- mem_approx_mapq_se of every region (mapq[]), then mem_reg2sam; the SAM
+ * text of the reads is concatenated into sam.  seqs are nt4 codes (what worker1 leaves in bseq1_t.seq); reads are named
+ * r<global index>, no qualities.  Returns the number of SAM bytes (nothing is written beyond cap_sam). */
+extern int mem_mark_primary_se(const mem_opt_t *opt, int n, mem_alnreg_t *a, int64_t id);
+extern void mem_reorder_primary5(int T, mem_alnreg_v *a);
+extern int mem_approx_mapq_se(const mem_opt_t *opt, const mem_alnreg_t *a);
+extern void mem_reg2sam(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, bseq1_t *s, mem_alnreg_v *a, int extra_flag, const mem_aln_t *m);
+
+int64_t ref_reg2sam_se(void *p, const void *opt_, int n_reads, int64_t n_processed, const uint8_t *seqs, const int64_t *off,
+                       void *regs_, const int32_t *cnt, int32_t *mapq, int64_t cap_sam, char *sam)
+{
+	bwaidx_t *idx = (bwaidx_t*)p;
+	const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	mem_alnreg_t *regs = (mem_alnreg_t*)regs_;
+	int64_t g = 0, ns = 0;
+	int r, k;
+	for (r = 0; r < n_reads; ++r) {
+		int l = (int)(off[r + 1] - off[r]);
+		mem_alnreg_v av;
+		bseq1_t s;
+		char name[32];
+		size_t ls;
+		av.n = av.m = cnt[r];
+		av.a = (mem_alnreg_t*)malloc((size_t)(cnt[r] > 0 ? cnt[r] : 1) * sizeof(mem_alnreg_t));
+		memcpy(av.a, regs + g, (size_t)cnt[r] * sizeof(mem_alnreg_t));
+		mem_mark_primary_se(opt, (int)av.n, av.a, n_processed + r);
+		if (opt->flag & MEM_F_PRIMARY5) mem_reorder_primary5(opt->T, &av);
+		memcpy(regs + g, av.a, (size_t)cnt[r] * sizeof(mem_alnreg_t));
+		for (k = 0; k < cnt[r]; ++k) mapq[g + k] = mem_approx_mapq_se(opt, &av.a[k]);
+		memset(&s, 0, sizeof(s));
+		snprintf(name, sizeof(name), "r%lld", (long long)(n_processed + r));
+		s.name = name; s.l_seq = l;
+		s.seq = (char*)malloc((size_t)l + 1);
+		memcpy(s.seq, seqs + off[r], (size_t)l);
+		mem_reg2sam(opt, idx->bns, idx->pac, &s, &av, 0, 0);
+		ls = strlen(s.sam);
+		if (ns + (int64_t)ls <= cap_sam) memcpy(sam + ns, s.sam, ls);
+		ns += (int64_t)ls;
+		free(s.sam); free(s.seq); free(av.a);
+		g += cnt[r];
+	}
+	return ns;
+}

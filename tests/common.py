@@ -47,11 +47,38 @@ GENOMES = {
     "tiny": ([20000, 12000, 7000], 5, 0.0),
     "small": ([200000, 100000], 7, 0.0),
     "rep": ([150000, 90000], 9, 0.08),
+    # explicit duplications (secondary hits, sub_n, XA within and beyond max_XA_hits) and an ALT contig (chr3) that is a
+    # diverged copy of a chr1 segment: see dup_genome()
+    "dup": ([60000, 40000, 5000], 11, 0.0),
 }
+ALT_CONTIGS = {"dup": [2]}
+
+
+def dup_genome():
+    lens, seed, _ = GENOMES["dup"]
+    rng = np.random.default_rng(seed)
+    c = [rng.integers(0, 4, size=int(n), dtype=np.uint8) for n in lens]
+
+    def mutated(x, div):
+        y = x.copy()
+        m = rng.random(len(y)) < div
+        y[m] = (y[m] + rng.integers(1, 4, size=int(m.sum()))) % 4
+        return y
+    a = c[0][1000:3000].copy()                               # 2 kb, 4 more copies at 0 - 2 % divergence
+    for k, (ci, pos, div) in enumerate([(0, 20000, 0.0), (1, 5000, 0.005), (1, 15000, 0.01), (0, 40000, 0.02)]):
+        y = mutated(a, div)
+        c[ci][pos:pos + len(y)] = (3 - y)[::-1] if k & 1 else y
+    b = c[1][30000:30400].copy()                             # 400 bp, 8 copies: more than max_XA_hits
+    for k in range(7):
+        c[0][45000 + 1000 * k:45400 + 1000 * k] = mutated(b, 0.003)
+    c[2][:] = mutated(c[0][10000:15000], 0.01)               # the ALT contig
+    return c
 
 
 @functools.lru_cache(maxsize=None)
 def genome(name: str):
+    if name == "dup":
+        return dup_genome()
     lens, seed, rep = GENOMES[name]
     return synth.make_genome(lens, seed=seed, repeat_frac=rep)
 
@@ -63,6 +90,9 @@ def ref_index(name: str):
     if not os.path.exists(pre + ".sa"):
         synth.write_fasta(pre + ".fa", genome(name))
         reflib().index_build(pre + ".fa", pre)
+    if name in ALT_CONTIGS and not os.path.exists(pre + ".alt"):     # bns_restore reads <prefix>.alt (bntseq.c:168-195)
+        with open(pre + ".alt", "w") as f:
+            f.write("".join(f"chr{i + 1}\n" for i in ALT_CONTIGS[name]))
     return reflib().index_load(pre)
 
 
@@ -71,6 +101,8 @@ def context(backend: str, name: str):
     """Device context holding the index of genome `name`, built by OUR host index builder."""
     lib = backend_lib(backend)
     h = L.HostIndex(genome(name), lib)
+    for i in ALT_CONTIGS.get(name, []):
+        h.ann_alt[i] = 1
     ctx = L.Context(0, lib)
     ctx.upload_host_index(h)
     ctx._host_index = h

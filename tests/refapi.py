@@ -247,6 +247,25 @@ class RefIndex:
                 continue
             return aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
 
+    def reg2sam_se(self, opt: MemOpt, seqs_nt4, off, regs, cnt, n_processed=0):
+        """worker2, SE (bwamem.c:1195-1205): mem_mark_primary_se (+ mem_reorder_primary5), mem_approx_mapq_se per region,
+        mem_reg2sam -> (regions as updated, mapq per region, SAM text bytes); reads are named r<global index>."""
+        n = len(off) - 1
+        regs = np.array(regs, copy=True); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        mapq = np.zeros(max(1, len(regs)), dtype=np.int32)
+        cap = 600 * max(1, n) + 4 * int(off[-1]) + 400 * len(regs) + 1024
+        self.lib.ref_reg2sam_se.restype = C.c_int64
+        while True:
+            sam = np.zeros(cap, dtype=np.uint8)
+            work = regs.copy()
+            need = self.lib.ref_reg2sam_se(self.h, C.byref(opt), C.c_int(n), C.c_int64(n_processed), _p(seqs_nt4, C.c_uint8),
+                                           _p(off, C.c_int64), C.c_void_p(work.ctypes.data), _p(cnt, C.c_int32),
+                                           _p(mapq, C.c_int32), C.c_int64(cap), C.c_void_p(sam.ctypes.data))
+            if need > cap:
+                cap = int(need) + 1024
+                continue
+            return work, mapq[: len(regs)], sam[:need].tobytes()
+
     def pestat(self, opt: MemOpt, regs, cnt):
         """mem_pestat (bwamem_pair.c:72) -> 4 x PESTAT_DTYPE"""
         from bwa_mem_gpu_b200.abi import PESTAT_DTYPE

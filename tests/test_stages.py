@@ -503,3 +503,74 @@ def test_align_batch_pipeline_edges(backend):
     assert np.array_equal(n0[n // 3:], n2) and r0[k:].tobytes() == r2.tobytes()
     assert tot == -len(r0) and np.array_equal(cnt, n0)
     assert len(r3) == 0 and len(n3) == 0
+
+
+def _nt4(seqs):
+    lut = np.full(256, 4, dtype=np.uint8)
+    for k, ch in enumerate("ACGT"):
+        lut[ord(ch)] = lut[ord(ch.lower())] = k
+    lut[:4] = np.arange(4)
+    return lut[np.asarray(seqs, dtype=np.uint8)]
+
+
+def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0):
+    """b200_reg2sam_se_batch + b200_sam_se_format against the reference's worker2 (mem_mark_primary_se,
+    mem_approx_mapq_se, mem_reg2sam): region arrays byte for byte, MAPQ, and the SAM text byte for byte."""
+    regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
+    r0, q0, sam0 = idx.reg2sam_se(opt, _nt4(seqs), off, regs, cnt, n_processed)
+    r1, sel, aln, cig, md = ctx.reg2sam_se(opt, seqs, off, regs, cnt, n_processed)
+    assert r0.tobytes() == r1.tobytes()                    # order, hash, sub, sub_n, alt_sc, secondary, secondary_all
+    rec = (sel["kind"] & 1) != 0
+    first = np.zeros(len(regs), dtype=bool)                # the first record of a read carries mem_approx_mapq_se unchanged
+    g = 0
+    for c in cnt:
+        ks = np.nonzero(rec[g:g + c])[0]
+        if len(ks):
+            first[g + ks[0]] = True
+        g += c
+    assert np.array_equal(sel["mapq"][first], q0[first])
+    names = [f"r{n_processed + i}" for i in range(len(off) - 1)]
+    sam1, soff = ctx.sam_se(opt, idx.anns()[3], names, seqs, off, cnt, sel, aln, cig, md)
+    if sam0 != sam1:
+        l0, l1 = sam0.split(b"\n"), sam1.split(b"\n")
+        for x, y in zip(l0, l1):
+            assert x == y
+        assert len(l0) == len(l1)
+    assert soff[-1] == len(sam1) and sam1[soff[1]:].startswith(names[1].encode()) if len(names) > 1 else True
+    return r1, sel, aln, sam1
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname", ["small", "rep", "dup"])
+def test_reg2sam_se(backend, gname):
+    """worker2's single-end half (bwamem.c:1195-1205): primary marking with the hash tie-break, MAPQ, record selection,
+    XA, SAM text -- clean reads, repeat-rich reads (secondary hits, sub / sub_n, XA), ragged / chimeric reads
+    (supplementary records, hard clips, SA tags), reads with no hit (unmapped record), -a, -Y, -5 and -M."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, _sizes(backend, 250, 20000), seed=91, sub=0.02, indel=0.01)
+    r1, sel, aln, sam = _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=12345)
+    if gname == "dup":                                     # duplicated segments and an ALT contig (tests/common.py dup_genome)
+        assert b"XA:Z:" in sam and b"pa:f:" in sam and (r1["sub_n"] > 0).any() and (sel["kind"] == 3).any()
+        assert (r1["secondary"] == 0x7fffffff).any() and (r1["alt_sc"] > 0).any()
+        assert (r1["secondary_all"] >= 0).sum() > (sel["kind"] & 2 != 0).sum()      # some reads exceed max_XA_hits: no XA for them
+    seqs, off = cm.ragged_reads(gname)
+    r1, sel, aln, sam = _check_reg2sam_se(idx, ctx, opt, seqs, off)
+    assert b"SA:Z:" in sam and (aln["flag"] & 0x800).any()
+    assert b"\t4\t*\t0\t0\t*" in sam                       # a read without any record
+    for flag in (0x8, 0x200, 0x800, 0x10, 0x8 | 0x2000 | 0x1000):      # MEM_F_ALL, SOFTCLIP, PRIMARY5, NO_MULTI, ALL|XB|KEEP_SUPP_MAPQ
+        o = abi.default_opt()
+        o.flag |= flag
+        _check_reg2sam_se(idx, ctx, o, seqs, off, n_processed=7)
+    o = abi.default_opt()
+    o.mapQ_coef_len = 0                                    # the other MAPQ formula (log(seedcov))
+    _check_reg2sam_se(idx, ctx, o, seqs, off)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_reg2sam_se_long_reads(backend):
+    idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
+    seqs, off = _long_reads("small", _sizes(backend, 6, 200), seed=19)
+    _check_reg2sam_se(idx, ctx, abi.default_opt(), seqs, off, n_processed=3)
