@@ -4,6 +4,8 @@
 // (bwamem_pair.c:72), worker2 = mem_mark_primary_se / mem_reg2sam / mem_sam_pe with MEM_F_NO_RESCUE
 // (bwamem.c:1197-1213) -- which this library does not contain: those symbols are resolved from the host
 // program the library is linked into (weak references, or the global symbol scope when loaded dynamically).
+// Single-end batches do not need them: worker2 runs on the device (b200_reg2sam_se_batch) and the SAM text is written
+// by b200_sam_se_format; b200_process_seqs_host_worker2(1) switches back to the host program's functions.
 // Nothing here computes alignments on the CPU; if the host functions are missing the call fails loudly.
 #include <dlfcn.h>
 #include <stdio.h>
@@ -59,6 +61,8 @@ static inline uint8_t nt4_of(uint8_t c)
 static std::vector<b200_ctx_t *> g_ps_ctxs;
 static const bwt_t *g_ps_bwt = nullptr;
 static int g_ps_want_devices = 1;
+static int g_ps_host_worker2 = 0;
+extern "C" void b200_process_seqs_host_worker2(int on) { g_ps_host_worker2 = on; }
 
 extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctxs.assign(1, ctx); g_ps_bwt = nullptr; }
 extern "C" void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs) { g_ps_ctxs.assign(ctxs, ctxs + n); g_ps_bwt = nullptr; }
@@ -68,6 +72,8 @@ struct Shard {
     b200_ctx_t *ctx; int r0, n;
     std::vector<mem_alnreg_t> regs; std::vector<int32_t> cnt;
     std::string err;
+    std::vector<b200_sel_t> sel; std::vector<b200_aln_t> aln; std::vector<uint32_t> cig; std::vector<char> md, sam;
+    std::vector<int64_t> sam_off;
 };
 
 static void shard_download(Shard &sh)
@@ -94,9 +100,10 @@ static void run_shards(std::vector<Shard> &shards, const std::function<void(Shar
 extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                                       int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
 {
-    mark_fn f_mark = (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
-    reg2sam_fn f_reg2sam = (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
     const bool pe = (opt->flag & MEM_F_PE) != 0;
+    const bool dev_worker2 = !pe && !g_ps_host_worker2;
+    mark_fn f_mark = dev_worker2 ? nullptr : (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
+    reg2sam_fn f_reg2sam = dev_worker2 ? nullptr : (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
     sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
     pestat_fn f_pestat = (pe && !pes0) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
 
@@ -133,6 +140,58 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         if (b200_batch_upload(sh.ctx, sh.n, flat.data(), off.data() + sh.r0) || b200_batch_run(sh.ctx, opt, nullptr)) { sh.err = b200_last_error(); return; }
         shard_download(sh);
     });
+    if (dev_worker2) {                                                // bwamem.c:1202-1207 for every read, on the device
+        int n_qual = 0;
+        for (int i = 0; i < n; ++i) n_qual += seqs[i].qual != nullptr;
+        if (n_qual && n_qual != n) { fprintf(stderr, "[b200::mem_process_seqs] reads with and without qualities in one batch\n"); exit(1); }
+        std::vector<uint8_t> qflat(n_qual ? (size_t)tot + 1 : 0);
+        std::vector<const char *> names((size_t)n + 1), comments((size_t)n + 1), ann_names((size_t)bns->n_seqs + 1), ann_annos((size_t)bns->n_seqs + 1);
+        for (int i = 0; i < n; ++i) {
+            if (n_qual) memcpy(qflat.data() + off[i], seqs[i].qual, (size_t)seqs[i].l_seq);
+            names[i] = seqs[i].name; comments[i] = seqs[i].comment;
+        }
+        for (int i = 0; i < bns->n_seqs; ++i) { ann_names[i] = bns->anns[i].name; ann_annos[i] = bns->anns[i].anno; }
+        const char *rg = (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
+        const int fmt_threads = std::max(1, (opt->n_threads > 0 ? opt->n_threads : 1) / G);
+        run_shards(shards, [&](Shard &sh) {
+            const size_t nr = sh.regs.size();
+            sh.sel.resize(nr + 1); sh.aln.resize(nr + 1);
+            sh.cig.resize(4 * nr + 64); sh.md.resize(16 * nr + 64);
+            int64_t totals[2];
+            const std::vector<mem_alnreg_t> unmarked = sh.regs;        // the call updates regs in place, also when a pool was too small
+            for (;;) {
+                const int64_t rc = b200_reg2sam_se_batch(sh.ctx, opt, sh.n, n_processed + sh.r0, flat.data(), off.data() + sh.r0,
+                                                         sh.regs.data(), sh.cnt.data(), sh.sel.data(), sh.aln.data(),
+                                                         (int64_t)sh.cig.size(), sh.cig.data(), (int64_t)sh.md.size(), sh.md.data(), totals);
+                if (rc == -2) {
+                    sh.cig.resize((size_t)totals[0] + 64); sh.md.resize((size_t)totals[1] + 64);
+                    sh.regs = unmarked;
+                    continue;
+                }
+                if (rc < 0) { sh.err = b200_last_error(); return; }
+                break;
+            }
+            sh.sam_off.assign((size_t)sh.n + 1, 0);
+            sh.sam.resize((size_t)sh.n * 420 + 4096);
+            for (;;) {
+                const int64_t rc = b200_sam_se_format(opt, ann_names.data(), ann_annos.data(), sh.n, names.data() + sh.r0,
+                                                      comments.data() + sh.r0, flat.data(), n_qual ? qflat.data() : nullptr,
+                                                      off.data() + sh.r0, sh.cnt.data(), sh.sel.data(), sh.aln.data(), sh.cig.data(),
+                                                      sh.md.data(), rg, fmt_threads, (int64_t)sh.sam.size(), sh.sam.data(), sh.sam_off.data());
+                if (rc < 0) { sh.sam.resize((size_t)-rc + 64); continue; }
+                break;
+            }
+            for (int i = 0; i < sh.n; ++i) {                           // seqs[i].sam: heap memory owned by the caller (bwamem.c:1054)
+                const size_t l = (size_t)(sh.sam_off[i + 1] - sh.sam_off[i]);
+                char *o = (char *)malloc(l + 1);
+                memcpy(o, sh.sam.data() + sh.sam_off[i], l); o[l] = 0;
+                seqs[sh.r0 + i].sam = o;
+            }
+        });
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < seqs[i].l_seq; ++j) seqs[i].seq[j] = (char)nt4_of((uint8_t)seqs[i].seq[j]);   // bwamem.c:1067-1068
+        return;
+    }
     mem_alnreg_v *rv = (mem_alnreg_v *)malloc((size_t)(n > 0 ? n : 1) * sizeof(mem_alnreg_v));
     auto fill_rv = [&](bool first) {
         for (auto &sh : shards)

@@ -206,7 +206,8 @@ int64_t b200_reg2aln_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, c
  *   mapq   final MAPQ of the record;  flag  0x800 / 0x10000 for supplementary records (also OR-ed into out_aln.flag).
  * out_aln[g].sub is -1 for secondary records as in mem_reg2sam.  A read none of whose regions has kind bit 0 gets the
  * unmapped record (mem_reg2aln with ar = 0: rid -1, pos -1, flag 0x4), which needs no device work: b200_sam_se_format
- * writes it.  Return value and pools as b200_reg2aln_batch. */
+ * writes it.  Return value and pools as b200_reg2aln_batch; after -2 regs may already be updated, so call again with
+ * the original regions (marking is not idempotent: sub_n accumulates, as in the reference). */
 typedef struct { int32_t kind, mapq, xa_of, flag; } b200_sel_t;
 int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, int64_t n_processed, const uint8_t *seqs,
                               const int64_t *off, mem_alnreg_t *regs, const int32_t *cnt, b200_sel_t *out_sel,
@@ -310,9 +311,12 @@ int b200_microbench(b200_ctx_t *ctx, int kind, int64_t table_bytes, int blocks_p
  * device code on a batch of one (parity tests call these one problem at a time).  The device
  * context/index is created lazily from the bwt_t identity on first use.
  * ===================================================================================== */
-/* mem_process_seqs (bwamem.h:69, bwamem.c:1215): worker1 on the device, then the REFERENCE's own host code for
- * mem_pestat / worker2 (mem_mark_primary_se, mem_reg2sam, mem_sam_pe), resolved from the program this library is
- * linked into.  seqs[i].sam is produced by that host code and owned by the caller, as in the reference.
+/* mem_process_seqs (bwamem.h:69, bwamem.c:1215): worker1 on the device.  Single-end batches: worker2 on the device
+ * too (b200_reg2sam_se_batch) and the SAM text from b200_sam_se_format -- no function of the host program is needed
+ * (RG tag: the host program's global bwa_rg_id, if it has one).  Paired-end batches, or after
+ * b200_process_seqs_host_worker2(1): the REFERENCE's own host code for mem_pestat / worker2 (mem_mark_primary_se,
+ * mem_reg2sam, mem_sam_pe), resolved from the program this library is linked into.  seqs[i].sam is heap memory
+ * owned by the caller, as in the reference.
  * b200_process_seqs_set_ctx() selects an existing context (index already uploaded); otherwise one is created on
  * device 0 from (bwt, bns, pac) at the first call. */
 void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
@@ -321,6 +325,7 @@ void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
  * already hold the index, or ask for contexts on devices 0..n-1 to be created at the first call. */
 void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs);
 void b200_process_seqs_use_devices(int n_devices);
+void b200_process_seqs_host_worker2(int on);
 void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                            int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
 

@@ -1,5 +1,5 @@
-"""End-to-end drop-in parity: our mem_process_seqs (worker1 on the device through the C ABI, then the reference's own
-worker2 host code) must produce byte-identical SAM records to the reference's mem_process_seqs (bwamem.c:1215) --
+"""End-to-end drop-in parity: our mem_process_seqs (worker1 on the device through the C ABI; worker2 on the device too
+for single-end batches, the reference's own worker2 host code for pairs) must produce byte-identical SAM records to the reference's mem_process_seqs (bwamem.c:1215) --
 POS, CIGAR, MAPQ, NM, MD, AS, XS, SA/XA tags, flags -- for single-end and paired-end batches.
 """
 import ctypes as C
@@ -22,7 +22,7 @@ class BSeq1(C.Structure):          # bseq1_t, bwa.h:56-63
                 ("l_name", C.c_int8), ("l_comment", C.c_int8), ("l_qual", C.c_int16)]
 
 
-def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards=1):
+def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards=1, quals=None, host_worker2=0):
     idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
     C.CDLL(refapi.REF_SO, mode=os.RTLD_GLOBAL)          # the "host program": the reference's worker2 functions
     lib = ctx.lib
@@ -36,6 +36,10 @@ def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards
         keep.append((s, nm))
         arr[i].l_seq = int(off[i + 1] - off[i]); arr[i].id = i
         arr[i].name = nm; arr[i].comment = None; arr[i].seq = C.cast(s, C.POINTER(C.c_char)); arr[i].qual = None
+        if quals is not None:
+            q = bytes(quals[off[i]:off[i + 1]]) + b"\0"
+            keep.append(q)
+            arr[i].qual = q
     if n_shards == 1:
         lib.b200_process_seqs_set_ctx(ctx.h)
     else:                                                   # several contexts (here: all on device 0), one block of reads each
@@ -47,6 +51,7 @@ def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards
         keep.append(extra)
         hs = (C.c_void_p * n_shards)(ctx.h, *[c.h for c in extra])
         lib.b200_process_seqs_set_ctxs(n_shards, hs)
+    lib.b200_process_seqs_host_worker2(host_worker2)
     lib.b200_mem_process_seqs(C.byref(opt), C.c_void_p(idx.bwt_struct()), C.c_void_p(idx.bns_struct()),
                               C.c_void_p(idx.pac().ctypes.data), C.c_int64(n_processed), C.c_int(n), arr, None)
     out = b"".join(C.string_at(arr[i].sam) for i in range(n))
@@ -57,8 +62,10 @@ def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("gname", ["small", "rep"])
+@pytest.mark.parametrize("gname", ["small", "rep", "dup"])
 def test_sam_single_end(backend, gname):
+    """Reads -> SAM text through the reference's batch entry.  worker2 on the device (the default) and through the host
+    program's functions; "dup": duplicated segments and an ALT contig (XA, pa, secondary_all); with qualities."""
     idx = cm.ref_index(gname)
     opt = abi.default_opt()
     opt.n_threads = 4
@@ -68,6 +75,15 @@ def test_sam_single_end(backend, gname):
     got = _our_sam(backend, gname, opt, seqs, off, n_processed=1000)
     assert got == exp
     assert exp.count(b"\n") >= n
+    assert _our_sam(backend, gname, opt, seqs, off, n_processed=1000, host_worker2=1) == exp
+    quals = np.random.default_rng(5).integers(35, 74, size=len(seqs), dtype=np.uint8)
+    seqs2, off2 = cm.ragged_reads(gname)
+    o = abi.default_opt()
+    o.n_threads = 2
+    o.flag |= 0x800 | 0x200                                 # -5 -Y
+    for oo in (opt, o):
+        exp = idx.process_seqs(oo, synth.to_ascii(seqs2), off2, quals=quals[: len(seqs2)], n_processed=5)
+        assert _our_sam(backend, gname, oo, seqs2, off2, n_processed=5, quals=quals[: len(seqs2)]) == exp
 
 
 @needs_ref
