@@ -164,7 +164,53 @@ def microbench_ceilings():
     return json.load(open(p)) if os.path.exists(p) else None
 
 
-def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None):
+def reads_to_sam(a, ctx, hidx, opt, seqs, off, regs, cnt, e2e_ms, threads):
+    """SURVEY.md 8(d) "reads in memory -> SAM text": the first m reads of the step's batch through b200_reg2sam_se_batch
+    (worker2 on the device: primary marking, MAPQ, record selection, XA, CIGAR/NM/MD) and b200_sam_se_format (host threads),
+    timed around the C calls with host buffers; the align share is the e2e time of those m reads."""
+    import ctypes as C
+    from bwa_mem_gpu_b200 import abi
+    m = min(a.reads, 2_000_000)
+    cnt = np.ascontiguousarray(cnt[:m]); nr = int(cnt.astype(np.int64).sum())
+    regs0 = np.array(regs[:nr], copy=True)
+    sel = np.zeros(nr + 1, dtype=abi.SEL_DTYPE); aln = np.zeros(nr + 1, dtype=abi.ALN_DTYPE)
+    cig = np.zeros(4 * nr + 64, dtype=np.uint32); md = np.zeros(16 * nr + 64, dtype=np.uint8)
+    tot2 = (C.c_int64 * 2)()
+    P = lambda x, ty: x.ctypes.data_as(C.POINTER(ty))
+    sub_off = np.ascontiguousarray(off[: m + 1])
+    t_w2 = None
+    for _ in range(2):                                     # the first call sizes the context's grow-only buffers
+        regs2 = regs0.copy()
+        t0 = time.perf_counter()
+        rc = ctx.lib.b200_reg2sam_se_batch(ctx.h, C.byref(opt), C.c_int(m), C.c_int64(0), P(seqs, C.c_uint8), P(sub_off, C.c_int64),
+                                           C.c_void_p(regs2.ctypes.data), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data),
+                                           C.c_void_p(aln.ctypes.data), C.c_int64(len(cig)), P(cig, C.c_uint32), C.c_int64(len(md)),
+                                           C.c_void_p(md.ctypes.data), tot2)
+        t_w2 = time.perf_counter() - t0
+        if rc != nr:
+            return {"error": ctx.lib.b200_last_error().decode()}, None
+    a_names = (C.c_char_p * len(hidx.names))(*[x.encode() for x in hidx.names])
+    r_names = (C.c_char_p * m)(*[b"r%d" % i for i in range(m)])
+    soff = np.zeros(m + 1, dtype=np.int64)
+    sam = np.zeros((a.read_len + 120) * m + 4096, dtype=np.uint8)
+    t_fmt = None
+    for _ in range(2):
+        t0 = time.perf_counter()
+        nb = ctx.lib.b200_sam_se_format(C.byref(opt), a_names, None, C.c_int(m), r_names, None, P(seqs, C.c_uint8), None,
+                                        P(sub_off, C.c_int64), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data),
+                                        P(cig, C.c_uint32), C.c_void_p(md.ctypes.data), None, C.c_int(threads), C.c_int64(len(sam)),
+                                        C.c_void_p(sam.ctypes.data), P(soff, C.c_int64))
+        t_fmt = time.perf_counter() - t0
+        if nb < 0:
+            sam = np.zeros(int(-nb) + 64, dtype=np.uint8)
+    t_al = e2e_ms * 1e-3 * m / a.reads
+    out = {"value": m / (t_al + t_w2 + t_fmt), "unit": UNIT, "reads": m, "sam_bytes": int(nb),
+           "align_s": t_al, "worker2_device_s": t_w2, "sam_format_s": t_fmt, "format_threads": threads,
+           "path": "b200_align_batch -> b200_reg2sam_se_batch -> b200_sam_se_format (host buffers throughout)"}
+    return out, (regs0, cnt, regs2, sam, soff)
+
+
+def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None, sam_check=None):
     """The reference's CPU implementation of the same path (mem_align1_core over kt_for), oracle/_ref."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import refapi
@@ -187,6 +233,19 @@ def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None):
         r0, c0 = idx.align(opt, seqs, off[: n_chk + 1], n_threads=threads, cap_per_read=64)
         same = bool(np.array_equal(c0, dev_cnt[:n_chk])) and r0.tobytes() == dev_regs[: int(c0.sum())].tobytes()
         out["parity_sample"] = {"reads": int(n_chk), "regions": int(c0.sum()), "identical_to_reference": same}
+    if sam_check is not None and check is not None:        # the reference's worker2 (mem_mark_primary_se + mem_reg2sam) on the sample
+        regs0, cnt_s, regs2, sam, soff = sam_check
+        n_chk = min(check[0], len(cnt_s))
+        k = int(cnt_s[:n_chk].astype(np.int64).sum())
+        lut = np.full(256, 4, dtype=np.uint8); lut[:4] = np.arange(4)
+        for c, ch in enumerate("ACGT"):
+            lut[ord(ch)] = lut[ord(ch.lower())] = c
+        t0 = time.time()
+        r0, _, sam0 = idx.reg2sam_se(opt, lut[seqs[: int(off[n_chk])]], off[: n_chk + 1], regs0[:k], cnt_s[:n_chk])
+        dt = time.time() - t0
+        out["sam_parity_sample"] = {"reads": int(n_chk), "sam_bytes": len(sam0), "ref_worker2_reads_per_s_1thread": n_chk / dt,
+                                    "regions_identical": bool(r0.tobytes() == regs2[:k].tobytes()),
+                                    "sam_identical_to_reference": bool(sam0 == sam[: int(soff[n_chk])].tobytes())}
     return out
 
 
@@ -362,12 +421,15 @@ def main():
                 dev_cnt = pin_n.numpy()[:n_chk].copy()
                 dev_regs = np.frombuffer(pin_out.numpy()[: int(dev_cnt.sum()) * abi.ALNREG_DTYPE.itemsize].tobytes(), dtype=abi.ALNREG_DTYPE)
                 chk = (n_chk, dev_regs, dev_cnt)
-            cb = cpu_reference(a, hidx, seqs, off, n_sample, cores, chk)
-            if cb is not None:
-                out["parity_sample"] = cb.pop("parity_sample", None)
-                out["cpu_baseline"] = cb
         all_cnt = pin_n.numpy()[: a.reads]
         all_regs = np.frombuffer(pin_out.numpy()[: int(all_cnt.astype(np.int64).sum()) * abi.ALNREG_DTYPE.itemsize], dtype=abi.ALNREG_DTYPE)
+        out["reads_to_sam"], sam_chk = reads_to_sam(a, ctx, hidx, opt, seqs, off, all_regs, all_cnt, e2e_ms_max, cores)
+        if not a.no_cpu_baseline:
+            cb = cpu_reference(a, hidx, seqs, off, n_sample, cores, chk, sam_chk)
+            if cb is not None:
+                out["parity_sample"] = cb.pop("parity_sample", None)
+                out["reads_to_sam"]["parity_sample"] = cb.pop("sam_parity_sample", None)
+                out["cpu_baseline"] = cb
         out["truth_check"] = truth_check(a, contigs, build_inputs.truth, all_regs, all_cnt)
         print(json.dumps(out))
     if world > 1:

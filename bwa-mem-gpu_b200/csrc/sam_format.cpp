@@ -87,11 +87,19 @@ void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &lis
             }
         }
         if (!a.is_rev) {
-            for (int i = qb; i < qe; ++i) s.push_back("ACGTN"[code_of(seq[i])]);
+            const int m = std::max(0, qe - qb);
+            const size_t o = s.size();
+            s.resize(o + (size_t)m);
+            char *d = &s[o];
+            for (int i = 0; i < m; ++i) d[i] = "ACGTN"[code_of(seq[qb + i])];
             s.push_back('\t');
             if (qual) s.append((const char *)qual + qb, (size_t)std::max(0, qe - qb)); else s.push_back('*');
         } else {
-            for (int i = qe - 1; i >= qb; --i) s.push_back("TGCAN"[code_of(seq[i])]);
+            const int m = std::max(0, qe - qb);
+            const size_t o = s.size();
+            s.resize(o + (size_t)m);
+            char *d = &s[o];
+            for (int i = 0; i < m; ++i) d[i] = "TGCAN"[code_of(seq[qe - 1 - i])];
             s.push_back('\t');
             if (qual) for (int i = qe - 1; i >= qb; --i) s.push_back((char)qual[i]); else s.push_back('*');
         }
@@ -134,12 +142,15 @@ void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &lis
     s.push_back('\n');
 }
 
-void one_read(std::string &s, const Job &J, int r)
+struct Scratch { std::vector<Rec> list; std::vector<int> reg_of; std::vector<std::string> xa; };      // reused over a thread's reads
+
+void one_read(std::string &s, const Job &J, int r, Scratch &W)
 {
     const int64_t g0 = J.roff[r];
     const int n = (int)(J.roff[r + 1] - g0);
-    std::vector<Rec> list;
-    std::vector<int> reg_of;
+    std::vector<Rec> &list = W.list;
+    std::vector<int> &reg_of = W.reg_of;
+    list.clear(); reg_of.clear();
     for (int k = 0; k < n; ++k)
         if (J.sel[g0 + k].kind & 1) {
             const b200_aln_t *a = J.aln + g0 + k;
@@ -147,7 +158,10 @@ void one_read(std::string &s, const Job &J, int r)
             reg_of.push_back(k);
         }
     if (list.empty()) { one_record(s, J, r, list, 0, nullptr); return; }
-    std::vector<std::string> xa(list.size());
+    if (n == 1) { one_record(s, J, r, list, 0, nullptr); return; }      // one region, one record: no XA, no SA
+    std::vector<std::string> &xa = W.xa;
+    if (xa.size() < list.size()) xa.resize(list.size());
+    for (size_t w = 0; w < list.size(); ++w) xa[w].clear();
     for (int i = 0; i < n; ++i) {                        // mem_gen_alt: entries appended in region order
         const b200_sel_t &e = J.sel[g0 + i];
         if (!(e.kind & 2)) continue;
@@ -184,9 +198,10 @@ extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *a
         std::string &s = part[t];
         s.reserve((size_t)(hi - lo) * 400);
         lens[t].reserve((size_t)(hi - lo));
+        Scratch W;
         for (int r = lo; r < hi; ++r) {
             const size_t before = s.size();
-            one_read(s, J, r);
+            one_read(s, J, r, W);
             lens[t].push_back((int64_t)(s.size() - before));
         }
     };
@@ -204,7 +219,14 @@ extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *a
         sam_off[n_reads] = o;
     }
     if (total > cap) return -total;
-    int64_t o = 0;
-    for (auto &s : part) { memcpy(sam + o, s.data(), s.size()); o += (int64_t)s.size(); }
+    std::vector<int64_t> start((size_t)nt, 0);
+    for (int t = 1; t < nt; ++t) start[t] = start[t - 1] + (int64_t)part[t - 1].size();
+    auto copy = [&](int t) { memcpy(sam + start[t], part[t].data(), part[t].size()); };
+    if (nt == 1) copy(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t) th.emplace_back(copy, t);
+        for (auto &x : th) x.join();
+    }
     return total;
 }

