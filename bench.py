@@ -164,50 +164,54 @@ def microbench_ceilings():
     return json.load(open(p)) if os.path.exists(p) else None
 
 
-def reads_to_sam(a, ctx, hidx, opt, seqs, off, regs, cnt, e2e_ms, threads):
-    """SURVEY.md 8(d) "reads in memory -> SAM text": the first m reads of the step's batch through b200_reg2sam_se_batch
-    (worker2 on the device: primary marking, MAPQ, record selection, XA, CIGAR/NM/MD) and b200_sam_se_format (host threads),
-    timed around the C calls with host buffers; the align share is the e2e time of those m reads."""
+def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
+    """SURVEY.md 8(d) "reads in memory -> SAM text": the first m reads of the step's batch through b200_align_batch (region
+    counts only come back: cap 0), b200_batch_reg2sam_se (worker2 on the resident batch: primary marking, MAPQ, record
+    selection, XA, CIGAR/NM/MD) and b200_sam_se_format (host threads); one timed region around the three C calls, pinned
+    host buffers for the reads, pageable numpy buffers for the results."""
     import ctypes as C
     from bwa_mem_gpu_b200 import abi
     m = min(a.reads, 2_000_000)
-    cnt = np.ascontiguousarray(cnt[:m]); nr = int(cnt.astype(np.int64).sum())
-    regs0 = np.array(regs[:nr], copy=True)
-    sel = np.zeros(nr + 1, dtype=abi.SEL_DTYPE); aln = np.zeros(nr + 1, dtype=abi.ALN_DTYPE)
-    cig = np.zeros(4 * nr + 64, dtype=np.uint32); md = np.zeros(16 * nr + 64, dtype=np.uint8)
-    tot2 = (C.c_int64 * 2)()
     P = lambda x, ty: x.ctypes.data_as(C.POINTER(ty))
-    sub_off = np.ascontiguousarray(off[: m + 1])
-    t_w2 = None
-    for _ in range(2):                                     # the first call sizes the context's grow-only buffers
-        regs2 = regs0.copy()
-        t0 = time.perf_counter()
-        rc = ctx.lib.b200_reg2sam_se_batch(ctx.h, C.byref(opt), C.c_int(m), C.c_int64(0), P(seqs, C.c_uint8), P(sub_off, C.c_int64),
-                                           C.c_void_p(regs2.ctypes.data), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data),
-                                           C.c_void_p(aln.ctypes.data), C.c_int64(len(cig)), P(cig, C.c_uint32), C.c_int64(len(md)),
-                                           C.c_void_p(md.ctypes.data), tot2)
-        t_w2 = time.perf_counter() - t0
-        if rc != nr:
-            return {"error": ctx.lib.b200_last_error().decode()}, None
+    seqs = pin_seq.numpy(); off = pin_off.numpy()[: m + 1]
+    cnt = np.zeros(m, dtype=np.int32)
     a_names = (C.c_char_p * len(hidx.names))(*[x.encode() for x in hidx.names])
     r_names = (C.c_char_p * m)(*[b"r%d" % i for i in range(m)])
     soff = np.zeros(m + 1, dtype=np.int64)
     sam = np.zeros((a.read_len + 120) * m + 4096, dtype=np.uint8)
-    t_fmt = None
-    for _ in range(2):
+    cap_r = int(m * 1.2) + 1024
+    sel = np.zeros(cap_r, dtype=abi.SEL_DTYPE); aln = np.zeros(cap_r, dtype=abi.ALN_DTYPE)
+    regs2 = np.zeros(cap_r, dtype=abi.ALNREG_DTYPE)
+    cig = np.zeros(4 * cap_r + 64, dtype=np.uint32); md = np.zeros(16 * cap_r + 64, dtype=np.uint8)
+    tot2 = (C.c_int64 * 2)()
+    best = None
+    for it in range(3):                                    # the first pass sizes the context's grow-only buffers
         t0 = time.perf_counter()
+        nr = -ctx.lib.b200_align_batch(ctx.h, C.byref(opt), C.c_int(m), P(seqs, C.c_uint8), P(off, C.c_int64), C.c_int64(0), None,
+                                       P(cnt, C.c_int32))
+        t1 = time.perf_counter()
+        if nr <= 0 or nr > cap_r:
+            return {"error": f"align: {nr}"}, None
+        rc = ctx.lib.b200_batch_reg2sam_se(ctx.h, C.byref(opt), C.c_int64(0), P(cnt, C.c_int32),
+                                           C.c_void_p(regs2.ctypes.data) if it == 0 else None, C.c_void_p(sel.ctypes.data),
+                                           C.c_void_p(aln.ctypes.data), C.c_int64(len(cig)), P(cig, C.c_uint32), C.c_int64(len(md)),
+                                           C.c_void_p(md.ctypes.data), tot2)
+        t2 = time.perf_counter()
+        if rc != nr:
+            return {"error": ctx.lib.b200_last_error().decode()}, None
         nb = ctx.lib.b200_sam_se_format(C.byref(opt), a_names, None, C.c_int(m), r_names, None, P(seqs, C.c_uint8), None,
-                                        P(sub_off, C.c_int64), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data),
+                                        P(off, C.c_int64), P(cnt, C.c_int32), C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data),
                                         P(cig, C.c_uint32), C.c_void_p(md.ctypes.data), None, C.c_int(threads), C.c_int64(len(sam)),
                                         C.c_void_p(sam.ctypes.data), P(soff, C.c_int64))
-        t_fmt = time.perf_counter() - t0
+        t3 = time.perf_counter()
         if nb < 0:
-            sam = np.zeros(int(-nb) + 64, dtype=np.uint8)
-    t_al = e2e_ms * 1e-3 * m / a.reads
-    out = {"value": m / (t_al + t_w2 + t_fmt), "unit": UNIT, "reads": m, "sam_bytes": int(nb),
-           "align_s": t_al, "worker2_device_s": t_w2, "sam_format_s": t_fmt, "format_threads": threads,
-           "path": "b200_align_batch -> b200_reg2sam_se_batch -> b200_sam_se_format (host buffers throughout)"}
-    return out, (regs0, cnt, regs2, sam, soff)
+            return {"error": f"sam buffer: {nb}"}, None
+        if it and (best is None or t3 - t0 < best[0]):
+            best = (t3 - t0, t1 - t0, t2 - t1, t3 - t2)
+    out = {"value": m / best[0], "unit": UNIT, "reads": m, "regions": int(nr), "sam_bytes": int(nb),
+           "align_s": best[1], "worker2_device_s": best[2], "sam_format_s": best[3], "format_threads": threads,
+           "path": "b200_align_batch (counts only) -> b200_batch_reg2sam_se (resident batch) -> b200_sam_se_format; best of 2 timed passes"}
+    return out, (cnt, regs2, sam, soff)
 
 
 def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None, sam_check=None):
@@ -234,9 +238,10 @@ def cpu_reference(a, hidx, seqs, off, n_sample, threads, check=None, sam_check=N
         same = bool(np.array_equal(c0, dev_cnt[:n_chk])) and r0.tobytes() == dev_regs[: int(c0.sum())].tobytes()
         out["parity_sample"] = {"reads": int(n_chk), "regions": int(c0.sum()), "identical_to_reference": same}
     if sam_check is not None and check is not None:        # the reference's worker2 (mem_mark_primary_se + mem_reg2sam) on the sample
-        regs0, cnt_s, regs2, sam, soff = sam_check
+        cnt_s, regs2, sam, soff = sam_check
         n_chk = min(check[0], len(cnt_s))
         k = int(cnt_s[:n_chk].astype(np.int64).sum())
+        regs0 = check[1]                                   # worker1's regions of the sample, as downloaded by the e2e call
         lut = np.full(256, 4, dtype=np.uint8); lut[:4] = np.arange(4)
         for c, ch in enumerate("ACGT"):
             lut[ord(ch)] = lut[ord(ch.lower())] = c
@@ -423,7 +428,7 @@ def main():
                 chk = (n_chk, dev_regs, dev_cnt)
         all_cnt = pin_n.numpy()[: a.reads]
         all_regs = np.frombuffer(pin_out.numpy()[: int(all_cnt.astype(np.int64).sum()) * abi.ALNREG_DTYPE.itemsize], dtype=abi.ALNREG_DTYPE)
-        out["reads_to_sam"], sam_chk = reads_to_sam(a, ctx, hidx, opt, seqs, off, all_regs, all_cnt, e2e_ms_max, cores)
+        out["reads_to_sam"], sam_chk = reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, cores)
         if not a.no_cpu_baseline:
             cb = cpu_reference(a, hidx, seqs, off, n_sample, cores, chk, sam_chk)
             if cb is not None:

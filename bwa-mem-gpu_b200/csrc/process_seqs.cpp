@@ -74,6 +74,7 @@ struct Shard {
     std::string err;
     std::vector<b200_sel_t> sel; std::vector<b200_aln_t> aln; std::vector<uint32_t> cig; std::vector<char> md, sam;
     std::vector<int64_t> sam_off;
+    int64_t n_regs = 0;
 };
 
 static void shard_download(Shard &sh)
@@ -138,6 +139,12 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         sh.cnt.assign((size_t)sh.n + 1, 0);
         sh.regs.resize((size_t)(2 * (int64_t)sh.n + 64));
         if (b200_batch_upload(sh.ctx, sh.n, flat.data(), off.data() + sh.r0) || b200_batch_run(sh.ctx, opt, nullptr)) { sh.err = b200_last_error(); return; }
+        if (dev_worker2) {                                            // the regions stay on the device: only their counts come back
+            const int64_t got = b200_batch_download(sh.ctx, 0, nullptr, sh.cnt.data());
+            if (got > 0 || (got < 0 && -got >= 0x7fffffff)) { sh.err = "region download"; return; }
+            sh.n_regs = -got;
+            return;
+        }
         shard_download(sh);
     });
     if (dev_worker2) {                                                // bwamem.c:1202-1207 for every read, on the device
@@ -154,18 +161,15 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         const char *rg = (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
         const int fmt_threads = std::max(1, (opt->n_threads > 0 ? opt->n_threads : 1) / G);
         run_shards(shards, [&](Shard &sh) {
-            const size_t nr = sh.regs.size();
+            const size_t nr = (size_t)sh.n_regs;
             sh.sel.resize(nr + 1); sh.aln.resize(nr + 1);
             sh.cig.resize(4 * nr + 64); sh.md.resize(16 * nr + 64);
             int64_t totals[2];
-            const std::vector<mem_alnreg_t> unmarked = sh.regs;        // the call updates regs in place, also when a pool was too small
-            for (;;) {
-                const int64_t rc = b200_reg2sam_se_batch(sh.ctx, opt, sh.n, n_processed + sh.r0, flat.data(), off.data() + sh.r0,
-                                                         sh.regs.data(), sh.cnt.data(), sh.sel.data(), sh.aln.data(),
+            for (;;) {                                                 // on the resident batch: nothing is uploaded
+                const int64_t rc = b200_batch_reg2sam_se(sh.ctx, opt, n_processed + sh.r0, sh.cnt.data(), nullptr, sh.sel.data(), sh.aln.data(),
                                                          (int64_t)sh.cig.size(), sh.cig.data(), (int64_t)sh.md.size(), sh.md.data(), totals);
                 if (rc == -2) {
                     sh.cig.resize((size_t)totals[0] + 64); sh.md.resize((size_t)totals[1] + 64);
-                    sh.regs = unmarked;
                     continue;
                 }
                 if (rc < 0) { sh.err = b200_last_error(); return; }

@@ -302,14 +302,19 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
                             mem_alnreg_t *regs_out, b200_sel_t *out_sel, int64_t n_processed)
 {
     const bool finalize = out_sel != nullptr;
+    const bool resident = regs == nullptr;                 // reads and regions are those of the batch the context just aligned
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
-    if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    if (resident) {
+        B200_CHECK(cudaSetDevice(ctx->device));
+        n_reads = ctx->n_reads;
+    } else if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
     cudaStream_t st = ctx->st;
     if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
     std::vector<i64> roff((size_t)n_reads + 1, 0);
     int max_cnt = 0;
     for (int r = 0; r < n_reads; ++r) { roff[r + 1] = roff[r] + cnt[r]; max_cnt = std::max(max_cnt, (int)cnt[r]); }
     const i64 n_regs = roff[n_reads];
+    if (resident && n_regs != ctx->total_regs) { b200_set_error("region counts do not match the resident batch"); return -1; }
     if (totals) totals[0] = totals[1] = 0;
     if (n_regs == 0) return 0;
     if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
@@ -360,7 +365,9 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             while (r_hi < n_reads && roff[r_hi + 1] - g0 <= chunk) ++r_hi;
             n = (int)(roff[r_hi] - g0);
         }
-        B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
+        if (resident)      // a copy: marking is not idempotent (sub_n accumulates), the resident regions stay as worker1 left them
+            B200_CHECK(cudaMemcpyAsync(d_regs.p, ctx->d_final.as<mem_alnreg_t>() + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st));
+        else B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
         B200_CHECK(cudaMemcpyAsync(d_rr.p, reg_read.data() + g0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
         B200_CHECK(cudaMemsetAsync(ctx->d_ctl.p, 0, CTL_SLOTS * 8, st));
         R2AParams P;
@@ -441,4 +448,12 @@ extern "C" int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, 
 {
     if (!out_sel || !regs) { b200_set_error("b200_reg2sam_se_batch: regs and out_sel are required"); return -1; }
     return reg2aln_impl(ctx, opt, n_reads, seqs, off, regs, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, regs, out_sel, n_processed);
+}
+
+extern "C" int64_t b200_batch_reg2sam_se(b200_ctx_t *ctx, const mem_opt_t *opt, int64_t n_processed, const int32_t *cnt,
+                                         mem_alnreg_t *regs_out, b200_sel_t *out_sel, b200_aln_t *out_aln, int64_t cap_cigar,
+                                         uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2])
+{
+    if (!out_sel || !cnt) { b200_set_error("b200_batch_reg2sam_se: cnt and out_sel are required"); return -1; }
+    return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, regs_out, out_sel, n_processed);
 }

@@ -24,7 +24,7 @@ _SYMBOLS = [
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
-    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_process_seqs_host_worker2",
+    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -54,6 +54,7 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_reg2aln_batch.restype = C.c_int64
     lib.b200_reg2sam_se_batch.restype = C.c_int64
     lib.b200_sam_se_format.restype = C.c_int64
+    lib.b200_batch_reg2sam_se.restype = C.c_int64
     lib.b200_hostidx_build.restype = C.c_void_p
     lib.b200_hostidx_build.argtypes = [C.c_void_p, C.c_int64]
     lib.b200_hostidx_free.argtypes = [C.c_void_p]
@@ -389,6 +390,26 @@ class Context:
                 cap_c, cap_m = int(tot[0]) + 64, int(tot[1]) + 64
                 continue
             self._chk(rc, "reg2sam_se")
+            return regs[:rc], sel[:rc], aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
+
+    def batch_reg2sam_se(self, opt: MemOpt, cnt, n_processed=0):
+        """b200_batch_reg2sam_se: worker2 on the batch this context has just aligned (nothing uploaded)."""
+        from .abi import SEL_DTYPE
+        cnt = np.ascontiguousarray(cnt, dtype=np.int32)
+        nr = int(cnt.astype(np.int64).sum())
+        regs = np.zeros(max(1, nr), dtype=ALNREG_DTYPE)
+        aln = np.zeros(max(1, nr), dtype=ALN_DTYPE); sel = np.zeros(max(1, nr), dtype=SEL_DTYPE)
+        tot = (C.c_int64 * 2)()
+        cap_c, cap_m = 8 * nr + 64, 24 * nr + 64
+        while True:
+            cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
+            rc = self.lib.b200_batch_reg2sam_se(self.h, C.byref(opt), C.c_int64(n_processed), _p(cnt, C.c_int32),
+                                                C.c_void_p(regs.ctypes.data), C.c_void_p(sel.ctypes.data), C.c_void_p(aln.ctypes.data),
+                                                C.c_int64(cap_c), _p(cig, C.c_uint32), C.c_int64(cap_m), C.c_void_p(md.ctypes.data), tot)
+            if rc == -2:
+                cap_c, cap_m = int(tot[0]) + 64, int(tot[1]) + 64
+                continue
+            self._chk(rc, "batch_reg2sam_se")
             return regs[:rc], sel[:rc], aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
 
     def sam_se(self, opt: MemOpt, ann_names, names, seqs, off, cnt, sel, aln, cig, md, quals=None, comments=None, rg_id=None,

@@ -214,6 +214,15 @@ int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads
                               b200_aln_t *out_aln, int64_t cap_cigar, uint32_t *out_cigar, int64_t cap_md, char *out_md,
                               int64_t totals[2]);
 
+/* The same on the batch the context has just aligned (b200_align_batch, or b200_batch_upload + b200_batch_run): reads
+ * and regions are taken where they lie in device memory -- nothing is uploaded, and the regions need not have been
+ * downloaded (b200_align_batch with cap 0 returns -(count) but still fills out_n).  cnt: the per-read region counts
+ * that call returned; regs_out (may be NULL): the regions as updated.  The resident regions themselves are left as
+ * worker1 produced them, so the call may be repeated (e.g. with larger pools after -2). */
+int64_t b200_batch_reg2sam_se(b200_ctx_t *ctx, const mem_opt_t *opt, int64_t n_processed, const int32_t *cnt,
+                              mem_alnreg_t *regs_out, b200_sel_t *out_sel, b200_aln_t *out_aln, int64_t cap_cigar,
+                              uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2]);
+
 /* SAM text of single-end reads from what b200_reg2sam_se_batch returned: mem_aln2sam (bwamem.c:832-956) with add_cigar
  * (:819-830; hard clips for supplementary records unless MEM_F_SOFTCLIP), the unmapped record of mem_reg2sam
  * (:1043-1047), SA and pa tags, the XA / XB strings of mem_gen_alt (bwamem_extra.c:143-161), RG (bwa_rg_id), the FASTQ

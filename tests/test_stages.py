@@ -537,6 +537,14 @@ def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0):
             assert x == y
         assert len(l0) == len(l1)
     assert soff[-1] == len(sam1) and sam1[soff[1]:].startswith(names[1].encode()) if len(names) > 1 else True
+    # the same on the batch the context has just aligned (b200_batch_reg2sam_se: nothing uploaded), twice: the resident
+    # regions are not modified by the call
+    regs_d, cnt_d = ctx.align(opt, seqs, off)
+    assert np.array_equal(cnt_d, cnt) and regs_d.tobytes() == regs.tobytes()
+    for _ in range(2):
+        r2, sel2, aln2, cig2, md2 = ctx.batch_reg2sam_se(opt, cnt_d, n_processed)
+        assert r2.tobytes() == r1.tobytes() and sel2.tobytes() == sel.tobytes() and aln2.tobytes() == aln.tobytes()
+        assert np.array_equal(cig2, cig) and md2.tobytes() == md.tobytes()
     return r1, sel, aln, sam1
 
 
