@@ -1,13 +1,17 @@
 // SAM text of single-end reads from the arrays b200_reg2sam_se_batch returns: mem_aln2sam (bwamem.c:832-956) with
 // add_cigar (:819-830), the unmapped record of mem_reg2sam (:1043-1047) and the XA strings of mem_gen_alt
 // (bwamem_extra.c:143-161).  Host code: this is string formatting, done by a pool of threads over blocks of reads;
-// every number in the text was computed on the device.
+// every number in the text was computed on the device.  Two passes over the same templated formatter: the first only
+// counts each read's bytes (no characters are produced), a prefix sum places the reads, the second writes every read
+// straight into its place in the caller's buffer -- no intermediate strings, no concatenation.
 #include <stdio.h>
 #include <string.h>
 #include <string>
 #include <thread>
 #include <vector>
 #include <algorithm>
+#include <functional>
+#include <stdint.h>
 #include "../../include/bwamem_b200.h"
 
 #define SF_SOFTCLIP 0x200      /* MEM_F_SOFTCLIP, bwa.h:80 */
@@ -16,7 +20,35 @@
 
 namespace {
 
-inline void put_int(std::string &s, long long v)        // kputw / kputl
+struct CountSink {                                       // pass 1: lengths only
+    size_t l = 0;
+    void push_back(char) { ++l; }
+    CountSink &operator+=(const char *z) { l += strlen(z); return *this; }
+    CountSink &operator+=(const std::string &z) { l += z.size(); return *this; }
+    void append(const char *, size_t n) { l += n; }
+    char *grow(size_t m) { l += m; return nullptr; }
+    size_t size() const { return l; }
+    void tabs_to_spaces(size_t) {}
+};
+struct WriteSink {                                       // pass 2: into the caller's buffer
+    char *p; size_t l = 0;
+    explicit WriteSink(char *q) : p(q) {}
+    void push_back(char c) { p[l++] = c; }
+    WriteSink &operator+=(const char *z) { const size_t n = strlen(z); memcpy(p + l, z, n); l += n; return *this; }
+    WriteSink &operator+=(const std::string &z) { memcpy(p + l, z.data(), z.size()); l += z.size(); return *this; }
+    void append(const char *z, size_t n) { memcpy(p + l, z, n); l += n; }
+    char *grow(size_t m) { char *d = p + l; l += m; return d; }
+    size_t size() const { return l; }
+    void tabs_to_spaces(size_t from) { for (size_t i = from; i < l; ++i) if (p[i] == '\t') p[i] = ' '; }
+};
+struct StrSink {                                         // XA strings
+    std::string s;
+    void push_back(char c) { s.push_back(c); }
+    StrSink &operator+=(const char *z) { s += z; return *this; }
+};
+
+template <class S>
+inline void put_int(S &s, long long v)                  // kputw / kputl
 {
     char buf[24]; int n = 0;
     unsigned long long x = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
@@ -34,7 +66,8 @@ inline int code_of(uint8_t c)                            // reads may be given a
 
 struct Rec { const b200_aln_t *a; const uint32_t *cig; const char *md; int mapq; };
 
-void put_cigar(std::string &s, const mem_opt_t *opt, const Rec &p, int which)        // add_cigar
+template <class S>
+void put_cigar(S &s, const mem_opt_t *opt, const Rec &p, int which)        // add_cigar
 {
     if (!p.a->n_cigar) { s.push_back('*'); return; }
     for (int i = 0; i < p.a->n_cigar; ++i) {
@@ -50,7 +83,8 @@ struct Job {
     const int64_t *roff; const b200_sel_t *sel; const b200_aln_t *aln; const uint32_t *cigar; const char *md; const char *rg;
 };
 
-void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &list, int which, const std::string *xa)
+template <class S>
+void one_record(S &s, const Job &J, int r, const std::vector<Rec> &list, int which, const std::string *xa)
 {
     const mem_opt_t *opt = J.opt;
     static const b200_aln_t unmapped = { -1, -1, 0x4, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 };
@@ -88,20 +122,19 @@ void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &lis
         }
         if (!a.is_rev) {
             const int m = std::max(0, qe - qb);
-            const size_t o = s.size();
-            s.resize(o + (size_t)m);
-            char *d = &s[o];
-            for (int i = 0; i < m; ++i) d[i] = "ACGTN"[code_of(seq[qb + i])];
+            char *d = s.grow((size_t)m);
+            if (d) for (int i = 0; i < m; ++i) d[i] = "ACGTN"[code_of(seq[qb + i])];
             s.push_back('\t');
-            if (qual) s.append((const char *)qual + qb, (size_t)std::max(0, qe - qb)); else s.push_back('*');
+            if (qual) s.append((const char *)qual + qb, (size_t)m); else s.push_back('*');
         } else {
             const int m = std::max(0, qe - qb);
-            const size_t o = s.size();
-            s.resize(o + (size_t)m);
-            char *d = &s[o];
-            for (int i = 0; i < m; ++i) d[i] = "TGCAN"[code_of(seq[qe - 1 - i])];
+            char *d = s.grow((size_t)m);
+            if (d) for (int i = 0; i < m; ++i) d[i] = "TGCAN"[code_of(seq[qe - 1 - i])];
             s.push_back('\t');
-            if (qual) for (int i = qe - 1; i >= qb; --i) s.push_back((char)qual[i]); else s.push_back('*');
+            if (qual) {
+                char *e = s.grow((size_t)m);
+                if (e) for (int i = 0; i < m; ++i) e[i] = (char)qual[qe - 1 - i];
+            } else s.push_back('*');
         }
     }
     if (a.n_cigar) {
@@ -137,14 +170,15 @@ void one_record(std::string &s, const Job &J, int r, const std::vector<Rec> &lis
         s += "\tXR:Z:";
         const size_t t = s.size();
         s += J.ann_annos[a.rid];
-        for (size_t i = t; i < s.size(); ++i) if (s[i] == '\t') s[i] = ' ';
+        s.tabs_to_spaces(t);
     }
     s.push_back('\n');
 }
 
-struct Scratch { std::vector<Rec> list; std::vector<int> reg_of; std::vector<std::string> xa; };      // reused over a thread's reads
+struct Scratch { std::vector<Rec> list; std::vector<int> reg_of; std::vector<StrSink> xa; };      // reused over a thread's reads
 
-void one_read(std::string &s, const Job &J, int r, Scratch &W)
+template <class S>
+void one_read(S &s, const Job &J, int r, Scratch &W)
 {
     const int64_t g0 = J.roff[r];
     const int n = (int)(J.roff[r + 1] - g0);
@@ -159,15 +193,15 @@ void one_read(std::string &s, const Job &J, int r, Scratch &W)
         }
     if (list.empty()) { one_record(s, J, r, list, 0, nullptr); return; }
     if (n == 1) { one_record(s, J, r, list, 0, nullptr); return; }      // one region, one record: no XA, no SA
-    std::vector<std::string> &xa = W.xa;
+    std::vector<StrSink> &xa = W.xa;
     if (xa.size() < list.size()) xa.resize(list.size());
-    for (size_t w = 0; w < list.size(); ++w) xa[w].clear();
+    for (size_t w = 0; w < list.size(); ++w) xa[w].s.clear();
     for (int i = 0; i < n; ++i) {                        // mem_gen_alt: entries appended in region order
         const b200_sel_t &e = J.sel[g0 + i];
         if (!(e.kind & 2)) continue;
         const auto it = std::find(reg_of.begin(), reg_of.end(), e.xa_of);
         if (it == reg_of.end()) continue;                // its record is not printed
-        std::string &x = xa[(size_t)(it - reg_of.begin())];
+        StrSink &x = xa[(size_t)(it - reg_of.begin())];
         const b200_aln_t &t = J.aln[g0 + i];
         const uint32_t *cg = J.cigar + t.cigar_off;
         x += J.ann_names[t.rid]; x.push_back(','); x.push_back("+-"[t.is_rev]); put_int(x, t.pos + 1); x.push_back(',');
@@ -176,7 +210,7 @@ void one_read(std::string &s, const Job &J, int r, Scratch &W)
         if (J.opt->flag & SF_XB) { x.push_back(','); put_int(x, t.score); }
         x.push_back(';');
     }
-    for (int w = 0; w < (int)list.size(); ++w) one_record(s, J, r, list, w, &xa[w]);
+    for (int w = 0; w < (int)list.size(); ++w) one_record(s, J, r, list, w, &xa[w].s);
 }
 
 }  // namespace
@@ -191,42 +225,33 @@ extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *a
     for (int r = 0; r < n_reads; ++r) roff[r + 1] = roff[r] + cnt[r];
     const Job J = { opt, ann_names, ann_annos, names, comments, seqs, quals, off, roff.data(), sel, aln, cigar, md, rg_id };
     const int nt = std::max(1, std::min(n_threads, std::max(1, n_reads / 256)));
-    std::vector<std::string> part((size_t)nt);
-    std::vector<std::vector<int64_t>> lens((size_t)nt);
-    auto work = [&](int t) {
-        const int lo = (int)((int64_t)n_reads * t / nt), hi = (int)((int64_t)n_reads * (t + 1) / nt);
-        std::string &s = part[t];
-        s.reserve((size_t)(hi - lo) * 400);
-        lens[t].reserve((size_t)(hi - lo));
+    std::vector<int64_t> own;
+    int64_t *pos = sam_off;                                // n_reads + 1 offsets of the reads' records
+    if (!pos) { own.resize((size_t)n_reads + 1); pos = own.data(); }
+    auto run = [&](const std::function<void(int, int, int)> &fn) {
+        if (nt == 1) { fn(0, 0, n_reads); return; }
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t)
+            th.emplace_back(fn, t, (int)((int64_t)n_reads * t / nt), (int)((int64_t)n_reads * (t + 1) / nt));
+        for (auto &x : th) x.join();
+    };
+    run([&](int, int lo, int hi) {                         // pass 1: pos[r + 1] = bytes of read r
+        Scratch W;
+        for (int r = lo; r < hi; ++r) { CountSink c; one_read(c, J, r, W); pos[r + 1] = (int64_t)c.l; }
+    });
+    pos[0] = 0;
+    for (int r = 0; r < n_reads; ++r) pos[r + 1] += pos[r];
+    const int64_t total = pos[n_reads];
+    if (total > cap) return -total;
+    std::vector<int> bad((size_t)nt, 0);
+    run([&](int t, int lo, int hi) {                       // pass 2: every read written in place
         Scratch W;
         for (int r = lo; r < hi; ++r) {
-            const size_t before = s.size();
-            one_read(s, J, r, W);
-            lens[t].push_back((int64_t)(s.size() - before));
+            WriteSink w(sam + pos[r]);
+            one_read(w, J, r, W);
+            if ((int64_t)w.l != pos[r + 1] - pos[r]) bad[t] = 1;
         }
-    };
-    if (nt == 1) work(0);
-    else {
-        std::vector<std::thread> th;
-        for (int t = 0; t < nt; ++t) th.emplace_back(work, t);
-        for (auto &x : th) x.join();
-    }
-    int64_t total = 0;
-    for (auto &s : part) total += (int64_t)s.size();
-    if (sam_off) {
-        int64_t o = 0; int r = 0;
-        for (int t = 0; t < nt; ++t) for (int64_t l : lens[t]) { sam_off[r++] = o; o += l; }
-        sam_off[n_reads] = o;
-    }
-    if (total > cap) return -total;
-    std::vector<int64_t> start((size_t)nt, 0);
-    for (int t = 1; t < nt; ++t) start[t] = start[t - 1] + (int64_t)part[t - 1].size();
-    auto copy = [&](int t) { memcpy(sam + start[t], part[t].data(), part[t].size()); };
-    if (nt == 1) copy(0);
-    else {
-        std::vector<std::thread> th;
-        for (int t = 0; t < nt; ++t) th.emplace_back(copy, t);
-        for (auto &x : th) x.join();
-    }
+    });
+    for (int b : bad) if (b) return INT64_MIN;             // the two passes disagree: a bug, never silent
     return total;
 }
