@@ -168,7 +168,7 @@ def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
     """SURVEY.md 8(d) "reads in memory -> SAM text": the first m reads of the step's batch through b200_align_batch (region
     counts only come back: cap 0), b200_batch_reg2sam_se (worker2 on the resident batch: primary marking, MAPQ, record
     selection, XA, CIGAR/NM/MD) and b200_sam_se_format (host threads); one timed region around the three C calls, pinned
-    host buffers for the reads, pageable numpy buffers for the results."""
+    host buffers for the reads and the records, a pageable buffer for the SAM text."""
     import ctypes as C
     from bwa_mem_gpu_b200 import abi
     m = min(a.reads, 2_000_000)
@@ -180,9 +180,13 @@ def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
     soff = np.zeros(m + 1, dtype=np.int64)
     sam = np.zeros((a.read_len + 120) * m + 4096, dtype=np.uint8)
     cap_r = int(m * 1.2) + 1024
-    sel = np.zeros(cap_r, dtype=abi.SEL_DTYPE); aln = np.zeros(cap_r, dtype=abi.ALN_DTYPE)
+    import torch
+
+    def pinned(n, dt):                                     # pinned host buffers, as a host program feeding a GPU would use
+        return torch.zeros(n * np.dtype(dt).itemsize, dtype=torch.uint8).pin_memory().numpy().view(dt)
+    sel = pinned(cap_r, abi.SEL_DTYPE); aln = pinned(cap_r, abi.ALN_DTYPE)
     regs2 = np.zeros(cap_r, dtype=abi.ALNREG_DTYPE)
-    cig = np.zeros(4 * cap_r + 64, dtype=np.uint32); md = np.zeros(16 * cap_r + 64, dtype=np.uint8)
+    cig = pinned(4 * cap_r + 64, np.uint32); md = pinned(16 * cap_r + 64, np.uint8)
     tot2 = (C.c_int64 * 2)()
     best = None
     for it in range(3):                                    # the first pass sizes the context's grow-only buffers

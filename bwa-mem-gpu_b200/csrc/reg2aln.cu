@@ -359,12 +359,18 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     i64 cig_total = 0, md_total = 0;
     bool fits = true;
     int r_lo = 0;
+    const bool timing = getenv("B200_R2A_TIMING") != nullptr;        // per-phase CUDA-event times on stderr (diagnostics)
+    cudaEvent_t tev[8];
+    float tacc[7] = {0, 0, 0, 0, 0, 0, 0};
+    if (timing) for (auto &e : tev) cudaEventCreate(&e);
+    auto tmark = [&](int k) { if (timing) cudaEventRecord(tev[k], st); };
     for (i64 g0 = 0; g0 < n_regs;) {
         int n = (int)std::min<i64>(chunk, n_regs - g0), r_hi = r_lo;
         if (finalize) {
             while (r_hi < n_reads && roff[r_hi + 1] - g0 <= chunk) ++r_hi;
             n = (int)(roff[r_hi] - g0);
         }
+        tmark(0);
         if (resident)      // a copy: marking is not idempotent (sub_n accumulates), the resident regions stay as worker1 left them
             B200_CHECK(cudaMemcpyAsync(d_regs.p, ctx->d_final.as<mem_alnreg_t>() + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st));
         else B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
@@ -378,6 +384,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
         P.dp_list = d_nc.as<i32>(); P.dp_n = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY); P.pass = 0;      // d_nc is free until the lengths kernel
+        tmark(1);
         if (finalize) {
             FinParams F;
             memset(&F, 0, sizeof(F));
@@ -395,9 +402,12 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
 #ifndef B200_EMU
         B200_CHECK(cudaFuncSetAttribute(reg2aln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
+        tmark(2);
         B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
+        tmark(3);
         P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);
         B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
+        tmark(4);
         B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
         B200_CHECK(cudaGetLastError());
         if (launch_exclusive_scan(d_nc.as<i32>(), d_co.as<i64>(), n, d_tmp.as<i64>(), st)) return -1;
@@ -406,6 +416,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
                     (const char *)d_md.p, md_stride, (const i64 *)d_co.p, (const i64 *)d_mo.p, d_pool_c.as<u32>(), d_pool_m.as<char>(),
                     cig_total, md_total);
         B200_CHECK(cudaGetLastError());
+        tmark(5);
         i64 nc = 0, nm = 0; u64 ovf = 0;
         B200_CHECK(cudaMemcpyAsync(&nc, d_co.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
         B200_CHECK(cudaMemcpyAsync(&nm, d_mo.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
@@ -425,9 +436,16 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             if (nc) B200_CHECK(cudaMemcpyAsync(out_cigar + cig_total, d_pool_c.p, (size_t)nc * 4, cudaMemcpyDeviceToHost, st));
             if (nm) B200_CHECK(cudaMemcpyAsync(out_md + md_total, d_pool_m.p, (size_t)nm, cudaMemcpyDeviceToHost, st));
         }
+        tmark(6);
         B200_CHECK(cudaStreamSynchronize(st));
+        if (timing) for (int k = 0; k < 6; ++k) { float ms = 0; cudaEventElapsedTime(&ms, tev[k], tev[k + 1]); tacc[k] += ms; }
         cig_total += nc; md_total += nm;
         g0 += n; r_lo = r_hi;
+    }
+    if (timing) {
+        fprintf(stderr, "[b200 reg2aln] %lld regions: regs in %.2f ms, finalize %.2f, pass0 %.2f, pass1 %.2f, compaction %.2f, out %.2f\n",
+                (long long)n_regs, tacc[0], tacc[1], tacc[2], tacc[3], tacc[4], tacc[5]);
+        for (auto &e : tev) cudaEventDestroy(e);
     }
     if (totals) { totals[0] = cig_total; totals[1] = md_total; }
     if (!fits) { b200_set_error("reg2aln: output pools too small (need %lld CIGAR words, %lld MD bytes)", (long long)cig_total, (long long)md_total); return -2; }
