@@ -70,11 +70,33 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     return 0;
 }
 
+// page-locked host memory for callers that want the copies of the batched calls to run at full speed and overlap
+extern "C" void *b200_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); b200_set_error("cudaHostAlloc(%zu) failed", bytes); return nullptr; }
+    return p;
+}
+extern "C" void b200_host_free(void *p) { if (p) cudaFreeHost(p); }
+// grow-only page-locked buffer owned by the context (released by b200_ctx_destroy); contents are not preserved on growth
+extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes)
+{
+    if (!ctx || slot < 0 || slot >= 12) { b200_set_error("b200_ctx_pinned: bad slot"); return nullptr; }
+    if (bytes <= ctx->pin_cap[slot] && ctx->pin_p[slot]) return ctx->pin_p[slot];
+    cudaSetDevice(ctx->device);
+    b200_host_free(ctx->pin_p[slot]);
+    ctx->pin_cap[slot] = bytes + bytes / 4 + 4096;
+    ctx->pin_p[slot] = b200_host_alloc(ctx->pin_cap[slot]);
+    if (!ctx->pin_p[slot]) ctx->pin_cap[slot] = 0;
+    return ctx->pin_p[slot];
+}
+
 extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->st);
+    for (void *&q : ctx->pin_p) { b200_host_free(q); q = nullptr; }
     DevBuf *bufs[] = { &ctx->d_occ32, &ctx->d_kmer, &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_jobs2, &ctx->d_jobs3, &ctx->d_jsort, &ctx->d_rstate, &ctx->d_njobs, &ctx->d_bwt, &ctx->d_sa, &ctx->d_sa_full, &ctx->d_pac, &ctx->d_ann_off, &ctx->d_ann_len, &ctx->d_ann_alt,
                        &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
                        &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,

@@ -69,6 +69,7 @@ struct b200_ctx {
     unsigned long long stats[CNT_N] = {0};
     DevBuf d_r2a[17];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
     int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
+    void *pin_p[12] = {}; size_t pin_cap[12] = {};   // page-locked host buffers of b200_align_sam_se_batch (b200_ctx_pinned)
     // scratch for the primitive batches
     DevBuf d_pa, d_pb, d_pc, d_pd, d_pe, d_pf, d_pg, d_ph;
 };

@@ -215,6 +215,9 @@ void one_read(S &s, const Job &J, int r, Scratch &W)
 
 }  // namespace
 
+extern "C" void *b200_host_alloc(size_t bytes);
+extern "C" void b200_host_free(void *p);
+
 extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos, int n_reads,
                                       const char *const *names, const char *const *comments, const uint8_t *seqs,
                                       const uint8_t *quals, const int64_t *off, const int32_t *cnt, const b200_sel_t *sel,
@@ -254,4 +257,63 @@ extern "C" int64_t b200_sam_se_format(const mem_opt_t *opt, const char *const *a
     });
     for (int b : bad) if (b) return INT64_MIN;             // the two passes disagree: a bug, never silent
     return total;
+}
+
+// ---- reads in host memory -> SAM text in host memory, single-end, as one call ------------------------------------
+// The batch is cut into sub-batches; for each: b200_align_batch (worker1; only region counts come back),
+// b200_batch_reg2sam_se (worker2 on the resident regions), then b200_sam_se_format on host threads -- which runs while
+// the device is already busy with the next sub-batch (two sets of page-locked record buffers).
+extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes);
+
+extern "C" int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos,
+                                           int n_reads, int64_t n_processed, const char *const *names, const char *const *comments,
+                                           const uint8_t *seqs, const uint8_t *quals, const int64_t *off, const char *rg_id, int n_threads,
+                                           int sub_reads, int64_t cap, char *sam, int64_t *sam_off)
+{
+    const int sub = sub_reads > 0 ? sub_reads : (1 << 19);
+    std::thread fmt;
+    int64_t written = 0, need = 0;                         // bytes placed so far / bytes the whole text needs
+    bool fmt_failed = false;
+    auto join = [&]() { if (fmt.joinable()) fmt.join(); };
+    if (sam_off) sam_off[0] = 0;
+    for (int r0 = 0, k = 0; r0 < n_reads; r0 += sub, ++k) {
+        const int n = std::min(sub, n_reads - r0);
+        const int s0 = (k & 1) * 5;                        // buffer set; the formatter of sub-batch k-2 was joined before k-1's started
+        int32_t *cnt = (int32_t *)b200_ctx_pinned(ctx, s0, (size_t)n * 4);
+        if (!cnt) { join(); return -1; }
+        int64_t nr = b200_align_batch(ctx, opt, n, seqs, off + r0, 0, nullptr, cnt);
+        if (nr > 0) { join(); return -1; }                 // cannot happen with cap 0
+        nr = -nr;
+        if (nr >= 0x7fffffff) { join(); return -1; }
+        b200_sel_t *sel = (b200_sel_t *)b200_ctx_pinned(ctx, s0 + 1, (size_t)(nr + 1) * sizeof(b200_sel_t));
+        b200_aln_t *aln = (b200_aln_t *)b200_ctx_pinned(ctx, s0 + 2, (size_t)(nr + 1) * sizeof(b200_aln_t));
+        int64_t cap_c = 4 * nr + 64, cap_m = 16 * nr + 64, totals[2];
+        uint32_t *cig = nullptr; char *md = nullptr;
+        if (!sel || !aln) { join(); return -1; }
+        for (;;) {
+            cig = (uint32_t *)b200_ctx_pinned(ctx, s0 + 3, (size_t)cap_c * 4);
+            md = (char *)b200_ctx_pinned(ctx, s0 + 4, (size_t)cap_m);
+            if (!cig || !md) { join(); return -1; }
+            const int64_t rc = nr ? b200_batch_reg2sam_se(ctx, opt, n_processed + r0, cnt, nullptr, sel, aln, cap_c, cig, cap_m, md, totals) : 0;
+            if (rc == -2) { cap_c = totals[0] + 64; cap_m = totals[1] + 64; continue; }
+            if (rc < 0) { join(); return -1; }
+            break;
+        }
+        join();                                            // the previous sub-batch's text is in place: `written` is final
+        if (fmt_failed) return -1;
+        fmt = std::thread([&, r0, n, cnt, sel, aln, cig, md]() {
+            int64_t *so = sam_off ? sam_off + r0 : nullptr;
+            const int64_t room = need > cap ? 0 : cap - written;
+            const int64_t rc = b200_sam_se_format(opt, ann_names, ann_annos, n, names + r0, comments ? comments + r0 : nullptr, seqs, quals,
+                                                  off + r0, cnt, sel, aln, cig, md, rg_id, n_threads, room, sam + written, so);
+            if (rc == INT64_MIN) { fmt_failed = true; return; }
+            const int64_t bytes = rc < 0 ? -rc : rc;
+            if (so) for (int i = 0; i <= n; ++i) so[i] += need;      // offsets of the whole text (so[n] is the next sub-batch's so[0])
+            need += bytes;
+            if (rc >= 0 && need <= cap) written += bytes;
+        });
+    }
+    join();
+    if (fmt_failed) { return -1; }
+    return need > cap ? -need : need;
 }

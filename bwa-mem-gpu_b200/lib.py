@@ -24,7 +24,7 @@ _SYMBOLS = [
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
-    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2",
+    "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_align_sam_se_batch", "b200_host_alloc", "b200_host_free", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -54,6 +54,10 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_reg2aln_batch.restype = C.c_int64
     lib.b200_reg2sam_se_batch.restype = C.c_int64
     lib.b200_sam_se_format.restype = C.c_int64
+    lib.b200_align_sam_se_batch.restype = C.c_int64
+    lib.b200_host_alloc.restype = C.c_void_p
+    lib.b200_host_alloc.argtypes = [C.c_size_t]
+    lib.b200_host_free.argtypes = [C.c_void_p]
     lib.b200_batch_reg2sam_se.restype = C.c_int64
     lib.b200_hostidx_build.restype = C.c_void_p
     lib.b200_hostidx_build.argtypes = [C.c_void_p, C.c_int64]
@@ -391,6 +395,25 @@ class Context:
                 continue
             self._chk(rc, "reg2sam_se")
             return regs[:rc], sel[:rc], aln[:rc], cig[: int(tot[0])], md[: int(tot[1])]
+
+    def align_sam_se(self, opt: MemOpt, ann_names, names, seqs, off, n_processed=0, quals=None, n_threads=8, sub_reads=0):
+        """b200_align_sam_se_batch: reads -> SAM text (bytes) and the n + 1 offsets of the reads' records, pipelined."""
+        n = len(off) - 1
+        a_names = (C.c_char_p * max(1, len(ann_names)))(*[s.encode() for s in ann_names])
+        r_names = (C.c_char_p * max(1, n))(*[s.encode() for s in names])
+        soff = np.zeros(n + 1, dtype=np.int64)
+        cap = 1 << 16
+        while True:
+            sam = np.zeros(cap, dtype=np.uint8)
+            rc = self.lib.b200_align_sam_se_batch(self.h, C.byref(opt), a_names, None, C.c_int(n), C.c_int64(n_processed), r_names, None,
+                                                  _p(seqs, C.c_uint8), None if quals is None else _p(quals, C.c_uint8), _p(off, C.c_int64),
+                                                  None, C.c_int(n_threads), C.c_int(sub_reads), C.c_int64(cap), C.c_void_p(sam.ctypes.data),
+                                                  _p(soff, C.c_int64))
+            if rc < -1:
+                cap = int(-rc) + 64
+                continue
+            self._chk(rc, "align_sam_se")
+            return sam[:rc].tobytes(), soff
 
     def batch_reg2sam_se(self, opt: MemOpt, cnt, n_processed=0):
         """b200_batch_reg2sam_se: worker2 on the batch this context has just aligned (nothing uploaded)."""

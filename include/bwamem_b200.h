@@ -214,6 +214,20 @@ int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads
                               b200_aln_t *out_aln, int64_t cap_cigar, uint32_t *out_cigar, int64_t cap_md, char *out_md,
                               int64_t totals[2]);
 
+/* Reads in host memory -> SAM text in host memory for single-end reads, as ONE call: the batch is cut into sub-batches
+ * of sub_reads reads (0 = 2^19); each goes through b200_align_batch (worker1; only region counts come back),
+ * b200_batch_reg2sam_se (worker2 on the resident regions) and b200_sam_se_format (n_threads host threads), and the text of
+ * sub-batch k is written while the device works on sub-batch k+1 (two sets of page-locked record buffers owned by the
+ * context).  Arguments as in the three calls; names / comments / sam_off are indexed by read.  Returns the number of
+ * bytes written, -(needed) when cap is too small (nothing useful in sam), -1 on error. */
+int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos,
+                                int n_reads, int64_t n_processed, const char *const *names, const char *const *comments,
+                                const uint8_t *seqs, const uint8_t *quals, const int64_t *off, const char *rg_id, int n_threads,
+                                int sub_reads, int64_t cap, char *sam, int64_t *sam_off);
+/* Page-locked host memory (cudaHostAlloc) for callers that want the copies of the batched calls at full speed. */
+void *b200_host_alloc(size_t bytes);
+void b200_host_free(void *p);
+
 /* The same on the batch the context has just aligned (b200_align_batch, or b200_batch_upload + b200_batch_run): reads
  * and regions are taken where they lie in device memory -- nothing is uploaded, and the regions need not have been
  * downloaded (b200_align_batch with cap 0 returns -(count) but still fills out_n).  cnt: the per-read region counts

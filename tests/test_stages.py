@@ -513,7 +513,7 @@ def _nt4(seqs):
     return lut[np.asarray(seqs, dtype=np.uint8)]
 
 
-def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0):
+def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0, resident=True):
     """b200_reg2sam_se_batch + b200_sam_se_format against the reference's worker2 (mem_mark_primary_se,
     mem_approx_mapq_se, mem_reg2sam): region arrays byte for byte, MAPQ, and the SAM text byte for byte."""
     regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
@@ -537,6 +537,8 @@ def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0):
             assert x == y
         assert len(l0) == len(l1)
     assert soff[-1] == len(sam1) and sam1[soff[1]:].startswith(names[1].encode()) if len(names) > 1 else True
+    if not resident:
+        return r1, sel, aln, sam1
     # the same on the batch the context has just aligned (b200_batch_reg2sam_se: nothing uploaded), twice: the resident
     # regions are not modified by the call
     regs_d, cnt_d = ctx.align(opt, seqs, off)
@@ -545,6 +547,10 @@ def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0):
         r2, sel2, aln2, cig2, md2 = ctx.batch_reg2sam_se(opt, cnt_d, n_processed)
         assert r2.tobytes() == r1.tobytes() and sel2.tobytes() == sel.tobytes() and aln2.tobytes() == aln.tobytes()
         assert np.array_equal(cig2, cig) and md2.tobytes() == md.tobytes()
+    # and as one pipelined call, cut into sub-batches (text of one written while the next is aligned)
+    for sub in (0, max(1, (len(off) - 1) // 3)):
+        sam2, soff2 = ctx.align_sam_se(opt, idx.anns()[3], names, seqs, off, n_processed, sub_reads=sub)
+        assert sam2 == sam1 and np.array_equal(soff2, soff)
     return r1, sel, aln, sam1
 
 
@@ -570,10 +576,10 @@ def test_reg2sam_se(backend, gname):
     for flag in (0x8, 0x200, 0x800, 0x10, 0x8 | 0x2000 | 0x1000):      # MEM_F_ALL, SOFTCLIP, PRIMARY5, NO_MULTI, ALL|XB|KEEP_SUPP_MAPQ
         o = abi.default_opt()
         o.flag |= flag
-        _check_reg2sam_se(idx, ctx, o, seqs, off, n_processed=7)
+        _check_reg2sam_se(idx, ctx, o, seqs, off, n_processed=7, resident=False)
     o = abi.default_opt()
     o.mapQ_coef_len = 0                                    # the other MAPQ formula (log(seedcov))
-    _check_reg2sam_se(idx, ctx, o, seqs, off)
+    _check_reg2sam_se(idx, ctx, o, seqs, off, resident=False)
 
 
 @needs_ref
@@ -581,4 +587,4 @@ def test_reg2sam_se(backend, gname):
 def test_reg2sam_se_long_reads(backend):
     idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
     seqs, off = _long_reads("small", _sizes(backend, 6, 200), seed=19)
-    _check_reg2sam_se(idx, ctx, abi.default_opt(), seqs, off, n_processed=3)
+    _check_reg2sam_se(idx, ctx, abi.default_opt(), seqs, off, n_processed=3, resident=backend != "emu")   # emulated long-read aligns are slow
