@@ -72,9 +72,7 @@ struct Shard {
     b200_ctx_t *ctx; int r0, n;
     std::vector<mem_alnreg_t> regs; std::vector<int32_t> cnt;
     std::string err;
-    std::vector<b200_sel_t> sel; std::vector<b200_aln_t> aln; std::vector<uint32_t> cig; std::vector<char> md, sam;
-    std::vector<int64_t> sam_off;
-    int64_t n_regs = 0;
+    std::vector<char> sam; std::vector<int64_t> sam_off;
 };
 
 static void shard_download(Shard &sh)
@@ -135,19 +133,7 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         if (pe) { lo &= ~1; hi = d == G - 1 ? n : hi & ~1; }          // mates stay together
         shards[d].ctx = g_ps_ctxs[d]; shards[d].r0 = lo; shards[d].n = hi - lo;
     }
-    run_shards(shards, [&](Shard &sh) {
-        sh.cnt.assign((size_t)sh.n + 1, 0);
-        sh.regs.resize((size_t)(2 * (int64_t)sh.n + 64));
-        if (b200_batch_upload(sh.ctx, sh.n, flat.data(), off.data() + sh.r0) || b200_batch_run(sh.ctx, opt, nullptr)) { sh.err = b200_last_error(); return; }
-        if (dev_worker2) {                                            // the regions stay on the device: only their counts come back
-            const int64_t got = b200_batch_download(sh.ctx, 0, nullptr, sh.cnt.data());
-            if (got > 0 || (got < 0 && -got >= 0x7fffffff)) { sh.err = "region download"; return; }
-            sh.n_regs = -got;
-            return;
-        }
-        shard_download(sh);
-    });
-    if (dev_worker2) {                                                // bwamem.c:1202-1207 for every read, on the device
+    if (dev_worker2) {                                                // worker1 + worker2 (bwamem.c:1183-1207) for every read, on the device
         int n_qual = 0;
         for (int i = 0; i < n; ++i) n_qual += seqs[i].qual != nullptr;
         if (n_qual && n_qual != n) { fprintf(stderr, "[b200::mem_process_seqs] reads with and without qualities in one batch\n"); exit(1); }
@@ -160,29 +146,16 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         for (int i = 0; i < bns->n_seqs; ++i) { ann_names[i] = bns->anns[i].name; ann_annos[i] = bns->anns[i].anno; }
         const char *rg = (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
         const int fmt_threads = std::max(1, (opt->n_threads > 0 ? opt->n_threads : 1) / G);
-        run_shards(shards, [&](Shard &sh) {
-            const size_t nr = (size_t)sh.n_regs;
-            sh.sel.resize(nr + 1); sh.aln.resize(nr + 1);
-            sh.cig.resize(4 * nr + 64); sh.md.resize(16 * nr + 64);
-            int64_t totals[2];
-            for (;;) {                                                 // on the resident batch: nothing is uploaded
-                const int64_t rc = b200_batch_reg2sam_se(sh.ctx, opt, n_processed + sh.r0, sh.cnt.data(), nullptr, sh.sel.data(), sh.aln.data(),
-                                                         (int64_t)sh.cig.size(), sh.cig.data(), (int64_t)sh.md.size(), sh.md.data(), totals);
-                if (rc == -2) {
-                    sh.cig.resize((size_t)totals[0] + 64); sh.md.resize((size_t)totals[1] + 64);
-                    continue;
-                }
-                if (rc < 0) { sh.err = b200_last_error(); return; }
-                break;
-            }
+        run_shards(shards, [&](Shard &sh) {                            // per device: align, finish and format, sub-batch by sub-batch
             sh.sam_off.assign((size_t)sh.n + 1, 0);
-            sh.sam.resize((size_t)sh.n * 420 + 4096);
+            sh.sam.resize((size_t)(tot / (n > 0 ? n : 1) + 160) * (size_t)sh.n + 4096);
             for (;;) {
-                const int64_t rc = b200_sam_se_format(opt, ann_names.data(), ann_annos.data(), sh.n, names.data() + sh.r0,
-                                                      comments.data() + sh.r0, flat.data(), n_qual ? qflat.data() : nullptr,
-                                                      off.data() + sh.r0, sh.cnt.data(), sh.sel.data(), sh.aln.data(), sh.cig.data(),
-                                                      sh.md.data(), rg, fmt_threads, (int64_t)sh.sam.size(), sh.sam.data(), sh.sam_off.data());
-                if (rc < 0) { sh.sam.resize((size_t)-rc + 64); continue; }
+                const int64_t rc = b200_align_sam_se_batch(sh.ctx, opt, ann_names.data(), ann_annos.data(), sh.n, n_processed + sh.r0,
+                                                           names.data() + sh.r0, comments.data() + sh.r0, flat.data(),
+                                                           n_qual ? qflat.data() : nullptr, off.data() + sh.r0, rg, fmt_threads, 0,
+                                                           (int64_t)sh.sam.size(), sh.sam.data(), sh.sam_off.data());
+                if (rc < -1) { sh.sam.resize((size_t)-rc + 64); continue; }
+                if (rc < 0) { sh.err = b200_last_error(); return; }
                 break;
             }
             for (int i = 0; i < sh.n; ++i) {                           // seqs[i].sam: heap memory owned by the caller (bwamem.c:1054)
@@ -196,6 +169,12 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
             for (int j = 0; j < seqs[i].l_seq; ++j) seqs[i].seq[j] = (char)nt4_of((uint8_t)seqs[i].seq[j]);   // bwamem.c:1067-1068
         return;
     }
+    run_shards(shards, [&](Shard &sh) {
+        sh.cnt.assign((size_t)sh.n + 1, 0);
+        sh.regs.resize((size_t)(2 * (int64_t)sh.n + 64));
+        if (b200_batch_upload(sh.ctx, sh.n, flat.data(), off.data() + sh.r0) || b200_batch_run(sh.ctx, opt, nullptr)) { sh.err = b200_last_error(); return; }
+        shard_download(sh);
+    });
     mem_alnreg_v *rv = (mem_alnreg_v *)malloc((size_t)(n > 0 ? n : 1) * sizeof(mem_alnreg_v));
     auto fill_rv = [&](bool first) {
         for (auto &sh : shards)
