@@ -63,6 +63,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "ext_sort")) ctx->ext_sort = (int)value;
     else if (!strcmp(key, "ext_phased")) ctx->ext_phased = (int)value;
     else if (!strcmp(key, "ssw_path")) ctx->ssw_path = (int)value;
+    else if (!strcmp(key, "r2a_small")) ctx->r2a_small = (int)value;
     else if (!strcmp(key, "l2_persist")) ctx->l2_persist = (int)value;
     else if (!strcmp(key, "idx_group_cap")) ctx->idx_group_cap = value > ((i64)1 << 30) ? ((i64)1 << 30) : value;   // before b200_index_build_device
     else if (!strcmp(key, "idx_tie_cap")) ctx->idx_tie_cap = value;

@@ -25,6 +25,9 @@ struct R2AParams {
     // two passes: pass 0 finishes the regions that need no DP (equal lengths, inferred band 0) and lists the others;
     // pass 1 runs the listed regions, so that the lanes of a warp are all inside ksw_global2 together
     i32 *dp_list; unsigned *dp_n; int pass;
+    // pass 1 runs with a small H / E row per lane (he_cap entries, rings of 2w + 2); regions whose band does not fit are
+    // listed again and run in pass 2 with a full row
+    i32 *dp_list2; unsigned *dp_n2;
     int he_smem;                         // H / E rows in shared memory (2 * he_cap * 64 ints per block)
     const b200_sel_t *sel;               // b200_reg2sam_se_batch: which regions reach the SAM (null: all)
 };
@@ -65,10 +68,14 @@ __device__ __forceinline__ void r2a_push(u32 *cigar, int &n_cigar, int cap, int 
 // H / E: entry j at H[j * hs] (hs = 1: lane-private global scratch; hs = block size: interleaved shared memory).
 // The traceback matrix keeps the reference's three direction fields as 4 bits per cell (h: 2 bits, "E continues", "F
 // continues"), eight cells per 32-bit word, rows padded to whole words: one store per eight cells instead of one per cell.
+// Row i reads columns [i - w, i + w] and writes [i - w, i + w + 1], all of which row i - 1 wrote, so the H / E row is kept
+// as a ring of M = 2w + 2 entries when that is less than qlen + 1 (M >= qlen + 1: no wrap-around): a lane needs
+// 16 (w + 1) bytes instead of 8 (qlen + 1), which is what lets many more warps share an SM's shared memory.
 template <class QF, class TF>
 __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins,
-                                  int w, i32 *H, i32 *E, int hs, u8 *z, i64 z_cap, u32 *cigar, int cig_cap, int &n_cigar, int *ovf)
+                                  int w, int M, i32 *H, i32 *E, int hs, u8 *z, i64 z_cap, u32 *cigar, int cig_cap, int &n_cigar, int *ovf)
 {
+    const bool ring = M < qlen + 1;
     const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins;
     const int n_col = qlen < 2 * w + 1 ? qlen : 2 * w + 1;
     const int row_words = (n_col + 7) >> 3;
@@ -78,7 +85,7 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
     int j;
     H[0] = 0; E[0] = R2A_MINUS_INF;
     for (j = 1; j <= qlen && j <= w; ++j) { H[j * hs] = -(o_ins + e_ins * j); E[j * hs] = R2A_MINUS_INF; }
-    for (; j <= qlen; ++j) H[j * hs] = E[j * hs] = R2A_MINUS_INF;
+    if (!ring) for (; j <= qlen; ++j) H[j * hs] = E[j * hs] = R2A_MINUS_INF;      // ring: columns > w are written before they are read
     for (int i = 0; i < tlen; ++i) {
         int f = R2A_MINUS_INF, t;
         const int8_t *mrow = mat + tf(i) * 5;
@@ -87,10 +94,13 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
         int h1 = beg == 0 ? -(o_del + e_del * (i + 1)) : R2A_MINUS_INF;
         u32 *zi = zw + (i64)i * row_words;
         u32 acc = 0;
+        int jm = ring ? beg % M : beg;                     // ring slot of column j
         for (j = beg; j < end; ++j) {
-            int m = H[j * hs], e = E[j * hs], h;
+            const int js = jm * hs;
+            if (++jm == M) jm = 0;                         // M > qlen when there is no ring: never taken
+            int m = H[js], e = E[js], h;
             u32 d;
-            H[j * hs] = h1;
+            H[js] = h1;
             m += mrow[qf(j)];
             d = m >= e ? 0u : 1u;
             h = m >= e ? m : e;
@@ -101,7 +111,7 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
             e -= e_del;
             d |= e > t ? 4u : 0u;
             e = e > t ? e : t;
-            E[j * hs] = e;
+            E[js] = e;
             t = m - oe_ins;
             f -= e_ins;
             d |= f > t ? 8u : 0u;
@@ -111,9 +121,10 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
             if ((c & 7) == 7) { zi[c >> 3] = acc; acc = 0; }
         }
         if ((end - beg) & 7) zi[(end - beg) >> 3] = acc;
-        H[end * hs] = h1; E[end * hs] = R2A_MINUS_INF;
+        H[jm * hs] = h1; E[jm * hs] = R2A_MINUS_INF;       // column `end`
     }
-    const int score = H[qlen * hs];
+    const int last_end = tlen + w < qlen ? tlen + w : qlen;
+    const int score = !ring ? H[qlen * hs] : (last_end == qlen ? H[(qlen % M) * hs] : R2A_MINUS_INF);
     {   // backtrack (ksw.c:587-602)
         int which = 0;
         int i = tlen - 1, k = (i + w + 1 < qlen ? i + w + 1 : qlen) - 1;
@@ -136,7 +147,8 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
 // bwa_gen_cigar2 (bwa.c:261-347): CIGAR + score + NM + MD of query[0, l_query) against text [rb, re)
 template <class QF, class TF>
 __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int w_, int l_query, QF qf, i64 rb, i64 rlen, TF tf, bool rev,
-                                      i32 *H, i32 *E, int hs, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf)
+                                      i32 *H, i32 *E, int hs, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf,
+                                      int he_avail, int *need_big)
 {
     const mem_opt_t &opt = P.opt;
     if (l_query == rlen && w_ == 0) {                                          // no gap; no need to do DP
@@ -154,7 +166,10 @@ __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int
         w = w < w_ ? w : w_;
         const int min_w = dl + 3;
         w = w > min_w ? w : min_w;
-        score = r2a_global2(l_query, qf, (int)rlen, tf, mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins, w, H, E, hs, z, P.z_cap,
+        int M = 2 * w + 2;
+        if (M >= l_query + 1) M = l_query + 2;             // the whole row: no ring
+        if ((M < l_query + 1 ? M : l_query + 1) > he_avail) { *need_big = 1; n_cigar = 0; score = 0; return; }     // H / E of this pass too small
+        score = r2a_global2(l_query, qf, (int)rlen, tf, mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins, w, M, H, E, hs, z, P.z_cap,
                             cigar, P.cig_stride, n_cigar, ovf);
     }
     {   // NM and MD (bwa.c:311-338)
@@ -202,6 +217,7 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
     for (;;) {
         unsigned g = atomicAdd(P.work_counter, 1u);
         if (P.pass == 1) { if (g >= *P.dp_n) break; g = (unsigned)P.dp_list[g]; }
+        else if (P.pass == 2) { if (g >= *P.dp_n2) break; g = (unsigned)P.dp_list2[g]; }
         else if (g >= (unsigned)P.n_regs) break;
         const mem_alnreg_t ar = P.regs[g];
         const int r = P.reg_read[g];
@@ -229,17 +245,24 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
             P.dp_list[atomicAdd(P.dp_n, 1u)] = (i32)g;
             continue;
         }
+        int need_big = 0;
         do {
             w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
             n_cigar = 0; NM = -1;
             if (ok) {
-                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf);
-                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf);
+                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
+                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
             }
+            if (need_big) break;
             if (score == last_sc || w2 == opt.w << 2) break;
             last_sc = score;
             w2 <<= 1;
         } while (++it < 3 && score < ar.truesc - opt.a);
+        if (need_big) {
+            if (P.pass == 1) P.dp_list2[atomicAdd(P.dp_n2, 1u)] = (i32)g;      // again in pass 2, with a full row
+            else ovf = 2;                                                       // cannot happen: pass 0 has no DP, pass 2 has the full row
+            continue;
+        }
         a.NM = NM;
         int is_rev;
         i64 pos = dev_depos(ix, rb < l_pac ? rb : re - 1, &is_rev);
@@ -406,7 +429,18 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
         tmark(3);
         P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);
-        B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
+        {   // pass 1 with a small row per lane: rings of up to HE_SMALL entries (w <= 23): 25 KB of shared memory per block instead of 78 KB at 150 bp
+            const int HE_SMALL = 48;
+            R2AParams Q = P;
+            Q.dp_list2 = d_lm.as<i32>(); Q.dp_n2 = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_TOTAL);      // d_lm is free until the lengths kernel
+            if (he_cap > HE_SMALL && ctx->r2a_small) {
+                Q.he_cap = HE_SMALL; Q.he_smem = 1;
+                B200_LAUNCH(reg2aln_kernel, grid, 64, (size_t)2 * HE_SMALL * 64 * 4, st, Q);
+                Q.pass = 2; Q.he_cap = he_cap; Q.he_smem = P.he_smem;
+                Q.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_ARENA_USED);
+                B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, Q);
+            } else B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, Q);
+        }
         tmark(4);
         B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
         B200_CHECK(cudaGetLastError());

@@ -459,6 +459,11 @@ def test_reg2aln(backend, gname):
     ops = c & 0xf
     assert (ops == 1).any() and (ops == 2).any() and (ops == 3).any()      # insertions, deletions and clips occurred
     assert a["is_rev"].any() and not a["is_rev"].all()
+    ctx.tune("r2a_small", 0)                               # full H / E row for every DP region (no ring pass)
+    try:
+        _check_reg2aln(idx, ctx, opt, seqs, off)
+    finally:
+        ctx.tune("r2a_small", 1)
     seqs, off = cm.ragged_reads(gname)
     _check_reg2aln(idx, ctx, opt, seqs, off)
     opt2 = abi.default_opt()
