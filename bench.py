@@ -171,7 +171,7 @@ def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
     host buffers for the reads and the records, a pageable buffer for the SAM text."""
     import ctypes as C
     from bwa_mem_gpu_b200 import abi
-    m = min(a.reads, 2_000_000)
+    m = min(a.reads, 4_000_000)
     P = lambda x, ty: x.ctypes.data_as(C.POINTER(ty))
     seqs = pin_seq.numpy(); off = pin_off.numpy()[: m + 1]
     cnt = np.zeros(m, dtype=np.int32)
@@ -230,7 +230,7 @@ def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
     same = bool(nb2 == nb and np.array_equal(sam[:nb2], sam1[:nb]) and np.array_equal(soff, soff1))
     out = {"value": m / t_pipe, "unit": UNIT, "reads": m, "regions": int(nr), "sam_bytes": int(nb2), "seconds": t_pipe,
            "format_threads": threads, "pipelined_equals_staged": same,
-           "path": "b200_align_sam_se_batch (reads in pinned host memory -> SAM text in host memory, sub-batches of 2^19 reads, "
+           "path": "b200_align_sam_se_batch (reads in pinned host memory -> SAM text in host memory, sub-batches of 2^20 reads, "
                    "host formatting overlapped with the device); best of 2 timed passes",
            "staged": staged}
     return out, (cnt, regs2, sam, soff)

@@ -270,7 +270,7 @@ extern "C" int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt
                                            const uint8_t *seqs, const uint8_t *quals, const int64_t *off, const char *rg_id, int n_threads,
                                            int sub_reads, int64_t cap, char *sam, int64_t *sam_off)
 {
-    const int sub = sub_reads > 0 ? sub_reads : (1 << 19);
+    const int sub = sub_reads > 0 ? sub_reads : (1 << 20);
     std::thread fmt;
     int64_t written = 0, need = 0;                         // bytes placed so far / bytes the whole text needs
     bool fmt_failed = false;

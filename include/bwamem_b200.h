@@ -215,7 +215,7 @@ int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads
                               int64_t totals[2]);
 
 /* Reads in host memory -> SAM text in host memory for single-end reads, as ONE call: the batch is cut into sub-batches
- * of sub_reads reads (0 = 2^19); each goes through b200_align_batch (worker1; only region counts come back),
+ * of sub_reads reads (0 = 2^20); each goes through b200_align_batch (worker1; only region counts come back),
  * b200_batch_reg2sam_se (worker2 on the resident regions) and b200_sam_se_format (n_threads host threads), and the text of
  * sub-batch k is written while the device works on sub-batch k+1 (two sets of page-locked record buffers owned by the
  * context).  Arguments as in the three calls; names / comments / sam_off are indexed by read.  Returns the number of
