@@ -28,11 +28,20 @@ struct R2AParams {
     // pass 1 runs with a small H / E row per lane (he_cap entries, rings of 2w + 2); regions whose band does not fit are
     // listed again and run in pass 2 with a full row
     i32 *dp_list2; unsigned *dp_n2;
+    // DP passes: the region's query codes staged in shared memory, 8 per word, [word][lane] (0 = read them from global
+    // memory): with the H / E rows taking most of the SM's shared memory little L1 is left, and the DP reads one query
+    // code per cell
+    int q_words;
     int he_smem;                         // H / E rows in shared memory (2 * he_cap * 64 ints per block)
     const b200_sel_t *sel;               // b200_reg2sam_se_batch: which regions reach the SAM (null: all)
 };
 
 #define R2A_MINUS_INF (-0x40000000)
+
+struct SeqSmem {                         // query codes in DP order, 4 bits each, word k of a lane at Q[k * 64]
+    const u32 *Q;
+    __device__ __forceinline__ int operator()(int j) const { return (int)(Q[(j >> 3) * 64] >> ((j & 7) << 2) & 0xfu); }
+};
 
 __device__ __forceinline__ int r2a_infer_bw(int l1, int l2, int score, int a, int q, int r)       // bwamem.c:799-806
 {
@@ -145,7 +154,7 @@ __device__ inline int r2a_global2(int qlen, QF qf, int tlen, TF tf, const int8_t
 }
 
 // bwa_gen_cigar2 (bwa.c:261-347): CIGAR + score + NM + MD of query[0, l_query) against text [rb, re)
-template <class QF, class TF>
+template <bool DP, class QF, class TF>
 __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int w_, int l_query, QF qf, i64 rb, i64 rlen, TF tf, bool rev,
                                       i32 *H, i32 *E, int hs, u8 *z, u32 *cigar, int &n_cigar, int &score, int &NM, R2AMd &md, int *ovf,
                                       int he_avail, int *need_big)
@@ -156,7 +165,7 @@ __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int
         n_cigar = 1;
         score = 0;
         for (int i = 0; i < l_query; ++i) score += mat[tf(i) * 5 + qf(i)];
-    } else {
+    } else if (DP) {
         int max_ins = (int)((double)(((l_query + 1) >> 1) * mat[0] - opt.o_ins) / opt.e_ins + 1.);
         int max_del = (int)((double)(((l_query + 1) >> 1) * mat[0] - opt.o_del) / opt.e_del + 1.);
         int max_gap = max_ins > max_del ? max_ins : max_del;
@@ -199,6 +208,9 @@ __device__ inline void r2a_gen_cigar2(const R2AParams &P, const int8_t *mat, int
     }
 }
 
+// MODE 0: pass 0 (no DP code in the kernel: few registers, no shared-memory rows); MODE 1: DP passes with the query codes
+// staged in shared memory (every read of the batch fits q_words); MODE 2: DP passes reading the query from global memory
+template <int MODE>
 __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
 {
     __shared__ int8_t s_mat[25];
@@ -209,6 +221,7 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
     i32 *H = P.he + lane_id * 2 * (size_t)P.he_cap, *E = H + P.he_cap;
     int hs = 1;
     if (P.he_smem) { H = (i32 *)r2a_raw + threadIdx.x; E = H + (size_t)P.he_cap * 64; hs = 64; }    // [column][lane], conflict-free
+    u32 *QW = (u32 *)r2a_raw + (P.he_smem ? (size_t)2 * P.he_cap * 64 : 0) + threadIdx.x;
     u8 *z = P.z + lane_id * (size_t)P.z_cap;
     const mem_opt_t &opt = P.opt;
     const DevIndex &ix = P.ix;
@@ -246,12 +259,27 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
             continue;
         }
         int need_big = 0;
+        const bool staged = MODE == 1 && ok;
+        if (staged) {
+            for (int k = 0; k * 8 < lq; ++k) {
+                u32 wd = 0;
+                for (int b = 0; b < 8 && k * 8 + b < lq; ++b) {
+                    const int j = k * 8 + b;
+                    wd |= (u32)(rev ? query[qb + lq - 1 - j] : query[qb + j]) << (b << 2);
+                }
+                QW[k * 64] = wd;
+            }
+        }
         do {
             w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
             n_cigar = 0; NM = -1;
-            if (ok) {
-                if (rev) r2a_gen_cigar2(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
-                else r2a_gen_cigar2(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
+            if (MODE == 1) {
+                if (!ok) ;
+                else if (rev) r2a_gen_cigar2<true>(P, s_mat, w2, lq, SeqSmem{QW}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
+                else r2a_gen_cigar2<true>(P, s_mat, w2, lq, SeqSmem{QW}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
+            } else if (ok) {
+                if (rev) r2a_gen_cigar2<MODE != 0>(P, s_mat, w2, lq, SeqRev{query + qb, lq}, rb, rlen, RefSeqRev{&ix, rb, rlen}, true, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
+                else r2a_gen_cigar2<MODE != 0>(P, s_mat, w2, lq, SeqFwd{query + qb}, rb, rlen, RefSeqFwd{&ix, rb}, false, H, E, hs, z, cigar, n_cigar, score, NM, md, &ovf, P.he_cap, &need_big);
             }
             if (need_big) break;
             if (score == last_sc || w2 == opt.w << 2) break;
@@ -420,13 +448,21 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         }
         const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
         const size_t he_bytes = (size_t)2 * he_cap * 64 * 4;
-        P.he_smem = he_bytes <= 100 * 1024 ? 1 : 0;
-        const size_t smem = P.he_smem ? he_bytes : 0;
+        P.q_words = ctx->r2a_small && max_len <= 256 ? (max_len + 7) / 8 : 0;
+        const size_t q_bytes = (size_t)P.q_words * 64 * 4;
+        P.he_smem = he_bytes + q_bytes <= 100 * 1024 ? 1 : 0;
+        const size_t smem = (P.he_smem ? he_bytes : 0) + q_bytes;
 #ifndef B200_EMU
-        B200_CHECK(cudaFuncSetAttribute(reg2aln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        B200_CHECK(cudaFuncSetAttribute(reg2aln_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        B200_CHECK(cudaFuncSetAttribute(reg2aln_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
         tmark(2);
-        B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, P);
+        {   // pass 0 does no DP: no shared-memory rows, so the registers (8 blocks per SM), not the rows (2), set its occupancy
+            R2AParams P0 = P;
+            P0.he_smem = 0; P0.q_words = 0;
+            const int grid0 = std::max(1, std::min(ctx->n_sms * 14, (n + 63) / 64));       // 72 registers, no scratch: 14 blocks per SM
+            B200_LAUNCH(reg2aln_kernel<0>, grid0, 64, 0, st, P0);
+        }
         tmark(3);
         P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);
         {   // pass 1 with a small row per lane: rings of up to HE_SMALL entries (w <= 23): 25 KB of shared memory per block instead of 78 KB at 150 bp
@@ -435,11 +471,14 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             Q.dp_list2 = d_lm.as<i32>(); Q.dp_n2 = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_TOTAL);      // d_lm is free until the lengths kernel
             if (he_cap > HE_SMALL && ctx->r2a_small) {
                 Q.he_cap = HE_SMALL; Q.he_smem = 1;
-                B200_LAUNCH(reg2aln_kernel, grid, 64, (size_t)2 * HE_SMALL * 64 * 4, st, Q);
+                if (Q.q_words) B200_LAUNCH(reg2aln_kernel<1>, grid, 64, (size_t)2 * HE_SMALL * 64 * 4 + q_bytes, st, Q);
+                else B200_LAUNCH(reg2aln_kernel<2>, grid, 64, (size_t)2 * HE_SMALL * 64 * 4, st, Q);
                 Q.pass = 2; Q.he_cap = he_cap; Q.he_smem = P.he_smem;
                 Q.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_ARENA_USED);
-                B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, Q);
-            } else B200_LAUNCH(reg2aln_kernel, grid, 64, smem, st, Q);
+                if (Q.q_words) B200_LAUNCH(reg2aln_kernel<1>, grid, 64, smem, st, Q);
+                else B200_LAUNCH(reg2aln_kernel<2>, grid, 64, smem, st, Q);
+            } else if (Q.q_words) B200_LAUNCH(reg2aln_kernel<1>, grid, 64, smem, st, Q);
+            else B200_LAUNCH(reg2aln_kernel<2>, grid, 64, smem, st, Q);
         }
         tmark(4);
         B200_LAUNCH(r2a_lengths_kernel, (n + 255) / 256, 256, 0, st, (const b200_aln_t *)d_aln.p, n, d_nc.as<i32>(), d_lm.as<i32>());
