@@ -178,8 +178,10 @@ def reads_to_sam(a, ctx, hidx, opt, pin_seq, pin_off, threads):
     a_names = (C.c_char_p * len(hidx.names))(*[x.encode() for x in hidx.names])
     r_names = (C.c_char_p * m)(*[b"r%d" % i for i in range(m)])
     soff = np.zeros(m + 1, dtype=np.int64)
-    sam = np.zeros((a.read_len + 120) * m + 4096, dtype=np.uint8)
-    cap_r = int(m * 1.2) + 1024
+    sam = np.zeros((a.read_len + 260) * m + 4096, dtype=np.uint8)
+    nr0 = -ctx.lib.b200_align_batch(ctx.h, C.byref(opt), C.c_int(m), P(seqs, C.c_uint8), P(off, C.c_int64), C.c_int64(0), None,
+                                    P(cnt, C.c_int32))                 # sizes the record buffers (regions per read vary with the genome)
+    cap_r = int(max(nr0, m) * 1.02) + 1024
     import torch
 
     def pinned(n, dt):                                     # pinned host buffers, as a host program feeding a GPU would use
