@@ -14,6 +14,7 @@
  *   (4) ksw_extend2 / ksw_align2 / ksw_global2 batches
  *   (5) mem_align1_core -> mem_alnreg_t per read
  *   (7) mem_process_seqs -> SAM text
+ *   (8) mem_reg2aln per region; worker2 single-end (mem_mark_primary_se, mem_approx_mapq_se, mem_reg2sam) -> regions + SAM text
  */
 #include <stdio.h>
 #include <stdlib.h>
