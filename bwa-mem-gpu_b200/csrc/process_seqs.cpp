@@ -61,7 +61,12 @@ static inline uint8_t nt4_of(uint8_t c)
 static std::vector<b200_ctx_t *> g_ps_ctxs;
 static const bwt_t *g_ps_bwt = nullptr;
 static int g_ps_want_devices = 1;
-static int g_ps_host_worker2 = 0;
+// worker2 of single-end batches: 0 = on the device, 1 = the host program's functions, -1 (default) = on the device unless
+// the batch holds long reads AND the host program has the functions: reg2aln_kernel maps one region to one lane, which
+// is the right shape for 100-300 bp reads (17.7 M reads/s) but not for kbp reads with bands of hundreds of columns
+// (profiles/r3q_long_sam.json: 0.9 k reads/s on the device vs 0.4 k per host thread) -- see DESIGN.md section 8
+static int g_ps_host_worker2 = -1;
+#define PS_LONG_READ 1000
 extern "C" void b200_process_seqs_host_worker2(int on) { g_ps_host_worker2 = on; }
 
 extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctxs.assign(1, ctx); g_ps_bwt = nullptr; }
@@ -100,7 +105,13 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
                                       int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
 {
     const bool pe = (opt->flag & MEM_F_PE) != 0;
-    const bool dev_worker2 = !pe && !g_ps_host_worker2;
+    bool dev_worker2 = !pe && g_ps_host_worker2 <= 0;
+    if (dev_worker2 && g_ps_host_worker2 < 0) {
+        int mx = 0;
+        for (int i = 0; i < n; ++i) mx = seqs[i].l_seq > mx ? seqs[i].l_seq : mx;
+        const bool host_has = (mem_mark_primary_se || dlsym(RTLD_DEFAULT, "mem_mark_primary_se")) && (mem_reg2sam || dlsym(RTLD_DEFAULT, "mem_reg2sam"));
+        if (mx > PS_LONG_READ && host_has) dev_worker2 = false;
+    }
     mark_fn f_mark = dev_worker2 ? nullptr : (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
     reg2sam_fn f_reg2sam = dev_worker2 ? nullptr : (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
     sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;

@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--contig-len", type=int, default=25_000_000)
     ap.add_argument("--chunk", type=int, default=0, help="reads per pipeline chunk (0 = the library's own choice)")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables")
+    ap.add_argument("--sam", action="store_true", help="also worker2 on the resident batch + SAM text (single-end), with a sample check")
     a = ap.parse_args()
     contigs = synth.make_genome([a.contig_len] * a.contigs)
     rng = np.random.default_rng(5)
@@ -62,6 +63,25 @@ def main():
         k = int(n[:m].sum())
         res.update({"parity_sample": m, "parity": bool(np.array_equal(n0, n[:m]) and r0.tobytes() == regs[:k].tobytes()),
                     "ref_reads_per_s_all_cores": m / t_ref, "ref_cores": os.cpu_count()})
+    if a.sam:                                              # worker2 on the resident batch (b200_batch_reg2sam_se) + b200_sam_se_format
+        os.environ["B200_R2A_TIMING"] = "1"
+        ctx.batch_reg2sam_se(opt, n)                       # sizes the buffers
+        t0 = time.time()
+        r2, sel, aln, cig, md = ctx.batch_reg2sam_se(opt, n)
+        t_w2 = time.time() - t0
+        names = [f"r{i}" for i in range(a.reads)]
+        t0 = time.time()
+        sam, soff = ctx.sam_se(opt, hidx.names, names, flat, off, n, sel, aln, cig, md, n_threads=os.cpu_count() or 8)
+        t_fmt = time.time() - t0
+        res.update({"worker2_call_s": t_w2, "sam_format_s_incl_python": t_fmt, "sam_bytes": len(sam), "regions": int(len(regs)),
+                    "cigar_words": int(len(cig))})
+        if refapi.available():
+            lut = np.full(256, 4, dtype=np.uint8); lut[:4] = np.arange(4)
+            k = int(n[:m].sum())
+            t0 = time.time()
+            _, _, sam0 = ridx.reg2sam_se(opt, lut[flat[: int(off[m])]], off[: m + 1], regs[:k], n[:m])
+            t_ref = time.time() - t0
+            res.update({"sam_parity": bool(sam0 == sam[: int(soff[m])]), "ref_worker2_reads_per_s_1thread": m / t_ref})
     print(json.dumps(res))
 
 

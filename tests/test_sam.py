@@ -22,7 +22,7 @@ class BSeq1(C.Structure):          # bseq1_t, bwa.h:56-63
                 ("l_name", C.c_int8), ("l_comment", C.c_int8), ("l_qual", C.c_int16)]
 
 
-def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards=1, quals=None, host_worker2=0):
+def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards=1, quals=None, host_worker2=-1):
     idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
     C.CDLL(refapi.REF_SO, mode=os.RTLD_GLOBAL)          # the "host program": the reference's worker2 functions
     lib = ctx.lib
@@ -72,9 +72,10 @@ def test_sam_single_end(backend, gname):
     n = 400 if backend == "emu" else 20000
     seqs, off = cm.reads_for(gname, n, seed=71, indel=0.004, sub=0.015)
     exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, n_processed=1000)
-    got = _our_sam(backend, gname, opt, seqs, off, n_processed=1000)
+    got = _our_sam(backend, gname, opt, seqs, off, n_processed=1000, host_worker2=-1)      # auto: short reads -> device worker2
     assert got == exp
     assert exp.count(b"\n") >= n
+    assert _our_sam(backend, gname, opt, seqs, off, n_processed=1000, host_worker2=0) == exp
     assert _our_sam(backend, gname, opt, seqs, off, n_processed=1000, host_worker2=1) == exp
     quals = np.random.default_rng(5).integers(35, 74, size=len(seqs), dtype=np.uint8)
     seqs2, off2 = cm.ragged_reads(gname)
