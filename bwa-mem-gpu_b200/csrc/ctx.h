@@ -67,7 +67,7 @@ struct b200_ctx {
     DevBuf d_final, d_final_n;
     i64 total_regs = 0;
     unsigned long long stats[CNT_N] = {0};
-    DevBuf d_r2a[17];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
+    DevBuf d_r2a[18];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
     int r2a_small = 1;                         // reg2aln pass 1 with ring-sized H / E rows (tunable)
     int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
     void *pin_p[12] = {}; size_t pin_cap[12] = {};   // page-locked host buffers of b200_align_sam_se_batch (b200_ctx_pinned)

@@ -24,7 +24,9 @@ struct R2AParams {
     unsigned *work_counter; int *overflow;
     // two passes: pass 0 finishes the regions that need no DP (equal lengths, inferred band 0) and lists the others;
     // pass 1 runs the listed regions, so that the lanes of a warp are all inside ksw_global2 together
-    i32 *dp_list; unsigned *dp_n; int pass;
+    // the list is kept as four lists by inferred band (one lane = one region, a warp costs what its widest band costs:
+    // lanes that fetch consecutive entries get bands of the same class), widest class first
+    i32 *dp_list; unsigned *dp_n; int pass; int dp_stride;
     // pass 1 runs with a small H / E row per lane (he_cap entries, rings of 2w + 2); regions whose band does not fit are
     // listed again and run in pass 2 with a full row
     i32 *dp_list2; unsigned *dp_n2;
@@ -229,7 +231,14 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
     int ovf = 0;
     for (;;) {
         unsigned g = atomicAdd(P.work_counter, 1u);
-        if (P.pass == 1) { if (g >= *P.dp_n) break; g = (unsigned)P.dp_list[g]; }
+        if (P.pass == 1) {
+            const unsigned n3 = P.dp_n[3], n2 = P.dp_n[2], n1 = P.dp_n[1], n0 = P.dp_n[0];
+            if (g >= n3 + n2 + n1 + n0) break;
+            if (g < n3) g = (unsigned)P.dp_list[3 * (size_t)P.dp_stride + g];
+            else if (g < n3 + n2) g = (unsigned)P.dp_list[2 * (size_t)P.dp_stride + (g - n3)];
+            else if (g < n3 + n2 + n1) g = (unsigned)P.dp_list[(size_t)P.dp_stride + (g - n3 - n2)];
+            else g = (unsigned)P.dp_list[g - n3 - n2 - n1];
+        }
         else if (P.pass == 2) { if (g >= *P.dp_n2) break; g = (unsigned)P.dp_list2[g]; }
         else if (g >= (unsigned)P.n_regs) break;
         const mem_alnreg_t ar = P.regs[g];
@@ -255,7 +264,8 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
         const bool ok = lq > 0 && rb < re && !(rb < l_pac && re > l_pac);      // bwa.c:272
         const bool rev = rb >= l_pac;
         if (P.pass == 0 && ok && !(lq == rlen && (w2 < opt.w << 2 ? w2 : opt.w << 2) == 0)) {   // needs ksw_global2: second pass
-            P.dp_list[atomicAdd(P.dp_n, 1u)] = (i32)g;
+            const int cls = w2 <= 12 ? 0 : w2 <= 18 ? 1 : w2 <= 26 ? 2 : 3;
+            P.dp_list[cls * (size_t)P.dp_stride + atomicAdd(P.dp_n + cls, 1u)] = (i32)g;
             continue;
         }
         int need_big = 0;
@@ -393,7 +403,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         d_nc.ensure((size_t)chunk * 4) || d_lm.ensure((size_t)chunk * 4) || d_co.ensure(((size_t)chunk + 1) * 8) ||
         d_mo.ensure(((size_t)chunk + 1) * 8) || d_tmp.ensure(((size_t)chunk / 1024 + 2) * 8) ||
         d_pool_c.ensure((size_t)chunk * cig_stride * 4) || d_pool_m.ensure((size_t)chunk * md_stride) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
-    DevBuf &d_roff = ctx->d_r2a[14], &d_sel = ctx->d_r2a[15], &d_log = ctx->d_r2a[16];
+    DevBuf &d_roff = ctx->d_r2a[14], &d_sel = ctx->d_r2a[15], &d_log = ctx->d_r2a[16], &d_dp = ctx->d_r2a[17];
+    if (d_dp.ensure(((size_t)4 * chunk + 8) * 4)) return -1;
     if (finalize) {
         if (d_roff.ensure(((size_t)n_reads + 1) * 8) || d_sel.ensure((size_t)chunk * sizeof(b200_sel_t))) return -1;
         B200_CHECK(cudaMemcpyAsync(d_roff.p, roff.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
@@ -434,7 +445,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         P.aln = d_aln.as<b200_aln_t>(); P.cig = d_cig.as<u32>(); P.cig_stride = cig_stride; P.md = d_md.as<char>(); P.md_stride = md_stride;
         P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
-        P.dp_list = d_nc.as<i32>(); P.dp_n = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY); P.pass = 0;      // d_nc is free until the lengths kernel
+        P.dp_list = d_dp.as<i32>(); P.dp_stride = chunk; P.dp_n = (unsigned *)(d_dp.as<i32>() + (size_t)4 * chunk); P.pass = 0;
+        B200_CHECK(cudaMemsetAsync(P.dp_n, 0, 32, st));
         tmark(1);
         if (finalize) {
             FinParams F;
