@@ -391,7 +391,15 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
     const int chunk = (int)std::max<i64>(std::max(1024, max_cnt), std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
-    const i64 lanes_fit = std::max<i64>(64, ((i64)12 << 30) / (i64)per_lane);
+    // lane-private traceback scratch: short reads need ~50 KB per lane (all 8 blocks per SM fit in a few GB); long reads need
+    // MBs per lane, and the number of lanes in flight is what bounds them, so they may take up to half of the free memory
+    i64 z_budget = (i64)12 << 30;
+    if ((i64)per_lane * ctx->n_sms * 8 * 64 > z_budget) {
+        size_t mem_free = 0, mem_total = 0;
+        if (cudaMemGetInfo(&mem_free, &mem_total) == cudaSuccess)
+            z_budget = std::max<i64>(z_budget, std::min<i64>((i64)80 << 30, (i64)(mem_free + ctx->d_r2a[5].bytes + ctx->d_r2a[6].bytes) / 2));
+    }
+    const i64 lanes_fit = std::max<i64>(64, z_budget / (i64)per_lane);
     const int grid_max = (int)std::max<i64>(1, std::min<i64>((i64)ctx->n_sms * 8, lanes_fit / 64));
     // grow-only buffers kept in the context: a second call of the same shape allocates nothing
     DevBuf &d_regs = ctx->d_r2a[0], &d_rr = ctx->d_r2a[1], &d_aln = ctx->d_r2a[2], &d_cig = ctx->d_r2a[3], &d_md = ctx->d_r2a[4],
