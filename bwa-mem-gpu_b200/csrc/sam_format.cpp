@@ -287,7 +287,8 @@ extern "C" int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt
         if (nr >= 0x7fffffff) { join(); return -1; }
         b200_sel_t *sel = (b200_sel_t *)b200_ctx_pinned(ctx, s0 + 1, (size_t)(nr + 1) * sizeof(b200_sel_t));
         b200_aln_t *aln = (b200_aln_t *)b200_ctx_pinned(ctx, s0 + 2, (size_t)(nr + 1) * sizeof(b200_aln_t));
-        int64_t cap_c = 4 * nr + 64, cap_m = 16 * nr + 64, totals[2];
+        const int64_t bases = off[r0 + n] - off[r0];             // indel-rich long reads: CIGAR / MD grow with the bases, not the regions
+        int64_t cap_c = 4 * nr + bases / 8 + 64, cap_m = 16 * nr + bases / 4 + 64, totals[2];
         uint32_t *cig = nullptr; char *md = nullptr;
         if (!sel || !aln) { join(); return -1; }
         for (;;) {

@@ -360,7 +360,7 @@ class Context:
         regs = np.ascontiguousarray(regs); cnt = np.ascontiguousarray(cnt, dtype=np.int32)
         aln = np.zeros(max(1, len(regs)), dtype=ALN_DTYPE)
         tot = (C.c_int64 * 2)()
-        cap_c, cap_m = 8 * len(regs) + 64, 24 * len(regs) + 64
+        cap_c, cap_m = 8 * len(regs) + int(off[-1] - off[0]) // 8 + 64, 24 * len(regs) + int(off[-1] - off[0]) // 4 + 64
         while True:
             cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
             rc = self.lib.b200_reg2aln_batch(self.h, C.byref(opt), C.c_int(n), _p(seqs, C.c_uint8), _p(off, C.c_int64),
@@ -382,7 +382,7 @@ class Context:
         aln = np.zeros(max(1, len(regs)), dtype=ALN_DTYPE)
         sel = np.zeros(max(1, len(regs)), dtype=SEL_DTYPE)
         tot = (C.c_int64 * 2)()
-        cap_c, cap_m = 8 * len(regs) + 64, 24 * len(regs) + 64
+        cap_c, cap_m = 8 * len(regs) + int(off[-1] - off[0]) // 8 + 64, 24 * len(regs) + int(off[-1] - off[0]) // 4 + 64
         while True:
             cig = np.zeros(cap_c, dtype=np.uint32); md = np.zeros(cap_m, dtype=np.uint8)
             regs[...] = regs0
