@@ -290,6 +290,29 @@ int b200_ksw_extend2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, cons
                            int o_del, int e_del, int o_ins, int e_ins, const int32_t *w, int end_bonus,
                            int zdrop, const int32_t *h0, int32_t *out);
 
+/* ksw_extend2 over an array of problems for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same arithmetic and the same 6 x int32 results per problem as b200_ksw_extend2_batch (a variant of its
+ * kernel), but: every array argument except `mat` (25 host bytes, copied into the kernel parameters) is DEVICE memory
+ * of `device`, owned by the caller; the warp-private H / E rows and the work counter live in one file-scope __device__
+ * array of b200_noalloc_scratch_bytes() = 19 398 912 bytes (18.5 MiB) that every GPU loading the library holds until the
+ * process exits; the call makes no cudaMalloc / cudaFree / allocating library call and no synchronisation: it enqueues one
+ * 256-byte memset (the work counter) and one kernel on `stream` (a cudaStream_t, NULL = the default stream) and returns.
+ * Limits: max_qlen (the longest query of the call, stated by the caller) <= B200_NOALLOC_MAX_QLEN and
+ * n <= B200_NOALLOC_MAX_PROBLEMS, else -2 and a message in b200_last_error(); a problem whose own qlen exceeds the limit or
+ * whose h0 <= 0 (ksw.c:385) gets INT32_MIN in all six outputs.  All calls share the one scratch array: calls that overlap
+ * on the GPU (different streams or host threads) race; serialise them. */
+#define B200_NOALLOC_MAX_QLEN     1022
+#define B200_NOALLOC_MAX_PROBLEMS ((int64_t)1 << 30)
+int b200_ksw_extend2_noalloc(int device, int64_t n, int max_qlen, const int32_t *d_qlen, const int64_t *d_qoff,
+                             const uint8_t *d_q, const int32_t *d_tlen, const int64_t *d_toff, const uint8_t *d_t,
+                             const int8_t *mat, int o_del, int e_del, int o_ins, int e_ins, const int32_t *d_w,
+                             int end_bonus, int zdrop, const int32_t *d_h0, int32_t *d_out, void *stream);
+int64_t b200_noalloc_scratch_bytes(void);
+/* optional set-up (once per device, e.g. before a graph capture starts): looks up the scratch array's device address;
+ * b200_ksw_extend2_noalloc otherwise does it on its first call for that device.  Also no counterpart in the reference. */
+int b200_noalloc_setup(int device);
+
 /* ksw_align2 (ksw.c:343) over an array of problems (striped u8 / i16 local SW incl. the KSW_XSTART reverse pass);
  * xtra per problem as in ksw.h:33-36; out: 7 x int32 per problem = kswr_t {score, te, qe, score2, te2, tb, qb} */
 int b200_ksw_align2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, const int64_t *qoff, const uint8_t *q,
