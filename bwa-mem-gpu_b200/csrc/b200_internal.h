@@ -160,7 +160,7 @@ size_t smem_fast3_bytes(int wide, int lcap, int pk_stride);
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, int qglob, cudaStream_t st);
 int launch_smem_p3(const SmemParams &p, int n_sms, int wide, int qglob, cudaStream_t st);
 int launch_build_occ32(const DevIndex &ix, uint4 *out, u64 n_blocks, cudaStream_t st);
-int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st);
+int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, int wide, cudaStream_t st);
 size_t kmer_tab_entries(int kmax);
 int launch_seed_count(const SeedParams &p, cudaStream_t st);
 int launch_seed_fill(const SeedParams &p, cudaStream_t st);

@@ -55,6 +55,14 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "smem_bps")) ctx->smem_bps = (int)value;
     else if (!strcmp(key, "split_p3")) ctx->split_p3 = (int)value;
     else if (!strcmp(key, "force_wide")) ctx->force_wide = (int)value;       // before the index upload
+    else if (!strcmp(key, "cap_retry")) ctx->cap_retry = (int)value;
+#ifndef B200_EMU
+    else if (!strcmp(key, "l2_fetch")) {                                      // L2 fetch granularity hint in bytes (32 / 64 / 128), device-wide
+        if (cudaSetDevice(ctx->device) != cudaSuccess || cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)value) != cudaSuccess) {
+            cudaGetLastError(); b200_set_error("cudaLimitMaxL2FetchGranularity %lld refused", (long long)value); return -1;
+        }
+    }
+#endif
     else if (!strcmp(key, "kmer_k")) ctx->kmer_k = (int)value;               // before the index upload
     else if (!strcmp(key, "ext_bin0")) ctx->ext_bin0 = (int)value;
     else if (!strcmp(key, "ext_bin1")) ctx->ext_bin1 = (int)value;
@@ -125,10 +133,11 @@ int b200_index_finish(b200_ctx *ctx, int flags)
         if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
         ix.occ32 = ctx->d_occ32.as<uint4>();
         ix.kmer_tab = nullptr; ix.kmer_k = 0;
-        if (ctx->kmer_k > 0) {                                       // k-mer interval table (kmer_tab.cu)
-            const bool wide = seq_len >= 0xfffffff0ull || ctx->force_wide;      // same rule as the seeding kernel template (pipeline.cu)
-            const int kk = ctx->kmer_k > 12 ? 12 : ctx->kmer_k;
-            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide ? 32 : 16))) return -1;
+        const int want_k = ctx->kmer_k >= 0 ? ctx->kmer_k : (seq_len >= 0xfffffff0ull ? 13 : 9);
+        if (want_k > 0) {                                            // k-mer interval table (kmer_tab.cu)
+            const int wide = b200_wide_mode(ctx);                               // same rule as the seeding kernel template (pipeline.cu)
+            const int kk = want_k > 13 ? 13 : want_k;                  // kmer_off[14]
+            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide == 1 ? 32 : 16))) return -1;
             if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
             ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;
         }

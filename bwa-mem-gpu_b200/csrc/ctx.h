@@ -2,6 +2,7 @@
 #pragma once
 #include "b200_internal.h"
 #include <vector>
+#include <mutex>
 
 struct DevBuf {
     void *p = nullptr;
@@ -21,6 +22,7 @@ struct DevBuf {
 };
 
 struct b200_ctx {
+    std::mutex call_mu;                        // serialises the same-name scalar shims (dropin.cu): they share this context's scratch and stream
     int device = 0;
     int n_sms = 148;
     cudaStream_t st = nullptr;
@@ -40,6 +42,8 @@ struct b200_ctx {
     // tunables
     int chunk_reads = 1 << 20; bool chunk_user = false;   // reads per pipeline chunk (tunable; unset: scaled down for long reads, pipeline.cu)
     int cap_intv = 0;                          // 0 = auto from read length
+    int cap_retry = 1;                         // a chunk that overflows the interval slots is re-run with the reported need (pipeline.cu)
+    int need_cap_intv = 0;                     // set by a chunk that overflowed
     int ext_path = 0;                          // 0 = auto, 1 = force the general warp-per-read kernel, 2 = force the round-based fast path
     int smem_path = 0;                         // 0 = auto (smem3 for short reads), 2 = smem2 kernel, 1 = general kernel only
     int l2_persist = 0;                        // 1: pin the seeding index in persisting L2 (set before the index upload)
@@ -51,8 +55,9 @@ struct b200_ctx {
     int ext_sort = 1;                          // byte-score extension kernel: jobs handed out ordered by flank shape (ext3.cu)
     int ext_rowsync = 1;                       // byte-score extension kernel: a lane finishes its row before the warp's control slot (ext3.cu)
     int split_p3 = 1;                          // third seeding pass in its own kernel (smem_p3_kernel) ahead of the main one
-    int force_wide = 0;                        // 1: run the 64-bit-position templates even when seq_len < 2^32 (tests); set before the index upload
-    int kmer_k = 9;                            // longest string in the k-mer interval table (0 = none); set before the index upload
+    int force_wide = 0;                        // tests: run the 64-bit-position templates even when seq_len < 2^32 (1: packed 33-bit records, 2: two-quad records); set before the index upload
+    int kmer_k = -1;                           // longest string in the k-mer interval table (0 = none, -1 = auto: 9, or 13 when seq_len >= 2^32:
+                                               // the upper levels of a deep table only pay when the index itself is DRAM-priced); set before the index upload
     int smem_bps = 0;                          // > 0: cap on resident blocks per SM of the seeding kernel (experiments)
     int smem_lcap = 0;                         // 0 = auto: shared-memory list entries per read in the fast SMEM kernel
     i64 idx_group_cap = 0, idx_tie_cap = 0;    // device index builder (index_dev.cu): suffixes per sort group / colliding suffixes per group (0 = default)
@@ -74,6 +79,16 @@ struct b200_ctx {
     // scratch for the primitive batches
     DevBuf d_pa, d_pb, d_pc, d_pd, d_pe, d_pf, d_pg, d_ph;
 };
+
+// Position width of the seeding kernels (smem3.cu): 0 = u32 (seq_len < 2^32), 2 = u64 with packed 16-byte records
+// (seq_len < 2^33: the 3.1 Gbp configs), 1 = u64 with two-quad records (anything larger)
+static inline int b200_wide_mode(const b200_ctx *ctx)
+{
+    const u64 n = ctx->ix.seq_len;
+    if (n < 0xfffffff0ull && !ctx->force_wide) return 0;
+    if (ctx->force_wide == 2 || n >= 0x1fffffff0ull) return 1;
+    return 2;
+}
 
 // layout of d_ctl (all 8-byte slots)
 enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_RETRY = 5, CTL_WORK2 = 6, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };

@@ -15,7 +15,7 @@
 #include "b200_internal.h"
 #include "occ32.cuh"
 
-template <class PT>
+template <class PT, bool PACK33>
 __global__ void build_kmer_tab_kernel(DevIndex ix, uint4 *tab, int k, u32 off)
 {
     const u64 W = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -29,6 +29,8 @@ __global__ void build_kmer_tab_kernel(DevIndex ix, uint4 *tab, int k, u32 off)
         x0 = n0; x1 = n1; x2 = n2;
     }
     if (sizeof(PT) == 4) tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, 0u);
+    else if (PACK33)                                             // Ent33 (smem3.cu): bit 32 of x0 / x1 / x2 in the top bits of the last word
+        tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, (u32)((u64)x0 >> 32) << 31 | ((u32)((u64)x1 >> 32) & 1u) << 30 | ((u32)((u64)x2 >> 32) & 1u) << 29);
     else {
         uint4 *p = tab + ((size_t)off + W) * 2;
         p[0] = make_uint4((u32)x0, (u32)((u64)x0 >> 32), (u32)x1, (u32)((u64)x1 >> 32));
@@ -37,15 +39,17 @@ __global__ void build_kmer_tab_kernel(DevIndex ix, uint4 *tab, int k, u32 off)
 }
 
 // fills ix.kmer_off; the caller sets ix.kmer_tab / ix.kmer_k after the build
-int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, bool wide, cudaStream_t st)
+// wide: 0 = 16-byte entries of u32, 1 = 32-byte entries of u64, 2 = 16-byte packed entries of 33-bit values
+int launch_build_kmer_tab(DevIndex &ix, uint4 *tab, int kmax, int wide, cudaStream_t st)
 {
     u32 off = 0;
     for (int k = 1; k <= kmax; ++k) { ix.kmer_off[k] = off; off += 1u << (2 * k); }
     for (int k = 1; k <= kmax; ++k) {
         const u64 n = 1ull << (2 * k);
         const int grid = (int)((n + 255) / 256);
-        if (wide) B200_LAUNCH(build_kmer_tab_kernel<u64>, grid, 256, 0, st, ix, tab, k, ix.kmer_off[k]);
-        else B200_LAUNCH(build_kmer_tab_kernel<u32>, grid, 256, 0, st, ix, tab, k, ix.kmer_off[k]);
+        if (wide == 2) B200_LAUNCH((build_kmer_tab_kernel<u64, true>), grid, 256, 0, st, ix, tab, k, ix.kmer_off[k]);
+        else if (wide) B200_LAUNCH((build_kmer_tab_kernel<u64, false>), grid, 256, 0, st, ix, tab, k, ix.kmer_off[k]);
+        else B200_LAUNCH((build_kmer_tab_kernel<u32, false>), grid, 256, 0, st, ix, tab, k, ix.kmer_off[k]);
         B200_CHECK(cudaGetLastError());
     }
     return 0;

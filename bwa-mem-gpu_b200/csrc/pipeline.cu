@@ -70,7 +70,27 @@ struct StageTimer {
 static int g_chain_stage = 1;
 #define SSW_MAX_Q 200                                    // mem_seed_sw only aligns windows shorter than MEM_SHORT_LEN
 
+static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
+
+// A chunk whose reads need more interval slots than the heuristic (or the tunable) gave them is run again with the
+// count the device reported: the buffers are grow-only and nothing of a chunk is committed before it has succeeded
+// (the reference has no such limit: bwtintv_v grows by realloc, bwt.c:306).  Tunable cap_retry=0 turns that off.
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms)
+{
+    for (int attempt = 0; ; ++attempt) {
+        ctx->need_cap_intv = 0;
+        float ms[6] = { 0, 0, 0, 0, 0, 0 };
+        const int rc = run_chunk_once(ctx, opt, r0, n, stop_after, stage_ms ? ms : nullptr);
+        if (rc == -2 && ctx->need_cap_intv > 0 && ctx->cap_retry && attempt < 4) {
+            ctx->cap_intv = ctx->need_cap_intv + 8;
+            continue;
+        }
+        if (stage_ms) for (int i = 0; i < 6; ++i) stage_ms[i] += ms[i];
+        return rc;
+    }
+}
+
+static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms)
 {
     cudaStream_t st = ctx->st;
     const i64 *d_off = ctx->d_off.as<i64>() + r0;
@@ -85,13 +105,14 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     tm.mark(st);
     // ---- K1 setup: which seeding kernel
     const int cap_intv = auto_cap_intv(ctx, opt);
-    const bool wide = ctx->ix.seq_len >= 0xfffffff0ull || ctx->force_wide;
+    const int wmode = b200_wide_mode(ctx);                                    // 0 u32, 1 u64 two-quad records, 2 u64 packed records
+    const bool wide = wmode != 0;
     const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
-    int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 12;
+    int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 8;      // 8: less shared memory = more L1 for the hot table levels (profiles/r4b_seed_ab.txt)
     lcap3 = lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);
     // reads too long to stage in shared memory: smem_fast_kernel (smem2.cu) by default -- measured faster on 1-10 kbp reads
     // (575 vs 758 ms per 200 k reads) -- or, with smem_path 3, the fast3 kernels fetching the read's 4-bit codes from global memory
-    const bool fits3 = smem_fast3_bytes(wide, lcap3, pk_stride) <= 100 * 1024;
+    const bool fits3 = smem_fast3_bytes(wmode, lcap3, pk_stride) <= 100 * 1024;
     const bool qglob = ctx->smem_path == 3;
     if (qglob) lcap3 = 16;
     const bool use3 = (ctx->smem_path == 0 && fits3) || qglob;
@@ -125,26 +146,26 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     SP.work_counter = ctl_u32(ctx, CTL_WORK); SP.stats = ctl_u64(ctx, CTL_STATS); SP.overflow = (int *)ctl_u32(ctx, CTL_OVF);
     SP.retry_n = ctl_u32(ctx, CTL_RETRY); SP.retry_ids = ctx->d_retry.as<i32>();
     if (use3) {
-        const size_t smem = smem_fast3_bytes(wide, lcap3, qglob ? 0 : pk_stride);
+        const size_t smem = smem_fast3_bytes(wmode, lcap3, qglob ? 0 : pk_stride);
         int per_sm = std::max(1, std::min(8, (int)((224 * 1024) / (smem + 1024))));
         if (ctx->smem_bps > 0) per_sm = std::min(per_sm, ctx->smem_bps);
         int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * per_sm));
         const int spill_cap = std::max(1, ctx->max_len + 1 - lcap3);
         {   // keep the per-lane spill areas of long reads under ~8 GB
-            const size_t per_block = (size_t)128 * spill_cap * (wide ? 32 : 16);
+            const size_t per_block = (size_t)128 * spill_cap * (wmode == 1 ? 32 : 16);
             fast_blocks = (int)std::max<size_t>(1, std::min<size_t>(fast_blocks, ((size_t)8 << 30) / per_block));
         }
-        if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wide ? 32 : 16))) return -1;
+        if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wmode == 1 ? 32 : 16))) return -1;
         SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
         SP.lists = (Intv *)ctx->d_spill.p;
         if (ctx->split_p3 && opt->max_mem_intv > 0) {                        // pass 3 first: uniform forward-only lanes
             SP.split_p3 = 1; SP.out3_n = ctx->d_retry.as<i32>();
             SP.work_counter = ctl_u32(ctx, CTL_WORK2);
-            if (launch_smem_p3(SP, ctx->n_sms, wide ? 1 : 0, qglob ? 1 : 0, st)) return -1;
+            if (launch_smem_p3(SP, ctx->n_sms, wmode, qglob ? 1 : 0, st)) return -1;
             SP.work_counter = ctl_u32(ctx, CTL_WORK);
             ++launches;
         }
-        if (launch_smem_fast3(SP, fast_blocks, wide ? 1 : 0, lcap3, qglob ? 1 : 0, st)) return -1;
+        if (launch_smem_fast3(SP, fast_blocks, wmode, lcap3, qglob ? 1 : 0, st)) return -1;
         ++launches;
     } else if (ctx->smem_path != 1) {
         const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);
@@ -164,7 +185,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     if (stop_after == 1) {
         u64 ovf;
         if (ctl_read(ctx, CTL_OVF, 1, &ovf)) return -1;
-        if ((int)(ovf & 0xffffffff)) { b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
+        if ((int)(ovf & 0xffffffff)) { ctx->need_cap_intv = (int)(ovf & 0xffffffff); tm.fini(); b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
         if (ovf >> 32) { b200_set_error("interval list scratch overflow"); return -2; }
         tm.fini();
         return 0;
@@ -187,7 +208,7 @@ int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_
     u64 ovf = 0;
     B200_CHECK(cudaMemcpyAsync(&tot_seeds, ctx->d_seed_off.as<i64>() + n, 8, cudaMemcpyDeviceToHost, st));
     if (ctl_read(ctx, CTL_OVF, 1, &ovf)) return -1;                         // also synchronises
-    if ((int)(ovf & 0xffffffff)) { b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
+    if ((int)(ovf & 0xffffffff)) { ctx->need_cap_intv = (int)(ovf & 0xffffffff); tm.fini(); b200_set_error("interval capacity %d too small (need %d)", cap_intv, (int)(ovf & 0xffffffff)); return -2; }
     if (ovf >> 32) { b200_set_error("interval list scratch overflow"); return -2; }
     if (ctx->d_seeds.ensure((size_t)(tot_seeds + 1) * sizeof(Seed))) return -1;
     DP.seeds = ctx->d_seeds.as<Seed>(); DP.n_seeds = tot_seeds;
@@ -439,12 +460,14 @@ extern "C" int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stag
 
 extern "C" int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
 {
-    if (!ctx) { b200_set_error("null context"); return -1; }
-    B200_CHECK(cudaSetDevice(ctx->device));
-    if (out_n && ctx->n_reads) B200_CHECK(cudaMemcpyAsync(out_n, ctx->d_final_n.p, (size_t)ctx->n_reads * 4, cudaMemcpyDeviceToHost, ctx->st));
+    if (!ctx) { b200_set_error("null context"); return B200_E_FAIL; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { b200_set_error("cudaSetDevice failed"); return B200_E_FAIL; }
+#define DL_CHECK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { b200_set_error("%s -> %s", #call, cudaGetErrorString(e_)); return B200_E_FAIL; } } while (0)
+    if (out_n && ctx->n_reads) DL_CHECK(cudaMemcpyAsync(out_n, ctx->d_final_n.p, (size_t)ctx->n_reads * 4, cudaMemcpyDeviceToHost, ctx->st));
     if (ctx->total_regs > cap) { cudaStreamSynchronize(ctx->st); return -ctx->total_regs; }
-    if (ctx->total_regs) B200_CHECK(cudaMemcpyAsync(out_regs, ctx->d_final.p, (size_t)ctx->total_regs * sizeof(mem_alnreg_t), cudaMemcpyDeviceToHost, ctx->st));
-    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    if (ctx->total_regs) DL_CHECK(cudaMemcpyAsync(out_regs, ctx->d_final.p, (size_t)ctx->total_regs * sizeof(mem_alnreg_t), cudaMemcpyDeviceToHost, ctx->st));
+    DL_CHECK(cudaStreamSynchronize(ctx->st));
+#undef DL_CHECK
     return ctx->total_regs;
 }
 
@@ -475,8 +498,8 @@ extern "C" int b200_batch_counters(b200_ctx_t *ctx, uint64_t *out)
 // their own stream while chunk k computes (the compute stream waits on a per-chunk event), and each chunk's records go
 // back on a third stream as soon as its read-ordered gather is done.  With pinned host buffers only the first chunk's
 // upload and the last chunk's download are exposed; pageable buffers make the same calls behave synchronously.
-extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
-                                    const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
+static int align_batch_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                            const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
 {
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
     B200_CHECK(cudaSetDevice(ctx->device));
@@ -538,9 +561,16 @@ extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n
     if (ctx->hoff == off) ctx->hoff = nullptr;                                          // the caller's array is not ours to keep
     if (rc) return rc;
     if (e != cudaSuccess) { b200_set_error("result download failed: %s", cudaGetErrorString(e)); return -1; }
-    if (ctx->total_regs > cap) return -ctx->total_regs;
     (void)copied;
-    return ctx->total_regs;
+    return 0;
+}
+
+extern "C" int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
+                                    const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n)
+{
+    const int rc = align_batch_impl(ctx, opt, n_reads, seqs, off, cap, out_regs, out_n);
+    if (rc) return rc == -2 ? B200_E_CAPACITY : B200_E_FAIL;                            // never confused with -(regions needed)
+    return ctx->total_regs > cap ? -ctx->total_regs : ctx->total_regs;
 }
 
 // ---- stage seams (parity tests) -----------------------------------------------------------------

@@ -28,11 +28,13 @@ void mem_reg2sam(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, 
 int  mem_sam_pe(const mem_opt_t *opt, const bntseq_t *bns, const uint8_t *pac, const mem_pestat_t pes[4], uint64_t id,
                 bseq1_t s[2], mem_alnreg_v a[2]) __attribute__((weak));
 void mem_pestat(const mem_opt_t *opt, int64_t l_pac, int n, const mem_alnreg_v *regs, mem_pestat_t pes[4]) __attribute__((weak));
+void mem_reorder_primary5(int T, mem_alnreg_v *a) __attribute__((weak));
 }
 
 typedef int  (*mark_fn)(const mem_opt_t *, int, mem_alnreg_t *, int64_t);
 typedef void (*reg2sam_fn)(const mem_opt_t *, const bntseq_t *, const uint8_t *, bseq1_t *, mem_alnreg_v *, int, const void *);
 typedef int  (*sam_pe_fn)(const mem_opt_t *, const bntseq_t *, const uint8_t *, const mem_pestat_t *, uint64_t, bseq1_t *, mem_alnreg_v *);
+typedef void (*reorder5_fn)(int, mem_alnreg_v *);
 typedef void (*pestat_fn)(const mem_opt_t *, int64_t, int, const mem_alnreg_v *, mem_pestat_t *);
 
 static void *host_symbol(void *weak_addr, const char *name)
@@ -85,7 +87,7 @@ static void shard_download(Shard &sh)
     for (;;) {
         int64_t got = b200_batch_download(sh.ctx, (int64_t)sh.regs.size(), sh.regs.data(), sh.cnt.data());
         if (got >= 0) return;
-        if (-got > (int64_t)sh.regs.size()) { sh.regs.resize((size_t)-got); continue; }
+        if (!B200_IS_ERROR(got) && -got > (int64_t)sh.regs.size()) { sh.regs.resize((size_t)-got); continue; }
         sh.err = b200_last_error();
         return;
     }
@@ -115,6 +117,10 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
     mark_fn f_mark = dev_worker2 ? nullptr : (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
     reg2sam_fn f_reg2sam = dev_worker2 ? nullptr : (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
     sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
+    // -5: single-end batches reorder between marking and mem_reg2sam (bwamem.c:1205, mem_reorder_primary5 bwamem.c:988 is a
+    // non-static function of the host program); mem_sam_pe applies it itself (bwamem_pair.c:305-307)
+    reorder5_fn f_reorder5 = (!pe && !dev_worker2 && (opt->flag & MEM_F_PRIMARY5_))
+                                 ? (reorder5_fn)host_symbol((void *)mem_reorder_primary5, "mem_reorder_primary5") : nullptr;
     pestat_fn f_pestat = (pe && !pes0) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
 
     if (g_ps_ctxs.empty() || (g_ps_bwt && g_ps_bwt != bwt)) {         // lazy contexts from the index identity
@@ -165,8 +171,8 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
                                                            names.data() + sh.r0, comments.data() + sh.r0, flat.data(),
                                                            n_qual ? qflat.data() : nullptr, off.data() + sh.r0, rg, fmt_threads, 0,
                                                            (int64_t)sh.sam.size(), sh.sam.data(), sh.sam_off.data());
-                if (rc < -1) { sh.sam.resize((size_t)-rc + 64); continue; }
-                if (rc < 0) { sh.err = b200_last_error(); return; }
+                if (B200_IS_ERROR(rc)) { sh.err = b200_last_error(); return; }
+                if (rc < 0) { sh.sam.resize((size_t)-rc + 64); continue; }
                 break;
             }
             for (int i = 0; i < sh.n; ++i) {                           // seqs[i].sam: heap memory owned by the caller (bwamem.c:1054)
@@ -228,6 +234,7 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
             if (i >= n_units) break;
             if (!pe) {                                                // bwamem.c:1202-1207
                 f_mark(opt, rv[i].n, rv[i].a, n_processed + i);
+                if (f_reorder5) f_reorder5(opt->T, &rv[i]);          // bwamem.c:1205
                 f_reg2sam(opt, bns, pac, &seqs[i], &rv[i], 0, nullptr);
                 free(rv[i].a);
             } else {                                                  // bwamem.c:1208-1212
@@ -236,10 +243,6 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
             }
         }
     };
-    if (opt->flag & MEM_F_PRIMARY5_) {
-        fprintf(stderr, "[b200::mem_process_seqs] -5 (MEM_F_PRIMARY5) needs the reference's static mem_reorder_primary5; not supported\n");
-        exit(1);
-    }
     std::vector<std::thread> pool;
     for (int t = 1; t < n_threads; ++t) pool.emplace_back(work);
     work();

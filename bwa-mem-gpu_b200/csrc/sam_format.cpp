@@ -280,28 +280,29 @@ extern "C" int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt
         const int n = std::min(sub, n_reads - r0);
         const int s0 = (k & 1) * 5;                        // buffer set; the formatter of sub-batch k-2 was joined before k-1's started
         int32_t *cnt = (int32_t *)b200_ctx_pinned(ctx, s0, (size_t)n * 4);
-        if (!cnt) { join(); return -1; }
+        if (!cnt) { join(); return B200_E_FAIL; }
         int64_t nr = b200_align_batch(ctx, opt, n, seqs, off + r0, 0, nullptr, cnt);
-        if (nr > 0) { join(); return -1; }                 // cannot happen with cap 0
+        if (B200_IS_ERROR(nr)) { join(); return nr; }      // a real error (message set), not "-(regions)"
+        if (nr > 0) { join(); return B200_E_FAIL; }        // cannot happen with cap 0
         nr = -nr;
-        if (nr >= 0x7fffffff) { join(); return -1; }
+        if (nr >= 0x7fffffff) { join(); return B200_E_FAIL; }
         b200_sel_t *sel = (b200_sel_t *)b200_ctx_pinned(ctx, s0 + 1, (size_t)(nr + 1) * sizeof(b200_sel_t));
         b200_aln_t *aln = (b200_aln_t *)b200_ctx_pinned(ctx, s0 + 2, (size_t)(nr + 1) * sizeof(b200_aln_t));
         const int64_t bases = off[r0 + n] - off[r0];             // indel-rich long reads: CIGAR / MD grow with the bases, not the regions
         int64_t cap_c = 4 * nr + bases / 8 + 64, cap_m = 16 * nr + bases / 4 + 64, totals[2];
         uint32_t *cig = nullptr; char *md = nullptr;
-        if (!sel || !aln) { join(); return -1; }
+        if (!sel || !aln) { join(); return B200_E_FAIL; }
         for (;;) {
             cig = (uint32_t *)b200_ctx_pinned(ctx, s0 + 3, (size_t)cap_c * 4);
             md = (char *)b200_ctx_pinned(ctx, s0 + 4, (size_t)cap_m);
-            if (!cig || !md) { join(); return -1; }
+            if (!cig || !md) { join(); return B200_E_FAIL; }
             const int64_t rc = nr ? b200_batch_reg2sam_se(ctx, opt, n_processed + r0, cnt, nullptr, sel, aln, cap_c, cig, cap_m, md, totals) : 0;
             if (rc == -2) { cap_c = totals[0] + 64; cap_m = totals[1] + 64; continue; }
-            if (rc < 0) { join(); return -1; }
+            if (rc < 0) { join(); return B200_E_FAIL; }
             break;
         }
         join();                                            // the previous sub-batch's text is in place: `written` is final
-        if (fmt_failed) return -1;
+        if (fmt_failed) return B200_E_FAIL;
         fmt = std::thread([&, r0, n, cnt, sel, aln, cig, md]() {
             int64_t *so = sam_off ? sam_off + r0 : nullptr;
             const int64_t room = need > cap ? 0 : cap - written;
@@ -315,6 +316,6 @@ extern "C" int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt
         });
     }
     join();
-    if (fmt_failed) { return -1; }
+    if (fmt_failed) { return B200_E_FAIL; }
     return need > cap ? -need : need;
 }

@@ -28,16 +28,25 @@
 
 enum { S3_TASK = 0, S3_FWD = 1, S3_BWD = 2, S3_P3 = 3, S3_FIN = 4 };
 
+// List entry / k-mer table entry formats.  PT = position type of the kernel's arithmetic.
+//   Ent<u32>  : seq_len < 2^32, one 16-byte record (x0, x1, x2, end)
+//   Ent<u64>  : any seq_len, two 16-byte records
+//   Ent33     : 2^32 <= seq_len < 2^33 (the 3.1 Gbp configs: 6.2 G rows), ONE 16-byte record: the low words of x0, x1, x2
+//               and `end` (< 2^29) with the three bit-32s in its top bits.  Half the shared memory of Ent<u64>: 6 resident
+//               blocks per SM instead of 3 on the human-sized index, and one LDG.128 per k-mer table hit instead of two.
 template <class PT> struct Ent;
 template <> struct Ent<u32> {
-    static constexpr int kQuads = 1;
+    typedef u32 PT;
+    static constexpr int kQuads = 1, kMinBlocks = 0;          // 0 = no bound (ptxas picks 80 registers, no spill)
     static __device__ __forceinline__ void st(uint4 *p, int stride, u32 x0, u32 x1, u32 x2, u32 end)
     { p[0] = make_uint4(x0, x1, x2, end); (void)stride; }
     static __device__ __forceinline__ void ld(const uint4 *p, int stride, u32 &x0, u32 &x1, u32 &x2, u32 &end)
     { const uint4 v = p[0]; x0 = v.x; x1 = v.y; x2 = v.z; end = v.w; (void)stride; }
+    static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &, u32 &x0, u32 &x1, u32 &x2) { x0 = a.x; x1 = a.y; x2 = a.z; }
 };
 template <> struct Ent<u64> {
-    static constexpr int kQuads = 2;
+    typedef u64 PT;
+    static constexpr int kQuads = 2, kMinBlocks = 0;
     static __device__ __forceinline__ void st(uint4 *p, int stride, u64 x0, u64 x1, u64 x2, u32 end)
     {
         p[0] = make_uint4((u32)x0, (u32)(x0 >> 32), (u32)x1, (u32)(x1 >> 32));
@@ -48,6 +57,22 @@ template <> struct Ent<u64> {
         const uint4 a = p[0], b = p[stride];
         x0 = (u64)a.y << 32 | a.x; x1 = (u64)a.w << 32 | a.z; x2 = (u64)b.y << 32 | b.x; end = b.z;
     }
+    static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &b, u64 &x0, u64 &x1, u64 &x2)
+    { x0 = (u64)a.y << 32 | a.x; x1 = (u64)a.w << 32 | a.z; x2 = (u64)b.y << 32 | b.x; }
+};
+struct Ent33 {
+    typedef u64 PT;
+#ifndef S3_MINB33
+#define S3_MINB33 6
+#endif
+    static constexpr int kQuads = 1, kMinBlocks = S3_MINB33;          // 92 registers unbounded; 80 (6 resident blocks per SM) measured faster
+    static __device__ __forceinline__ uint4 pack(u64 x0, u64 x1, u64 x2, u32 end)
+    { return make_uint4((u32)x0, (u32)x1, (u32)x2, end | (u32)(x0 >> 32) << 31 | ((u32)(x1 >> 32) & 1u) << 30 | ((u32)(x2 >> 32) & 1u) << 29); }
+    static __device__ __forceinline__ void unpack(const uint4 &v, u64 &x0, u64 &x1, u64 &x2, u32 &end)
+    { x0 = (u64)(v.w >> 31) << 32 | v.x; x1 = (u64)(v.w >> 30 & 1u) << 32 | v.y; x2 = (u64)(v.w >> 29 & 1u) << 32 | v.z; end = v.w & 0x1fffffffu; }
+    static __device__ __forceinline__ void st(uint4 *p, int stride, u64 x0, u64 x1, u64 x2, u32 end) { p[0] = pack(x0, x1, x2, end); (void)stride; }
+    static __device__ __forceinline__ void ld(const uint4 *p, int stride, u64 &x0, u64 &x1, u64 &x2, u32 &end) { unpack(p[0], x0, x1, x2, end); (void)stride; }
+    static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &, u64 &x0, u64 &x1, u64 &x2) { u32 e; unpack(a, x0, x1, x2, e); }
 };
 
 __device__ __forceinline__ void s3_emit(Intv *out, int &n_out, int cap_out, u64 x0, u64 x1, u64 x2, int start, int end)
@@ -92,11 +117,11 @@ __global__ void pack4_kernel(u8 *seq, const i64 *off, int n_reads, u32 *pk, int 
 
 // QGLOB: the read is too long to stage in shared memory (long reads): its 4-bit codes are fetched from the packed
 // copy in global memory instead (consecutive positions of a lane share a 32-byte sector, so these are L1 hits).
-template <class PT, int LCAP, bool SPLIT, bool QGLOB>                       // SPLIT: pass 3 ran in smem_p3_kernel
-__global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
+template <class E, int LCAP, bool SPLIT, bool QGLOB>                        // SPLIT: pass 3 ran in smem_p3_kernel
+__global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(s3_raw);
-    typedef Ent<PT> E;
+    typedef typename E::PT PT;
     constexpr int EQ = E::kQuads;
     uint4 *L = (uint4 *)s3_raw + threadIdx.x;                            // slot s: L[s * EQ * S3_THREADS]
     u32 *Q = (u32 *)((uint4 *)s3_raw + LCAP * EQ * S3_THREADS) + threadIdx.x;   // word w: Q[w * S3_THREADS]
@@ -167,8 +192,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
         // ------------------------------------------------------------ the single gather site: consume the sectors
         PT n0, n1, n2; int two;
         if (ptab) {                                                         // table entry: the child's bi-interval itself
-            if (sizeof(PT) == 4) { n0 = (PT)Bk.cnt.x; n1 = (PT)Bk.cnt.y; n2 = (PT)Bk.cnt.z; }
-            else { n0 = (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x); n1 = (PT)((u64)Bk.cnt.w << 32 | Bk.cnt.z); n2 = (PT)((u64)Bk.pl.y << 32 | Bk.pl.x); }
+            E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
             two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
         } else occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
         ++n_ext; n_two += two;
@@ -347,11 +371,12 @@ __global__ void __launch_bounds__(S3_THREADS) smem_fast3_kernel(SmemParams P)
 // Third seeding pass on its own (bwamem.c:167-182 around bwt_seed_strategy1, bwt.c:358-379): forward-only sweeps that
 // restart right after every seed, so every lane runs the same short loop -- no lists, no backward phase.  One read per
 // lane (persistent), requests issued at the bottom of the loop and consumed at the top like in the main kernel.
-template <class PT, bool QGLOB>
+template <class E, bool QGLOB>
 __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(p3_raw);
-    constexpr int EQ = Ent<PT>::kQuads;
+    typedef typename E::PT PT;
+    constexpr int EQ = E::kQuads;
     u32 *Q = (u32 *)p3_raw + threadIdx.x;                                   // word w: Q[w * S3_THREADS]
     const u32 *Qg = P.pk;
     const DevIndex &ix = P.ix;
@@ -370,8 +395,7 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
         if (pending) {
             PT n0, n1, n2; int two;
             if (ptab) {
-                if (sizeof(PT) == 4) { n0 = (PT)Bk.cnt.x; n1 = (PT)Bk.cnt.y; n2 = (PT)Bk.cnt.z; }
-                else { n0 = (PT)((u64)Bk.cnt.y << 32 | Bk.cnt.x); n1 = (PT)((u64)Bk.cnt.w << 32 | Bk.cnt.z); n2 = (PT)((u64)Bk.pl.y << 32 | Bk.pl.x); }
+                E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
                 two = occ32_two_ref<PT>(ix, k0, k1, kk2, 0);
             } else occ32_finish<PT>(ix, k0, k1, kk2, 0, c, Bk, Bl, n0, n1, n2, two);
             ++n_ext; n_two += two;
@@ -435,27 +459,28 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
 }
 
-template <class PT, bool QGLOB>
+template <class E, bool QGLOB>
 static int launch_p3_t(const SmemParams &p, int n_sms, cudaStream_t st)
 {
     const size_t smem = QGLOB ? 0 : (size_t)p.pk_stride * 4 * S3_THREADS;
     int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute((smem_p3_kernel<PT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((smem_p3_kernel<E, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     int occ = 0;                                                            // resident blocks per SM (registers + shared memory)
-    B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (smem_p3_kernel<PT, QGLOB>), S3_THREADS, smem));
+    B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (smem_p3_kernel<E, QGLOB>), S3_THREADS, smem));
     if (occ > 0) per_sm = std::min(per_sm, occ);
 #endif
     const int grid = std::max(1, std::min((p.n_reads + S3_THREADS - 1) / S3_THREADS, n_sms * per_sm));
-    B200_LAUNCH((smem_p3_kernel<PT, QGLOB>), grid, S3_THREADS, smem, st, p);
+    B200_LAUNCH((smem_p3_kernel<E, QGLOB>), grid, S3_THREADS, smem, st, p);
     B200_CHECK(cudaGetLastError());
     return 0;
 }
 
+// wide: 0 = 32-bit positions, 1 = 64-bit positions with two-quad records, 2 = 64-bit positions < 2^33 with packed records
 int launch_smem_p3(const SmemParams &p, int n_sms, int wide, int qglob, cudaStream_t st)
 {
-    if (qglob) return wide ? launch_p3_t<u64, true>(p, n_sms, st) : launch_p3_t<u32, true>(p, n_sms, st);
-    return wide ? launch_p3_t<u64, false>(p, n_sms, st) : launch_p3_t<u32, false>(p, n_sms, st);
+    if (qglob) return wide == 2 ? launch_p3_t<Ent33, true>(p, n_sms, st) : wide ? launch_p3_t<Ent<u64>, true>(p, n_sms, st) : launch_p3_t<Ent<u32>, true>(p, n_sms, st);
+    return wide == 2 ? launch_p3_t<Ent33, false>(p, n_sms, st) : wide ? launch_p3_t<Ent<u64>, false>(p, n_sms, st) : launch_p3_t<Ent<u32>, false>(p, n_sms, st);
 }
 
 int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cudaStream_t st)
@@ -468,40 +493,36 @@ int launch_pack4(u8 *seq, const i64 *off, int n_reads, u32 *pk, int stride, cuda
 
 size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)             // pk_stride = 0: read not staged (QGLOB)
 {
-    return (size_t)lcap * (wide ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
+    return (size_t)lcap * (wide == 1 ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
 }
 
-template <class PT, int LCAP, bool SPLIT, bool QGLOB>
+template <class E, int LCAP, bool SPLIT, bool QGLOB>
 static int launch_fast3_ts(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
 {
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute((smem_fast3_kernel<PT, LCAP, SPLIT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
 #endif
-    B200_LAUNCH((smem_fast3_kernel<PT, LCAP, SPLIT, QGLOB>), grid, S3_THREADS, smem, st, p);
+    B200_LAUNCH((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB>), grid, S3_THREADS, smem, st, p);
     B200_CHECK(cudaGetLastError());
     return 0;
 }
 
-template <class PT, int LCAP>
-static int launch_fast3_t(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
+template <class E>
+static int launch_fast3_e(const SmemParams &p, int grid, int wide, int lcap, int qglob, cudaStream_t st)
 {
-    return p.split_p3 ? launch_fast3_ts<PT, LCAP, true, false>(p, grid, smem, st) : launch_fast3_ts<PT, LCAP, false, false>(p, grid, smem, st);
+    if (qglob) {                                                            // long reads: lcap 16, read in global memory
+        const size_t smem = smem_fast3_bytes(wide, 16, 0);
+        return p.split_p3 ? launch_fast3_ts<E, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, true>(p, grid, smem, st);
+    }
+    const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
+    if (lcap == 8) return p.split_p3 ? launch_fast3_ts<E, 8, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 8, false, false>(p, grid, smem, st);
+    if (lcap == 12) return p.split_p3 ? launch_fast3_ts<E, 12, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 12, false, false>(p, grid, smem, st);
+    return p.split_p3 ? launch_fast3_ts<E, 16, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, false>(p, grid, smem, st);
 }
 
 int launch_smem_fast3(const SmemParams &p, int grid, int wide, int lcap, int qglob, cudaStream_t st)
 {
-    if (qglob) {                                                            // long reads: lcap 16, read in global memory
-        const size_t smem = smem_fast3_bytes(wide, 16, 0);
-        if (wide) return p.split_p3 ? launch_fast3_ts<u64, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<u64, 16, false, true>(p, grid, smem, st);
-        return p.split_p3 ? launch_fast3_ts<u32, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<u32, 16, false, true>(p, grid, smem, st);
-    }
-    const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
-    if (wide) {
-        if (lcap == 8) return launch_fast3_t<u64, 8>(p, grid, smem, st);
-        if (lcap == 12) return launch_fast3_t<u64, 12>(p, grid, smem, st);
-        return launch_fast3_t<u64, 16>(p, grid, smem, st);
-    }
-    if (lcap == 8) return launch_fast3_t<u32, 8>(p, grid, smem, st);
-    if (lcap == 12) return launch_fast3_t<u32, 12>(p, grid, smem, st);
-    return launch_fast3_t<u32, 16>(p, grid, smem, st);
+    if (wide == 2) return launch_fast3_e<Ent33>(p, grid, wide, lcap, qglob, st);
+    if (wide) return launch_fast3_e<Ent<u64> >(p, grid, wide, lcap, qglob, st);
+    return launch_fast3_e<Ent<u32> >(p, grid, wide, lcap, qglob, st);
 }

@@ -17,6 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PRODUCT_SO = os.path.join(HERE, "libbwamem_b200.so")
 
 IDX_FULL_SA = 0x1
+E_FAIL, E_CAPACITY = -(1 << 63) + 1, -(1 << 63) + 2      # B200_E_FAIL / B200_E_CAPACITY (include/bwamem_b200.h)
 
 _SYMBOLS = [
     "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
@@ -350,7 +351,7 @@ class Context:
                                             C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
             if tot >= 0:
                 return out[:tot], cnt[:n]
-            if -tot > cap:
+            if tot > E_CAPACITY and -tot > cap:
                 cap = int(-tot)
                 continue
             self._chk(tot, "align")
@@ -410,7 +411,7 @@ class Context:
                                                   _p(seqs, C.c_uint8), None if quals is None else _p(quals, C.c_uint8), _p(off, C.c_int64),
                                                   None, C.c_int(n_threads), C.c_int(sub_reads), C.c_int64(cap), C.c_void_p(sam.ctypes.data),
                                                   _p(soff, C.c_int64))
-            if rc < -1:
+            if E_CAPACITY < rc < 0:
                 cap = int(-rc) + 64
                 continue
             self._chk(rc, "align_sam_se")
@@ -473,6 +474,8 @@ class Context:
         out = np.zeros(cap, dtype=ALNREG_DTYPE)
         cnt = np.zeros(max(n_reads, 1), dtype=np.int32)
         tot = self.lib.b200_batch_download(self.h, C.c_int64(cap), C.c_void_p(out.ctypes.data), _p(cnt, C.c_int32))
+        if tot <= E_CAPACITY:
+            self._chk(tot, "batch_download")
         if tot < 0:
             return None, int(-tot)
         return out[:tot], cnt[:n_reads]

@@ -51,6 +51,15 @@ def align_sharded(ctx, opt, seqs: np.ndarray, off: np.ndarray, dist=None, pestat
     world = dist.get_world_size() if dist is not None else 1
     n = len(off) - 1
     pe = bool(opt.flag & MEM_F_PE)
+    if pe and not (opt.flag & 0x20):                    # rank 0 needs pestat_fn; every rank learns of a missing one BEFORE any gather
+        missing = int(rank == 0 and pestat_fn is None)
+        if world > 1:
+            import torch
+            t = torch.tensor([missing], dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            missing = int(t[0])
+        if missing:
+            raise ValueError("paired-end batches need the host program's mem_pestat (pestat_fn) on rank 0")
     lo, hi = block_bounds(n, world, pe)[rank]
     my_off = np.ascontiguousarray(off[lo: hi + 1])
     ctx.batch_upload(seqs, my_off)
@@ -77,8 +86,6 @@ def align_sharded(ctx, opt, seqs: np.ndarray, off: np.ndarray, dist=None, pestat
     regs, cnt = download()
     if not pe or (opt.flag & 0x20):                     # MEM_F_NO_RESCUE
         return gather(regs, cnt)
-    if rank == 0 and pestat_fn is None:
-        raise ValueError("paired-end batches need the host program's mem_pestat (pestat_fn)")
     all_regs, all_cnt = gather(regs, cnt)
     pes = np.zeros(4, dtype=PESTAT_DTYPE)
     if rank == 0:

@@ -135,11 +135,19 @@ typedef struct { int score; int te, qe; int score2, te2; int tb, qb; } kswr_t;
  * ===================================================================================== */
 typedef struct b200_ctx b200_ctx_t;
 
+/* Error returns of the calls whose non-negative result is a COUNT and whose small negative results mean "-(needed)":
+ * b200_align_batch, b200_batch_download, b200_align_sam_se_batch.  Anything <= B200_E_CAPACITY is an error (message in
+ * b200_last_error()), never a count. */
+#define B200_E_FAIL      (INT64_MIN + 1)   /* CUDA error, missing index, out of memory ... */
+#define B200_E_CAPACITY  (INT64_MIN + 2)   /* an internal capacity was exceeded and re-running with the reported need did not help */
+#define B200_IS_ERROR(rc) ((int64_t)(rc) <= B200_E_CAPACITY)
+
 b200_ctx_t *b200_ctx_create(int device);
 void        b200_ctx_destroy(b200_ctx_t *ctx);
 const char *b200_last_error(void);
 /* tunables: "chunk_reads" (reads per pipeline chunk), "smem_lcap" (shared-memory list entries per read in the
- * seeding kernel; longer lists take the general kernel), "cap_intv" (interval slots per read; 0 = auto) */
+ * seeding kernel; longer lists take the general kernel), "cap_intv" (interval slots per read; 0 = auto; a chunk that
+ * needs more is re-run with the reported need unless "cap_retry" is 0, in which case the call fails) */
 int         b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value);
 /* flags for b200_index_upload */
 #define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device */
@@ -219,7 +227,7 @@ int64_t b200_reg2sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads
  * b200_batch_reg2sam_se (worker2 on the resident regions) and b200_sam_se_format (n_threads host threads), and the text of
  * sub-batch k is written while the device works on sub-batch k+1 (two sets of page-locked record buffers owned by the
  * context).  Arguments as in the three calls; names / comments / sam_off are indexed by read.  Returns the number of
- * bytes written, -(needed) when cap is too small (nothing useful in sam), -1 on error. */
+ * bytes written, -(needed) when cap is too small (nothing useful in sam), B200_E_FAIL / B200_E_CAPACITY on error. */
 int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, const char *const *ann_names, const char *const *ann_annos,
                                 int n_reads, int64_t n_processed, const char *const *names, const char *const *comments,
                                 const uint8_t *seqs, const uint8_t *quals, const int64_t *off, const char *rg_id, int n_threads,
@@ -322,7 +330,8 @@ int b200_ksw_align2_batch(b200_ctx_t *ctx, int64_t n, const int32_t *qlen, const
 /* mem_align1_core (bwamem.c:1061) for a batch = worker1 of mem_process_seqs (bwamem.c:1183):
  * seeding -> chaining -> filtering -> extension -> mem_sort_dedup_patch.  Reads may be ASCII or nt4.
  * out_regs holds cap records; read r's regions are the next out_n[r] records in read order.
- * Returns the total number of regions, or -(needed) if cap is too small. */
+ * Returns the total number of regions, or -(needed) if cap is too small (out_n is filled either way), or
+ * B200_E_FAIL / B200_E_CAPACITY on error (test with B200_IS_ERROR before negating). */
 int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs,
                          const int64_t *off, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n);
 

@@ -124,3 +124,33 @@ def test_scalar_smem1a_and_align1(backend):
         assert got == regs[k:k + nreg[i]].tobytes()
         k += int(nreg[i])
         C.CDLL(None).free(C.c_void_p(v.a))
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_scalar_shims_from_several_threads():
+    """The reference's primitives are re-entrant and called from kt_for workers; the same-name shims serialise per context."""
+    import threading
+    rl = cm.reflib()
+    lib = cm.backend_lib("cuda")
+    opt = abi.default_opt()
+    rng = np.random.default_rng(5)
+    n = 64
+    ql = rng.integers(20, 120, size=n).astype(np.int32); tl = (ql + rng.integers(0, 40, size=n)).astype(np.int32)
+    qoff = np.concatenate([[0], np.cumsum(ql)[:-1]]).astype(np.int64); toff = np.concatenate([[0], np.cumsum(tl)[:-1]]).astype(np.int64)
+    q = rng.integers(0, 4, size=int(ql.sum()), dtype=np.uint8); t = rng.integers(0, 4, size=int(tl.sum()), dtype=np.uint8)
+    for i in range(n):
+        m = min(ql[i], tl[i]); t[toff[i]:toff[i] + m] = q[qoff[i]:qoff[i] + m]
+    t[rng.random(len(t)) < 0.05] = 0
+    w = np.full(n, 50, np.int32); h0 = rng.integers(10, 60, size=n).astype(np.int32)
+    exp = rl.ksw_extend2(ql, qoff, q, tl, toff, t, opt, w, 5, 100, h0)
+    got = np.zeros(n, dtype=np.int64)
+
+    def work(lo, hi):
+        for i in range(lo, hi):
+            qi = np.ascontiguousarray(q[qoff[i]:qoff[i] + ql[i]]); ti = np.ascontiguousarray(t[toff[i]:toff[i] + tl[i]])
+            got[i] = lib.ksw_extend2(int(ql[i]), _u8p(qi), int(tl[i]), _u8p(ti), 5, opt.mat, opt.o_del, opt.e_del, opt.o_ins,
+                                     opt.e_ins, int(w[i]), 5, 100, int(h0[i]), None, None, None, None, None)
+    th = [threading.Thread(target=work, args=(k * 16, k * 16 + 16)) for k in range(4)]
+    [x.start() for x in th]; [x.join() for x in th]
+    assert np.array_equal(got, exp[:, 0])

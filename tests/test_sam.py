@@ -107,6 +107,9 @@ def test_sam_paired_end(backend, damage):
     got = _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names)
     assert got == exp
     assert exp.count(b"\n") >= 2 * npairs
+    opt.flag |= 0x800 | 0x200                               # -5 -Y on pairs (Hi-C usage): mem_sam_pe reorders itself (bwamem_pair.c:305-307)
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0)
+    assert _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names) == exp
 
 
 @needs_ref

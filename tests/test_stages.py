@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import common as cm
-from bwa_mem_gpu_b200 import abi
+from bwa_mem_gpu_b200 import abi, lib as L
 
 BACKENDS = [pytest.param("emu", id="emu"), pytest.param("cuda", id="cuda", marks=pytest.mark.gpu)]
 needs_ref = pytest.mark.skipif(not cm.have_ref(), reason="oracle/_ref not built")
@@ -407,8 +407,9 @@ def test_align_long_reads(backend):
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("tune", [{"force_wide": 1}, {"force_wide": 1, "kmer_k": 0}, {"kmer_k": 0}, {"kmer_k": 6}, {"kmer_k": 12},
-                                  {"smem_path": 3}, {"smem_path": 3, "force_wide": 1}, {"smem_path": 3, "split_p3": 0}])
+@pytest.mark.parametrize("tune", [{"force_wide": 1}, {"force_wide": 1, "kmer_k": 0}, {"force_wide": 2}, {"force_wide": 2, "kmer_k": 0, "smem_lcap": 8},
+                                  {"kmer_k": 0}, {"kmer_k": 6}, {"kmer_k": 12},
+                                  {"smem_path": 3}, {"smem_path": 3, "force_wide": 1}, {"smem_path": 3, "force_wide": 2}, {"smem_path": 3, "split_p3": 0}])
 def test_seeding_variants(backend, tune):
     """The 64-bit-position templates of the seeding kernel (used when the doubled text reaches 2^32 rows) forced on a
     small genome, k-mer interval tables of other depths, and the long-read variant that fetches the read's codes from
@@ -593,3 +594,28 @@ def test_reg2sam_se_long_reads(backend):
     idx, ctx = cm.ref_index("small"), cm.context(backend, "small")
     seqs, off = _long_reads("small", _sizes(backend, 6, 200), seed=19)
     _check_reg2sam_se(idx, ctx, abi.default_opt(), seqs, off, n_processed=3, resident=backend != "emu")   # emulated long-read aligns are slow
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_interval_capacity_retry_and_error(backend):
+    """A chunk whose reads need more interval slots than they were given is re-run with the reported need (same result as
+    the reference); with cap_retry=0 the call fails -- in the reads -> SAM call too, which must not produce text."""
+    idx, ctx = cm.ref_index("rep"), cm.context(backend, "rep")
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for("rep", _sizes(backend, 300, 5000), seed=91)
+    r0, n0 = idx.align(opt, seqs, off, cap_per_read=512)
+    try:
+        ctx.tune("cap_intv", 1)
+        r1, n1 = ctx.align(opt, seqs, off)
+        assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
+        ctx.tune("cap_intv", 1)
+        ctx.tune("cap_retry", 0)
+        with pytest.raises(L.B200Error, match="interval capacity"):
+            ctx.align(opt, seqs, off)
+        names = [f"r{i}" for i in range(len(off) - 1)]
+        with pytest.raises(L.B200Error, match="interval capacity"):
+            ctx.align_sam_se(opt, ctx._host_index.names, names, seqs, off)
+    finally:
+        ctx.tune("cap_intv", 0)
+        ctx.tune("cap_retry", 1)
