@@ -114,6 +114,8 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
                        &ctx->d_pa, &ctx->d_pb, &ctx->d_pc, &ctx->d_pd, &ctx->d_pe, &ctx->d_pf, &ctx->d_pg, &ctx->d_ph };
     for (DevBuf *b : bufs) b->release();
     for (DevBuf &b : ctx->d_r2a) b.release();
+    for (DevBuf &b : ctx->d_sam) b.release();
+    for (cudaEvent_t &e : ctx->sam_ev) if (e) { cudaEventDestroy(e); e = nullptr; }
     if (ctx->st_h2d) cudaStreamDestroy(ctx->st_h2d);
     if (ctx->st_d2h) cudaStreamDestroy(ctx->st_d2h);
     cudaStreamDestroy(ctx->st);

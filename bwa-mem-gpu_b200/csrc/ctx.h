@@ -72,6 +72,8 @@ struct b200_ctx {
     DevBuf d_final, d_final_n;
     i64 total_regs = 0;
     unsigned long long stats[CNT_N] = {0};
+    DevBuf d_sam[16];                          // device SAM formatter / reads -> SAM driver (reads2sam.cu)
+    cudaEvent_t sam_ev[2] = { nullptr, nullptr };  // D2H copies of the two text buffers
     DevBuf d_r2a[18];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
     int r2a_small = 1;                         // reg2aln pass 1 with ring-sized H / E rows (tunable)
     int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
@@ -92,6 +94,16 @@ static inline int b200_wide_mode(const b200_ctx *ctx)
 
 // layout of d_ctl (all 8-byte slots)
 enum { CTL_WORK = 0, CTL_OVF = 1, CTL_OVF2 = 2, CTL_ARENA_USED = 3, CTL_TOTAL = 4, CTL_RETRY = 5, CTL_WORK2 = 6, CTL_STATS = 8, CTL_SLOTS = 8 + CNT_N };
+
+// worker2 on the resident batch with the results LEFT on the device: `fn` is called once per chunk of whole reads while
+// the chunk's records are valid (they are overwritten by the next chunk); reg2aln.cu
+struct R2AChunk {
+    int r_lo, r_hi; i64 g0; int n;              // reads r_lo .. r_hi of the batch = regions g0 .. g0 + n
+    const mem_alnreg_t *regs; const b200_aln_t *aln; const b200_sel_t *sel; const u32 *cig; const char *md; i64 cig_base, md_base;
+    const i64 *d_roff;                          // n_reads + 1 region offsets of the batch, on the device
+};
+typedef int (*r2a_chunk_fn)(void *user, const R2AChunk &c);
+int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user);
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
 int b200_index_finish(b200_ctx *ctx, int flags);

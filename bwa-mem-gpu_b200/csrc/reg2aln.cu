@@ -360,9 +360,10 @@ __global__ void r2a_gather_kernel(b200_aln_t *aln, int n, const u32 *cig, int ci
 static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
                             const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
                             uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2],
-                            mem_alnreg_t *regs_out, b200_sel_t *out_sel, int64_t n_processed)
+                            mem_alnreg_t *regs_out, b200_sel_t *out_sel, int64_t n_processed,
+                            r2a_chunk_fn sink = nullptr, void *sink_user = nullptr)
 {
-    const bool finalize = out_sel != nullptr;
+    const bool finalize = out_sel != nullptr || sink != nullptr;
     const bool resident = regs == nullptr;                 // reads and regions are those of the batch the context just aligned
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
     if (resident) {
@@ -377,6 +378,15 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     const i64 n_regs = roff[n_reads];
     if (resident && n_regs != ctx->total_regs) { b200_set_error("region counts do not match the resident batch"); return -1; }
     if (totals) totals[0] = totals[1] = 0;
+    if (n_regs == 0 && sink) {                             // nothing aligned: the consumer still sees every read (unmapped records)
+        DevBuf &zr = ctx->d_r2a[14];
+        if (zr.ensure(((size_t)n_reads + 1) * 8)) return -1;
+        B200_CHECK(cudaMemsetAsync(zr.p, 0, ((size_t)n_reads + 1) * 8, st));
+        R2AChunk c;
+        memset(&c, 0, sizeof(c));
+        c.r_hi = n_reads; c.d_roff = zr.as<i64>();
+        return sink(sink_user, c) ? -1 : 0;
+    }
     if (n_regs == 0) return 0;
     if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
     std::vector<i32> reg_read((size_t)n_regs);
@@ -519,6 +529,16 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             b200_set_error("reg2aln: per-region %s capacity exceeded", (int)ovf == 3 ? "log table" : (int)ovf == 2 ? "traceback" : "CIGAR/MD");
             return -1;
         }
+        if (sink) {                                        // results stay on the device: the consumer runs on this chunk now
+            R2AChunk c;
+            c.r_lo = r_lo; c.r_hi = r_hi; c.g0 = g0; c.n = n; c.regs = d_regs.as<mem_alnreg_t>(); c.aln = d_aln.as<b200_aln_t>();
+            c.sel = d_sel.as<b200_sel_t>(); c.cig = d_pool_c.as<u32>(); c.md = d_pool_m.as<char>(); c.cig_base = cig_total; c.md_base = md_total;
+            c.d_roff = d_roff.as<i64>();
+            if (sink(sink_user, c)) return -1;
+            cig_total += nc; md_total += nm;
+            g0 += n; r_lo = r_hi;
+            continue;
+        }
         B200_CHECK(cudaMemcpyAsync(out_aln + g0, d_aln.p, (size_t)n * sizeof(b200_aln_t), cudaMemcpyDeviceToHost, st));
         if (finalize) {
             B200_CHECK(cudaMemcpyAsync(out_sel + g0, d_sel.p, (size_t)n * sizeof(b200_sel_t), cudaMemcpyDeviceToHost, st));
@@ -567,4 +587,10 @@ extern "C" int64_t b200_batch_reg2sam_se(b200_ctx_t *ctx, const mem_opt_t *opt, 
 {
     if (!out_sel || !cnt) { b200_set_error("b200_batch_reg2sam_se: cnt and out_sel are required"); return -1; }
     return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, regs_out, out_sel, n_processed);
+}
+
+int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user)
+{
+    if (!fn || !cnt) { b200_set_error("b200_batch_reg2sam_dev: cnt and fn are required"); return -1; }
+    return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, nullptr, n_processed, fn, user);
 }

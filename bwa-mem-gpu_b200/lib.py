@@ -26,7 +26,7 @@ _SYMBOLS = [
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_align_sam_se_batch", "b200_host_alloc", "b200_host_free", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2",
-    "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
+    "b200_reads_to_sam", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -57,6 +57,7 @@ def load(path: str | None = None) -> C.CDLL:
     lib.b200_reg2sam_se_batch.restype = C.c_int64
     lib.b200_sam_se_format.restype = C.c_int64
     lib.b200_align_sam_se_batch.restype = C.c_int64
+    lib.b200_reads_to_sam.restype = C.c_int64
     lib.b200_host_alloc.restype = C.c_void_p
     lib.b200_host_alloc.argtypes = [C.c_size_t]
     lib.b200_host_free.argtypes = [C.c_void_p]
@@ -115,6 +116,67 @@ class B200Error(RuntimeError):
     pass
 
 
+class ReadsT(C.Structure):          # b200_reads_t
+    _fields_ = [("n_reads", C.c_int64), ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("qual", C.c_void_p),
+                ("name", C.c_void_p), ("name_off", C.c_void_p), ("comment", C.c_void_p), ("comment_off", C.c_void_p)]
+
+
+def flat_strings(strs):
+    """list of str / bytes -> (uint8 array, int64 offsets) as b200_reads_t wants names and comments."""
+    bs = [x if isinstance(x, bytes) else x.encode() for x in strs]
+    off = np.zeros(len(bs) + 1, dtype=np.int64)
+    np.cumsum([len(b) for b in bs], out=off[1:])
+    return np.frombuffer(b"".join(bs) + b"\0", dtype=np.uint8), off
+
+
+def numbered_names(prefix: bytes, first: int, n: int):
+    """Names prefix + decimal(first + i), i < n, as (flat uint8 array, int64 offsets), vectorised (10^8 names in seconds)."""
+    idx = np.arange(first, first + n, dtype=np.int64)
+    nd = np.ones(n, dtype=np.int64)
+    for k in range(1, 19):
+        nd += idx >= 10 ** k
+    ln = nd + len(prefix)
+    off = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(ln, out=off[1:])
+    flat = np.empty(int(off[n]) + 1, dtype=np.uint8)
+    for j, ch in enumerate(prefix):
+        flat[off[:-1] + j] = ch
+    for d in range(1, int(nd.max()) + 1 if n else 1):          # digit d counted from the right
+        m = nd >= d
+        flat[off[1:][m] - d] = 48 + (idx[m] // 10 ** (d - 1)) % 10
+    return flat, off
+
+
+def reads_to_sam(ctxs, opt, ann_names, seqs, off, names_flat, name_off, quals=None, comments=None, n_processed=0, rg=None,
+                 sub_reads=0, sam=None, want_off=True):
+    """b200_reads_to_sam over the contexts `ctxs` (one per device).  Returns (SAM bytes as a numpy view, offsets, stats)."""
+    lib = ctxs[0].lib
+    n = len(off) - 1
+    R = ReadsT()
+    R.n_reads = n
+    R.seq = seqs.ctypes.data; R.seq_off = off.ctypes.data
+    R.qual = quals.ctypes.data if quals is not None else None
+    R.name = names_flat.ctypes.data; R.name_off = name_off.ctypes.data
+    if comments is not None:
+        cf, co = comments
+        R.comment = cf.ctypes.data; R.comment_off = co.ctypes.data
+    a_names = (C.c_char_p * max(1, len(ann_names)))(*[s.encode() for s in ann_names])
+    hs = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    soff = np.zeros(n + 1, dtype=np.int64) if want_off else None
+    stats = (C.c_double * 8)()
+    if sam is None:
+        sam = np.zeros(max(1 << 16, int(off[-1] - off[0]) * 2 + 300 * n), dtype=np.uint8)
+    while True:
+        rc = lib.b200_reads_to_sam(hs, len(ctxs), C.byref(opt), a_names, None, C.byref(R), C.c_int64(n_processed), None,
+                                   rg.encode() if rg else None, C.c_int(sub_reads), C.c_int64(len(sam)), C.c_void_p(sam.ctypes.data),
+                                   C.c_void_p(soff.ctypes.data) if want_off else None, stats)
+        if E_CAPACITY < rc < 0:
+            sam = np.zeros(int(-rc) + 64, dtype=np.uint8)
+            continue
+        ctxs[0]._chk(rc, "reads_to_sam")
+        return sam[:rc], soff, list(stats)
+
+
 def pack_pac(contigs):
     """2-bit forward reference in the layout of the reference's .pac (bntseq.c:230: base i in byte i>>2, bits (~i&3)*2)."""
     l_pac = int(sum(len(c) for c in contigs))
@@ -144,10 +206,15 @@ def pack_pac(contigs):
 class DeviceBuiltIndex:
     """Host-side view of an index built on the device by Context.build_index_device (same attributes as HostIndex)."""
 
-    def __init__(self, ctx: "Context", contigs, names=None):
+    def __init__(self, ctx: "Context", contigs, names=None, pac=None, contig_lens=None):
         self.ctx = ctx
-        self._pac, self.l_pac = pack_pac(contigs)
-        lens = np.array([len(c) for c in contigs], dtype=np.int64)
+        if pac is not None:                                   # already packed (bntseq.c:230 layout), contig lengths given
+            self._pac, self.l_pac = np.ascontiguousarray(pac, dtype=np.uint8), int(sum(contig_lens))
+            lens = np.array(contig_lens, dtype=np.int64)
+            contigs = contig_lens
+        else:
+            self._pac, self.l_pac = pack_pac(contigs)
+            lens = np.array([len(c) for c in contigs], dtype=np.int64)
         self.ann_off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
         self.ann_len = lens.astype(np.int32)
         self.ann_alt = np.zeros(len(contigs), dtype=np.int32)
@@ -243,6 +310,15 @@ class Context:
         """Index the genome ON the device (b200_index_build_device) and leave it resident.  Returns a DeviceBuiltIndex
         with the attributes of HostIndex (arrays are downloaded on demand)."""
         d = DeviceBuiltIndex(self, contigs, names)
+        self._chk(self.lib.b200_index_build_device(
+            self.h, _p(d._pac, C.c_uint8), C.c_int64(d.l_pac), C.c_int(len(d.ann_off)), _p(d.ann_off, C.c_int64),
+            _p(d.ann_len, C.c_int32), _p(d.ann_alt, C.c_int32), C.c_int(flags)), "index_build_device")
+        d._fill_info()
+        return d
+
+    def build_index_device_pac(self, pac, contig_lens, flags=IDX_FULL_SA, names=None):
+        """The same from the 2-bit packed forward reference (`.pac` layout) and the contig lengths."""
+        d = DeviceBuiltIndex(self, None, names, pac=pac, contig_lens=contig_lens)
         self._chk(self.lib.b200_index_build_device(
             self.h, _p(d._pac, C.c_uint8), C.c_int64(d.l_pac), C.c_int(len(d.ann_off)), _p(d.ann_off, C.c_int64),
             _p(d.ann_len, C.c_int32), _p(d.ann_alt, C.c_int32), C.c_int(flags)), "index_build_device")

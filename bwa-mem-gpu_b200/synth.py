@@ -183,3 +183,60 @@ def simulate_pairs(contigs, n_pairs: int, read_len: int = 150, ins_mean: float =
         seg = reads[r, w0:w0 + 100]
         seg[m] = (seg[m] + rng.integers(1, 4, size=int(m.sum()))) % 4
     return reads, {"contig": cid, "pos": pos, "isize": isz, "flip": flip}
+
+
+# ---- counter-based read simulator: read i depends on (seed, i) only, so any slice of a 10^8-read set can be produced
+# on its own -- by numpy on the host (the CPU arm's sample) or by torch on the GPU (the full set in seconds) -- with
+# identical results: everything is wrap-around int64 arithmetic, which both libraries implement the same way.
+_M1, _M2, _G = 0xBF58476D1CE4E5B9 - (1 << 64), 0x94D049BB133111EB - (1 << 64), 0x9E3779B97F4A7C15 - (1 << 64)
+
+
+def _lsr(x, s):                                   # logical shift right of int64
+    return (x >> s) & ((1 << (64 - s)) - 1)
+
+
+def _mix(x):                                      # splitmix64 finaliser on int64 arrays / tensors
+    z = x + _G
+    z = (z ^ _lsr(z, 30)) * _M1
+    z = (z ^ _lsr(z, 27)) * _M2
+    return z ^ _lsr(z, 31)
+
+
+def counter_reads(xp, genome, n_contigs: int, contig_len: int, i0: int, i1: int, read_len: int = 150, seed: int = 1004,
+                  sub_per_64k: int = 655, indel_per_64k_read: int = 1475):
+    """Reads i0 .. i1 of the fixed read set `seed` over a genome of n_contigs equal contigs (concatenated nt4 array /
+    tensor `genome`): uniform start inside a contig, strand 50/50, substitutions at sub_per_64k / 65536 per base (1 %),
+    one 1-bp insertion or deletion in indel_per_64k_read / 65536 of the reads (2.25 % = 0.015 % per base).
+    xp = numpy or torch; `genome` on the device the reads should be made on.  Returns (reads [n, read_len] uint8,
+    contig, pos, rev)."""
+    is_t = xp.__name__ == "torch"
+    ar = (lambda a, b: xp.arange(a, b, dtype=xp.int64, device=genome.device)) if is_t else (lambda a, b: xp.arange(a, b, dtype=xp.int64))
+    i = ar(i0, i1)
+    h = _mix(i * 2 + seed * 1000003)
+    h63 = h & ((1 << 63) - 1)
+    contig = h63 % n_contigs
+    pos = (h63 // n_contigs) % (contig_len - read_len - 8)
+    rev = _lsr(h, 63)
+    g = contig * contig_len + pos
+    h2 = _mix(i * 2 + 1 + seed * 1000003)
+    has_indel = (h2 & 0xffff) < indel_per_64k_read
+    is_ins = (_lsr(h2, 16) & 1) == 1
+    ip = 1 + (_lsr(h2, 17) & 0xffff) % (read_len - 2)                # event position 1 .. read_len - 2
+    ibase = _lsr(h2, 40) & 3
+    j = ar(0, read_len)[None, :]
+    # source offset of read base j: deletion skips source base ip, insertion repeats from ip on
+    dele = (has_indel & ~is_ins)[:, None]
+    inse = (has_indel & is_ins)[:, None]
+    shift = (dele & (j >= ip[:, None])) * 1 - (inse & (j > ip[:, None])) * 1
+    src = g[:, None] + j + shift
+    reads = genome[src] if not is_t else genome[src.reshape(-1)].reshape(src.shape)
+    reads = reads.to(xp.int64) if is_t else reads.astype(xp.int64)
+    at_ins = inse & (j == ip[:, None])
+    reads = xp.where(at_ins, ibase[:, None] + 0 * j, reads)
+    hb = _mix((i[:, None] * read_len + j) * 4 + 3 + seed * 7000003)
+    sub = (hb & 0xffff) < sub_per_64k
+    reads = xp.where(sub, (reads + 1 + (_lsr(hb, 16) & 0xffff) % 3) % 4, reads)
+    r2 = 3 - (xp.flip(reads, (1,)) if is_t else reads[:, ::-1])
+    reads = xp.where((rev == 1)[:, None], r2, reads)
+    reads = reads.to(xp.uint8) if is_t else reads.astype(xp.uint8)
+    return reads, contig, pos, rev

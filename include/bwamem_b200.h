@@ -232,6 +232,30 @@ int64_t b200_align_sam_se_batch(b200_ctx_t *ctx, const mem_opt_t *opt, const cha
                                 int n_reads, int64_t n_processed, const char *const *names, const char *const *comments,
                                 const uint8_t *seqs, const uint8_t *quals, const int64_t *off, const char *rg_id, int n_threads,
                                 int sub_reads, int64_t cap, char *sam, int64_t *sam_off);
+/* Reads in host memory -> SAM text in host memory on one or several devices, as ONE call, with NO host formatting:
+ * the per-GPU shard driver (csrc/reads2sam.cu).  The read set is cut into sub-batches of sub_reads reads (0 = about 2^20,
+ * their number a multiple of n_ctx), handed to the contexts' host threads from one counter; each sub-batch runs worker1 and
+ * worker2 (bwamem.c:1183-1213) and the SAM formatter (mem_aln2sam, bwamem.c:832-956; csrc/samdev.cu) on its device, and its
+ * text is copied straight to its place in `sam` -- input order, offsets fixed by a running prefix over the sub-batches'
+ * byte counts.  Every context must hold the same index (replicated FM-index); nothing moves between devices.
+ * reads: flat fields as a FASTQ reader produces them (b200_fastq_read); names / comments are not 0-terminated.
+ * `sam` should be page-locked (b200_host_alloc) for the copies to overlap the kernels.  sam_off (may be NULL): n_reads + 1
+ * offsets of the reads' records.  stats (may be NULL, 8 doubles): [0] wall seconds, [1..3] summed over the device threads:
+ * worker1, worker2 + formatter, waiting for placement; [4] sub-batches.
+ * Returns the bytes written, -(needed) when cap is too small, B200_E_FAIL / B200_E_CAPACITY on error.  Single-end reads;
+ * pes0 is reserved for the paired-end variant (b200_pairs_to_sam). */
+typedef struct {
+	int64_t n_reads;
+	const uint8_t *seq; const int64_t *seq_off;          /* bases (letters or nt4 codes), n_reads + 1 offsets */
+	const uint8_t *qual;                                  /* same offsets; NULL = no qualities ('*') */
+	const char *name; const int64_t *name_off;            /* n_reads + 1 offsets */
+	const char *comment; const int64_t *comment_off;      /* NULL = none; an empty slice = no comment for that read */
+} b200_reads_t;
+int64_t b200_reads_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const mem_opt_t *opt, const char *const *ann_names,
+                          const char *const *ann_annos, const b200_reads_t *reads, int64_t n_processed,
+                          const mem_pestat_t *pes0, const char *rg_id, int sub_reads, int64_t cap, char *sam,
+                          int64_t *sam_off, double *stats);
+
 /* Page-locked host memory (cudaHostAlloc) for callers that want the copies of the batched calls at full speed. */
 void *b200_host_alloc(size_t bytes);
 void b200_host_free(void *p);

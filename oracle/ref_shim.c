@@ -19,6 +19,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include <stdint.h>
 #include <zlib.h>
 #include "bwa.h"
@@ -365,6 +366,47 @@ int64_t ref_process_seqs(void *p, const void *opt_, int64_t n_processed, int n, 
 		for (i = 0; i < n; ++i) { size_t l = strlen(bs[i].sam); memcpy(o, bs[i].sam, l); o += l; }
 	}
 	for (i = 0; i < n; ++i) { free(bs[i].name); free(bs[i].seq); free(bs[i].qual); free(bs[i].sam); }
+	free(bs);
+	return tot <= cap ? tot : -tot;
+}
+
+/* the same with FASTQ comments (NUL-separated list, an empty string = no comment; may be NULL) and a read group id
+ * (bwa_rg_id, bwa.c:44; may be NULL) */
+extern char bwa_rg_id[256];
+static double ref_last_s = 0;
+/* wall seconds of the last mem_process_seqs call itself (what its own "[M::mem_process_seqs] ... real sec" line reports) */
+double ref_last_process_seqs_seconds(void) { return ref_last_s; }
+int64_t ref_process_seqs2(void *p, const void *opt_, int64_t n_processed, int n, const char *names, const char *comments,
+                          const uint8_t *seqs, const int64_t *off, const uint8_t *quals, const char *rg,
+                          const void *pes0, int64_t cap, char *out)
+{
+	bwaidx_t *idx = (bwaidx_t*)p; const mem_opt_t *opt = (const mem_opt_t*)opt_;
+	bseq1_t *bs = calloc(n, sizeof(bseq1_t));
+	const char *nm = names, *cm = comments; int64_t tot = 0; int i;
+	for (i = 0; i < n; ++i) {
+		int l = (int)(off[i+1] - off[i]);
+		bs[i].name = strdup(nm); nm += strlen(nm) + 1;
+		if (cm) { if (*cm) bs[i].comment = strdup(cm); cm += strlen(cm) + 1; }
+		bs[i].seq = malloc(l + 1); memcpy(bs[i].seq, seqs + off[i], l); bs[i].seq[l] = 0;
+		if (quals) { bs[i].qual = malloc(l + 1); memcpy(bs[i].qual, quals + off[i], l); bs[i].qual[l] = 0; }
+		bs[i].l_seq = l; bs[i].id = i;
+	}
+	memset(bwa_rg_id, 0, 256);
+	if (rg) strncpy(bwa_rg_id, rg, 255);
+	{
+		struct timespec t0, t1;
+		clock_gettime(CLOCK_MONOTONIC, &t0);
+		mem_process_seqs(opt, idx->bwt, idx->bns, idx->pac, n_processed, n, bs, (const mem_pestat_t*)pes0);
+		clock_gettime(CLOCK_MONOTONIC, &t1);
+		ref_last_s = (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+	}
+	memset(bwa_rg_id, 0, 256);
+	for (i = 0; i < n; ++i) tot += strlen(bs[i].sam);
+	if (tot <= cap) {
+		char *o = out;
+		for (i = 0; i < n; ++i) { size_t l = strlen(bs[i].sam); memcpy(o, bs[i].sam, l); o += l; }
+	}
+	for (i = 0; i < n; ++i) { free(bs[i].name); free(bs[i].comment); free(bs[i].seq); free(bs[i].qual); free(bs[i].sam); }
 	free(bs);
 	return tot <= cap ? tot : -tot;
 }

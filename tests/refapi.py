@@ -291,16 +291,20 @@ class RefIndex:
         assert tot >= 0
         return out[:tot].copy(), ocnt[:n], nsw.value
 
-    def process_seqs(self, opt: MemOpt, seqs, off, names=None, quals=None, n_processed=0, pes0=None):
+    def process_seqs(self, opt: MemOpt, seqs, off, names=None, quals=None, n_processed=0, pes0=None, comments=None, rg=None):
         n = len(off) - 1
         if names is None:
             names = [f"r{n_processed + i}" for i in range(n)]
         nm = b"\0".join(s.encode() for s in names) + b"\0"
+        cm = b"\0".join((c or "").encode() for c in comments) + b"\0" if comments is not None else None
         cap = int(off[-1]) * 6 + n * 512 + 4096
         buf = C.create_string_buffer(cap)
-        tot = self.lib.ref_process_seqs(self.h, C.byref(opt), C.c_int64(n_processed), C.c_int(n), nm,
-                                        _p(seqs, C.c_uint8), _p(off, C.c_int64),
-                                        _p(quals, C.c_uint8) if quals is not None else None,
-                                        C.byref(pes0) if pes0 is not None else None, C.c_int64(cap), buf)
+        self.lib.ref_process_seqs2.restype = C.c_int64
+        tot = self.lib.ref_process_seqs2(self.h, C.byref(opt), C.c_int64(n_processed), C.c_int(n), nm, cm,
+                                         _p(seqs, C.c_uint8), _p(off, C.c_int64),
+                                         _p(quals, C.c_uint8) if quals is not None else None, rg.encode() if rg else None,
+                                         C.byref(pes0) if pes0 is not None else None, C.c_int64(cap), buf)
         assert tot >= 0, f"SAM buffer too small ({-tot})"
+        self.lib.ref_last_process_seqs_seconds.restype = C.c_double
+        self.last_process_seqs_s = self.lib.ref_last_process_seqs_seconds()      # the mem_process_seqs call alone
         return buf.raw[:tot]

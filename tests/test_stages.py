@@ -543,6 +543,13 @@ def _check_reg2sam_se(idx, ctx, opt, seqs, off, n_processed=0, resident=True):
             assert x == y
         assert len(l0) == len(l1)
     assert soff[-1] == len(sam1) and sam1[soff[1]:].startswith(names[1].encode()) if len(names) > 1 else True
+    # the whole way on the device: worker1, worker2 and the device SAM formatter (samdev.cu) through b200_reads_to_sam
+    nf, no = L.flat_strings(names)
+    sam3, soff3, _ = L.reads_to_sam([ctx], opt, idx.anns()[3], seqs, off, nf, no, n_processed=n_processed, sub_reads=max(2, (len(off) - 1) // 3))
+    if sam3.tobytes() != sam1:
+        for x, y in zip(sam1.split(b"\n"), sam3.tobytes().split(b"\n")):
+            assert x == y
+    assert sam3.tobytes() == sam1 and np.array_equal(soff3, soff)
     if not resident:
         return r1, sel, aln, sam1
     # the same on the batch the context has just aligned (b200_batch_reg2sam_se: nothing uploaded), twice: the resident
