@@ -72,7 +72,7 @@ struct b200_ctx {
     DevBuf d_final, d_final_n;
     i64 total_regs = 0;
     unsigned long long stats[CNT_N] = {0};
-    DevBuf d_sam[16];                          // device SAM formatter / reads -> SAM driver (reads2sam.cu)
+    DevBuf d_sam[28];                          // device SAM formatter / reads -> SAM driver (reads2sam.cu)
     cudaEvent_t sam_ev[2] = { nullptr, nullptr };  // D2H copies of the two text buffers
     DevBuf d_r2a[18];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
     int r2a_small = 1;                         // reg2aln pass 1 with ring-sized H / E rows (tunable)
@@ -101,9 +101,14 @@ struct R2AChunk {
     int r_lo, r_hi; i64 g0; int n;              // reads r_lo .. r_hi of the batch = regions g0 .. g0 + n
     const mem_alnreg_t *regs; const b200_aln_t *aln; const b200_sel_t *sel; const u32 *cig; const char *md; i64 cig_base, md_base;
     const i64 *d_roff;                          // n_reads + 1 region offsets of the batch, on the device
+    const i32 *mate_reg, *read_flag;            // paired-end (else null): per read of the batch, see samdev.cuh
 };
 typedef int (*r2a_chunk_fn)(void *user, const R2AChunk &c);
-int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user);
+int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user,
+                               const mem_pestat_t *pes = nullptr);
+
+// per-pair summary for mem_pestat (finalize_pe.cuh): out[p] = 0, or (insert size << 2 | orientation) + 1
+int launch_pestat_pairs(const mem_opt_t *opt, i64 l_pac, const mem_alnreg_t *regs, const i64 *roff, int n_pairs, u64 *out, cudaStream_t st);
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
 int b200_index_finish(b200_ctx *ctx, int flags);

@@ -227,6 +227,47 @@ __device__ __forceinline__ int fin_pri_idx(double xa_ratio, const mem_alnreg_t *
     return -1;
 }
 
+// mem_gen_alt (bwamem_extra.c:124-170): which regions become XA entries, and of which record
+__device__ void fin_mark_xa(const mem_opt_t &opt, int n, const mem_alnreg_t *a, b200_sel_t *sel)
+{
+    const double xr = (double)opt.XA_drop_ratio;
+    for (int i = 0; i < n; ++i) {
+        const int pr = fin_pri_idx(xr, a, i);
+        if (pr < 0) continue;
+        int cnt = 0, has_alt = 0;
+        for (int j = 0; j < n; ++j)
+            if (fin_pri_idx(xr, a, j) == pr) { ++cnt; if (a[j].is_alt) has_alt = 1; }
+        if (cnt > opt.max_XA_hits_alt || (!has_alt && cnt > opt.max_XA_hits)) continue;
+        sel[i].kind |= 2; sel[i].xa_of = pr;           // kind 3: a record of its own as well (a primary-assembly hit under an ALT hit)
+    }
+}
+
+// mem_reg2sam's walk over one read's regions (bwamem.c:1024-1042): which become records, their MAPQ and flags
+__device__ void fin_reg2sam_walk(const FinParams &P, int n, const mem_alnreg_t *a, b200_sel_t *sel, int extra_flag, int *ovf)
+{
+    const mem_opt_t &opt = P.opt;
+    int l = 0, mapq0 = 0;
+    for (int k = 0; k < n; ++k) {
+        const mem_alnreg_t &p = a[k];
+        b200_sel_t s; s.kind = 0; s.mapq = 0; s.xa_of = -1; s.flag = 0;
+        bool keep = p.score >= opt.T;
+        if (keep && p.secondary >= 0 && (p.is_alt || !(opt.flag & MEM_F_ALL))) keep = false;
+        if (keep && p.secondary >= 0 && p.secondary < 0x7fffffff &&
+            (float)p.score < fin_fmul((float)a[p.secondary].score, opt.drop_ratio)) keep = false;
+        if (keep) {
+            s.kind = 1;
+            s.flag = extra_flag;
+            s.mapq = p.secondary < 0 ? fin_approx_mapq_se(P, p, ovf) : 0;                    // mem_reg2aln, bwamem.c:1150
+            if (l && p.secondary < 0) s.flag |= (opt.flag & MEM_F_NO_MULTI) ? 0x10000 : 0x800;
+            if (!(opt.flag & MEM_F_KEEP_SUPP_MAPQ) && l && !p.is_alt && s.mapq > mapq0) s.mapq = mapq0;
+            if (l == 0) mapq0 = s.mapq;
+            ++l;
+        }
+        sel[k] = s;
+    }
+    if (!(opt.flag & MEM_F_ALL)) fin_mark_xa(opt, n, a, sel);
+}
+
 __global__ void __launch_bounds__(128) finalize_se_kernel(FinParams P)
 {
     const mem_opt_t &opt = P.opt;
@@ -239,36 +280,7 @@ __global__ void __launch_bounds__(128) finalize_se_kernel(FinParams P)
         b200_sel_t *sel = P.sel + b;
         fin_mark_primary_se(opt, n, a, P.id0 + P.r0 + r);
         if (opt.flag & MEM_F_PRIMARY5) fin_reorder_primary5(opt.T, n, a);
-        int l = 0, mapq0 = 0;                          // mem_reg2sam's walk (bwamem.c:1024-1042)
-        for (int k = 0; k < n; ++k) {
-            const mem_alnreg_t &p = a[k];
-            b200_sel_t s; s.kind = 0; s.mapq = 0; s.xa_of = -1; s.flag = 0;
-            bool keep = p.score >= opt.T;
-            if (keep && p.secondary >= 0 && (p.is_alt || !(opt.flag & MEM_F_ALL))) keep = false;
-            if (keep && p.secondary >= 0 && p.secondary < 0x7fffffff &&
-                (float)p.score < fin_fmul((float)a[p.secondary].score, opt.drop_ratio)) keep = false;
-            if (keep) {
-                s.kind = 1;
-                s.mapq = p.secondary < 0 ? fin_approx_mapq_se(P, p, &ovf) : 0;                // mem_reg2aln, bwamem.c:1150
-                if (l && p.secondary < 0) s.flag |= (opt.flag & MEM_F_NO_MULTI) ? 0x10000 : 0x800;
-                if (!(opt.flag & MEM_F_KEEP_SUPP_MAPQ) && l && !p.is_alt && s.mapq > mapq0) s.mapq = mapq0;
-                if (l == 0) mapq0 = s.mapq;
-                ++l;
-            }
-            sel[k] = s;
-        }
-        if (!(opt.flag & MEM_F_ALL)) {                 // mem_gen_alt: which regions become XA entries, and of which record
-            const double xr = (double)opt.XA_drop_ratio;
-            for (int i = 0; i < n; ++i) {
-                const int pr = fin_pri_idx(xr, a, i);
-                if (pr < 0) continue;
-                int cnt = 0, has_alt = 0;
-                for (int j = 0; j < n; ++j)
-                    if (fin_pri_idx(xr, a, j) == pr) { ++cnt; if (a[j].is_alt) has_alt = 1; }
-                if (cnt > opt.max_XA_hits_alt || (!has_alt && cnt > opt.max_XA_hits)) continue;
-                sel[i].kind |= 2; sel[i].xa_of = pr;   // kind 3: a record of its own as well (a primary-assembly hit under an ALT hit)
-            }
-        }
+        fin_reg2sam_walk(P, n, a, sel, 0, &ovf);
     }
     if (ovf) atomicMax(P.overflow, ovf);
 }

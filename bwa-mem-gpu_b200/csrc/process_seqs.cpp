@@ -1,12 +1,12 @@
-// Drop-in mem_process_seqs (bwamem.h:69, bwamem.c:1215-1244): worker1 (mem_align1_core for every read,
-// bwamem.c:1183-1195) runs on the GPU through b200_align_batch, and so does the mate-rescue block of mem_sam_pe
-// (bwamem_pair.c:291-302, b200_batch_rescue); the rest stays the REFERENCE's own host code -- mem_pestat
-// (bwamem_pair.c:72), worker2 = mem_mark_primary_se / mem_reg2sam / mem_sam_pe with MEM_F_NO_RESCUE
-// (bwamem.c:1197-1213) -- which this library does not contain: those symbols are resolved from the host
-// program the library is linked into (weak references, or the global symbol scope when loaded dynamically).
-// Single-end batches do not need them: worker2 runs on the device (b200_reg2sam_se_batch) and the SAM text is written
-// by b200_sam_se_format; b200_process_seqs_host_worker2(1) switches back to the host program's functions.
-// Nothing here computes alignments on the CPU; if the host functions are missing the call fails loudly.
+// Drop-in mem_process_seqs (bwamem.h:69, bwamem.c:1215-1244).  By default the whole batch -- worker1 (mem_align1_core for
+// every read, bwamem.c:1183-1195), the batch's mem_pestat (bwamem_pair.c:72), mate rescue (:291-302), worker2 (mem_mark_primary_se,
+// mem_pair, the MAPQ arithmetic and flags of mem_sam_pe, mem_reg2aln, bwamem.c:1197-1213) and the SAM text (mem_aln2sam) -- runs
+// on the device(s) through b200_reads_to_sam (csrc/reads2sam.cu); no function of the host program is used.
+// b200_process_seqs_host_worker2(1) selects the older route, kept for single-end batches of long reads (the device worker2 maps one
+// region to one lane) and as a cross-check: worker1 and mate rescue on the device, then the REFERENCE's own host functions
+// (mem_pestat, mem_mark_primary_se / mem_reg2sam / mem_sam_pe with MEM_F_NO_RESCUE), which this library does not contain: those
+// symbols are resolved from the host program the library is linked into (weak references, or the global symbol scope).
+// Nothing here computes alignments on the CPU; if that route is selected and the host functions are missing the call fails loudly.
 #include <dlfcn.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -107,8 +107,8 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
                                       int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
 {
     const bool pe = (opt->flag & MEM_F_PE) != 0;
-    bool dev_worker2 = !pe && g_ps_host_worker2 <= 0;
-    if (dev_worker2 && g_ps_host_worker2 < 0) {
+    bool dev_worker2 = g_ps_host_worker2 <= 0;             // pairs too: mem_pestat / mem_pair / mem_sam_pe are csrc/reads2sam.cu + finalize_pe.cuh
+    if (dev_worker2 && g_ps_host_worker2 < 0 && !pe) {
         int mx = 0;
         for (int i = 0; i < n; ++i) mx = seqs[i].l_seq > mx ? seqs[i].l_seq : mx;
         const bool host_has = (mem_mark_primary_se || dlsym(RTLD_DEFAULT, "mem_mark_primary_se")) && (mem_reg2sam || dlsym(RTLD_DEFAULT, "mem_reg2sam"));
@@ -116,12 +116,12 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
     }
     mark_fn f_mark = dev_worker2 ? nullptr : (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
     reg2sam_fn f_reg2sam = dev_worker2 ? nullptr : (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
-    sam_pe_fn f_sam_pe = pe ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
+    sam_pe_fn f_sam_pe = (pe && !dev_worker2) ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;
     // -5: single-end batches reorder between marking and mem_reg2sam (bwamem.c:1205, mem_reorder_primary5 bwamem.c:988 is a
     // non-static function of the host program); mem_sam_pe applies it itself (bwamem_pair.c:305-307)
     reorder5_fn f_reorder5 = (!pe && !dev_worker2 && (opt->flag & MEM_F_PRIMARY5_))
                                  ? (reorder5_fn)host_symbol((void *)mem_reorder_primary5, "mem_reorder_primary5") : nullptr;
-    pestat_fn f_pestat = (pe && !pes0) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
+    pestat_fn f_pestat = (pe && !pes0 && !dev_worker2) ? (pestat_fn)host_symbol((void *)mem_pestat, "mem_pestat") : nullptr;
 
     if (g_ps_ctxs.empty() || (g_ps_bwt && g_ps_bwt != bwt)) {         // lazy contexts from the index identity
         g_ps_ctxs.clear();
@@ -150,38 +150,47 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         if (pe) { lo &= ~1; hi = d == G - 1 ? n : hi & ~1; }          // mates stay together
         shards[d].ctx = g_ps_ctxs[d]; shards[d].r0 = lo; shards[d].n = hi - lo;
     }
-    if (dev_worker2) {                                                // worker1 + worker2 (bwamem.c:1183-1207) for every read, on the device
+    if (dev_worker2) {                                                // worker1, mem_pestat, worker2 and the SAM text (bwamem.c:1183-1244) on the device(s)
         int n_qual = 0;
         for (int i = 0; i < n; ++i) n_qual += seqs[i].qual != nullptr;
         if (n_qual && n_qual != n) { fprintf(stderr, "[b200::mem_process_seqs] reads with and without qualities in one batch\n"); exit(1); }
         std::vector<uint8_t> qflat(n_qual ? (size_t)tot + 1 : 0);
-        std::vector<const char *> names((size_t)n + 1), comments((size_t)n + 1), ann_names((size_t)bns->n_seqs + 1), ann_annos((size_t)bns->n_seqs + 1);
+        std::vector<int64_t> name_off((size_t)n + 1, 0), com_off((size_t)n + 1, 0);
+        bool any_comment = false;
+        for (int i = 0; i < n; ++i) {
+            name_off[i + 1] = name_off[i] + (int64_t)strlen(seqs[i].name);
+            const size_t lc = seqs[i].comment ? strlen(seqs[i].comment) : 0;
+            com_off[i + 1] = com_off[i] + (int64_t)lc;
+            any_comment |= lc != 0;
+        }
+        std::vector<char> nflat((size_t)name_off[n] + 1), cflat((size_t)com_off[n] + 1);
         for (int i = 0; i < n; ++i) {
             if (n_qual) memcpy(qflat.data() + off[i], seqs[i].qual, (size_t)seqs[i].l_seq);
-            names[i] = seqs[i].name; comments[i] = seqs[i].comment;
+            memcpy(nflat.data() + name_off[i], seqs[i].name, (size_t)(name_off[i + 1] - name_off[i]));
+            if (com_off[i + 1] > com_off[i]) memcpy(cflat.data() + com_off[i], seqs[i].comment, (size_t)(com_off[i + 1] - com_off[i]));
         }
+        std::vector<const char *> ann_names((size_t)bns->n_seqs + 1), ann_annos((size_t)bns->n_seqs + 1);
         for (int i = 0; i < bns->n_seqs; ++i) { ann_names[i] = bns->anns[i].name; ann_annos[i] = bns->anns[i].anno; }
         const char *rg = (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
-        const int fmt_threads = std::max(1, (opt->n_threads > 0 ? opt->n_threads : 1) / G);
-        run_shards(shards, [&](Shard &sh) {                            // per device: align, finish and format, sub-batch by sub-batch
-            sh.sam_off.assign((size_t)sh.n + 1, 0);
-            sh.sam.resize((size_t)(tot / (n > 0 ? n : 1) + 160) * (size_t)sh.n + 4096);
-            for (;;) {
-                const int64_t rc = b200_align_sam_se_batch(sh.ctx, opt, ann_names.data(), ann_annos.data(), sh.n, n_processed + sh.r0,
-                                                           names.data() + sh.r0, comments.data() + sh.r0, flat.data(),
-                                                           n_qual ? qflat.data() : nullptr, off.data() + sh.r0, rg, fmt_threads, 0,
-                                                           (int64_t)sh.sam.size(), sh.sam.data(), sh.sam_off.data());
-                if (B200_IS_ERROR(rc)) { sh.err = b200_last_error(); return; }
-                if (rc < 0) { sh.sam.resize((size_t)-rc + 64); continue; }
-                break;
-            }
-            for (int i = 0; i < sh.n; ++i) {                           // seqs[i].sam: heap memory owned by the caller (bwamem.c:1054)
-                const size_t l = (size_t)(sh.sam_off[i + 1] - sh.sam_off[i]);
-                char *o = (char *)malloc(l + 1);
-                memcpy(o, sh.sam.data() + sh.sam_off[i], l); o[l] = 0;
-                seqs[sh.r0 + i].sam = o;
-            }
-        });
+        b200_reads_t R;
+        R.n_reads = n; R.seq = flat.data(); R.seq_off = off.data(); R.qual = n_qual ? qflat.data() : nullptr;
+        R.name = nflat.data(); R.name_off = name_off.data();
+        R.comment = any_comment ? cflat.data() : nullptr; R.comment_off = any_comment ? com_off.data() : nullptr;
+        std::vector<int64_t> sam_off((size_t)n + 1, 0);
+        std::vector<char> sam((size_t)(2 * tot + (int64_t)n * 200 + name_off[n] + com_off[n] + 4096));
+        for (;;) {
+            const int64_t rc = b200_reads_to_sam(g_ps_ctxs.data(), G, opt, ann_names.data(), ann_annos.data(), &R, n_processed, pes0, rg, 0,
+                                                 (int64_t)sam.size(), sam.data(), sam_off.data(), nullptr);
+            if (B200_IS_ERROR(rc)) { fprintf(stderr, "[b200::mem_process_seqs] %s\n", b200_last_error()); exit(1); }      // err_fatal style (bwamem_pair.c:386)
+            if (rc < 0) { sam.resize((size_t)-rc + 64); continue; }
+            break;
+        }
+        for (int i = 0; i < n; ++i) {                                 // seqs[i].sam: heap memory owned by the caller (bwamem.c:1054)
+            const size_t l = (size_t)(sam_off[i + 1] - sam_off[i]);
+            char *o = (char *)malloc(l + 1);
+            memcpy(o, sam.data() + sam_off[i], l); o[l] = 0;
+            seqs[i].sam = o;
+        }
         for (int i = 0; i < n; ++i)
             for (int j = 0; j < seqs[i].l_seq; ++j) seqs[i].seq[j] = (char)nt4_of((uint8_t)seqs[i].seq[j]);   // bwamem.c:1067-1068
         return;

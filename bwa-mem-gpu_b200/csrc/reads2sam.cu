@@ -18,6 +18,7 @@
 #include <string.h>
 #include <thread>
 #include <vector>
+#include <math.h>
 #include "samdev.cuh"        // after the standard headers: the emulator build redefines __noinline__
 
 extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes);
@@ -51,6 +52,12 @@ struct Job {                                               // one call
     i64 cap; char *sam; i64 *sam_off;
     Placer placer; std::atomic<int> next_sub{0};
     double t_align = 0, t_worker2 = 0, t_wait = 0; std::mutex tmu;
+    // paired-end: worker1 of every sub-batch first (phase A: regions saved on their device, per-pair insert sizes to the
+    // host), then mem_pestat over the whole call, then rescue + worker2 + text per sub-batch on the device that holds it
+    bool pe = false; mem_pestat_t pes[4];
+    std::vector<u64> isz;                                  // per pair: 0, or (insert size << 2 | orientation) + 1
+    struct Saved { int owner = -1; DevBuf regs, cnt; i64 total = 0; };
+    std::vector<Saved> saved;
 };
 
 struct Sub {                                               // one sub-batch on one device
@@ -89,6 +96,7 @@ int sam_chunk(void *user, const R2AChunk &c)
     SamDevParams P = S.P;
     P.r_lo = c.r_lo; P.n_reads = n; P.roff = c.d_roff; P.g0 = c.g0;
     P.sel = c.sel; P.aln = c.aln; P.cig = c.cig; P.md = c.md; P.cig_base = c.cig_base; P.md_base = c.md_base;
+    P.mate_reg = c.mate_reg; P.read_flag = c.read_flag;
     P.len = d_len.as<i32>(); P.pos = d_pos.as<i64>(); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
     if (launch_sam_count(P, ctx->n_sms, st)) return -1;
     if (launch_exclusive_scan(P.len, d_pos.as<i64>(), n, d_tmp.as<i64>(), st)) return -1;
@@ -132,7 +140,147 @@ int upload_slice(b200_ctx *ctx, const char *chars, const i64 *off, int r0, int n
     return 0;
 }
 
-void worker(b200_ctx *ctx, Job *job)
+// ---- paired-end, phase A: worker1 of this device's share of the sub-batches; regions stay on the device, the per-pair
+// summary mem_pestat needs (bwamem_pair.c:76-90) goes to the host
+void worker_pe_a(b200_ctx *ctx, int dev_index, Job *job)
+{
+    Placer &pl = job->placer;
+    auto die = [&]() { pl.fail(b200_last_error()); };
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { b200_set_error("cudaSetDevice(%d) failed", ctx->device); die(); return; }
+    const b200_reads_t &R = *job->reads;
+    double t_align = 0;
+    for (;;) {
+        const int j = job->next_sub.fetch_add(1);
+        if (j >= job->n_sub || pl.failed) break;
+        const int r0 = (int)((i64)j * job->sub), n = (int)std::min<i64>(job->sub, R.n_reads - r0);
+        const double t0 = now_s();
+        i32 *cnt = (i32 *)b200_ctx_pinned(ctx, 0, (size_t)n * 4 + 4);
+        if (!cnt) { die(); return; }
+        const i64 nr = b200_align_batch(ctx, job->opt, n, R.seq, R.seq_off + r0, 0, nullptr, cnt);
+        if (B200_IS_ERROR(nr) || nr > 0) { die(); return; }
+        Job::Saved &sv = job->saved[j];
+        sv.owner = dev_index; sv.total = ctx->total_regs;
+        cudaStream_t st = ctx->st;
+        const int n_pairs = n >> 1;
+        auto fail = [&](const char *what) { b200_set_error("paired-end phase A: %s", what); die(); };
+        if (sv.regs.ensure((size_t)(sv.total + 1) * sizeof(mem_alnreg_t)) || sv.cnt.ensure((size_t)n * 4 + 4) ||
+            ctx->d_pa.ensure(((size_t)n + 1) * 8) || ctx->d_pb.ensure((size_t)n_pairs * 8 + 8) || ctx->d_scan_tmp.ensure(((size_t)n / 1024 + 2) * 8)) { die(); return; }
+        if (sv.total && cudaMemcpyAsync(sv.regs.p, ctx->d_final.p, (size_t)sv.total * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st) != cudaSuccess) { fail("copy"); return; }
+        if (cudaMemcpyAsync(sv.cnt.p, ctx->d_final_n.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) { fail("copy"); return; }
+        if (launch_exclusive_scan(ctx->d_final_n.as<i32>(), ctx->d_pa.as<i64>(), n, ctx->d_scan_tmp.as<i64>(), st)) { die(); return; }
+        if (n_pairs) {
+            if (launch_pestat_pairs(job->opt, ctx->ix.l_pac, (const mem_alnreg_t *)ctx->d_final.p, (const i64 *)ctx->d_pa.p, n_pairs,
+                                    ctx->d_pb.as<u64>(), st)) { die(); return; }
+            if (cudaMemcpyAsync(job->isz.data() + (r0 >> 1), ctx->d_pb.p, (size_t)n_pairs * 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) { fail("summary download"); return; }
+        }
+        if (cudaStreamSynchronize(st) != cudaSuccess) { fail("synchronize"); return; }
+        t_align += now_s() - t0;
+    }
+    std::lock_guard<std::mutex> lk(job->tmu);
+    job->t_align += t_align;
+}
+
+// mem_pestat (bwamem_pair.c:72-135) from the per-pair summaries: insert-size quartiles, mean / std.dev inside the outlier
+// bounds, the proper-pair window per orientation.  Host code: a reduction over the whole batch, a few
+// microseconds per 10^6 pairs once the sizes are sorted.
+void pestat_host(const mem_opt_t *opt, const std::vector<u64> &isz, mem_pestat_t pes[4])
+{
+    (void)opt;
+    std::vector<u64> q[4];
+    memset(pes, 0, 4 * sizeof(mem_pestat_t));
+    for (u64 v : isz) if (v) { const u64 w = v - 1; q[w & 3].push_back(w >> 2); }
+    const bool verbose = getenv("B200_VERBOSE") != nullptr;
+    for (int d = 0; d < 4; ++d) {
+        mem_pestat_t *r = &pes[d];
+        std::vector<u64> &a = q[d];
+        if (a.size() < 10) { r->failed = 1; continue; }                    // MIN_DIR_CNT
+        std::sort(a.begin(), a.end());
+        const int p25 = (int)a[(size_t)(int)(.25 * a.size() + .499)];
+        const int p50 = (int)a[(size_t)(int)(.50 * a.size() + .499)];
+        const int p75 = (int)a[(size_t)(int)(.75 * a.size() + .499)];
+        r->low = (int)(p25 - 2.0 * (p75 - p25) + .499);                     // OUTLIER_BOUND
+        if (r->low < 1) r->low = 1;
+        r->high = (int)(p75 + 2.0 * (p75 - p25) + .499);
+        size_t x = 0;
+        r->avg = 0;
+        for (u64 v : a) if (v >= (u64)r->low && v <= (u64)r->high) { r->avg += v; ++x; }
+        r->avg /= x;
+        r->std = 0;
+        for (u64 v : a) if (v >= (u64)r->low && v <= (u64)r->high) r->std += (v - r->avg) * (v - r->avg);
+        r->std = sqrt(r->std / x);
+        r->low = (int)(p25 - 3.0 * (p75 - p25) + .499);                     // MAPPING_BOUND
+        r->high = (int)(p75 + 3.0 * (p75 - p25) + .499);
+        if (r->low > r->avg - 4.0 * r->std) r->low = (int)(r->avg - 4.0 * r->std + .499);      // MAX_STDDEV
+        if (r->high < r->avg + 4.0 * r->std) r->high = (int)(r->avg + 4.0 * r->std + .499);
+        if (r->low < 1) r->low = 1;
+        if (verbose) fprintf(stderr, "[b200::mem_pestat] %c%c: %zu pairs, (25, 50, 75) percentile (%d, %d, %d), mean %.2f std %.2f, proper pairs (%d, %d)\n",
+                             "FR"[d >> 1 & 1], "FR"[d & 1], a.size(), p25, p50, p75, r->avg, r->std, r->low, r->high);
+    }
+    size_t mx = 0;
+    for (int d = 0; d < 4; ++d) mx = std::max(mx, q[d].size());
+    for (int d = 0; d < 4; ++d)
+        if (pes[d].failed == 0 && (double)q[d].size() < mx * 0.05) pes[d].failed = 1;          // MIN_DIR_RATIO
+}
+
+// ---- worker2 + text of one sub-batch whose worker1 regions are resident in ctx (single-end: straight after
+// b200_align_batch; paired-end phase B: after the restore + mate rescue), then placement and the copy to the host
+struct DevLoop {
+    b200_ctx *ctx; Job *job; SamDevParams base; cudaEvent_t ev_written = nullptr; bool pending[2] = { false, false }; int iter = 0;
+    double t_w2 = 0, t_wait = 0;
+};
+
+int finish_sub(DevLoop &L, int j, int r0, int n, const i32 *cnt)
+{
+    b200_ctx *ctx = L.ctx; Job *job = L.job;
+    const b200_reads_t &R = *job->reads;
+    const double t1 = now_s();
+    Sub S;
+    S.ctx = ctx; S.job = job; S.r0 = r0; S.n = n; S.P = L.base;
+    S.P.seq = ctx->d_seq.as<u8>(); S.P.off = ctx->d_off.as<i64>();
+    if (upload_slice(ctx, R.name, R.name_off, r0, n, ctx->d_sam[5], ctx->d_sam[6], &S.P.names)) return -1;
+    S.P.name_off = ctx->d_sam[6].as<i64>();
+    if (R.comment && R.comment_off) {
+        if (upload_slice(ctx, R.comment, R.comment_off, r0, n, ctx->d_sam[8], ctx->d_sam[9], &S.P.comments)) return -1;
+        S.P.comment_off = ctx->d_sam[9].as<i64>();
+    }
+    if (R.qual) {
+        const i64 b0 = R.seq_off[r0], b1 = R.seq_off[r0 + n];
+        if (ctx->d_sam[7].ensure((size_t)(b1 - b0) + 16)) return -1;
+        if (b1 > b0) B200_CHECK(cudaMemcpyAsync(ctx->d_sam[7].p, R.qual + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, ctx->st));
+        S.P.qual = ctx->d_sam[7].as<u8>();
+    }
+    const int tb = L.iter & 1;                             // text buffer; its previous copy (two sub-batches ago) must have left
+    ++L.iter;
+    if (L.pending[tb]) { cudaEventSynchronize(ctx->sam_ev[tb]); L.pending[tb] = false; }
+    S.text = &ctx->d_sam[14 + tb];
+    if (S.text->ensure((size_t)n * 64 + 4096)) return -1;
+    if (job->sam_off) { S.h_pos = (i64 *)b200_ctx_pinned(ctx, 1 + tb, ((size_t)n + 1) * 8); if (!S.h_pos) return -1; }
+    if (b200_batch_reg2sam_dev(ctx, job->opt, job->n_processed + r0, cnt, sam_chunk, &S, job->pe ? job->pes : nullptr) < 0) return -1;
+    B200_CHECK(cudaEventRecord(L.ev_written, ctx->st));
+    const double t2 = now_s();
+    const i64 O = job->placer.place(j, S.local_bytes);     // input order: after every earlier sub-batch has been counted
+    const double t3 = now_s();
+    if (O < 0) return -2;                                  // another device failed
+    if (O + S.local_bytes <= job->cap) {
+        cudaStreamWaitEvent(ctx->st_d2h, L.ev_written, 0);
+        if (S.local_bytes) B200_CHECK(cudaMemcpyAsync(job->sam + O, S.text->p, (size_t)S.local_bytes, cudaMemcpyDeviceToHost, ctx->st_d2h));
+        cudaEventRecord(ctx->sam_ev[tb], ctx->st_d2h);
+        L.pending[tb] = true;
+    }
+    if (job->sam_off) {                                    // offsets of the reads' records in the whole text
+        size_t c = 0;
+        for (int r = 0; r < n; ++r) {
+            while (c + 1 < S.chunk_base.size() && S.chunk_base[c + 1].first <= r) ++c;
+            job->sam_off[r0 + r] = O + (S.chunk_base.empty() ? 0 : S.chunk_base[c].second) + S.h_pos[r];
+        }
+        if (r0 + n == R.n_reads) job->sam_off[R.n_reads] = O + S.local_bytes;
+    }
+    L.t_w2 += t2 - t1; L.t_wait += t3 - t2;
+    return 0;
+}
+
+// single-end: all of it; paired-end: phase B (dev_index >= 0: only the sub-batches this device holds)
+void worker(b200_ctx *ctx, int dev_index, Job *job)
 {
     Placer &pl = job->placer;
     auto die = [&]() { pl.fail(b200_last_error()); };
@@ -143,88 +291,63 @@ void worker(b200_ctx *ctx, Job *job)
     }
     for (cudaEvent_t &e : ctx->sam_ev)
         if (!e && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { b200_set_error("cudaEventCreate failed"); die(); return; }
-    cudaEvent_t ev_written = nullptr;
-    if (cudaEventCreateWithFlags(&ev_written, cudaEventDisableTiming) != cudaSuccess) { b200_set_error("cudaEventCreate failed"); die(); return; }
+    DevLoop L;
+    L.ctx = ctx; L.job = job;
+    if (cudaEventCreateWithFlags(&L.ev_written, cudaEventDisableTiming) != cudaSuccess) { b200_set_error("cudaEventCreate failed"); die(); return; }
     const b200_reads_t &R = *job->reads;
     const mem_opt_t *opt = job->opt;
-    SamDevParams base;
-    memset(&base, 0, sizeof(base));
-    base.opt = *opt;
+    memset(&L.base, 0, sizeof(L.base));
+    L.base.opt = *opt;
     if (upload_strings(ctx, job->ann_names, job->n_seqs, ctx->d_sam[0], ctx->d_sam[1])) { die(); return; }
-    base.ann_names = ctx->d_sam[0].as<char>(); base.ann_name_off = ctx->d_sam[1].as<i32>();
+    L.base.ann_names = ctx->d_sam[0].as<char>(); L.base.ann_name_off = ctx->d_sam[1].as<i32>();
     if (job->ann_annos && (opt->flag & 0x100)) {
         if (upload_strings(ctx, job->ann_annos, job->n_seqs, ctx->d_sam[2], ctx->d_sam[3])) { die(); return; }
-        base.ann_annos = ctx->d_sam[2].as<char>(); base.ann_anno_off = ctx->d_sam[3].as<i32>();
+        L.base.ann_annos = ctx->d_sam[2].as<char>(); L.base.ann_anno_off = ctx->d_sam[3].as<i32>();
     }
     if (job->rg && job->rg[0]) {
         const char *one[1] = { job->rg };
         if (upload_strings(ctx, one, 1, ctx->d_sam[4], ctx->d_sam[13])) { die(); return; }
-        base.rg = ctx->d_sam[4].as<char>(); base.rg_len = (int)strlen(job->rg);
+        L.base.rg = ctx->d_sam[4].as<char>(); L.base.rg_len = (int)strlen(job->rg);
     }
-    double t_align = 0, t_w2 = 0, t_wait = 0;
-    int iter = 0;
-    bool pending[2] = { false, false };
-    for (;; ++iter) {
-        const int j = job->next_sub.fetch_add(1);
-        if (j >= job->n_sub) break;
+    double t_align = 0;
+    for (int jj = 0; ; ++jj) {
+        int j;
+        if (job->pe) { j = jj; if (j >= job->n_sub) break; if (job->saved[j].owner != dev_index) continue; }
+        else { j = job->next_sub.fetch_add(1); if (j >= job->n_sub) break; }
+        if (pl.failed) break;
         const int r0 = (int)((i64)j * job->sub), n = (int)std::min<i64>(job->sub, R.n_reads - r0);
-        double t0 = now_s();
+        const double t0 = now_s();
         i32 *cnt = (i32 *)b200_ctx_pinned(ctx, 0, (size_t)n * 4 + 4);
         if (!cnt) { die(); return; }
-        const i64 nr = b200_align_batch(ctx, opt, n, R.seq, R.seq_off + r0, 0, nullptr, cnt);       // worker1; regions stay on the device
-        if (B200_IS_ERROR(nr) || nr > 0) { if (nr > 0) b200_set_error("internal: b200_align_batch with cap 0 returned %lld", (long long)nr); die(); return; }
-        double t1 = now_s();
-        Sub S;
-        S.ctx = ctx; S.job = job; S.r0 = r0; S.n = n; S.P = base;
-        S.P.seq = ctx->d_seq.as<u8>(); S.P.off = ctx->d_off.as<i64>();
-        if (upload_slice(ctx, R.name, R.name_off, r0, n, ctx->d_sam[5], ctx->d_sam[6], &S.P.names)) { die(); return; }
-        S.P.name_off = ctx->d_sam[6].as<i64>();
-        if (R.comment && R.comment_off) {
-            if (upload_slice(ctx, R.comment, R.comment_off, r0, n, ctx->d_sam[8], ctx->d_sam[9], &S.P.comments)) { die(); return; }
-            S.P.comment_off = ctx->d_sam[9].as<i64>();
+        if (!job->pe) {
+            const i64 nr = b200_align_batch(ctx, opt, n, R.seq, R.seq_off + r0, 0, nullptr, cnt);       // worker1; regions stay on the device
+            if (B200_IS_ERROR(nr) || nr > 0) { if (nr > 0) b200_set_error("internal: b200_align_batch with cap 0 returned %lld", (long long)nr); die(); return; }
+        } else {                                           // reads back on the device, worker1's regions restored, mate rescue, new counts
+            Job::Saved &sv = job->saved[j];
+            if (b200_batch_upload(ctx, n, R.seq, R.seq_off + r0)) { die(); return; }
+            if (ctx->d_final.ensure((size_t)(sv.total + 1) * sizeof(mem_alnreg_t)) || ctx->d_final_n.ensure((size_t)n * 4 + 4)) { die(); return; }
+            bool ok = true;
+            if (sv.total) ok = ok && cudaMemcpyAsync(ctx->d_final.p, sv.regs.p, (size_t)sv.total * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, ctx->st) == cudaSuccess;
+            ok = ok && cudaMemcpyAsync(ctx->d_final_n.p, sv.cnt.p, (size_t)n * 4, cudaMemcpyDeviceToDevice, ctx->st) == cudaSuccess;
+            ok = ok && (ctx->n_bytes == 0 || launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, ctx->st) == 0);
+            ok = ok && cudaStreamSynchronize(ctx->st) == cudaSuccess;
+            if (!ok) { b200_set_error("paired-end phase B: restoring the regions failed"); die(); return; }
+            ctx->total_regs = sv.total;
+            sv.regs.release(); sv.cnt.release();
+            if (!(opt->flag & 0x20) && b200_batch_rescue(ctx, opt, job->pes, nullptr, nullptr)) { die(); return; }      // MEM_F_NO_RESCUE
+            const i64 got = b200_batch_download(ctx, 0, nullptr, cnt);                                               // counts only
+            if (B200_IS_ERROR(got)) { die(); return; }
         }
-        if (R.qual) {
-            const i64 b0 = R.seq_off[r0], b1 = R.seq_off[r0 + n];
-            if (ctx->d_sam[7].ensure((size_t)(b1 - b0) + 16)) { die(); return; }
-            if (b1 > b0 && cudaMemcpyAsync(ctx->d_sam[7].p, R.qual + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, ctx->st) != cudaSuccess) {
-                b200_set_error("quality upload failed"); die(); return;
-            }
-            S.P.qual = ctx->d_sam[7].as<u8>();
-        }
-        const int tb = iter & 1;                           // text buffer; its previous copy (two sub-batches ago) must have left
-        if (pending[tb]) { cudaEventSynchronize(ctx->sam_ev[tb]); pending[tb] = false; }
-        S.text = &ctx->d_sam[14 + tb];
-        if (S.text->ensure((size_t)n * 64 + 4096)) { die(); return; }
-        if (job->sam_off) { S.h_pos = (i64 *)b200_ctx_pinned(ctx, 1 + tb, ((size_t)n + 1) * 8); if (!S.h_pos) { die(); return; } }
-        if (b200_batch_reg2sam_dev(ctx, opt, job->n_processed + r0, cnt, sam_chunk, &S) < 0) { die(); return; }
-        if (cudaEventRecord(ev_written, ctx->st) != cudaSuccess) { b200_set_error("cudaEventRecord failed"); die(); return; }
-        double t2 = now_s();
-        const i64 O = pl.place(j, S.local_bytes);          // input order: after every earlier sub-batch has been counted
-        double t3 = now_s();
-        if (O < 0) return;                                 // another device failed
-        if (O + S.local_bytes <= job->cap) {
-            cudaStreamWaitEvent(ctx->st_d2h, ev_written, 0);
-            if (S.local_bytes && cudaMemcpyAsync(job->sam + O, S.text->p, (size_t)S.local_bytes, cudaMemcpyDeviceToHost, ctx->st_d2h) != cudaSuccess) {
-                b200_set_error("SAM download failed"); die(); return;
-            }
-            cudaEventRecord(ctx->sam_ev[tb], ctx->st_d2h);
-            pending[tb] = true;
-        }
-        if (job->sam_off) {                                // offsets of the reads' records in the whole text
-            size_t c = 0;
-            for (int r = 0; r < n; ++r) {
-                while (c + 1 < S.chunk_base.size() && S.chunk_base[c + 1].first <= r) ++c;
-                job->sam_off[r0 + r] = O + (S.chunk_base.empty() ? 0 : S.chunk_base[c].second) + S.h_pos[r];
-            }
-            if (r0 + n == R.n_reads) job->sam_off[R.n_reads] = O + S.local_bytes;
-        }
-        t_align += t1 - t0; t_w2 += t2 - t1; t_wait += t3 - t2;
+        t_align += now_s() - t0;
+        const int rc = finish_sub(L, j, r0, n, cnt);
+        if (rc == -2) break;
+        if (rc) { die(); return; }
     }
     cudaStreamSynchronize(ctx->st_d2h);
     cudaStreamSynchronize(ctx->st);
-    cudaEventDestroy(ev_written);
+    cudaEventDestroy(L.ev_written);
     std::lock_guard<std::mutex> lk(job->tmu);
-    job->t_align += t_align; job->t_worker2 += t_w2; job->t_wait += t_wait;
+    job->t_align += t_align; job->t_worker2 += L.t_w2; job->t_wait += L.t_wait;
 }
 
 }  // namespace
@@ -237,15 +360,23 @@ extern "C" int64_t b200_reads_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
     if (!ctxs || n_ctx < 1 || !opt || !reads || !ann_names) { b200_set_error("b200_reads_to_sam: null argument"); return B200_E_FAIL; }
     for (int d = 0; d < n_ctx; ++d)
         if (!ctxs[d] || !ctxs[d]->has_index) { b200_set_error("b200_reads_to_sam: context %d has no index", d); return B200_E_FAIL; }
-    if (opt->flag & MEM_F_PE) { b200_set_error("b200_reads_to_sam: paired-end batches go through b200_pairs_to_sam"); return B200_E_FAIL; }
-    (void)pes0;
+    const bool pe = (opt->flag & MEM_F_PE) != 0;
     if (reads->n_reads < 0 || reads->n_reads > 0x7fffffff) { b200_set_error("b200_reads_to_sam: %lld reads in one call", (long long)reads->n_reads); return B200_E_FAIL; }
+    if (pe && ((reads->n_reads & 1) || (n_processed & 1))) { b200_set_error("b200_reads_to_sam: paired-end batches hold whole pairs (interleaved mates)"); return B200_E_FAIL; }
     if (sam_off) sam_off[0] = 0;
     if (reads->n_reads == 0) return 0;
     if (!reads->seq || !reads->seq_off || !reads->name || !reads->name_off) { b200_set_error("b200_reads_to_sam: reads need seq and name fields"); return B200_E_FAIL; }
+    if (pe)                                                // mem_sam_pe refuses mates with different names (bwamem_pair.c:386)
+        for (int64_t r = 0; r < reads->n_reads; r += 2) {
+            const int64_t a0 = reads->name_off[r], a1 = reads->name_off[r + 1], a2 = reads->name_off[r + 2];
+            if (a1 - a0 != a2 - a1 || memcmp(reads->name + a0, reads->name + a1, (size_t)(a1 - a0)) != 0) {
+                b200_set_error("paired reads have different names (reads %lld and %lld)", (long long)r, (long long)r + 1);
+                return B200_E_FAIL;
+            }
+        }
     Job job;
     job.opt = opt; job.ann_names = ann_names; job.ann_annos = ann_annos; job.n_seqs = ctxs[0]->ix.n_seqs;
-    job.reads = reads; job.n_processed = n_processed; job.rg = rg_id;
+    job.reads = reads; job.n_processed = n_processed; job.rg = rg_id; job.pe = pe;
     // sub-batches of about 2^20 reads, their number a multiple of the device count so that the last round is full
     const i64 want = sub_reads > 0 ? sub_reads : (1 << 20);
     i64 n_sub = (reads->n_reads + want - 1) / want;
@@ -255,10 +386,26 @@ extern "C" int64_t b200_reads_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
     job.sub = (int)sub; job.n_sub = (int)((reads->n_reads + sub - 1) / sub);
     job.cap = cap; job.sam = sam; job.sam_off = sam_off;
     const double t0 = now_s();
-    std::vector<std::thread> th;
-    for (int d = 1; d < n_ctx; ++d) th.emplace_back(worker, ctxs[d], &job);
-    worker(ctxs[0], &job);
-    for (auto &t : th) t.join();
+    auto run_all = [&](void (*fn)(b200_ctx *, int, Job *)) {
+        std::vector<std::thread> th;
+        for (int d = 1; d < n_ctx; ++d) th.emplace_back(fn, ctxs[d], d, &job);
+        fn(ctxs[0], 0, &job);
+        for (auto &t : th) t.join();
+    };
+    if (pe) {
+        job.isz.assign((size_t)(reads->n_reads >> 1), 0);
+        job.saved.resize((size_t)job.n_sub);
+        run_all(worker_pe_a);                              // worker1 everywhere, then the batch-level statistic, then the rest
+        if (!job.placer.failed) {
+            if (pes0) memcpy(job.pes, pes0, 4 * sizeof(mem_pestat_t));      // bwamem.c:1237
+            else pestat_host(opt, job.isz, job.pes);                        // bwamem.c:1238
+            job.next_sub = 0;
+            run_all(worker);
+        }
+        for (auto &sv : job.saved) {
+            if (sv.owner >= 0 && (sv.regs.p || sv.cnt.p)) { cudaSetDevice(ctxs[sv.owner]->device); sv.regs.release(); sv.cnt.release(); }
+        }
+    } else run_all(worker);
     if (stats) { stats[0] = now_s() - t0; stats[1] = job.t_align; stats[2] = job.t_worker2; stats[3] = job.t_wait; stats[4] = (double)job.n_sub; }
     if (job.placer.failed) { b200_set_error("%s", job.placer.err.c_str()); return B200_E_FAIL; }
     return job.placer.offset > cap ? -job.placer.offset : job.placer.offset;

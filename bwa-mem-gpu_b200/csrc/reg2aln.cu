@@ -10,7 +10,7 @@
 // E over F, `>=` for H, `>` for continuing a gap), so CIGARs are identical, not just equivalent.
 #include "ctx.h"
 #include "extend_common.cuh"
-#include "finalize.cuh"
+#include "finalize_pe.cuh"
 #include <cmath>
 
 struct R2AParams {
@@ -356,20 +356,29 @@ __global__ void r2a_gather_kernel(b200_aln_t *aln, int n, const u32 *cig, int ci
     aln[g].md_off = md_base + md_off[g];
 }
 
+__global__ void pe_unmapped_fill_kernel(i32 *mate_reg, i32 *read_flag, int n)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n) { mate_reg[r] = -1; read_flag[r] = (r & 1) ? 0x81 : 0x41; }
+}
+
 // regs_out / out_sel non-null: the worker2 steps of finalize.cuh run first on each chunk (chunks then hold whole reads)
 static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, const uint8_t *seqs, const int64_t *off,
                             const mem_alnreg_t *regs, const int32_t *cnt, b200_aln_t *out_aln, int64_t cap_cigar,
                             uint32_t *out_cigar, int64_t cap_md, char *out_md, int64_t totals[2],
                             mem_alnreg_t *regs_out, b200_sel_t *out_sel, int64_t n_processed,
-                            r2a_chunk_fn sink = nullptr, void *sink_user = nullptr)
+                            r2a_chunk_fn sink = nullptr, void *sink_user = nullptr, const mem_pestat_t *pes = nullptr)
 {
     const bool finalize = out_sel != nullptr || sink != nullptr;
+    const bool pe = pes != nullptr;                        // pairs: reads 2i / 2i + 1 are mates, mem_sam_pe's decisions (finalize_pe.cuh)
+
     const bool resident = regs == nullptr;                 // reads and regions are those of the batch the context just aligned
     if (!ctx || !ctx->has_index) { b200_set_error("no index uploaded"); return -1; }
     if (resident) {
         B200_CHECK(cudaSetDevice(ctx->device));
         n_reads = ctx->n_reads;
     } else if (b200_batch_upload(ctx, n_reads, seqs, off)) return -1;
+    if (pe && (!sink || (n_reads & 1) || (n_processed & 1))) { b200_set_error("paired-end worker2 needs the device consumer and whole pairs"); return -1; }
     cudaStream_t st = ctx->st;
     if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
     std::vector<i64> roff((size_t)n_reads + 1, 0);
@@ -385,6 +394,12 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         R2AChunk c;
         memset(&c, 0, sizeof(c));
         c.r_hi = n_reads; c.d_roff = zr.as<i64>();
+        if (pe) {                                          // every read unmapped: mates unmapped too, flags 0x41 / 0x81 (no_pairing, bwamem_pair.c:395-416)
+            DevBuf &d_mate = ctx->d_sam[16], &d_rflag = ctx->d_sam[17];
+            if (d_mate.ensure((size_t)n_reads * 4 + 4) || d_rflag.ensure((size_t)n_reads * 4 + 4)) return -1;
+            B200_LAUNCH(pe_unmapped_fill_kernel, (n_reads + 255) / 256, 256, 0, st, d_mate.as<i32>(), d_rflag.as<i32>(), n_reads);
+            c.mate_reg = d_mate.as<i32>(); c.read_flag = d_rflag.as<i32>();
+        }
         return sink(sink_user, c) ? -1 : 0;
     }
     if (n_regs == 0) return 0;
@@ -399,7 +414,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = max_len + 2;
     const i64 z_cap = (((i64)(std::min(max_len, 2 * w4 + 1) + 7) / 8 * 4) * ((i64)max_len + w4) + 15) / 16 * 16;   // 4 bits per cell, rows padded to words
     const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
-    const int chunk = (int)std::max<i64>(std::max(1024, max_cnt), std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
+    const int chunk = (int)std::max<i64>(std::max(1024, 2 * max_cnt), std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
     // lane-private traceback scratch: short reads need ~50 KB per lane (all 8 blocks per SM fit in a few GB); long reads need
     // MBs per lane, and the number of lanes in flight is what bounds them, so they may take up to half of the free memory
@@ -436,6 +451,32 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             ctx->log_cap = want;
         }
     }
+    FinPeParams PE;
+    memset(&PE, 0, sizeof(PE));
+    if (pe) {                                              // per-orientation tables of the pairing score's transcendental term (finalize_pe.cuh)
+        DevBuf &d_mate = ctx->d_sam[16], &d_rflag = ctx->d_sam[17], &d_vscr = ctx->d_sam[18];
+        if (d_mate.ensure((size_t)n_reads * 4 + 4) || d_rflag.ensure((size_t)n_reads * 4 + 4) || d_vscr.ensure((size_t)chunk * 16 + 16)) return -1;
+        memcpy(PE.pes, pes, 4 * sizeof(mem_pestat_t));
+        for (int d = 0; d < 4; ++d) {
+            PE.ptab[d] = nullptr; PE.ptab_n[d] = 0;
+            if (pes[d].failed || pes[d].high < pes[d].low) continue;
+            const i64 m = (i64)pes[d].high - pes[d].low + 1;
+            if (m > ((i64)1 << 24)) { b200_set_error("paired-end: insert-size window of %lld values", (long long)m); return -1; }
+            std::vector<double> tab((size_t)m);
+            for (i64 k = 0; k < m; ++k) {                  // bwamem_pair.c:243-244, the host's libm as in the reference
+                const i64 dist = pes[d].low + k;
+                const double ns = (dist - pes[d].avg) / pes[d].std;
+                tab[(size_t)k] = .721 * log(2. * erfc(fabs(ns) * M_SQRT1_2)) * opt->a;
+            }
+            DevBuf &dt = ctx->d_sam[19 + d];
+            if (dt.ensure((size_t)m * 8)) return -1;
+            B200_CHECK(cudaMemcpyAsync(dt.p, tab.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
+            B200_CHECK(cudaStreamSynchronize(st));          // tab is a local
+            PE.ptab[d] = dt.as<double>(); PE.ptab_n[d] = (int)m;
+        }
+        PE.mate_reg = d_mate.as<i32>(); PE.read_flag = d_rflag.as<i32>(); PE.vscr = d_vscr.as<u64>();
+        PE.l_pac = ctx->ix.l_pac; PE.ann_off = ctx->ix.ann_off;
+    }
     i64 cig_total = 0, md_total = 0;
     bool fits = true;
     int r_lo = 0;
@@ -447,7 +488,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     for (i64 g0 = 0; g0 < n_regs;) {
         int n = (int)std::min<i64>(chunk, n_regs - g0), r_hi = r_lo;
         if (finalize) {
-            while (r_hi < n_reads && roff[r_hi + 1] - g0 <= chunk) ++r_hi;
+            const int step = pe ? 2 : 1;                   // paired-end chunks hold whole pairs
+            while (r_hi + step <= n_reads && roff[r_hi + step] - g0 <= chunk) r_hi += step;
             n = (int)(roff[r_hi] - g0);
         }
         tmark(0);
@@ -473,7 +515,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             F.id0 = n_processed; F.sel = d_sel.as<b200_sel_t>(); F.logtab = d_log.as<double>(); F.log_cap = ctx->log_cap;
             F.overflow = P.overflow;
             const int fgrid = std::max(1, std::min(ctx->n_sms * 8, (F.n_reads + 127) / 128));
-            B200_LAUNCH(finalize_se_kernel, fgrid, 128, 0, st, F);
+            if (pe) { PE.F = F; B200_LAUNCH(finalize_pe_kernel, fgrid, 128, 0, st, PE); }
+            else B200_LAUNCH(finalize_se_kernel, fgrid, 128, 0, st, F);
             P.sel = d_sel.as<b200_sel_t>();
         }
         const int grid = std::max(1, std::min(grid_max, (n + 63) / 64));
@@ -534,6 +577,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             c.r_lo = r_lo; c.r_hi = r_hi; c.g0 = g0; c.n = n; c.regs = d_regs.as<mem_alnreg_t>(); c.aln = d_aln.as<b200_aln_t>();
             c.sel = d_sel.as<b200_sel_t>(); c.cig = d_pool_c.as<u32>(); c.md = d_pool_m.as<char>(); c.cig_base = cig_total; c.md_base = md_total;
             c.d_roff = d_roff.as<i64>();
+            c.mate_reg = pe ? PE.mate_reg : nullptr; c.read_flag = pe ? PE.read_flag : nullptr;
             if (sink(sink_user, c)) return -1;
             cig_total += nc; md_total += nm;
             g0 += n; r_lo = r_hi;
@@ -589,8 +633,17 @@ extern "C" int64_t b200_batch_reg2sam_se(b200_ctx_t *ctx, const mem_opt_t *opt, 
     return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, out_aln, cap_cigar, out_cigar, cap_md, out_md, totals, regs_out, out_sel, n_processed);
 }
 
-int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user)
+int64_t b200_batch_reg2sam_dev(b200_ctx *ctx, const mem_opt_t *opt, i64 n_processed, const i32 *cnt, r2a_chunk_fn fn, void *user,
+                               const mem_pestat_t *pes)
 {
     if (!fn || !cnt) { b200_set_error("b200_batch_reg2sam_dev: cnt and fn are required"); return -1; }
-    return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, nullptr, n_processed, fn, user);
+    return reg2aln_impl(ctx, opt, 0, nullptr, nullptr, nullptr, cnt, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, nullptr, n_processed, fn, user, pes);
+}
+
+int launch_pestat_pairs(const mem_opt_t *opt, i64 l_pac, const mem_alnreg_t *regs, const i64 *roff, int n_pairs, u64 *out, cudaStream_t st)
+{
+    if (n_pairs <= 0) return 0;
+    B200_LAUNCH(pestat_pairs_kernel, (n_pairs + 255) / 256, 256, 0, st, *opt, l_pac, regs, roff, n_pairs, out);
+    B200_CHECK(cudaGetLastError());
+    return 0;
 }

@@ -148,7 +148,7 @@ def numbered_names(prefix: bytes, first: int, n: int):
 
 
 def reads_to_sam(ctxs, opt, ann_names, seqs, off, names_flat, name_off, quals=None, comments=None, n_processed=0, rg=None,
-                 sub_reads=0, sam=None, want_off=True):
+                 sub_reads=0, sam=None, want_off=True, pes0=None):
     """b200_reads_to_sam over the contexts `ctxs` (one per device).  Returns (SAM bytes as a numpy view, offsets, stats)."""
     lib = ctxs[0].lib
     n = len(off) - 1
@@ -167,7 +167,8 @@ def reads_to_sam(ctxs, opt, ann_names, seqs, off, names_flat, name_off, quals=No
     if sam is None:
         sam = np.zeros(max(1 << 16, int(off[-1] - off[0]) * 2 + 300 * n), dtype=np.uint8)
     while True:
-        rc = lib.b200_reads_to_sam(hs, len(ctxs), C.byref(opt), a_names, None, C.byref(R), C.c_int64(n_processed), None,
+        rc = lib.b200_reads_to_sam(hs, len(ctxs), C.byref(opt), a_names, None, C.byref(R), C.c_int64(n_processed),
+                                   C.c_void_p(pes0.ctypes.data) if pes0 is not None else None,
                                    rg.encode() if rg else None, C.c_int(sub_reads), C.c_int64(len(sam)), C.c_void_p(sam.ctypes.data),
                                    C.c_void_p(soff.ctypes.data) if want_off else None, stats)
         if E_CAPACITY < rc < 0:

@@ -303,7 +303,8 @@ class RefIndex:
         tot = self.lib.ref_process_seqs2(self.h, C.byref(opt), C.c_int64(n_processed), C.c_int(n), nm, cm,
                                          _p(seqs, C.c_uint8), _p(off, C.c_int64),
                                          _p(quals, C.c_uint8) if quals is not None else None, rg.encode() if rg else None,
-                                         C.byref(pes0) if pes0 is not None else None, C.c_int64(cap), buf)
+                                         (C.c_void_p(pes0.ctypes.data) if isinstance(pes0, np.ndarray) else C.byref(pes0)) if pes0 is not None else None,
+                                         C.c_int64(cap), buf)
         assert tot >= 0, f"SAM buffer too small ({-tot})"
         self.lib.ref_last_process_seqs_seconds.restype = C.c_double
         self.last_process_seqs_s = self.lib.ref_last_process_seqs_seconds()      # the mem_process_seqs call alone

@@ -74,3 +74,82 @@ def test_reads_to_sam_nothing_aligned(backend):
     nf, no = L.flat_strings(names)
     sam, _, _ = L.reads_to_sam([ctx], opt, idx.anns()[3], seqs, off, nf, no)
     assert sam.tobytes() == exp
+
+
+def _pairs(gname, npairs, seed, damage, damaged_frac=0.1):
+    reads, _ = synth.simulate_pairs(cm.genome(gname), npairs, seed=seed, damaged_frac=damaged_frac, damage=damage)
+    seqs = np.ascontiguousarray(reads.reshape(-1))
+    off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
+    names = [f"p{i // 2}" for i in range(2 * npairs)]
+    return seqs, off, names
+
+
+def _cmp_sam(got, exp):
+    if got != exp:
+        for x, y in zip(exp.split(b"\n"), got.split(b"\n")):
+            assert x == y
+    assert got == exp
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("gname,damage", [("small", "window"), ("small", "periodic"), ("dup", "periodic"), ("rep", "window")])
+def test_pairs_to_sam_matches_reference(backend, gname, damage):
+    """Interleaved pairs through b200_reads_to_sam with MEM_F_PE: worker1, the batch's mem_pestat (host reduction over the
+    device-made per-pair summaries), mate rescue, mem_pair / MAPQ / flags (finalize_pe.cuh), mem_reg2aln and the SAM text with
+    mate fields on the device -- against the reference's mem_process_seqs (bwamem.c:1215; mem_sam_pe bwamem_pair.c:276)."""
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    opt = abi.default_opt()
+    opt.flag |= 0x2
+    opt.n_threads = 4
+    npairs = 250 if backend == "emu" else 10000
+    seqs, off, names = _pairs(gname, npairs, 181, damage)
+    quals = np.random.default_rng(9).integers(35, 74, size=len(seqs), dtype=np.uint8)
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, quals=quals, n_processed=20)
+    nf, no = L.flat_strings(names)
+    for sub in (0, 100 if backend == "emu" else 3000):
+        sam, soff, _ = L.reads_to_sam([ctx], opt, idx.anns()[3], seqs, off, nf, no, quals=quals, n_processed=20, sub_reads=sub)
+        _cmp_sam(sam.tobytes(), exp)
+        assert soff[-1] == len(exp)
+    assert b"\t99\t" in exp or b"\t83\t" in exp           # proper pairs exist
+    # option variants: -5 -Y (Hi-C usage), -a, -P (no pairing), -S (no rescue), given insert-size statistics
+    for flag in (0x800 | 0x200, 0x8, 0x4, 0x20):
+        o = abi.default_opt()
+        o.flag |= 0x2 | flag
+        o.n_threads = 4
+        exp = idx.process_seqs(o, synth.to_ascii(seqs), off, names=names, n_processed=0)
+        sam, _, _ = L.reads_to_sam([ctx], o, idx.anns()[3], seqs, off, nf, no, sub_reads=sub)
+        _cmp_sam(sam.tobytes(), exp)
+    pes = np.zeros(4, dtype=abi.PESTAT_DTYPE)
+    pes["failed"] = 1
+    pes[1] = (300, 700, 0, 500.0, 50.0)
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0, pes0=pes)
+    sam, _, _ = L.reads_to_sam([ctx], opt, idx.anns()[3], seqs, off, nf, no, sub_reads=sub, pes0=pes)
+    _cmp_sam(sam.tobytes(), exp)
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_pairs_to_sam_two_contexts_and_few_pairs(backend):
+    """Two contexts share the sub-batches of a paired batch (phase A regions stay where they were made); a batch with too
+    few pairs for any orientation (every mem_pestat orientation fails: no rescue windows, no pairing)."""
+    gname = "small"
+    idx, ctx = cm.ref_index(gname), cm.context(backend, gname)
+    ctx2 = L.Context(0, ctx.lib)
+    ctx2.upload_host_index(ctx._host_index)
+    opt = abi.default_opt()
+    opt.flag |= 0x2
+    opt.n_threads = 4
+    npairs = 301 if backend == "emu" else 9001
+    seqs, off, names = _pairs(gname, npairs, 183, "periodic", 0.2)
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=64)
+    nf, no = L.flat_strings(names)
+    sam, _, st = L.reads_to_sam([ctx, ctx2], opt, idx.anns()[3], seqs, off, nf, no, n_processed=64, sub_reads=90 if backend == "emu" else 2500)
+    _cmp_sam(sam.tobytes(), exp)
+    assert st[4] >= 4
+    seqs, off, names = _pairs(gname, 6, 185, "window")
+    exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names)
+    nf, no = L.flat_strings(names)
+    sam, _, _ = L.reads_to_sam([ctx, ctx2], opt, idx.anns()[3], seqs, off, nf, no)
+    _cmp_sam(sam.tobytes(), exp)
+    ctx2.close()

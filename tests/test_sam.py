@@ -1,5 +1,5 @@
-"""End-to-end drop-in parity: our mem_process_seqs (worker1 on the device through the C ABI; worker2 on the device too
-for single-end batches, the reference's own worker2 host code for pairs) must produce byte-identical SAM records to the reference's mem_process_seqs (bwamem.c:1215) --
+"""End-to-end drop-in parity: our mem_process_seqs (worker1, mem_pestat, mate rescue, worker2 and the SAM text on the device;
+optionally the reference's own worker2 host code) must produce byte-identical SAM records to the reference's mem_process_seqs (bwamem.c:1215) --
 POS, CIGAR, MAPQ, NM, MD, AS, XS, SA/XA tags, flags -- for single-end and paired-end batches.
 """
 import ctypes as C
@@ -44,8 +44,11 @@ def _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=None, n_shards
         lib.b200_process_seqs_set_ctx(ctx.h)
     else:                                                   # several contexts (here: all on device 0), one block of reads each
         extra = []
-        for _ in range(n_shards - 1):
-            c = L.Context(0, lib)
+        for k in range(n_shards - 1):
+            try:                                            # a second physical GPU when there is one
+                c = L.Context((k + 1) % 2 if backend == "cuda" else 0, lib)
+            except L.B200Error:
+                c = L.Context(0, lib)
             c.upload_host_index(ctx._host_index)
             extra.append(c)
         keep.append(extra)
@@ -91,8 +94,9 @@ def test_sam_single_end(backend, gname):
 @pytest.mark.parametrize("backend", BACKENDS)
 @pytest.mark.parametrize("damage", ["window", "periodic"])
 def test_sam_paired_end(backend, damage):
-    """Interleaved pairs (MEM_F_PE): batch-level mem_pestat on the host, mate rescue on the device, mem_sam_pe (with
-    MEM_F_NO_RESCUE) on the host; "periodic" damage leaves mates that only mem_matesw can place."""
+    """Interleaved pairs (MEM_F_PE) through the drop-in: worker1, mate rescue, mem_pair / MAPQ / flags and the paired SAM text
+    on the device, the batch's mem_pestat as a host reduction; then the older route with the host program's mem_pestat and
+    mem_sam_pe; "periodic" damage leaves mates that only mem_matesw can place."""
     gname = "small"
     idx = cm.ref_index(gname)
     opt = abi.default_opt()
@@ -104,9 +108,10 @@ def test_sam_paired_end(backend, damage):
     off = np.arange(0, 2 * npairs + 1, dtype=np.int64) * reads.shape[1]
     names = [f"p{i // 2}" for i in range(2 * npairs)]
     exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0)
-    got = _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names)
+    got = _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names)                  # everything on the device
     assert got == exp
     assert exp.count(b"\n") >= 2 * npairs
+    assert _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names, host_worker2=1) == exp      # the host program's mem_sam_pe
     opt.flag |= 0x800 | 0x200                               # -5 -Y on pairs (Hi-C usage): mem_sam_pe reorders itself (bwamem_pair.c:305-307)
     exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0)
     assert _our_sam(backend, gname, opt, seqs, off, n_processed=0, names=names) == exp
