@@ -240,3 +240,14 @@ def counter_reads(xp, genome, n_contigs: int, contig_len: int, i0: int, i1: int,
     reads = xp.where((rev == 1)[:, None], r2, reads)
     reads = reads.to(xp.uint8) if is_t else reads.astype(xp.uint8)
     return reads, contig, pos, rev
+
+
+def write_fastq(path: str, reads_nt4, off, names, quals=None, comments=None) -> None:
+    """FASTQ file of reads given as flat nt4 codes + offsets; quals: flat ASCII bytes with the same offsets (default 'I')."""
+    asc = to_ascii(np.asarray(reads_nt4))
+    with open(path, "wb") as f:
+        for i, nm in enumerate(names):
+            s = asc[off[i]:off[i + 1]].tobytes()
+            q = quals[off[i]:off[i + 1]].tobytes() if quals is not None else b"I" * len(s)
+            c = (" " + comments[i]) if comments is not None and comments[i] else ""
+            f.write(b"@" + nm.encode() + c.encode() + b"\n" + s + b"\n+\n" + q + b"\n")
