@@ -70,6 +70,9 @@ static int g_ps_want_devices = 1;
 static int g_ps_host_worker2 = -1;
 #define PS_LONG_READ 1000
 extern "C" void b200_process_seqs_host_worker2(int on) { g_ps_host_worker2 = on; }
+// read group id for the RG:Z tag (the host program's bwa_rg_id, bwa.c:44); unset: looked up as a dynamic symbol of the host program
+static const char *g_ps_rg = nullptr;
+extern "C" void b200_process_seqs_set_rg_id(const char *rg_id) { g_ps_rg = rg_id; }
 
 extern "C" void b200_process_seqs_set_ctx(b200_ctx_t *ctx) { g_ps_ctxs.assign(1, ctx); g_ps_bwt = nullptr; }
 extern "C" void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs) { g_ps_ctxs.assign(ctxs, ctxs + n); g_ps_bwt = nullptr; }
@@ -171,7 +174,7 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
         }
         std::vector<const char *> ann_names((size_t)bns->n_seqs + 1), ann_annos((size_t)bns->n_seqs + 1);
         for (int i = 0; i < bns->n_seqs; ++i) { ann_names[i] = bns->anns[i].name; ann_annos[i] = bns->anns[i].anno; }
-        const char *rg = (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
+        const char *rg = g_ps_rg ? g_ps_rg : (const char *)dlsym(RTLD_DEFAULT, "bwa_rg_id");      // bwa.c:44, set by -R; absent = no RG tag
         b200_reads_t R;
         R.n_reads = n; R.seq = flat.data(); R.seq_off = off.data(); R.qual = n_qual ? qflat.data() : nullptr;
         R.name = nflat.data(); R.name_off = name_off.data();

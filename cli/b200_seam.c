@@ -18,6 +18,8 @@ extern int bwa_verbose;
 void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                            int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
 void b200_process_seqs_use_devices(int n_devices);
+void b200_process_seqs_set_rg_id(const char *rg_id);
+extern char bwa_rg_id[256];
 #define ALIGN_BATCH b200_mem_process_seqs
 #else
 #define ALIGN_BATCH mem_process_seqs
@@ -78,6 +80,7 @@ void b200_batch_main(ktp_aux_t *aux)
 #ifdef B200_SEAM_GPU
 	const char *nd = getenv("B200_DEVICES");
 	if (nd && atoi(nd) > 1) b200_process_seqs_use_devices(atoi(nd));
+	b200_process_seqs_set_rg_id(bwa_rg_id);             /* -R (bwa_set_rg, bwa.c:559) */
 #endif
 	kt_pipeline(2, step, aux, 3);                       /* reading overlaps aligning, as upstream (no_mt_io would make it 1) */
 }

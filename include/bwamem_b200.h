@@ -405,6 +405,7 @@ void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
  * already hold the index, or ask for contexts on devices 0..n-1 to be created at the first call. */
 void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs);
 void b200_process_seqs_use_devices(int n_devices);
+void b200_process_seqs_set_rg_id(const char *rg_id);   /* the host program's bwa_rg_id (bwa.c:44, set by -R) for the RG:Z tag; the pointer is kept */
 void b200_process_seqs_host_worker2(int on);   /* 0 device, 1 host program, -1 (default) device unless the batch has reads > 1000 bp and the host program has worker2 */
 void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                            int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
