@@ -168,7 +168,7 @@ static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, in
         if (launch_smem_fast3(SP, fast_blocks, wmode, lcap3, qglob ? 1 : 0, st)) return -1;
         ++launches;
     } else if (ctx->smem_path != 1) {
-        const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 16 : 20);
+        const int lcap = ctx->smem_lcap > 0 ? ctx->smem_lcap : (wide ? 24 : 20);      // 64-bit indexes: ~17 interval-size changes per forward sweep at 3.1 Gbp; 16 sent every read to the general kernel (profiles/r4i_long_ab.jsonl)
         const int per_sm = std::max(1, (int)((200 * 1024) / ((size_t)lcap * 128 * (wide ? 32 : 16))));
         const int fast_blocks = std::max(1, std::min((n + 127) / 128, ctx->n_sms * std::min(per_sm, 6)));
         SP.list_cap = lcap;

@@ -1,0 +1,35 @@
+"""A/B of context tunables on the long-read workload (configs[4] shape) over the cached bench index.
+    python scripts/long_ab.py [--small] --reads 50000 --set smem_path=3 --set smem_lcap=24"""
+import argparse, json, os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench
+from bwa_mem_gpu_b200 import abi, bench_index as BI, lib as L, synth
+ap = argparse.ArgumentParser()
+ap.add_argument("--small", action="store_true")
+ap.add_argument("--reads", type=int, default=50000)
+ap.add_argument("--set", action="append", default=[])
+a = ap.parse_args()
+a.contigs, a.contig_len = (4, 25_000_000) if a.small else (24, 129_166_667)
+d = bench.ensure_index_cache(a)
+meta, pac, bwt, sa = BI.load(d)
+span = min(a.contig_len, 20_000_000)
+contigs = [BI.unpack_pac_numpy(pac, c * a.contig_len, c * a.contig_len + span) for c in range(4)]
+seqs, off = synth.simulate_long_reads(contigs, a.reads, seed=1005)
+opt = abi.default_opt()
+base = None
+for s in a.set or [""]:
+    ctx = L.Context(0)
+    for kv in filter(None, s.split(",")):
+        k, v = kv.split("="); ctx.tune(k, int(v))
+    ctx.build_index_device_pac(np.asarray(pac), [a.contig_len] * a.contigs)
+    ctx.batch_upload(seqs, off)
+    ctx.batch_run(opt, want_stage_ms=True)
+    st = ctx.batch_run(opt, want_stage_ms=True)
+    c = ctx.counters()
+    base = base or c["regs"]
+    print(json.dumps({"set": s, "reads": a.reads, "bases": int(off[-1]), "reads_per_s": a.reads / (st[5] * 1e-3),
+                      "stage_ms": dict(zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], [round(float(x), 1) for x in st])),
+                      "regs": c["regs"], "same_regs": c["regs"] == base}), flush=True)
+    ctx.close()
