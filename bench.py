@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sub", action="store_true", help="skip the paired-end and long-read sub-records")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables (b200_ctx_tune)")
+    ap.add_argument("--ctx-per-gpu", type=int, default=2, help="e2e: host threads (contexts sharing one index) per device")
     ap.add_argument("--check", type=int, default=20000, help="reads compared with the reference CPU code (regions and SAM text)")
     a = ap.parse_args()
     if a.small:
@@ -313,26 +314,37 @@ def run_ours(a, world, cores, barrier):
     nf, no = nf_pin.numpy(), no_pin.numpy().view(np.int64)
     nf[:] = nf0; no[:] = no0
     del nf0, no0
-    # ---- one context per device, index built on every device from the cached .pac
-    ctxs, hidx_box, errs = [None] * N, [None] * N, []
+    # ---- one context per device: the index is built on device 0 from the cached .pac and fanned out device to device
+    #      (b200_index_replicate: peer copies over NVLink); a device whose peer copy fails builds its own
+    ctxs, errs = [None] * N, []
+
+    def tuned(dv):
+        c = L.Context(dv)
+        for kv in filter(None, a.tune.split(",")):
+            k, v = kv.split("=")
+            c.tune(k, int(v))
+        return c
+    t0 = time.time()
+    ctxs[0] = tuned(0)
+    hidx = ctxs[0].build_index_device_pac(np.asarray(pac), [a.contig_len] * a.contigs)
+    t_index = time.time() - t0
 
     def mk(dv):
         try:
-            c = L.Context(dv)
-            for kv in filter(None, a.tune.split(",")):
-                k, v = kv.split("=")
-                c.tune(k, int(v))
-            hidx_box[dv] = c.build_index_device_pac(np.asarray(pac), [a.contig_len] * a.contigs)
+            c = tuned(dv)
+            try:
+                c.replicate_index_from(ctxs[0])
+            except L.B200Error:
+                c.build_index_device_pac(np.asarray(pac), [a.contig_len] * a.contigs)
             ctxs[dv] = c
         except Exception as e:  # noqa: BLE001
             errs.append(f"device {dv}: {e}")
     t0 = time.time()
-    ths = [threading.Thread(target=mk, args=(dv,)) for dv in range(N)]
+    ths = [threading.Thread(target=mk, args=(dv,)) for dv in range(1, N)]
     [t.start() for t in ths]; [t.join() for t in ths]
     if errs:
         raise SystemExit("; ".join(errs))
-    t_index = time.time() - t0
-    hidx = hidx_box[0]
+    t_fanout = time.time() - t0
     opt = abi.default_opt()
     bounds = [(int(a.reads * dv // N), int(a.reads * (dv + 1) // N)) for dv in range(N)]
 
@@ -373,9 +385,19 @@ def run_ours(a, world, cores, barrier):
     sam_pin = pinned(torch, sam_cap)
     sam = sam_pin.numpy()
     e2e_s, e2e_stats, sam_bytes = [], None, 0
+    e2e_ctxs = []                                          # --ctx-per-gpu host threads per device, each with its own context borrowing the device's index
+    for dv in range(N):
+        e2e_ctxs.append(ctxs[dv])
+        for _ in range(max(1, a.ctx_per_gpu) - 1):
+            c2 = L.Context(dv)
+            for kv in filter(None, a.tune.split(",")):
+                k, v = kv.split("=")
+                c2.tune(k, int(v))
+            c2.replicate_index_from(ctxs[dv])
+            e2e_ctxs.append(c2)
     for s in range(a.warmup + a.steps):
         t0 = time.perf_counter()
-        out, _, st = L.reads_to_sam(ctxs, opt, hidx.names, seqs, off, nf, no, sam=sam, want_off=False)
+        out, _, st = L.reads_to_sam(e2e_ctxs, opt, hidx.names, seqs, off, nf, no, sam=sam, want_off=False)
         dt = time.perf_counter() - t0
         if s >= a.warmup:
             e2e_s.append(dt)
@@ -412,7 +434,7 @@ def run_ours(a, world, cores, barrier):
         "config": config_of(a),
         "e2e": {"value": a.reads / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(len(seqs) + off.nbytes + len(nf) + no.nbytes),
                 "d2h_bytes_per_step": int(sam_bytes), "ms_per_step": e2e_ms, "sam_bytes": int(sam_bytes),
-                "call": "b200_reads_to_sam (one process, one host thread per device; worker1 + worker2 + SAM text on the devices; text placed in input order)",
+                "call": f"b200_reads_to_sam (one process, {max(1, a.ctx_per_gpu)} host threads per device sharing its index; worker1 + worker2 + SAM text on the devices; text placed in input order)",
                 "thread_seconds": {"worker1": e2e_stats[1], "worker2_and_text": e2e_stats[2], "placement_wait": e2e_stats[3]},
                 "sub_batches": int(e2e_stats[4])},
         "gpu_launches": int(cnt["launches"]) * a.steps,
@@ -426,7 +448,8 @@ def run_ours(a, world, cores, barrier):
                        "dpx_ops_per_cell": 5, "peak_source": "profiles/microbench.json: measured DPX issue rate / 5 instructions per cell",
                        "ms_per_step_all_devices": ext_ms}],
         "smem_lookups_per_sec": cnt["extend"] / (smem_ms * 1e-3) * N if smem_ms > 0 else None,
-        "setup": {"index": "cached .pac -> b200_index_build_device on every device", "index_build_s": t_index, "read_sim_s": t_reads,
+        "setup": {"index": "cached .pac -> b200_index_build_device on device 0, b200_index_replicate (peer copy) to the others", "index_build_s": t_index,
+                  "index_fanout_s": t_fanout, "read_sim_s": t_reads,
                   "seq_len": hidx.seq_len, "wall_value_phase_s": wall_value, "setup_s": None},
     }
     # ---------------- checks against the reference CPU code on a sample (and the CPU baseline at N = 1)
@@ -468,7 +491,7 @@ def run_ours(a, world, cores, barrier):
             out_rec["sub_records"] = {"error": str(e)[:500]}
     out_rec["setup"]["setup_s"] = time.time() - t_setup
     print(json.dumps(out_rec))
-    for c in ctxs:
+    for c in e2e_ctxs[::-1]:
         c.close()
 
 

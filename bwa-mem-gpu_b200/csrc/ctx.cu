@@ -264,6 +264,65 @@ b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t 
     return c;
 }
 
+// ---- one index, several contexts ---------------------------------------------------------------
+// The FM-index is read-only, so contexts can have it in common.  Same device: `dst` borrows src's arrays (no copy, no
+// memory; src must outlive dst) -- two contexts per device let two host threads keep one GPU busy across each other's host
+// gaps and synchronisations.  Another device: the arrays are copied device to device (cudaMemcpyPeerAsync: NVLink where the
+// box has it) instead of being uploaded or built again -- the "one H2D + 7 peer copies" fan-out of SURVEY.md 8(e).
+extern "C" int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src)
+{
+    if (!dst || !src || !src->has_index) { b200_set_error("b200_index_replicate: source context has no index"); return -1; }
+    if (dst == src) return 0;
+    dst->force_wide = src->force_wide; dst->kmer_k = src->kmer_k;
+    dst->idx_bwt_size = src->idx_bwt_size; dst->idx_groups = src->idx_groups; dst->idx_ties = src->idx_ties;
+    dst->bwt_identity = nullptr; dst->stub_pac = src->stub_pac;
+    if (dst->device == src->device) {
+        dst->ix = src->ix;
+        dst->has_index = true;
+        return 0;
+    }
+#ifdef B200_EMU
+    b200_set_error("b200_index_replicate: one device only in the emulated build"); return -1;
+#else
+    B200_CHECK(cudaSetDevice(dst->device));
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, dst->device, src->device) == cudaSuccess && can) {
+        cudaError_t e = cudaDeviceEnablePeerAccess(src->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else cudaGetLastError();
+    }
+    DevBuf *sb[] = { &src->d_bwt, &src->d_sa, &src->d_sa_full, &src->d_pac, &src->d_ann_off, &src->d_ann_len, &src->d_ann_alt, &src->d_occ32, &src->d_kmer };
+    DevBuf *db[] = { &dst->d_bwt, &dst->d_sa, &dst->d_sa_full, &dst->d_pac, &dst->d_ann_off, &dst->d_ann_len, &dst->d_ann_alt, &dst->d_occ32, &dst->d_kmer };
+    const int nb = (int)(sizeof(sb) / sizeof(sb[0]));
+    for (int i = 0; i < nb; ++i) {
+        if (!sb[i]->p) continue;
+        if (db[i]->ensure(sb[i]->bytes)) return -1;
+        B200_CHECK(cudaMemcpyPeerAsync(db[i]->p, dst->device, sb[i]->p, src->device, sb[i]->bytes, dst->st));
+    }
+    B200_CHECK(cudaStreamSynchronize(dst->st));
+    auto move = [&](const void *p) -> const void * {       // the same offset inside the copy of the array that holds p
+        if (!p) return nullptr;
+        for (int i = 0; i < nb; ++i) {
+            const char *b = (const char *)sb[i]->p;
+            if (b && (const char *)p >= b && (const char *)p < b + sb[i]->bytes) return (const char *)db[i]->p + ((const char *)p - b);
+        }
+        return nullptr;
+    };
+    DevIndex ix = src->ix;
+    ix.bwt = (const uint4 *)move(src->ix.bwt); ix.sa = (const u64 *)move(src->ix.sa);
+    ix.sa_full32 = (const u32 *)move(src->ix.sa_full32); ix.sa_full64 = (const u64 *)move(src->ix.sa_full64);
+    ix.pac = (const u8 *)move(src->ix.pac); ix.ann_off = (const i64 *)move(src->ix.ann_off);
+    ix.ann_len = (const i32 *)move(src->ix.ann_len); ix.ann_alt = (const i32 *)move(src->ix.ann_alt);
+    ix.occ32 = (const uint4 *)move(src->ix.occ32); ix.kmer_tab = (const uint4 *)move(src->ix.kmer_tab);
+    if (!ix.bwt || !ix.pac || !ix.occ32 || (src->ix.kmer_tab && !ix.kmer_tab) || (src->ix.sa_full64 && !ix.sa_full64) || (src->ix.sa_full32 && !ix.sa_full32)) {
+        b200_set_error("b200_index_replicate: an index array lies outside the context's buffers"); return -1;
+    }
+    dst->ix = ix;
+    dst->has_index = true;
+    return 0;
+#endif
+}
+
 // ---- primitive batches -----------------------------------------------------------------------
 static int need_index(b200_ctx *ctx)
 {

@@ -26,7 +26,7 @@ _SYMBOLS = [
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_align_sam_se_batch", "b200_host_alloc", "b200_host_free", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2", "b200_process_seqs_set_rg_id",
-    "b200_reads_to_sam", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
+    "b200_reads_to_sam", "b200_index_replicate", "b200_fastq_open", "b200_fastq_read", "b200_fastq_close", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -119,6 +119,43 @@ class B200Error(RuntimeError):
 class ReadsT(C.Structure):          # b200_reads_t
     _fields_ = [("n_reads", C.c_int64), ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("qual", C.c_void_p),
                 ("name", C.c_void_p), ("name_off", C.c_void_p), ("comment", C.c_void_p), ("comment_off", C.c_void_p)]
+
+
+class FastqReader:
+    """b200_fastq_*: batches of reads from FASTQ / FASTA files (plain, gzip, BGZF) as numpy views of the reader's buffers."""
+
+    def __init__(self, fn1, fn2=None, n_threads=8, lib=None):
+        self.lib = lib or load()
+        self.lib.b200_fastq_open.restype = C.c_void_p
+        self.lib.b200_fastq_read.restype = C.c_int64
+        h = self.lib.b200_fastq_open(fn1.encode(), fn2.encode() if fn2 else None, C.c_int(n_threads))
+        if not h:
+            raise B200Error(self.lib.b200_last_error().decode())
+        self.h = C.c_void_p(h)
+
+    def read(self, chunk_bases):
+        """Next batch: dict with n, seqs, off, quals, names (flat, off), comments ((flat, off) or None); None at the end."""
+        R = ReadsT()
+        n = self.lib.b200_fastq_read(self.h, C.c_int64(chunk_bases), C.byref(R))
+        if n < 0:
+            raise B200Error(self.lib.b200_last_error().decode())
+        if n == 0:
+            return None
+        view = lambda p, cnt, ty: np.ctypeslib.as_array(C.cast(C.c_void_p(p), C.POINTER(ty)), shape=(max(1, cnt),))[:cnt]
+        off = view(R.seq_off, n + 1, C.c_int64)
+        noff = view(R.name_off, n + 1, C.c_int64)
+        out = {"n": int(n), "off": off, "seqs": view(R.seq, int(off[n]), C.c_uint8),
+               "quals": view(R.qual, int(off[n]), C.c_uint8) if R.qual else None,
+               "names": (view(R.name, int(noff[n]), C.c_uint8), noff), "comments": None, "struct": R}
+        if R.comment:
+            coff = view(R.comment_off, n + 1, C.c_int64)
+            out["comments"] = (view(R.comment, int(coff[n]), C.c_uint8), coff)
+        return out
+
+    def close(self):
+        if self.h:
+            self.lib.b200_fastq_close(self.h)
+            self.h = None
 
 
 def flat_strings(strs):
@@ -325,6 +362,11 @@ class Context:
             _p(d.ann_len, C.c_int32), _p(d.ann_alt, C.c_int32), C.c_int(flags)), "index_build_device")
         d._fill_info()
         return d
+
+    def replicate_index_from(self, src: "Context"):
+        """b200_index_replicate: borrow (same device) or peer-copy (other device) src's index."""
+        self._chk(self.lib.b200_index_replicate(self.h, src.h), "index_replicate")
+        self._index_src = src                                  # keep the owner alive
 
     def index_info(self):
         info = np.zeros(13, dtype=np.uint64)

@@ -158,6 +158,12 @@ int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_siz
                           const uint8_t *pac, int64_t l_pac, int n_seqs, const int64_t *ann_offset,
                           const int32_t *ann_len, const int32_t *ann_is_alt, int flags);
 
+/* One index, several contexts.  dst on src's device: dst BORROWS src's index arrays (no copy; src must outlive dst) -- two
+ * contexts per device let two host threads of b200_reads_to_sam keep one GPU busy.  dst on another device: the arrays are
+ * copied device to device (peer copy; NVLink where present) instead of being uploaded or rebuilt: the fan-out of one index
+ * to the GPUs of a box (replaces the per-process transferIndex of cuda/streams.cu:8-104). */
+int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src);
+
 /* Host-side index construction for in-memory genomes: the same arrays `bwa index` writes
  * (bwa_idx_build, bwtindex.c:253-323: pac, BWT+Occ blocks, SA sampled every 32 rows), built with an
  * own SA-IS suffix sorter.  fwd = nt4 codes 0..3 of the concatenated contigs.
@@ -255,6 +261,18 @@ int64_t b200_reads_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const mem_opt_t *o
                           const char *const *ann_annos, const b200_reads_t *reads, int64_t n_processed,
                           const mem_pestat_t *pes0, const char *rg_id, int sub_reads, int64_t cap, char *sam,
                           int64_t *sam_off, double *stats);
+
+/* Input side: FASTQ / FASTA files (plain, gzip, or BGZF = gzip by block) -> batches of reads in the flat layout above, in
+ * page-locked memory, parsed by n_threads threads (csrc/fastq.cpp).  Same record grammar as kseq.h, same name trimming
+ * (trim_readno, bwa.c:64-68) and the same batch boundaries as bseq_read (bwa.c:191-224): records in file order -- mates
+ * alternating when two files are given -- until the batch holds chunk_bases bases on an even record count.
+ * b200_fastq_read fills *out with pointers into buffers owned by the reader, valid until the next call or the close;
+ * returns the number of reads, 0 at the end of the input, < 0 on error.  Sequences are the file's letters (the aligner
+ * converts), qualities as in the file or NULL, comments NULL when no record of the batch has one. */
+typedef struct b200_fastq b200_fastq_t;
+b200_fastq_t *b200_fastq_open(const char *fn1, const char *fn2 /* NULL: one file */, int n_threads);
+int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_reads_t *out);
+void b200_fastq_close(b200_fastq_t *f);
 
 /* Page-locked host memory (cudaHostAlloc) for callers that want the copies of the batched calls at full speed. */
 void *b200_host_alloc(size_t bytes);

@@ -50,7 +50,7 @@ def test_reads_to_sam_matches_reference(backend, gname):
         assert soff[0] == 0 and soff[-1] == len(got) and got[soff[n // 2]:].startswith(names[n // 2].encode() + b"\t")
     # ASCII input, a read group, too small a buffer (-(needed), then the same text), and two contexts sharing the sub-batches
     ctx2 = L.Context(0, ctx.lib)
-    ctx2.upload_host_index(ctx._host_index)
+    ctx2.replicate_index_from(ctx)                              # same device: the index is borrowed, not copied
     exp = idx.process_seqs(opt, synth.to_ascii(seqs), off, names=names, n_processed=0, rg="grp1")
     small = np.zeros(1000, dtype=np.uint8)
     sam, soff, stats = L.reads_to_sam([ctx, ctx2], opt, idx.anns()[3], synth.to_ascii(seqs), off, nf, no, rg="grp1",
