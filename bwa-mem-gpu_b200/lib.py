@@ -26,7 +26,7 @@ _SYMBOLS = [
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_align_sam_se_batch", "b200_host_alloc", "b200_host_free", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2", "b200_process_seqs_set_rg_id",
-    "b200_reads_to_sam", "b200_index_replicate", "b200_fastq_open", "b200_fastq_read", "b200_fastq_close", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
+    "b200_reads_to_sam", "b200_index_replicate", "b200_index_save", "b200_index_load", "b200_fastq_open", "b200_fastq_read", "b200_fastq_close", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -362,6 +362,12 @@ class Context:
             _p(d.ann_len, C.c_int32), _p(d.ann_alt, C.c_int32), C.c_int(flags)), "index_build_device")
         d._fill_info()
         return d
+
+    def save_index(self, path: str, with_full_sa: bool = False):
+        self._chk(self.lib.b200_index_save(self.h, path.encode(), C.c_int(1 if with_full_sa else 0)), "index_save")
+
+    def load_index(self, path: str, flags=IDX_FULL_SA):
+        self._chk(self.lib.b200_index_load(self.h, path.encode(), C.c_int(flags)), "index_load")
 
     def replicate_index_from(self, src: "Context"):
         """b200_index_replicate: borrow (same device) or peer-copy (other device) src's index."""

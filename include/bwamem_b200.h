@@ -164,6 +164,14 @@ int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_siz
  * to the GPUs of a box (replaces the per-process transferIndex of cuda/streams.cu:8-104). */
 int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src);
 
+/* On-disk device-ready index (csrc/index_io.cu): everything the context's index holds in HBM -- the reference-layout arrays
+ * of bwa_idx_load (bwa.c:384-434) AND the derived occ32 sectors and k-mer interval table, with_full_sa != 0 also the full
+ * suffix array (8 bytes per row on 64-bit indexes: 50 GB at 3.1 Gbp; without it b200_index_load with B200_IDX_FULL_SA
+ * re-expands the sampled SA on the device) -- written as it lies, and read back with large copies instead of the re-layout
+ * of every start.  The file is specific to this library version (magic "B200IDX2"). */
+int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_sa);
+int b200_index_load(b200_ctx_t *ctx, const char *path, int flags);
+
 /* Host-side index construction for in-memory genomes: the same arrays `bwa index` writes
  * (bwa_idx_build, bwtindex.c:253-323: pac, BWT+Occ blocks, SA sampled every 32 rows), built with an
  * own SA-IS suffix sorter.  fwd = nt4 codes 0..3 of the concatenated contigs.

@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 import common as cm
-from bwa_mem_gpu_b200 import lib as L
+from bwa_mem_gpu_b200 import abi, lib as L
 
 needs_ref = pytest.mark.skipif(not cm.have_ref(), reason="oracle/_ref not built")
 
@@ -86,3 +86,29 @@ def test_pack_pac_ragged():
 @pytest.mark.parametrize("gname,tune", [("tiny", (("idx_group_cap", 3000),)), ("rep", ()), ("small", ())])
 def test_device_index_matches_host_cuda(gname, tune):
     _device_vs_host("cuda", gname, tune)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("with_sa", [False, True])
+def test_index_save_load_replicate(tmp_path, with_sa):
+    """On-disk device-ready index: save from one context, load into another (with and without the full SA in the file);
+    a third context borrows the loaded index (b200_index_replicate); all give the regions of the original."""
+    gname = "rep"
+    ctx = cm.context("cuda", gname)
+    opt = abi.default_opt()
+    seqs, off = cm.reads_for(gname, 5000, seed=61, indel=0.004)
+    r0, n0 = ctx.align(opt, seqs, off)
+    path = str(tmp_path / "idx.b200")
+    ctx.save_index(path, with_full_sa=with_sa)
+    c2 = L.Context(0, ctx.lib)
+    c2.load_index(path)
+    r1, n1 = c2.align(opt, seqs, off)
+    assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
+    assert np.array_equal(c2.index_info()[:11], ctx.index_info()[:11])
+    c3 = L.Context(0, ctx.lib)
+    c3.replicate_index_from(c2)
+    r2, n2 = c3.align(opt, seqs, off)
+    assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
+    c3.close(); c2.close()
+    with pytest.raises(L.B200Error):
+        L.Context(0, ctx.lib).load_index(str(tmp_path / "nope"))
