@@ -138,6 +138,7 @@ struct Ext2Params {
     i64 *reg_off; i32 *reg_n;
     unsigned *work_counter;
     unsigned long long *stats;
+    ExtJob *tail_jobs;               // tail mode (ext3.cu): one job slot per resident DP lane
 };
 
 struct KswBatchParams {
@@ -171,6 +172,7 @@ int launch_ext2_plan(const Ext2Params &p, int round, int n_threads, cudaStream_t
 int launch_ext2_dp(const Ext2Params &p, int round, int bin, int he_cols, int grid, int rowsync, int phased, cudaStream_t st);
 size_t ext2_dp8_smem(int n_groups);
 int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int grid, int rowsync, int phased, cudaStream_t st);
+int launch_ext2_dp8_tail(const Ext2Params &p, int round, int n_groups, int grid, cudaStream_t st);
 int launch_ext2_sort(const Ext2Params &p, int round, int n_jobs, int n_sms, cudaStream_t st);
 int launch_ext2_finish(const Ext2Params &p, int grid, cudaStream_t st);
 int launch_ksw_batch(const KswBatchParams &p, int grid, int block, cudaStream_t st);

@@ -22,6 +22,7 @@
 // non-zero columns per cell.
 #include "b200_internal.h"
 #include "extend_common.cuh"
+#include "ext_plan.cuh"
 
 #define D8_THREADS 64
 
@@ -109,7 +110,20 @@ __device__ __forceinline__ unsigned d8_nz8(const uint4 w)
 // retries, next 32 jobs -- a lane whose next DP belongs to a later phase parks until no lane is mid-DP.  Together with the
 // job order (same flank shape next to each other) the rows a warp executes in one step then have the same number of
 // column groups, instead of a short left flank in one lane waiting for a long right flank in another.
-template <bool ROWSYNC>
+// job t of a round, counted over the three bins in the order the planning kernel reads them back
+__device__ __forceinline__ bool d8_locate(const Ext2Params &P, int round, unsigned t, int &bin, unsigned &slot)
+{
+    const unsigned *nj = P.njobs + 8 * round;
+    bin = 0; slot = t;
+    if (slot >= nj[0]) { slot -= nj[0]; bin = 2; if (slot >= nj[2]) { slot -= nj[2]; bin = 1; if (slot >= nj[1]) return false; } }
+    return true;
+}
+
+// TAIL: the last rounds of a chunk hold few jobs each (the k-th extended seed of the few reads that have one) and cost a
+// planning launch, a host round trip and up to three nearly empty DP launches per round.  In tail mode ONE launch finishes
+// the chunk: a lane takes a job of the current round (from any bin; rows are sized for the longest flank) and, when it is
+// done, plans the next seed of that read itself (ext_plan_read) and runs it, until the read has no seed left.
+template <bool ROWSYNC, bool TAIL>
 __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int round, int bin, int n_groups, int phased)
 {
     B200_DYN_SMEM(d8_raw);
@@ -141,8 +155,10 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
     K.ne_del2 = ((u32)(-e_del) & 0xffffu) * 0x10001u; K.noe_del2 = ((u32)(-oe_del) & 0xffffu) * 0x10001u;
     K.noe_ins2 = ((u32)(-oe_ins) & 0xffffu) * 0x10001u; K.ne_ins2 = ((u32)(-e_ins) & 0xffffu) * 0x10001u;
     K.ne_ins_hi = ((u32)(-e_ins) & 0xffffu) << 16;
-    const unsigned njobs = P.njobs[8 * round + bin];
-    unsigned *work_counter = P.njobs + 8 * round + 4 + bin;
+    const unsigned njobs = TAIL ? P.njobs[8 * round] + P.njobs[8 * round + 1] + P.njobs[8 * round + 2] : P.njobs[8 * round + bin];
+    unsigned *work_counter = P.njobs + 8 * round + 4 + (TAIL ? 3 : bin);
+    ExtJob *my_job = TAIL ? P.tail_jobs + ((size_t)blockIdx.x * D8_THREADS + threadIdx.x) : nullptr;     // the jobs this lane plans itself
+    bool have_done = false;
     const i64 l_pac = ix.l_pac;
     u64 n_ksw = 0, n_cells = 0;
     unsigned ncell32 = 0;
@@ -253,12 +269,25 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
         }
         // job / side / retry transitions; loops only when a DP has no rows (tlen <= 0)
         const bool may_fetch = !phased || !__any_sync(B200_FULL_MASK, active);              // phased: the warp takes 32 jobs at a time
-        while ((active && ksw_fin) || (!active && !exhausted && may_fetch)) {
+        while ((active && ksw_fin) || (!active && (!exhausted || (TAIL && have_done)) && may_fetch)) {
             int next_side = -1, next_t = 0;
             if (!active) {                                                                // fetch a job
-                const unsigned slot = atomicAdd(work_counter, 1u);
-                if (slot >= njobs) { exhausted = true; break; }
-                L.job = d8_job_slot(P, round & 1, bin, P.perm ? P.perm[(size_t)bin * P.jobs_cap + slot] : slot);
+                ExtJob *nj = nullptr;
+                if (TAIL && have_done) {                                                  // the read of the job just finished: its next seed, if any
+                    have_done = false;
+                    ExtJob tmp;
+                    if (ext_plan_read(P, L.job->read, L.job, false, &tmp)) { *my_job = tmp; nj = my_job; }
+                }
+                if (!nj) {
+                    const unsigned slot = atomicAdd(work_counter, 1u);
+                    if (slot >= njobs) { exhausted = true; break; }
+                    if (TAIL) {
+                        int jb; unsigned js;
+                        d8_locate(P, round, slot, jb, js);
+                        nj = d8_job_slot(P, round & 1, jb, js);
+                    } else nj = d8_job_slot(P, round & 1, bin, P.perm ? P.perm[(size_t)bin * P.jobs_cap + slot] : slot);
+                }
+                L.job = nj;
                 active = true;
                 L.a_score = -1;
                 if (L.job->qbeg) { next_side = 0; next_t = 0; L.prev = -1; }
@@ -294,6 +323,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
                         J->w = J->w > aw ? J->w : aw;
                         J->score = score;
                         active = false;                                                   // job done
+                        if (TAIL) have_done = true;
                         n_cells += ncell32; ncell32 = 0;
                         continue;
                     }
@@ -304,6 +334,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
                 if (J->qbeg + J->slen == J->lq) {                                         // bwamem.c:778
                     J->qe = J->lq; J->re = J->rbeg + J->slen; J->score = L.a_score;
                     active = false;
+                    if (TAIL) have_done = true;
                     n_cells += ncell32; ncell32 = 0;
                     continue;
                 }
@@ -381,7 +412,7 @@ __global__ void __launch_bounds__(D8_THREADS) ext_dp8_kernel(Ext2Params P, int r
         }
         need_init = false;
         __syncwarp();
-        if (__all_sync(B200_FULL_MASK, exhausted && !active)) break;
+        if (__all_sync(B200_FULL_MASK, exhausted && !active && !(TAIL && have_done))) break;
     }
     if (n_ksw) {
         atomicAdd(&P.stats[CNT_KSW], (unsigned long long)n_ksw);
@@ -445,11 +476,23 @@ int launch_ext2_dp8(const Ext2Params &p, int round, int bin, int n_groups, int g
 {
     const size_t smem = ext2_dp8_smem(n_groups);
 #ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    B200_CHECK(cudaFuncSetAttribute(ext_dp8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((ext_dp8_kernel<true, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    B200_CHECK(cudaFuncSetAttribute((ext_dp8_kernel<false, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 #endif
-    if (rowsync) B200_LAUNCH(ext_dp8_kernel<true>, grid, D8_THREADS, smem, st, p, round, bin, n_groups, phased);
-    else B200_LAUNCH(ext_dp8_kernel<false>, grid, D8_THREADS, smem, st, p, round, bin, n_groups, 0);
+    if (rowsync) B200_LAUNCH((ext_dp8_kernel<true, false>), grid, D8_THREADS, smem, st, p, round, bin, n_groups, phased);
+    else B200_LAUNCH((ext_dp8_kernel<false, false>), grid, D8_THREADS, smem, st, p, round, bin, n_groups, 0);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
+// the rest of the chunk in one launch: every job of `round` and every later seed of their reads (p.tail_jobs: one slot per lane)
+int launch_ext2_dp8_tail(const Ext2Params &p, int round, int n_groups, int grid, cudaStream_t st)
+{
+    const size_t smem = ext2_dp8_smem(n_groups);
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute((ext_dp8_kernel<true, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#endif
+    B200_LAUNCH((ext_dp8_kernel<true, true>), grid, D8_THREADS, smem, st, p, round, 2, n_groups, 0);
     B200_CHECK(cudaGetLastError());
     return 0;
 }

@@ -337,6 +337,17 @@ static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, in
             B200_CHECK(cudaMemcpyAsync(nj, XP.njobs + 8 * round, 12, cudaMemcpyDeviceToHost, st));
             B200_CHECK(cudaStreamSynchronize(st));
             if (nj[0] + nj[1] + nj[2] == 0) break;
+            if (dp8 && ctx->ext_tail > 0 && nj[0] + nj[1] + nj[2] <= (unsigned)ctx->ext_tail) {      // few jobs left: one launch finishes the chunk (ext3.cu, TAIL)
+                const int n_groups = (ctx->max_len >> 3) + 1;
+                const int dp_per_sm = std::max(1, std::min(8, (int)((200 * 1024) / (ext2_dp8_smem(n_groups) + 1024))));
+                const int grid = std::max(1, std::min((int)((nj[0] + nj[1] + nj[2] + 63) / 64), ctx->n_sms * dp_per_sm));
+                if (ctx->d_pe.ensure((size_t)grid * 64 * sizeof(ExtJob))) return -1;
+                XP.tail_jobs = (ExtJob *)ctx->d_pe.p;
+                if (launch_ext2_dp8_tail(XP, round, n_groups, grid, st)) return -1;
+                ++launches;
+                ctx->stats[CNT_DP8] += nj[0] + nj[1] + nj[2];
+                break;
+            }
             if (XP.perm) {                                                   // hand jobs out by shape (ext3.cu)
                 if (launch_ext2_sort(XP, round, (int)(nj[0] + nj[1] + nj[2]), ctx->n_sms, st)) return -1;
                 launches += 3;

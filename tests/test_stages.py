@@ -279,6 +279,14 @@ def test_align_general_extension_kernel(backend):
     finally:
         ctx.tune("ext_path", 0)
     r2, n2 = ctx.align(opt, seqs, off)
+    for tail in (0, 40, 1 << 30):                    # rounds only / rounds, then one tail launch once <= 40 jobs remain / tail from round 0
+        ctx.tune("ext_tail", tail)
+        try:
+            r6, n6 = ctx.align(opt, seqs, off)
+        finally:
+            ctx.tune("ext_tail", 16384)
+        assert np.array_equal(n0, n6) and r0.tobytes() == r6.tobytes(), tail
+    ctx.tune("ext_tail", 0)                          # the scheduling variants below are those of the per-round kernels
     ctx.tune("ext_rowsync", 0)                       # byte-score kernel as a one-slot-per-iteration state machine
     try:
         r3, n3 = ctx.align(opt, seqs, off)
@@ -304,6 +312,7 @@ def test_align_general_extension_kernel(backend):
         finally:
             ctx.tune(key, 1)
         assert np.array_equal(n0, n4) and r0.tobytes() == r4.tobytes()
+    ctx.tune("ext_tail", 16384)
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
     assert np.array_equal(n0, n2) and r0.tobytes() == r2.tobytes()
     assert np.array_equal(n0, n3) and r0.tobytes() == r3.tobytes()
