@@ -450,7 +450,7 @@ def run_ours(a, world, cores, barrier):
         "smem_lookups_per_sec": cnt["extend"] / (smem_ms * 1e-3) * N if smem_ms > 0 else None,
         "setup": {"index": "cached .pac -> b200_index_build_device on device 0, b200_index_replicate (peer copy) to the others", "index_build_s": t_index,
                   "index_fanout_s": t_fanout, "read_sim_s": t_reads,
-                  "seq_len": hidx.seq_len, "wall_value_phase_s": wall_value, "setup_s": None},
+                  "seq_len": hidx.seq_len, "wall_value_phase_s": wall_value, "total_wall_s": None},
     }
     # ---------------- checks against the reference CPU code on a sample (and the CPU baseline at N = 1)
     n_chk = min(a.check, a.reads)
@@ -489,7 +489,7 @@ def run_ours(a, world, cores, barrier):
             out_rec["sub_records"] = bench_sub.run(a, ctxs[0], hidx, pac, cores)
         except Exception as e:  # noqa: BLE001
             out_rec["sub_records"] = {"error": str(e)[:500]}
-    out_rec["setup"]["setup_s"] = time.time() - t_setup
+    out_rec["setup"]["total_wall_s"] = time.time() - t_setup
     print(json.dumps(out_rec))
     for c in e2e_ctxs[::-1]:
         c.close()

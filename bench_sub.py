@@ -44,6 +44,15 @@ def long_reads(a, ctx, hidx, pac, cores, n_reads=100_000, n_check=300):
            "reads_per_s": n_reads / (st[5] * 1e-3), "bases_per_s": float(off[-1]) / (st[5] * 1e-3), "ms": st[5],
            "stage_ms": dict(zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], [float(x) for x in st])),
            "ksw_extend2_gcups": c["cells"] / (st[4] * 1e-3) / 1e9 if st[4] > 0 else None, "regions": c["regs"], "read_sim_s": t_sim}
+    # reads in host memory -> SAM text in host memory (worker2 of long regions: one region per warp, reg2aln_warp_kernel)
+    from bwa_mem_gpu_b200 import lib as L
+    nf, no = L.numbered_names(b"lr", 0, n_reads)
+    L.reads_to_sam([ctx], opt, hidx.names, seqs, off, nf, no, want_off=False)
+    t0 = time.perf_counter()
+    sam, _, stt = L.reads_to_sam([ctx], opt, hidx.names, seqs, off, nf, no, want_off=False)
+    dt = time.perf_counter() - t0
+    rec["reads_to_sam"] = {"reads_per_s": n_reads / dt, "seconds": dt, "sam_bytes": int(len(sam)), "worker1_s": stt[1], "worker2_and_text_s": stt[2],
+                           "call": "b200_reads_to_sam (pageable host buffers)"}
     idx = _ref_index(pac_c, meta, bwt, sa, a.contigs, a.contig_len)
     if idx is not None:
         m = min(n_check, n_reads)
@@ -54,8 +63,13 @@ def long_reads(a, ctx, hidx, pac, cores, n_reads=100_000, n_check=300):
         r1, c1 = ctx.align(opt, seqs, sub_off)
         rec["parity_sample"] = {"reads": int(m), "regions": int(c0.sum()),
                                 "identical_to_reference": bool(np.array_equal(c0, c1) and r0.tobytes() == r1.tobytes())}
+        o2 = abi.default_opt(); o2.n_threads = cores
+        exp = idx.process_seqs(o2, synth.to_ascii(seqs[: int(off[m])]), sub_off, names=[f"lr{i}" for i in range(m)])
+        got, _, _ = L.reads_to_sam([ctx], opt, hidx.names, seqs, sub_off, nf, no, want_off=False)
+        rec["parity_sample"]["sam_identical_to_reference"] = bool(got.tobytes() == exp)
         rec["cpu_baseline"] = {"value": m / dt, "unit": "reads/s", "cores": cores, "kind": "reference",
-                               "sample": f"first {m} reads, mem_align1_core via kt_for, {dt:.2f} s"}
+                               "sample": f"first {m} reads, mem_align1_core via kt_for, {dt:.2f} s",
+                               "e2e_value": m / idx.last_process_seqs_s, "e2e_sample": f"mem_process_seqs (reads -> SAM) {idx.last_process_seqs_s:.2f} s"}
     return rec
 
 

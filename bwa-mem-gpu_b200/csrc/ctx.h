@@ -76,6 +76,7 @@ struct b200_ctx {
     DevBuf d_sam[28];                          // device SAM formatter / reads -> SAM driver (reads2sam.cu)
     cudaEvent_t sam_ev[2] = { nullptr, nullptr };  // D2H copies of the two text buffers
     DevBuf d_r2a[18];                          // b200_reg2aln_batch / b200_reg2sam_se_batch (reg2aln.cu)
+    int r2a_warp = 1;                          // reg2aln: regions with a query part > 400 bases go to the warp-per-region kernel (tunable)
     int r2a_small = 1;                         // reg2aln pass 1 with ring-sized H / E rows (tunable)
     int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
     void *pin_p[12] = {}; size_t pin_cap[12] = {};   // page-locked host buffers of b200_align_sam_se_batch (b200_ctx_pinned)

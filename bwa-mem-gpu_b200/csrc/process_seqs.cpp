@@ -2,8 +2,8 @@
 // every read, bwamem.c:1183-1195), the batch's mem_pestat (bwamem_pair.c:72), mate rescue (:291-302), worker2 (mem_mark_primary_se,
 // mem_pair, the MAPQ arithmetic and flags of mem_sam_pe, mem_reg2aln, bwamem.c:1197-1213) and the SAM text (mem_aln2sam) -- runs
 // on the device(s) through b200_reads_to_sam (csrc/reads2sam.cu); no function of the host program is used.
-// b200_process_seqs_host_worker2(1) selects the older route, kept for single-end batches of long reads (the device worker2 maps one
-// region to one lane) and as a cross-check: worker1 and mate rescue on the device, then the REFERENCE's own host functions
+// b200_process_seqs_host_worker2(1) selects the older route, kept as a cross-check: worker1 and mate rescue on the device, then the
+// REFERENCE's own host functions
 // (mem_pestat, mem_mark_primary_se / mem_reg2sam / mem_sam_pe with MEM_F_NO_RESCUE), which this library does not contain: those
 // symbols are resolved from the host program the library is linked into (weak references, or the global symbol scope).
 // Nothing here computes alignments on the CPU; if that route is selected and the host functions are missing the call fails loudly.
@@ -63,12 +63,10 @@ static inline uint8_t nt4_of(uint8_t c)
 static std::vector<b200_ctx_t *> g_ps_ctxs;
 static const bwt_t *g_ps_bwt = nullptr;
 static int g_ps_want_devices = 1;
-// worker2 of single-end batches: 0 = on the device, 1 = the host program's functions, -1 (default) = on the device unless
-// the batch holds long reads AND the host program has the functions: reg2aln_kernel maps one region to one lane, which
-// is the right shape for 100-300 bp reads (17.7 M reads/s) but not for kbp reads with bands of hundreds of columns
-// (profiles/r3q_long_sam.json: 0.9 k reads/s on the device vs 0.4 k per host thread) -- see DESIGN.md section 8
+// worker2: 0 or -1 (default) = on the device -- long regions too since reg2aln_warp_kernel (one region per warp;
+// profiles/r5d_long_sam.jsonl: 50 000 reads of 1-10 kbp in 0.8 s, was 36 s with one region per lane); 1 = the host
+// program's functions (kept as a cross-check)
 static int g_ps_host_worker2 = -1;
-#define PS_LONG_READ 1000
 extern "C" void b200_process_seqs_host_worker2(int on) { g_ps_host_worker2 = on; }
 // read group id for the RG:Z tag (the host program's bwa_rg_id, bwa.c:44); unset: looked up as a dynamic symbol of the host program
 static const char *g_ps_rg = nullptr;
@@ -110,13 +108,7 @@ extern "C" void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, co
                                       int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0)
 {
     const bool pe = (opt->flag & MEM_F_PE) != 0;
-    bool dev_worker2 = g_ps_host_worker2 <= 0;             // pairs too: mem_pestat / mem_pair / mem_sam_pe are csrc/reads2sam.cu + finalize_pe.cuh
-    if (dev_worker2 && g_ps_host_worker2 < 0 && !pe) {
-        int mx = 0;
-        for (int i = 0; i < n; ++i) mx = seqs[i].l_seq > mx ? seqs[i].l_seq : mx;
-        const bool host_has = (mem_mark_primary_se || dlsym(RTLD_DEFAULT, "mem_mark_primary_se")) && (mem_reg2sam || dlsym(RTLD_DEFAULT, "mem_reg2sam"));
-        if (mx > PS_LONG_READ && host_has) dev_worker2 = false;
-    }
+    const bool dev_worker2 = g_ps_host_worker2 <= 0;       // everything on the device(s) unless the host program's worker2 was asked for explicitly
     mark_fn f_mark = dev_worker2 ? nullptr : (mark_fn)host_symbol((void *)mem_mark_primary_se, "mem_mark_primary_se");
     reg2sam_fn f_reg2sam = dev_worker2 ? nullptr : (reg2sam_fn)host_symbol((void *)mem_reg2sam, "mem_reg2sam");
     sam_pe_fn f_sam_pe = (pe && !dev_worker2) ? (sam_pe_fn)host_symbol((void *)mem_sam_pe, "mem_sam_pe") : nullptr;

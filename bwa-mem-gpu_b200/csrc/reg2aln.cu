@@ -36,7 +36,10 @@ struct R2AParams {
     int q_words;
     int he_smem;                         // H / E rows in shared memory (2 * he_cap * 64 ints per block)
     const b200_sel_t *sel;               // b200_reg2sam_se_batch: which regions reach the SAM (null: all)
+    int warp_list;                       // 1: regions with a query part longer than R2A_WARP_LQ are listed for reg2aln_warp_kernel (list 4)
 };
+
+#define R2A_WARP_LQ 400
 
 #define R2A_MINUS_INF (-0x40000000)
 
@@ -264,7 +267,8 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
         const bool ok = lq > 0 && rb < re && !(rb < l_pac && re > l_pac);      // bwa.c:272
         const bool rev = rb >= l_pac;
         if (P.pass == 0 && ok && !(lq == rlen && (w2 < opt.w << 2 ? w2 : opt.w << 2) == 0)) {   // needs ksw_global2: second pass
-            const int cls = w2 <= 12 ? 0 : w2 <= 18 ? 1 : w2 <= 26 ? 2 : 3;
+            // long regions: one per warp (reg2aln_warp_kernel); the others by inferred band, one per lane
+            const int cls = lq > R2A_WARP_LQ && P.warp_list ? 4 : w2 <= 12 ? 0 : w2 <= 18 ? 1 : w2 <= 26 ? 2 : 3;
             P.dp_list[cls * (size_t)P.dp_stride + atomicAdd(P.dp_n + cls, 1u)] = (i32)g;
             continue;
         }
@@ -331,6 +335,143 @@ __global__ void __launch_bounds__(64) reg2aln_kernel(R2AParams P)
             if (ar.secondary >= 0) a.sub = -1;
         }
         P.aln[g] = a;
+    }
+    if (ovf) atomicMax(P.overflow, ovf);
+}
+
+#include "reg2aln_warp.cuh"
+
+// mem_reg2aln (bwamem.c:1099-1169) for the regions of list 4: one region per warp.  The scalar decisions are those of
+// reg2aln_kernel (every lane computes them, they are warp-uniform); the DP is r2a_global2_warp; lane 0 does the rest.
+__global__ void __launch_bounds__(128) reg2aln_warp_kernel(R2AParams P)
+{
+    __shared__ int8_t s_mat[25];
+    if (threadIdx.x < 25) s_mat[threadIdx.x] = P.opt.mat[threadIdx.x];
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31;
+    const size_t wi = (size_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    i32 *H = P.he + wi * 2 * (size_t)P.he_cap, *E = H + P.he_cap;
+    u8 *z = P.z + wi * (size_t)P.z_cap;
+    const mem_opt_t &opt = P.opt;
+    const DevIndex &ix = P.ix;
+    const i64 l_pac = ix.l_pac;
+    const unsigned n_list = P.dp_n[4];
+    int ovf = 0;
+    for (;;) {
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(P.work_counter, 1u);
+        t = __shfl_sync(B200_FULL_MASK, t, 0);
+        if (t >= n_list) break;
+        const unsigned g = (unsigned)P.dp_list[4 * (size_t)P.dp_stride + t];
+        const mem_alnreg_t ar = P.regs[g];
+        const int r = P.reg_read[g];
+        const u8 *query = P.seq + P.off[r];
+        const int l_seq = (int)(P.off[r + 1] - P.off[r]);
+        u32 *cigar = P.cig + (size_t)g * P.cig_stride;
+        R2AMd md; md.s = P.md + (size_t)g * P.md_stride; md.l = 0; md.cap = P.md_stride; md.ovf = &ovf;
+        b200_aln_t a;
+        memset(&a, 0, sizeof(a));
+        const int qb = ar.qb, qe = ar.qe;
+        const i64 rb = ar.rb, re = ar.re;
+        if (ar.secondary >= 0) a.flag |= 0x100;
+        int tmp = r2a_infer_bw(qe - qb, (int)(re - rb), ar.truesc, opt.a, opt.o_del, opt.e_del);
+        int w2 = r2a_infer_bw(qe - qb, (int)(re - rb), ar.truesc, opt.a, opt.o_ins, opt.e_ins);
+        w2 = w2 > tmp ? w2 : tmp;
+        if (w2 > opt.w) w2 = w2 < ar.w ? w2 : ar.w;
+        int n_cigar = 0, NM = -1, score = 0, last_sc = -(1 << 30), it = 0;
+        const int lq = qe - qb;
+        const i64 rlen = re - rb;
+        const bool ok = lq > 0 && rb < re && !(rb < l_pac && re > l_pac);      // bwa.c:272
+        const bool rev = rb >= l_pac;
+        do {
+            w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
+            n_cigar = 0; NM = -1;
+            if (ok) {
+                // bwa_gen_cigar2 (bwa.c:261-347): band as in r2a_gen_cigar2, the DP across the warp, NM / MD by lane 0
+                int max_ins = (int)((double)(((lq + 1) >> 1) * s_mat[0] - opt.o_ins) / opt.e_ins + 1.);
+                int max_del = (int)((double)(((lq + 1) >> 1) * s_mat[0] - opt.o_del) / opt.e_del + 1.);
+                int max_gap = max_ins > max_del ? max_ins : max_del;
+                max_gap = max_gap > 1 ? max_gap : 1;
+                const int dl = (int)rlen > lq ? (int)rlen - lq : lq - (int)rlen;
+                int w = (max_gap + dl + 1) >> 1;
+                w = w < w2 ? w : w2;
+                const int min_w = dl + 3;
+                w = w > min_w ? w : min_w;
+                if (lq + 2 > P.he_cap) { ovf = 2; score = 0; }
+                else if (lq == rlen && w2 == 0) {                               // no gap (cannot be listed here, kept for completeness)
+                    if (lane == 0 && P.cig_stride > 0) cigar[0] = (u32)lq << 4;
+                    n_cigar = 1; score = 0;
+                    for (int i = 0; i < lq; ++i) score += s_mat[(rev ? RefSeqRev{&ix, rb, rlen}(i) : RefSeqFwd{&ix, rb}(i)) * 5 + (rev ? SeqRev{query + qb, lq}(i) : SeqFwd{query + qb}(i))];
+                } else if (rev) score = r2a_global2_warp(lq, SeqRev{query + qb, lq}, (int)rlen, RefSeqRev{&ix, rb, rlen}, s_mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+                                                         w, H, E, z, P.z_cap, cigar, P.cig_stride, n_cigar, &ovf);
+                else score = r2a_global2_warp(lq, SeqFwd{query + qb}, (int)rlen, RefSeqFwd{&ix, rb}, s_mat, opt.o_del, opt.e_del, opt.o_ins, opt.e_ins,
+                                              w, H, E, z, P.z_cap, cigar, P.cig_stride, n_cigar, &ovf);
+            }
+            if (score == last_sc || w2 == opt.w << 2) break;
+            last_sc = score;
+            w2 <<= 1;
+        } while (++it < 3 && score < ar.truesc - opt.a);
+        if (lane == 0) {
+            if (ok) {                                                          // NM and MD (bwa.c:311-338)
+                int x = 0, y = 0, u = 0, n_mm = 0, n_gap = 0;
+                const int nc = n_cigar < P.cig_stride ? n_cigar : P.cig_stride;
+                for (int k = 0; k < nc; ++k) {
+                    const int op = (int)(cigar[k] & 0xf), len = (int)(cigar[k] >> 4);
+                    if (op == 0) {
+                        for (int i = 0; i < len; ++i) {
+                            const int rc = rev ? RefSeqRev{&ix, rb, rlen}(y + i) : RefSeqFwd{&ix, rb}(y + i);
+                            const int qc = rev ? SeqRev{query + qb, lq}(x + i) : SeqFwd{query + qb}(x + i);
+                            if (qc != rc) { md.putw(u); md.putc_((rev ? "TGCAN" : "ACGTN")[rc]); ++n_mm; u = 0; }
+                            else ++u;
+                        }
+                        x += len; y += len;
+                    } else if (op == 2) {
+                        if (k > 0 && k < n_cigar - 1) {
+                            md.putw(u); md.putc_('^');
+                            for (int i = 0; i < len; ++i) {
+                                const int rc = rev ? RefSeqRev{&ix, rb, rlen}(y + i) : RefSeqFwd{&ix, rb}(y + i);
+                                md.putc_((rev ? "TGCAN" : "ACGTN")[rc]);
+                            }
+                            u = 0; n_gap += len;
+                        }
+                        y += len;
+                    } else if (op == 1) { x += len; n_gap += len; }
+                }
+                md.putw(u);
+                NM = n_mm + n_gap;
+            }
+            a.NM = NM;
+            int is_rev;
+            i64 pos = dev_depos(ix, rb < l_pac ? rb : re - 1, &is_rev);
+            a.is_rev = is_rev;
+            const int cap = P.cig_stride;
+            if (n_cigar > 0 && n_cigar <= cap) {                                       // squeeze out leading or trailing deletions
+                if ((cigar[0] & 0xf) == 2) {
+                    pos += cigar[0] >> 4;
+                    --n_cigar;
+                    for (int k = 0; k < n_cigar; ++k) cigar[k] = cigar[k + 1];
+                } else if ((cigar[n_cigar - 1] & 0xf) == 2) --n_cigar;
+            }
+            if (qb != 0 || qe != l_seq) {                                              // add clipping to CIGAR
+                const int clip5 = is_rev ? l_seq - qe : qb, clip3 = is_rev ? qb : l_seq - qe;
+                if (n_cigar + 2 > cap) ovf = 1;
+                else {
+                    if (clip5) { for (int k = n_cigar; k > 0; --k) cigar[k] = cigar[k - 1]; cigar[0] = (u32)clip5 << 4 | 3; ++n_cigar; }
+                    if (clip3) cigar[n_cigar++] = (u32)clip3 << 4 | 3;
+                }
+            }
+            a.n_cigar = n_cigar; a.l_md = md.l;
+            a.rid = dev_pos2rid(ix, pos);
+            a.pos = pos - (a.rid >= 0 ? ix.ann_off[a.rid] : 0);
+            a.score = ar.score; a.sub = ar.sub > ar.csub ? ar.sub : ar.csub;
+            a.is_alt = ar.is_alt; a.alt_sc = ar.alt_sc;
+            if (P.sel) {                                                               // mem_reg2sam, bwamem.c:1035-1038
+                a.flag |= P.sel[g].flag;
+                if (ar.secondary >= 0) a.sub = -1;
+            }
+            P.aln[g] = a;
+        }
+        __syncwarp();
     }
     if (ovf) atomicMax(P.overflow, ovf);
 }
@@ -411,8 +552,15 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     }
     const int max_len = std::max(1, ctx->max_len);
     const int w4 = (opt->w << 2) + 64;
-    const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = max_len + 2;
-    const i64 z_cap = (((i64)(std::min(max_len, 2 * w4 + 1) + 7) / 8 * 4) * ((i64)max_len + w4) + 15) / 16 * 16;   // 4 bits per cell, rows padded to words
+    // regions with a query part longer than R2A_WARP_LQ go to the warp-per-region kernel (tunable r2a_warp = 0: never); the
+    // lane-per-region passes then only see short regions, and their rows / traceback scratch are sized for those
+    const bool use_warp = ctx->r2a_warp && max_len > R2A_WARP_LQ;
+    const int ml_lane = use_warp ? R2A_WARP_LQ : max_len;
+    const int cig_stride = 2 * max_len + 8, md_stride = 3 * max_len + 64, he_cap = ml_lane + 2;
+    auto zcap_of = [&](int ml) { return (((i64)(std::min(ml, 2 * w4 + 1) + 7) / 8 * 4) * ((i64)ml + w4) + 15) / 16 * 16; };   // 4 bits per cell, rows padded to words
+    const i64 z_cap = zcap_of(ml_lane);
+    const int he_cap_w = max_len + 2;
+    const i64 z_cap_w = zcap_of(max_len);
     const size_t per_reg = (size_t)cig_stride * 4 + md_stride + sizeof(b200_aln_t) + sizeof(mem_alnreg_t) + 32;
     const int chunk = (int)std::max<i64>(std::max(1024, 2 * max_cnt), std::min<i64>((i64)1 << 20, ((i64)6 << 30) / (i64)per_reg));
     const size_t per_lane = (size_t)z_cap + (size_t)he_cap * 8;
@@ -426,18 +574,26 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     }
     const i64 lanes_fit = std::max<i64>(64, z_budget / (i64)per_lane);
     const int grid_max = (int)std::max<i64>(1, std::min<i64>((i64)ctx->n_sms * 8, lanes_fit / 64));
+    int n_warps = 0;                                        // warps of reg2aln_warp_kernel: each needs a full-size traceback area
+    if (use_warp) {
+        size_t mem_free = 0, mem_total = 0;
+        i64 budget = (i64)16 << 30;
+        if (cudaMemGetInfo(&mem_free, &mem_total) == cudaSuccess) budget = std::min<i64>(budget, (i64)(mem_free + ctx->d_r2a[6].bytes) / 2);
+        n_warps = (int)std::max<i64>(4, std::min<i64>((i64)ctx->n_sms * 8, budget / (z_cap_w + (i64)he_cap_w * 8))) & ~3;
+    }
     // grow-only buffers kept in the context: a second call of the same shape allocates nothing
     DevBuf &d_regs = ctx->d_r2a[0], &d_rr = ctx->d_r2a[1], &d_aln = ctx->d_r2a[2], &d_cig = ctx->d_r2a[3], &d_md = ctx->d_r2a[4],
            &d_he = ctx->d_r2a[5], &d_z = ctx->d_r2a[6], &d_nc = ctx->d_r2a[7], &d_lm = ctx->d_r2a[8], &d_co = ctx->d_r2a[9],
            &d_mo = ctx->d_r2a[10], &d_tmp = ctx->d_r2a[11], &d_pool_c = ctx->d_r2a[12], &d_pool_m = ctx->d_r2a[13];
     if (d_regs.ensure((size_t)chunk * sizeof(mem_alnreg_t)) || d_rr.ensure((size_t)chunk * 4) || d_aln.ensure((size_t)chunk * sizeof(b200_aln_t)) ||
         d_cig.ensure((size_t)chunk * cig_stride * 4) || d_md.ensure((size_t)chunk * md_stride) ||
-        d_he.ensure((size_t)grid_max * 64 * he_cap * 8) || d_z.ensure((size_t)grid_max * 64 * (size_t)z_cap) ||
+        d_he.ensure(std::max((size_t)grid_max * 64 * he_cap * 8, (size_t)n_warps * he_cap_w * 8)) ||
+        d_z.ensure(std::max((size_t)grid_max * 64 * (size_t)z_cap, (size_t)n_warps * (size_t)z_cap_w)) ||
         d_nc.ensure((size_t)chunk * 4) || d_lm.ensure((size_t)chunk * 4) || d_co.ensure(((size_t)chunk + 1) * 8) ||
         d_mo.ensure(((size_t)chunk + 1) * 8) || d_tmp.ensure(((size_t)chunk / 1024 + 2) * 8) ||
         d_pool_c.ensure((size_t)chunk * cig_stride * 4) || d_pool_m.ensure((size_t)chunk * md_stride) || ctx->d_ctl.ensure(CTL_SLOTS * 8)) return -1;
     DevBuf &d_roff = ctx->d_r2a[14], &d_sel = ctx->d_r2a[15], &d_log = ctx->d_r2a[16], &d_dp = ctx->d_r2a[17];
-    if (d_dp.ensure(((size_t)4 * chunk + 8) * 4)) return -1;
+    if (d_dp.ensure(((size_t)5 * chunk + 8) * 4)) return -1;
     if (finalize) {
         if (d_roff.ensure(((size_t)n_reads + 1) * 8) || d_sel.ensure((size_t)chunk * sizeof(b200_sel_t))) return -1;
         B200_CHECK(cudaMemcpyAsync(d_roff.p, roff.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
@@ -505,7 +661,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         P.aln = d_aln.as<b200_aln_t>(); P.cig = d_cig.as<u32>(); P.cig_stride = cig_stride; P.md = d_md.as<char>(); P.md_stride = md_stride;
         P.he = d_he.as<i32>(); P.he_cap = he_cap; P.z = d_z.as<u8>(); P.z_cap = z_cap;
         P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK); P.overflow = (int *)(ctx->d_ctl.as<u64>() + CTL_OVF2);
-        P.dp_list = d_dp.as<i32>(); P.dp_stride = chunk; P.dp_n = (unsigned *)(d_dp.as<i32>() + (size_t)4 * chunk); P.pass = 0;
+        P.dp_list = d_dp.as<i32>(); P.dp_stride = chunk; P.dp_n = (unsigned *)(d_dp.as<i32>() + (size_t)5 * chunk); P.pass = 0;
+        P.warp_list = use_warp ? 1 : 0;
         B200_CHECK(cudaMemsetAsync(P.dp_n, 0, 32, st));
         tmark(1);
         if (finalize) {
@@ -535,6 +692,12 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
             P0.he_smem = 0; P0.q_words = 0;
             const int grid0 = std::max(1, std::min(ctx->n_sms * 14, (n + 63) / 64));       // 72 registers, no scratch: 14 blocks per SM
             B200_LAUNCH(reg2aln_kernel<0>, grid0, 64, 0, st, P0);
+        }
+        if (use_warp) {                                     // the long regions pass 0 listed: one per warp
+            R2AParams W = P;
+            W.he_cap = he_cap_w; W.z_cap = z_cap_w; W.he_smem = 0; W.q_words = 0;
+            W.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_RETRY);
+            B200_LAUNCH(reg2aln_warp_kernel, n_warps / 4, 128, 0, st, W);
         }
         tmark(3);
         P.pass = 1; P.work_counter = (unsigned *)(ctx->d_ctl.as<u64>() + CTL_WORK2);

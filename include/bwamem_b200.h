@@ -416,13 +416,13 @@ int b200_microbench(b200_ctx_t *ctx, int kind, int64_t table_bytes, int blocks_p
  * device code on a batch of one (parity tests call these one problem at a time).  The device
  * context/index is created lazily from the bwt_t identity on first use.
  * ===================================================================================== */
-/* mem_process_seqs (bwamem.h:69, bwamem.c:1215): worker1 on the device.  Single-end batches: worker2 on the device
- * too (b200_reg2sam_se_batch) and the SAM text from b200_sam_se_format -- no function of the host program is needed
- * (RG tag: the host program's global bwa_rg_id, if it has one).  Paired-end batches, batches with reads longer than
- * 1000 bp when the host program has the functions (the device worker2 maps one region to one lane: built for short
- * reads), or after b200_process_seqs_host_worker2(1): the REFERENCE's own host code for mem_pestat / worker2 (mem_mark_primary_se,
- * mem_reg2sam, mem_sam_pe), resolved from the program this library is linked into.  seqs[i].sam is heap memory
- * owned by the caller, as in the reference.
+/* mem_process_seqs (bwamem.h:69, bwamem.c:1215) with everything on the device(s): worker1, the batch's mem_pestat (a host
+ * reduction over device-made per-pair summaries), mate rescue, worker2 (mem_mark_primary_se, mem_pair, the MAPQ arithmetic and
+ * flags of mem_sam_pe, mem_reg2aln) and the SAM text, through b200_reads_to_sam; no function of the host program is needed
+ * (RG tag: b200_process_seqs_set_rg_id, else the host program's global bwa_rg_id if it is a dynamic symbol).
+ * b200_process_seqs_host_worker2(1) selects the older route instead: worker1 and mate rescue on the device, then the
+ * REFERENCE's own host code for mem_pestat / worker2 (mem_mark_primary_se, mem_reg2sam, mem_sam_pe), resolved from the program
+ * this library is linked into (a cross-check).  seqs[i].sam is heap memory owned by the caller, as in the reference.
  * b200_process_seqs_set_ctx() selects an existing context (index already uploaded); otherwise one is created on
  * device 0 from (bwt, bns, pac) at the first call. */
 void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
@@ -432,7 +432,7 @@ void b200_process_seqs_set_ctx(b200_ctx_t *ctx);
 void b200_process_seqs_set_ctxs(int n, b200_ctx_t **ctxs);
 void b200_process_seqs_use_devices(int n_devices);
 void b200_process_seqs_set_rg_id(const char *rg_id);   /* the host program's bwa_rg_id (bwa.c:44, set by -R) for the RG:Z tag; the pointer is kept */
-void b200_process_seqs_host_worker2(int on);   /* 0 device, 1 host program, -1 (default) device unless the batch has reads > 1000 bp and the host program has worker2 */
+void b200_process_seqs_host_worker2(int on);   /* 0 / -1 (default): worker2 and SAM on the device; 1: the host program's worker2 */
 void b200_mem_process_seqs(const mem_opt_t *opt, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac,
                            int64_t n_processed, int n, bseq1_t *seqs, const mem_pestat_t *pes0);
 

@@ -10,6 +10,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--small", action="store_true")
 ap.add_argument("--reads", type=int, default=50000)
 ap.add_argument("--set", action="append", default=[])
+ap.add_argument("--sam", action="store_true", help="also time reads -> SAM text (b200_reads_to_sam) and check a sample against the reference")
 a = ap.parse_args()
 a.contigs, a.contig_len = (4, 25_000_000) if a.small else (24, 129_166_667)
 d = bench.ensure_index_cache(a)
@@ -29,7 +30,30 @@ for s in a.set or [""]:
     st = ctx.batch_run(opt, want_stage_ms=True)
     c = ctx.counters()
     base = base or c["regs"]
-    print(json.dumps({"set": s, "reads": a.reads, "bases": int(off[-1]), "reads_per_s": a.reads / (st[5] * 1e-3),
+    extra = {}
+    if a.sam:
+        import time
+        nf, no = L.numbered_names(b"lr", 0, a.reads)
+        hn = [f"chr{i + 1}" for i in range(a.contigs)]
+        L.reads_to_sam([ctx], opt, hn, seqs, off, nf, no, want_off=False)
+        t0 = time.perf_counter()
+        sam, _, stt = L.reads_to_sam([ctx], opt, hn, seqs, off, nf, no, want_off=False)
+        dt = time.perf_counter() - t0
+        extra = {"reads_to_sam_s": dt, "reads_to_sam_reads_per_s": a.reads / dt, "sam_bytes": len(sam), "worker1_s": stt[1], "worker2_text_s": stt[2]}
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import refapi
+        if refapi.available() and not extra.get("checked"):
+            rl = refapi.RefLib()
+            lens = np.full(a.contigs, a.contig_len, dtype=np.int64)
+            ann_off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+            idx = rl.index_from_arrays(np.asarray(bwt), meta["primary"], meta["L2"], meta["seq_len"], np.asarray(sa), meta["sa_intv"], np.asarray(pac), meta["l_pac"], ann_off, lens.astype(np.int32))
+            m = min(300, a.reads)
+            o2 = abi.default_opt(); o2.n_threads = os.cpu_count() or 1
+            exp = idx.process_seqs(o2, synth.to_ascii(seqs[: int(off[m])]), off[: m + 1], names=[f"lr{i}" for i in range(m)])
+            extra["ref_process_seqs_reads_per_s"] = m / idx.last_process_seqs_s
+            got, _, _ = L.reads_to_sam([ctx], opt, hn, seqs, off[: m + 1], nf, no, want_off=False)
+            extra["sam_sample_identical"] = bool(got.tobytes() == exp)
+    print(json.dumps({"set": s, "reads": a.reads, **extra, "bases": int(off[-1]), "reads_per_s": a.reads / (st[5] * 1e-3),
                       "stage_ms": dict(zip(["pack", "smem", "seed_sa", "chain", "extend", "total"], [round(float(x), 1) for x in st])),
                       "regs": c["regs"], "same_regs": c["regs"] == base}), flush=True)
     ctx.close()
