@@ -185,28 +185,39 @@ void worker_pe_a(b200_ctx *ctx, int dev_index, Job *job)
 // microseconds per 10^6 pairs once the sizes are sorted.
 void pestat_host(const mem_opt_t *opt, const std::vector<u64> &isz, mem_pestat_t pes[4])
 {
-    (void)opt;
-    std::vector<u64> q[4];
+    // insert sizes are integers in [1, max_ins] (the kernel applied bwamem_pair.c:89), so "sorted order" is a histogram walk:
+    // the sums below add the values one by one in ascending order exactly as the reference does over its sorted array
+    const size_t nbin = (size_t)(opt->max_ins > 0 ? opt->max_ins : 0) + 2;
+    std::vector<u32> hist[4];
+    size_t cnt[4] = { 0, 0, 0, 0 };
     memset(pes, 0, 4 * sizeof(mem_pestat_t));
-    for (u64 v : isz) if (v) { const u64 w = v - 1; q[w & 3].push_back(w >> 2); }
+    for (int d = 0; d < 4; ++d) hist[d].assign(nbin, 0);
+    for (u64 v : isz) if (v) { const u64 w = v - 1, is = w >> 2; if (is < nbin) { ++hist[w & 3][is]; ++cnt[w & 3]; } }
     const bool verbose = getenv("B200_VERBOSE") != nullptr;
     for (int d = 0; d < 4; ++d) {
         mem_pestat_t *r = &pes[d];
-        std::vector<u64> &a = q[d];
-        if (a.size() < 10) { r->failed = 1; continue; }                    // MIN_DIR_CNT
-        std::sort(a.begin(), a.end());
-        const int p25 = (int)a[(size_t)(int)(.25 * a.size() + .499)];
-        const int p50 = (int)a[(size_t)(int)(.50 * a.size() + .499)];
-        const int p75 = (int)a[(size_t)(int)(.75 * a.size() + .499)];
+        const std::vector<u32> &h = hist[d];
+        const size_t n = cnt[d];
+        if (n < 10) { r->failed = 1; continue; }                           // MIN_DIR_CNT
+        auto at = [&](size_t idx) -> int {                                 // element idx of the sorted array
+            size_t cum = 0;
+            for (size_t v = 0; v < nbin; ++v) { cum += h[v]; if (cum > idx) return (int)v; }
+            return (int)nbin - 1;
+        };
+        const int p25 = at((size_t)(int)(.25 * n + .499));
+        const int p50 = at((size_t)(int)(.50 * n + .499));
+        const int p75 = at((size_t)(int)(.75 * n + .499));
         r->low = (int)(p25 - 2.0 * (p75 - p25) + .499);                     // OUTLIER_BOUND
         if (r->low < 1) r->low = 1;
         r->high = (int)(p75 + 2.0 * (p75 - p25) + .499);
         size_t x = 0;
         r->avg = 0;
-        for (u64 v : a) if (v >= (u64)r->low && v <= (u64)r->high) { r->avg += v; ++x; }
+        for (size_t v = 0; v < nbin; ++v)
+            if (h[v] && (i64)v >= r->low && (i64)v <= r->high) { for (u32 c = 0; c < h[v]; ++c) r->avg += (double)v; x += h[v]; }
         r->avg /= x;
         r->std = 0;
-        for (u64 v : a) if (v >= (u64)r->low && v <= (u64)r->high) r->std += (v - r->avg) * (v - r->avg);
+        for (size_t v = 0; v < nbin; ++v)
+            if (h[v] && (i64)v >= r->low && (i64)v <= r->high) { const double t = ((double)v - r->avg) * ((double)v - r->avg); for (u32 c = 0; c < h[v]; ++c) r->std += t; }
         r->std = sqrt(r->std / x);
         r->low = (int)(p25 - 3.0 * (p75 - p25) + .499);                     // MAPPING_BOUND
         r->high = (int)(p75 + 3.0 * (p75 - p25) + .499);
@@ -214,12 +225,12 @@ void pestat_host(const mem_opt_t *opt, const std::vector<u64> &isz, mem_pestat_t
         if (r->high < r->avg + 4.0 * r->std) r->high = (int)(r->avg + 4.0 * r->std + .499);
         if (r->low < 1) r->low = 1;
         if (verbose) fprintf(stderr, "[b200::mem_pestat] %c%c: %zu pairs, (25, 50, 75) percentile (%d, %d, %d), mean %.2f std %.2f, proper pairs (%d, %d)\n",
-                             "FR"[d >> 1 & 1], "FR"[d & 1], a.size(), p25, p50, p75, r->avg, r->std, r->low, r->high);
+                             "FR"[d >> 1 & 1], "FR"[d & 1], n, p25, p50, p75, r->avg, r->std, r->low, r->high);
     }
     size_t mx = 0;
-    for (int d = 0; d < 4; ++d) mx = std::max(mx, q[d].size());
+    for (int d = 0; d < 4; ++d) mx = std::max(mx, cnt[d]);
     for (int d = 0; d < 4; ++d)
-        if (pes[d].failed == 0 && (double)q[d].size() < mx * 0.05) pes[d].failed = 1;          // MIN_DIR_RATIO
+        if (pes[d].failed == 0 && (double)cnt[d] < mx * 0.05) pes[d].failed = 1;              // MIN_DIR_RATIO
 }
 
 // ---- worker2 + text of one sub-batch whose worker1 regions are resident in ctx (single-end: straight after

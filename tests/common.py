@@ -18,7 +18,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DATA = os.path.join(ROOT, "tests", "_data")
 GOLDEN = os.path.join(ROOT, "tests", "golden")
-EMU_SO = os.path.join(ROOT, "tests", "emu", "_build", "libbwamem_b200_emu.so")
+EMU_SO = os.environ.get("B200_EMU_SO") or os.path.join(ROOT, "tests", "emu", "_build", "libbwamem_b200_emu.so")      # B200_EMU_SO: e.g. the AddressSanitizer build of scripts/emu_asan.sh
 
 from bwa_mem_gpu_b200 import abi, lib as L, synth  # noqa: E402
 import refapi  # noqa: E402
