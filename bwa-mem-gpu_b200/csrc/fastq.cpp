@@ -237,7 +237,10 @@ struct HBuf {                                              // grow-only host buf
 
 struct b200_fastq {
     Stream s[2]; int n_files = 0, n_threads = 1;
-    HBuf seq, qual, name, comment, seq_off, name_off, com_off;         // the batch handed out last
+    // two sets of output buffers, used alternately: a batch stays valid until the call AFTER the next one, so a consumer can
+    // work on batch k while another thread already reads batch k + 1
+    struct Out { HBuf seq, qual, name, comment, seq_off, name_off, com_off; } out[2];
+    int parity = 0;
     bool warned = false;
 };
 
@@ -256,8 +259,10 @@ extern "C" void b200_fastq_close(b200_fastq_t *f)
 {
     if (!f) return;
     for (int k = 0; k < f->n_files; ++k) f->s[k].close();
-    HBuf *all[] = { &f->seq, &f->qual, &f->name, &f->comment, &f->seq_off, &f->name_off, &f->com_off };
-    for (HBuf *b : all) b->release();
+    for (auto &o : f->out) {
+        HBuf *all[] = { &o.seq, &o.qual, &o.name, &o.comment, &o.seq_off, &o.name_off, &o.com_off };
+        for (HBuf *b : all) b->release();
+    }
     delete f;
 }
 
@@ -355,8 +360,10 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
     const size_t per = f->n_files == 2 ? (size_t)n / 2 : (size_t)n;
     auto rec_of = [&](int64_t i) -> const Rec & { return f->n_files == 2 ? recs[i & 1][(size_t)(i >> 1)] : recs[0][(size_t)i]; };
     const size_t need_n = ((size_t)n + 1) * 8;
-    if (!f->seq_off.grow(need_n) || !f->name_off.grow(need_n) || !f->com_off.grow(need_n)) { b200_set_error("out of memory"); return -1; }
-    int64_t *seq_off = (int64_t *)f->seq_off.p, *name_off = (int64_t *)f->name_off.p, *com_off = (int64_t *)f->com_off.p;
+    b200_fastq::Out &O = f->out[f->parity];
+    f->parity ^= 1;
+    if (!O.seq_off.grow(need_n) || !O.name_off.grow(need_n) || !O.com_off.grow(need_n)) { b200_set_error("out of memory"); return -1; }
+    int64_t *seq_off = (int64_t *)O.seq_off.p, *name_off = (int64_t *)O.name_off.p, *com_off = (int64_t *)O.com_off.p;
     int64_t so = 0, no = 0, co = 0;
     bool any_qual = false, all_qual = true, any_com = false;
     for (int64_t i = 0; i < n; ++i) {
@@ -367,8 +374,8 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
     }
     seq_off[n] = so; name_off[n] = no; com_off[n] = co;
     if (any_qual && !all_qual) { b200_set_error("FASTQ batch mixes reads with and without (complete) qualities"); return -1; }
-    if (!f->seq.grow((size_t)so + 64) || (any_qual && !f->qual.grow((size_t)so + 64)) || !f->name.grow((size_t)no + 64) ||
-        !f->comment.grow((size_t)co + 64)) { b200_set_error("out of memory"); return -1; }
+    if (!O.seq.grow((size_t)so + 64) || (any_qual && !O.qual.grow((size_t)so + 64)) || !O.name.grow((size_t)no + 64) ||
+        !O.comment.grow((size_t)co + 64)) { b200_set_error("out of memory"); return -1; }
     // ---- pass 2: every thread writes its share of the records into place
     const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(f->n_threads, n / 4096));
     auto fillw = [&](int t) {
@@ -376,9 +383,9 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
         for (int64_t i = lo; i < hi; ++i) {
             const Rec &r = rec_of(i);
             const Stream &S = f->s[f->n_files == 2 ? (int)(i & 1) : 0];
-            copy_body(r, S.cur_end, f->seq.p + seq_off[i], any_qual ? f->qual.p + seq_off[i] : nullptr);
-            memcpy(f->name.p + name_off[i], r.name, (size_t)r.l_name);
-            if (r.l_comment) memcpy(f->comment.p + com_off[i], r.comment, (size_t)r.l_comment);
+            copy_body(r, S.cur_end, O.seq.p + seq_off[i], any_qual ? O.qual.p + seq_off[i] : nullptr);
+            memcpy(O.name.p + name_off[i], r.name, (size_t)r.l_name);
+            if (r.l_comment) memcpy(O.comment.p + com_off[i], r.comment, (size_t)r.l_comment);
         }
     };
     std::vector<std::thread> th;
@@ -394,7 +401,7 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
         f->s[k].consumed(next);
         if (f->s[k].plain) f->s[k].eof = false;               // plain mappings are "filled" again on the next call
     }
-    out->n_reads = n; out->seq = (const uint8_t *)f->seq.p; out->seq_off = seq_off; out->qual = any_qual ? (const uint8_t *)f->qual.p : nullptr;
-    out->name = f->name.p; out->name_off = name_off; out->comment = any_com ? f->comment.p : nullptr; out->comment_off = any_com ? com_off : nullptr;
+    out->n_reads = n; out->seq = (const uint8_t *)O.seq.p; out->seq_off = seq_off; out->qual = any_qual ? (const uint8_t *)O.qual.p : nullptr;
+    out->name = O.name.p; out->name_off = name_off; out->comment = any_com ? O.comment.p : nullptr; out->comment_off = any_com ? com_off : nullptr;
     return n;
 }

@@ -19,6 +19,7 @@
 #include <thread>
 #include <vector>
 #include <math.h>
+#include <unistd.h>
 #include "samdev.cuh"        // after the standard headers: the emulator build redefines __noinline__
 
 extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes);
@@ -420,4 +421,81 @@ extern "C" int64_t b200_reads_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
     if (stats) { stats[0] = now_s() - t0; stats[1] = job.t_align; stats[2] = job.t_worker2; stats[3] = job.t_wait; stats[4] = (double)job.n_sub; }
     if (job.placer.failed) { b200_set_error("%s", job.placer.err.c_str()); return B200_E_FAIL; }
     return job.placer.offset > cap ? -job.placer.offset : job.placer.offset;
+}
+
+// ---- FASTQ files -> SAM text on a file descriptor: the whole `bwa mem` data path (reader -> devices -> writer) in one call.
+// Three stages run concurrently, as upstream's kt_pipeline does with its three steps (fastmap.c:305): a reader thread parses
+// batch k + 1 (b200_fastq_read: chunk_bases bases per batch = bseq_read's rule, so mem_pestat sees the reference's batches),
+// the calling thread aligns batch k on the devices (b200_reads_to_sam), a writer thread writes batch k - 1.
+extern "C" int64_t b200_fastq_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const mem_opt_t *opt, const char *const *ann_names,
+                                     const char *const *ann_annos, const char *fn1, const char *fn2, int64_t chunk_bases,
+                                     const mem_pestat_t *pes0, const char *rg_id, int n_threads, int copy_comment, int out_fd, double *stats)
+{
+    b200_fastq_t *f = b200_fastq_open(fn1, fn2, n_threads);
+    if (!f) return B200_E_FAIL;
+    struct Slot { b200_reads_t R; i64 n = 0; };
+    Slot cur, next;
+    std::mutex mu; std::condition_variable cv;
+    bool next_ready = false, next_taken = true, reader_done = false, failed = false;
+    std::string err;
+    double t_read = 0, t_align = 0, t_write = 0;
+    std::thread reader([&]() {
+        for (;;) {
+            {   std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&]() { return next_taken || failed; }); if (failed) return; }
+            const double t0 = now_s();
+            b200_reads_t R;
+            const i64 n = b200_fastq_read(f, chunk_bases, &R);
+            t_read += now_s() - t0;
+            std::lock_guard<std::mutex> lk(mu);
+            if (n < 0) { failed = true; err = b200_last_error(); cv.notify_all(); return; }
+            next.R = R; next.n = n; next_ready = true; next_taken = false;
+            if (n == 0) reader_done = true;
+            cv.notify_all();
+            if (n == 0) return;
+        }
+    });
+    // two SAM buffers: the writer drains one while the devices fill the other
+    char *sam[2] = { nullptr, nullptr }; size_t cap[2] = { 0, 0 };
+    std::thread writer;
+    i64 w_bytes = 0; bool w_failed = false;
+    i64 n_processed = 0, total_bytes = 0, n_batches = 0;
+    const double t_all = now_s();
+    for (int k = 0; ; ++k) {
+        {   std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&]() { return next_ready || failed; });
+            if (failed) break;
+            cur = next; next_ready = false; next_taken = true; cv.notify_all(); }
+        if (cur.n == 0) break;
+        if (!copy_comment) { cur.R.comment = nullptr; cur.R.comment_off = nullptr; }                 // fastmap.c: comments only with -C
+        mem_opt_t o = *opt;
+        const int b = k & 1;
+        const double t0 = now_s();
+        i64 rc;
+        for (;;) {
+            const size_t want = cap[b] ? cap[b] : (size_t)(cur.R.seq_off[cur.n] * 2 + cur.n * 220 + cur.R.name_off[cur.n] + 4096);
+            if (cap[b] < want) { b200_host_free(sam[b]); sam[b] = (char *)b200_host_alloc(want); cap[b] = sam[b] ? want : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } }
+            rc = b200_reads_to_sam(ctxs, n_ctx, &o, ann_names, ann_annos, &cur.R, n_processed, pes0, rg_id, 0, (i64)cap[b], sam[b], nullptr, nullptr);
+            if (!B200_IS_ERROR(rc) && rc < 0) { b200_host_free(sam[b]); sam[b] = nullptr; cap[b] = 0; const size_t nw = (size_t)-rc + 4096; sam[b] = (char *)b200_host_alloc(nw); cap[b] = sam[b] ? nw : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } continue; }
+            break;
+        }
+        t_align += now_s() - t0;
+        if (B200_IS_ERROR(rc)) { std::lock_guard<std::mutex> lk(mu); failed = true; err = b200_last_error(); cv.notify_all(); break; }
+        if (writer.joinable()) writer.join();                   // batch k - 1 is out: its buffer (the other one) is free again
+        if (w_failed) { std::lock_guard<std::mutex> lk(mu); failed = true; err = "writing the SAM text failed"; cv.notify_all(); break; }
+        const char *p = sam[b]; const i64 nb = rc;
+        writer = std::thread([&, p, nb]() {
+            const double tw = now_s();
+            i64 done = 0;
+            while (out_fd >= 0 && done < nb) { const ssize_t w = write(out_fd, p + done, (size_t)std::min<i64>(nb - done, (i64)1 << 30)); if (w <= 0) { w_failed = true; break; } done += w; }
+            w_bytes += nb; t_write += now_s() - tw;
+        });
+        n_processed += cur.n; total_bytes += nb; ++n_batches;
+    }
+    if (writer.joinable()) writer.join();
+    {   std::lock_guard<std::mutex> lk(mu); if (!reader_done) failed = true; cv.notify_all(); }     // an early exit: release the reader
+    reader.join();
+    b200_fastq_close(f);
+    b200_host_free(sam[0]); b200_host_free(sam[1]);
+    if (stats) { stats[0] = now_s() - t_all; stats[1] = t_read; stats[2] = t_align; stats[3] = t_write; stats[4] = (double)n_batches; stats[5] = (double)total_bytes; }
+    if (!err.empty() || w_failed) { b200_set_error("%s", err.empty() ? "writing the SAM text failed" : err.c_str()); return B200_E_FAIL; }
+    return n_processed;
 }

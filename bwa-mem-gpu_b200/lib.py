@@ -26,7 +26,7 @@ _SYMBOLS = [
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
     "b200_hostidx_build", "b200_hostidx_free", "b200_hostidx_info", "b200_hostidx_bwt", "b200_hostidx_sa",
     "b200_hostidx_pac", "b200_index_upload_host", "b200_index_build_device", "b200_index_info", "b200_index_download", "b200_reg2aln_batch", "b200_reg2sam_se_batch", "b200_sam_se_format", "b200_align_sam_se_batch", "b200_host_alloc", "b200_host_free", "b200_batch_reg2sam_se", "b200_process_seqs_host_worker2", "b200_process_seqs_set_rg_id",
-    "b200_reads_to_sam", "b200_index_replicate", "b200_index_save", "b200_index_load", "b200_fastq_open", "b200_fastq_read", "b200_fastq_close", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
+    "b200_reads_to_sam", "b200_index_replicate", "b200_index_save", "b200_index_load", "b200_fastq_open", "b200_fastq_read", "b200_fastq_close", "b200_fastq_to_sam", "b200_ksw_extend2_noalloc", "b200_noalloc_scratch_bytes", "b200_noalloc_setup",
     "b200_process_seqs_set_ctx", "b200_process_seqs_set_ctxs", "b200_process_seqs_use_devices", "b200_mem_process_seqs", "mem_process_seqs",
     "bwt_occ4", "bwt_2occ4", "bwt_extend", "bwt_sa", "bwt_smem1a", "ksw_extend2", "mem_align1_core",
 ]
@@ -156,6 +156,25 @@ class FastqReader:
         if self.h:
             self.lib.b200_fastq_close(self.h)
             self.h = None
+
+
+def fastq_to_sam(ctxs, opt, ann_names, fn1, fn2=None, chunk_bases=100_000_000, out_path=None, n_threads=8, copy_comment=False, rg=None):
+    """b200_fastq_to_sam: FASTQ file(s) -> SAM records appended to out_path (None: discarded).  Returns (reads, stats)."""
+    lib = ctxs[0].lib
+    lib.b200_fastq_to_sam.restype = C.c_int64
+    a_names = (C.c_char_p * max(1, len(ann_names)))(*[s.encode() for s in ann_names])
+    hs = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    stats = (C.c_double * 8)()
+    fd = os.open(out_path, os.O_WRONLY | os.O_CREAT | os.O_APPEND, 0o644) if out_path else -1
+    try:
+        n = lib.b200_fastq_to_sam(hs, len(ctxs), C.byref(opt), a_names, None, fn1.encode(), fn2.encode() if fn2 else None,
+                                  C.c_int64(chunk_bases), None, rg.encode() if rg else None, C.c_int(n_threads),
+                                  C.c_int(1 if copy_comment else 0), C.c_int(fd), stats)
+    finally:
+        if fd >= 0:
+            os.close(fd)
+    ctxs[0]._chk(n, "fastq_to_sam")
+    return n, list(stats)
 
 
 def flat_strings(strs):

@@ -282,6 +282,16 @@ b200_fastq_t *b200_fastq_open(const char *fn1, const char *fn2 /* NULL: one file
 int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_reads_t *out);
 void b200_fastq_close(b200_fastq_t *f);
 
+/* FASTQ files -> SAM text on a file descriptor, the whole data path of `bwa mem` behind the option parsing: a reader thread
+ * (b200_fastq_read, batches of chunk_bases bases = the batches bseq_read would make, so mem_pestat sees the reference's
+ * batches), the devices (b200_reads_to_sam) and a writer thread (write(2) on out_fd; < 0 = discard) run concurrently, as the
+ * three steps of upstream's kt_pipeline do (fastmap.c:305).  copy_comment = the -C option.  Returns the number of reads, or
+ * B200_E_FAIL.  stats (may be NULL, 8 doubles): [0] wall seconds, [1] reading / parsing, [2] aligning, [3] writing,
+ * [4] batches, [5] SAM bytes. */
+int64_t b200_fastq_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const mem_opt_t *opt, const char *const *ann_names,
+                          const char *const *ann_annos, const char *fn1, const char *fn2, int64_t chunk_bases,
+                          const mem_pestat_t *pes0, const char *rg_id, int n_threads, int copy_comment, int out_fd, double *stats);
+
 /* Page-locked host memory (cudaHostAlloc) for callers that want the copies of the batched calls at full speed. */
 void *b200_host_alloc(size_t bytes);
 void b200_host_free(void *p);

@@ -173,5 +173,10 @@ def test_fastq_files_to_sam_matches_reference_program(tmp_path):
         nf, no = b["names"]
         sam, _, _ = L.reads_to_sam([ctx], opt, h.names, b["seqs"], b["off"], nf, no, quals=b["quals"], n_processed=n_processed)
         got += sam.tobytes(); n_processed += b["n"]
-    r.close(); ctx.close()
+    r.close()
     assert got == exp_body
+    # the same as one streaming call: reader thread | devices | writer thread
+    out = str(tmp_path / "out.sam")
+    n, st = L.fastq_to_sam([ctx], opt, h.names, str(tmp_path / "p1.fq"), str(tmp_path / "p2.fq"), chunk_bases=chunk, out_path=out, n_threads=4)
+    assert n == 8000 and open(out, "rb").read() == exp_body and st[4] >= 2
+    ctx.close()
