@@ -21,6 +21,7 @@
 #include <unistd.h>
 #include <zlib.h>
 #include <algorithm>
+#include <functional>
 #include <string>
 #include <thread>
 #include <vector>
@@ -242,12 +243,13 @@ struct b200_fastq {
     struct Out { HBuf seq, qual, name, comment, seq_off, name_off, com_off; } out[2];
     int parity = 0;
     bool warned = false;
+    Rec *recs[2] = { nullptr, nullptr }; size_t recs_cap[2] = { 0, 0 }, n_recs[2] = { 0, 0 };     // records indexed for the current call
 };
 
 extern "C" b200_fastq_t *b200_fastq_open(const char *fn1, const char *fn2, int n_threads)
 {
     b200_fastq *f = new b200_fastq();
-    f->n_threads = n_threads > 0 ? n_threads : 1;
+    f->n_threads = n_threads > 0 ? (n_threads < 64 ? n_threads : 64) : 1;
     f->n_files = fn2 ? 2 : 1;
     const char *fn[2] = { fn1, fn2 };
     for (int k = 0; k < f->n_files; ++k)
@@ -259,6 +261,7 @@ extern "C" void b200_fastq_close(b200_fastq_t *f)
 {
     if (!f) return;
     for (int k = 0; k < f->n_files; ++k) f->s[k].close();
+    free(f->recs[0]); free(f->recs[1]);
     for (auto &o : f->out) {
         HBuf *all[] = { &o.seq, &o.qual, &o.name, &o.comment, &o.seq_off, &o.name_off, &o.com_off };
         for (HBuf *b : all) b->release();
@@ -267,7 +270,7 @@ extern "C" void b200_fastq_close(b200_fastq_t *f)
 }
 
 // records of stream s up to `max_recs` / `want_bases` (bseq_read's cut is applied by the caller over both streams)
-static bool index_stream(b200_fastq *f, Stream &s, size_t text_budget, std::vector<Rec> &recs, const char **upto)
+static bool index_stream(b200_fastq *f, int which, Stream &s, size_t text_budget, const char **upto)
 {
     if (!s.fill(text_budget, f->n_threads)) { b200_set_error("%s", s.err.c_str()); return false; }
     const char *lo = s.cur, *end = s.cur_end;
@@ -303,6 +306,13 @@ static bool index_stream(b200_fastq *f, Stream &s, size_t text_budget, std::vect
         Piece &P = pieces[(size_t)k];
         const char *p = cuts[(size_t)k], *hi = cuts[(size_t)k + 1];
         const bool last = k == np - 1;
+#ifdef MADV_POPULATE_READ
+        if (s.plain && hi > p) {                             // fault the piece's pages in with one call instead of one fault per 4 KB
+            const uintptr_t a0 = (uintptr_t)p & ~(uintptr_t)4095, a1 = ((uintptr_t)hi + 4095) & ~(uintptr_t)4095;
+            const uintptr_t mend = ((uintptr_t)s.map + s.map_len + 4095) & ~(uintptr_t)4095;
+            madvise((void *)a0, (size_t)((a1 < mend ? a1 : mend) - a0), MADV_POPULATE_READ);
+        }
+#endif
         while (p < hi) {
             while (p < hi && (*p == '\n' || *p == '\r')) ++p;
             if (p >= hi) break;
@@ -319,8 +329,22 @@ static bool index_stream(b200_fastq *f, Stream &s, size_t text_budget, std::vect
     for (int k = 1; k < np; ++k) th.emplace_back(work, k);
     work(0);
     for (auto &x : th) x.join();
-    recs.clear();
-    for (int k = 0; k < np; ++k) recs.insert(recs.end(), pieces[(size_t)k].recs.begin(), pieces[(size_t)k].recs.end());
+    // the pieces' records side by side in one array (copied by the pieces' threads)
+    std::vector<size_t> base((size_t)np + 1, 0);
+    for (int k = 0; k < np; ++k) base[(size_t)k + 1] = base[(size_t)k] + pieces[(size_t)k].recs.size();
+    const size_t total = base[(size_t)np];
+    if (total > f->recs_cap[which]) {
+        free(f->recs[which]);
+        f->recs_cap[which] = total + total / 4 + 1024;
+        f->recs[which] = (Rec *)malloc(f->recs_cap[which] * sizeof(Rec));
+        if (!f->recs[which]) { f->recs_cap[which] = 0; b200_set_error("out of memory"); return false; }
+    }
+    f->n_recs[which] = total;
+    auto gather = [&](int k) { if (!pieces[(size_t)k].recs.empty()) memcpy(f->recs[which] + base[(size_t)k], pieces[(size_t)k].recs.data(), pieces[(size_t)k].recs.size() * sizeof(Rec)); };
+    th.clear();
+    for (int k = 1; k < np; ++k) th.emplace_back(gather, k);
+    gather(0);
+    for (auto &x : th) x.join();
     *upto = stop[(size_t)np - 1];
     return true;
 }
@@ -330,49 +354,72 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
     if (!f || !out || chunk_bases <= 0) { b200_set_error("b200_fastq_read: bad argument"); return -1; }
     memset(out, 0, sizeof(*out));
     // text budget: a record of l bases takes about 2 l + name + 6 bytes; index a little more than one batch needs
-    size_t budget = (size_t)chunk_bases * 5 / 2 + ((size_t)4 << 20);
-    std::vector<Rec> recs[2];
+    size_t budget = (size_t)chunk_bases * 9 / 4 + ((size_t)2 << 20);
     const char *upto[2] = { nullptr, nullptr };
     int64_t n = 0;
+    const int two = f->n_files == 2;
+    auto rec_of = [&](int64_t i) -> const Rec & { return two ? f->recs[i & 1][(size_t)(i >> 1)] : f->recs[0][(size_t)i]; };
+    auto par = [&](int64_t count, const std::function<void(int, int64_t, int64_t)> &fn) {      // fn(thread, lo, hi) over [0, count)
+        const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(f->n_threads, count / 8192));
+        std::vector<std::thread> th;
+        for (int t = 1; t < nt; ++t) th.emplace_back(fn, t, count * t / nt, count * (t + 1) / nt);
+        fn(0, 0, count / nt);
+        for (auto &x : th) x.join();
+        return nt;
+    };
+    b200_fastq::Out &O = f->out[f->parity];
+    int64_t *seq_off = nullptr, *name_off = nullptr, *com_off = nullptr;
     for (;;) {
         for (int k = 0; k < f->n_files; ++k)
-            if (!index_stream(f, f->s[k], f->n_files == 2 ? budget / 2 : budget, recs[k], &upto[k])) return -1;
-        // bseq_read's cut (bwa.c:191-224): records (pairs) in order until size >= chunk_size on an even count
-        int64_t size = 0; n = 0;
+            if (!index_stream(f, k, f->s[k], two ? budget / 2 : budget, &upto[k])) return -1;
+        // offsets of every field of every indexed record, in batch order (mates alternate): a two-level prefix sum
+        const int64_t avail = two ? 2 * (int64_t)std::min(f->n_recs[0], f->n_recs[1]) : (int64_t)f->n_recs[0];
+        const size_t need_n = ((size_t)avail + 1) * 8;
+        if (!O.seq_off.grow(need_n) || !O.name_off.grow(need_n) || !O.com_off.grow(need_n)) { b200_set_error("out of memory"); return -1; }
+        seq_off = (int64_t *)O.seq_off.p; name_off = (int64_t *)O.name_off.p; com_off = (int64_t *)O.com_off.p;
+        int64_t part[64][3];
+        const int nt = par(avail, [&](int t, int64_t lo, int64_t hi) {
+            int64_t a = 0, b = 0, c = 0;
+            for (int64_t i = lo; i < hi; ++i) { const Rec &r = rec_of(i); a += r.l_seq; b += r.l_name; c += r.l_comment; }
+            part[t][0] = a; part[t][1] = b; part[t][2] = c;
+        });
+        int64_t run[3] = { 0, 0, 0 };
+        for (int t = 0; t < nt; ++t) for (int q = 0; q < 3; ++q) { const int64_t v = part[t][q]; part[t][q] = run[q]; run[q] += v; }
+        par(avail, [&](int t, int64_t lo, int64_t hi) {
+            int64_t a = part[t][0], b = part[t][1], c = part[t][2];
+            for (int64_t i = lo; i < hi; ++i) { const Rec &r = rec_of(i); seq_off[i] = a; name_off[i] = b; com_off[i] = c; a += r.l_seq; b += r.l_name; c += r.l_comment; }
+        });
+        seq_off[avail] = run[0]; name_off[avail] = run[1]; com_off[avail] = run[2];
+        // bseq_read's cut (bwa.c:191-224): records in order until size >= chunk_size on an even count (sizes only grow, so
+        // that is the first count with size >= chunk, rounded up to even)
         bool cut = false;
-        const size_t avail = f->n_files == 2 ? std::min(recs[0].size(), recs[1].size()) : recs[0].size();
-        if (f->n_files == 2) {
-            for (size_t i = 0; i < avail; ++i) { size += recs[0][i].l_seq + recs[1][i].l_seq; n += 2; if (size >= chunk_bases) { cut = true; break; } }
-        } else {
-            for (size_t i = 0; i < avail; ++i) { size += recs[0][i].l_seq; ++n; if (size >= chunk_bases && (n & 1) == 0) { cut = true; break; } }
+        n = avail;
+        if (run[0] >= chunk_bases) {
+            const int64_t n0 = std::lower_bound(seq_off, seq_off + avail + 1, chunk_bases) - seq_off;      // first count whose size reaches the chunk
+            const int64_t ne = (n0 + 1) & ~(int64_t)1;
+            if (ne <= avail) { n = ne; cut = true; }
         }
         bool all_in = true;                                  // every stream fully indexed to its end?
         for (int k = 0; k < f->n_files; ++k) all_in = all_in && f->s[k].eof && upto[k] == f->s[k].cur_end;
         if (cut || all_in) break;
         budget *= 2;                                         // long records: look at more text
     }
-    if (f->n_files == 2 && recs[0].size() != recs[1].size() && !f->warned) {
+    f->parity ^= 1;
+    if (two && f->n_recs[0] != f->n_recs[1] && !f->warned) {
         bool e0 = f->s[0].eof && upto[0] == f->s[0].cur_end, e1 = f->s[1].eof && upto[1] == f->s[1].cur_end;
-        if (e0 && e1) { fprintf(stderr, "[W::b200_fastq_read] the %s file has fewer sequences.\n", recs[0].size() < recs[1].size() ? "1st" : "2nd"); f->warned = true; }
+        if (e0 && e1) { fprintf(stderr, "[W::b200_fastq_read] the %s file has fewer sequences.\n", f->n_recs[0] < f->n_recs[1] ? "1st" : "2nd"); f->warned = true; }
     }
     if (n == 0) return 0;
-    // ---- place: offsets of every field of every record of the batch
-    const size_t per = f->n_files == 2 ? (size_t)n / 2 : (size_t)n;
-    auto rec_of = [&](int64_t i) -> const Rec & { return f->n_files == 2 ? recs[i & 1][(size_t)(i >> 1)] : recs[0][(size_t)i]; };
-    const size_t need_n = ((size_t)n + 1) * 8;
-    b200_fastq::Out &O = f->out[f->parity];
-    f->parity ^= 1;
-    if (!O.seq_off.grow(need_n) || !O.name_off.grow(need_n) || !O.com_off.grow(need_n)) { b200_set_error("out of memory"); return -1; }
-    int64_t *seq_off = (int64_t *)O.seq_off.p, *name_off = (int64_t *)O.name_off.p, *com_off = (int64_t *)O.com_off.p;
-    int64_t so = 0, no = 0, co = 0;
+    const size_t per = two ? (size_t)n / 2 : (size_t)n;
+    const int64_t so = seq_off[n], no = name_off[n], co = com_off[n];
+    int fl[64][3];
+    const int ntf = par(n, [&](int t, int64_t lo, int64_t hi) {
+        int aq = 0, nq = 0, ac = 0;
+        for (int64_t i = lo; i < hi; ++i) { const Rec &r = rec_of(i); aq |= r.l_qual > 0; nq |= r.l_qual != r.l_seq; ac |= r.l_comment > 0; }
+        fl[t][0] = aq; fl[t][1] = nq; fl[t][2] = ac;
+    });
     bool any_qual = false, all_qual = true, any_com = false;
-    for (int64_t i = 0; i < n; ++i) {
-        const Rec &r = rec_of(i);
-        seq_off[i] = so; name_off[i] = no; com_off[i] = co;
-        so += r.l_seq; no += r.l_name; co += r.l_comment;
-        any_qual |= r.l_qual > 0; all_qual &= r.l_qual == r.l_seq; any_com |= r.l_comment > 0;
-    }
-    seq_off[n] = so; name_off[n] = no; com_off[n] = co;
+    for (int t = 0; t < ntf; ++t) { any_qual |= fl[t][0] != 0; all_qual &= fl[t][1] == 0; any_com |= fl[t][2] != 0; }
     if (any_qual && !all_qual) { b200_set_error("FASTQ batch mixes reads with and without (complete) qualities"); return -1; }
     if (!O.seq.grow((size_t)so + 64) || (any_qual && !O.qual.grow((size_t)so + 64)) || !O.name.grow((size_t)no + 64) ||
         !O.comment.grow((size_t)co + 64)) { b200_set_error("out of memory"); return -1; }
@@ -382,7 +429,7 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
         const int64_t lo = n * t / nt, hi = n * (t + 1) / nt;
         for (int64_t i = lo; i < hi; ++i) {
             const Rec &r = rec_of(i);
-            const Stream &S = f->s[f->n_files == 2 ? (int)(i & 1) : 0];
+            const Stream &S = f->s[two ? (int)(i & 1) : 0];
             copy_body(r, S.cur_end, O.seq.p + seq_off[i], any_qual ? O.qual.p + seq_off[i] : nullptr);
             memcpy(O.name.p + name_off[i], r.name, (size_t)r.l_name);
             if (r.l_comment) memcpy(O.comment.p + com_off[i], r.comment, (size_t)r.l_comment);
@@ -394,9 +441,8 @@ extern "C" int64_t b200_fastq_read(b200_fastq_t *f, int64_t chunk_bases, b200_re
     for (auto &x : th) x.join();
     // ---- consume the text of the records handed out
     for (int k = 0; k < f->n_files; ++k) {
-        const std::vector<Rec> &rv = recs[k];
         const char *next;
-        if (per < rv.size()) next = rv[per].name - 1;         // the header character of the first record left over
+        if (per < f->n_recs[k]) next = f->recs[k][per].name - 1;      // the header character of the first record left over
         else next = upto[k];
         f->s[k].consumed(next);
         if (f->s[k].plain) f->s[k].eof = false;               // plain mappings are "filled" again on the next call

@@ -454,8 +454,8 @@ extern "C" int64_t b200_fastq_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
             if (n == 0) return;
         }
     });
-    // two SAM buffers: the writer drains one while the devices fill the other
-    char *sam[2] = { nullptr, nullptr }; size_t cap[2] = { 0, 0 };
+    // two SAM buffers: the writer drains one while the devices fill the other (page-locked, kept by the first context across calls)
+    char *sam[2] = { (char *)ctxs[0]->pin_p[10], (char *)ctxs[0]->pin_p[11] }; size_t cap[2] = { ctxs[0]->pin_cap[10], ctxs[0]->pin_cap[11] };
     std::thread writer;
     i64 w_bytes = 0; bool w_failed = false;
     i64 n_processed = 0, total_bytes = 0, n_batches = 0;
@@ -472,9 +472,9 @@ extern "C" int64_t b200_fastq_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
         i64 rc;
         for (;;) {
             const size_t want = cap[b] ? cap[b] : (size_t)(cur.R.seq_off[cur.n] * 2 + cur.n * 220 + cur.R.name_off[cur.n] + 4096);
-            if (cap[b] < want) { b200_host_free(sam[b]); sam[b] = (char *)b200_host_alloc(want); cap[b] = sam[b] ? want : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } }
+            if (cap[b] < want) { sam[b] = (char *)b200_ctx_pinned(ctxs[0], 10 + b, want); cap[b] = sam[b] ? ctxs[0]->pin_cap[10 + b] : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } }
             rc = b200_reads_to_sam(ctxs, n_ctx, &o, ann_names, ann_annos, &cur.R, n_processed, pes0, rg_id, 0, (i64)cap[b], sam[b], nullptr, nullptr);
-            if (!B200_IS_ERROR(rc) && rc < 0) { b200_host_free(sam[b]); sam[b] = nullptr; cap[b] = 0; const size_t nw = (size_t)-rc + 4096; sam[b] = (char *)b200_host_alloc(nw); cap[b] = sam[b] ? nw : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } continue; }
+            if (!B200_IS_ERROR(rc) && rc < 0) { sam[b] = (char *)b200_ctx_pinned(ctxs[0], 10 + b, (size_t)-rc + 4096); cap[b] = sam[b] ? ctxs[0]->pin_cap[10 + b] : 0; if (!sam[b]) { rc = B200_E_FAIL; break; } continue; }
             break;
         }
         t_align += now_s() - t0;
@@ -494,7 +494,6 @@ extern "C" int64_t b200_fastq_to_sam(b200_ctx_t *const *ctxs, int n_ctx, const m
     {   std::lock_guard<std::mutex> lk(mu); if (!reader_done) failed = true; cv.notify_all(); }     // an early exit: release the reader
     reader.join();
     b200_fastq_close(f);
-    b200_host_free(sam[0]); b200_host_free(sam[1]);
     if (stats) { stats[0] = now_s() - t_all; stats[1] = t_read; stats[2] = t_align; stats[3] = t_write; stats[4] = (double)n_batches; stats[5] = (double)total_bytes; }
     if (!err.empty() || w_failed) { b200_set_error("%s", err.empty() ? "writing the SAM text failed" : err.c_str()); return B200_E_FAIL; }
     return n_processed;
