@@ -26,9 +26,8 @@ __device__ __forceinline__ Occ32Blk occ32_load(const uint4 *occ32, u64 blk)
 // Both sectors of one extension in ONE issue group: the four 128-bit loads are emitted back to back so that the
 // extension costs one memory round trip (ptxas otherwise sinks the second sector's loads below the first
 // sector's arithmetic, which serialises two round trips).  When bl == bk the second pair hits the sector in flight.
-__device__ __forceinline__ void occ32_load2(const uint4 *occ32, u64 bk, u64 bl, Occ32Blk &K, Occ32Blk &L)
+__device__ __forceinline__ void occ32_load2p(const uint4 *pk, const uint4 *pl, Occ32Blk &K, Occ32Blk &L)
 {
-    const uint4 *pk = occ32 + (bk << 1), *pl = occ32 + (bl << 1);
 #ifdef B200_EMU
     K.cnt = pk[0]; K.pl = pk[1]; L.cnt = pl[0]; L.pl = pl[1];
 #else
@@ -38,8 +37,12 @@ __device__ __forceinline__ void occ32_load2(const uint4 *occ32, u64 bk, u64 bl, 
                  : "=r"(K.cnt.x), "=r"(K.cnt.y), "=r"(K.cnt.z), "=r"(K.cnt.w), "=r"(K.pl.x), "=r"(K.pl.y), "=r"(K.pl.z), "=r"(K.pl.w),
                    "=r"(L.cnt.x), "=r"(L.cnt.y), "=r"(L.cnt.z), "=r"(L.cnt.w), "=r"(L.pl.x), "=r"(L.pl.y), "=r"(L.pl.z), "=r"(L.pl.w)
                  : "l"(pk), "l"(pl));
-    if (bk == bl) L = K;
+    if (pk == pl) L = K;
 #endif
+}
+__device__ __forceinline__ void occ32_load2(const uint4 *occ32, u64 bk, u64 bl, Occ32Blk &K, Occ32Blk &L)
+{
+    occ32_load2p(occ32 + (bk << 1), occ32 + (bl << 1), K, L);
 }
 
 // (# of symbol c, # of symbols > c) among rows [block start, block start + off] of a block, plus checkpoint
@@ -73,6 +76,19 @@ __device__ __forceinline__ void occ32_issue(const DevIndex &ix, PT x0, PT x1, PT
     const PT k = a - 1, l = k + x2;                                   // bwt.c:265
     const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary); // bwt.c:192-193
     occ32_load2(ix.occ32, (u64)kp >> 6, (u64)lp >> 6, Bk, Bl);
+}
+
+// The two sector addresses of an extension without the loads: a caller whose lanes take their data from different
+// tables (smem3.cu: k-mer table entry or index sectors) forms the addresses per lane and then issues ONE load group for
+// the whole warp -- loads into the same registers from two sides of a branch would wait for each other.
+template <class PT>
+__device__ __forceinline__ void occ32_addr(const DevIndex &ix, PT x0, PT x1, PT x2, int is_back, const uint4 *&pk, const uint4 *&pl)
+{
+    const PT primary = (PT)ix.primary;
+    const PT a = is_back ? x0 : x1;
+    const PT k = a - 1, l = k + x2;
+    const PT kp = k - (PT)(k >= primary), lp = l - (PT)(l >= primary);
+    pk = ix.occ32 + (((u64)kp >> 6) << 1); pl = ix.occ32 + (((u64)lp >> 6) << 1);
 }
 
 // 1 when the reference's bwt_2occ4 (bwt.c:189-220) would have read two 128-row blocks for this extension

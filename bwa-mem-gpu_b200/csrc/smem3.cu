@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
     const uint4 *const ktab = ix.kmer_tab;
     u32 wf = 0, wst = 0, wb = 0;
     int flen = 0;
-    bool ptab = false;
+    int ptab = 0;
 
 #define S3_QGET(pos) (((QGLOB ? __ldg(Qg + ((pos) >> 3)) : Q[((pos) >> 3) * S3_THREADS]) >> (((pos) & 7) << 2)) & 7u)
 #define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
@@ -192,7 +192,8 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         // ------------------------------------------------------------ the single gather site: consume the sectors
         PT n0, n1, n2; int two;
         if (ptab) {                                                         // table entry: the child's bi-interval itself
-            E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
+            if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
+            else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
             two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
         } else occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
         ++n_ext; n_two += two;
@@ -355,13 +356,17 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         c = is_back ? (int)b : 3 - (int)b;
         {
             const int cur = is_back ? (int)pend - (i + 1) : flen;           // length of the string whose interval is extended
+            // One load group for the whole warp whatever the lanes read: a 16-byte table record is fetched as the 32-byte
+            // sector that holds it (ptab = 1 / 2: low / high half), two-quad records as one "sector".
+            const uint4 *pk, *pl;
             ptab = cur < KT;
             if (ptab) {                                                     // child = string of cur + 1 <= KT bases: table
                 const u32 wn = is_back ? (b << (2 * cur)) | (cur ? wb >> (2 * (KT - cur)) : 0u) : (wf << 2) | b;
-                const uint4 *e = ktab + (size_t)(ix.kmer_off[cur + 1] + wn) * EQ;
-                Bk.cnt = __ldg(e);
-                if (EQ == 2) Bk.pl = __ldg(e + 1);
-            } else occ32_issue<PT>(ix, k0, k1, kk2, is_back, Bk, Bl);       // requests in flight across the back-edge
+                const size_t e = (size_t)(ix.kmer_off[cur + 1] + wn) * EQ;
+                if (EQ == 1) { ptab = 1 + (int)(e & 1); pk = ktab + (e & ~(size_t)1); } else pk = ktab + e;
+                pl = pk;
+            } else occ32_addr<PT>(ix, k0, k1, kk2, is_back, pk, pl);
+            occ32_load2p(pk, pl, Bk, Bl);                                   // requests in flight across the back-edge
         }
         pending = true;
     }
