@@ -147,12 +147,24 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
     u32 wf = 0, wst = 0, wb = 0;
     int flen = 0;
     int ptab = 0;
+    // "Virtual" list entries.  A change point of the forward sweep whose string is shorter than KT bases is extended
+    // backwards through the k-mer table for its first KT - length steps: those extensions are looked up by STRING, the
+    // entry's own interval is never read, and it cannot be emitted (an emitted match has >= min_seed_len > KT bases,
+    // bwamem.c:150).  Such an entry is therefore only a bit: bit L of `vm` = the entry with end sx + L.  In the forward
+    // sweep vm collects them; in the backward sweep vm holds those of the current position still to be visited (after
+    // the real entries, longest first), vnext the survivors for the next position, and an entry whose child reaches KT
+    // bases is written to the real list (it is shorter than every real entry, so the order of bwt.c:326-341 is kept).
+    // Virtual entries still take a list index in the forward sweep (they are the first ones), so that the slots below the
+    // real entries exist for the ones that become real.
+    // vtwo: bit L = the reference's bwt_2occ4 would read two blocks for that entry's next extension (traffic counter).
+    const int KTV = KT < min_seed_len ? KT : 0;
+    u32 vm = 0, vnext = 0, vtwo = 0;
 
 #define S3_QGET(pos) (((QGLOB ? __ldg(Qg + ((pos) >> 3)) : Q[((pos) >> 3) * S3_THREADS]) >> (((pos) & 7) << 2)) & 7u)
 #define S3_SLOT(e) (L + ((e) % LCAP) * EQ * S3_THREADS)
 #define S3_PUSH(endv)                                                                                   \
     do {                                                                                                \
-        if (nfw >= LCAP) {                                 /* evict entry nfw - LCAP to the spill area */ \
+        if (nfw - LCAP >= (int)__popc(vm)) {               /* evict entry nfw - LCAP (a real one) to the spill area */ \
             PT t0, t1, t2; u32 te;                                                                      \
             E::ld(S3_SLOT(nfw), S3_THREADS, t0, t1, t2, te);                                            \
             if (nfw - LCAP < P.spill_cap) E::st(SP + (size_t)(nfw - LCAP) * EQ, 1, t0, t1, t2, te);     \
@@ -172,11 +184,23 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         if ((jj) < LCAP) E::st(S3_SLOT(e_), S3_THREADS, a0, a1, a2, ev);                                \
         else E::st(SP + (size_t)e_ * EQ, 1, a0, a1, a2, ev);                                            \
     } while (0)
+#define S3_NEXT_ENTRY()                                /* real entry j, else the longest virtual one left */ \
+    do {                                                                                                \
+        if (j < nprev) S3_LOAD_ENTRY(j);                                                                \
+        else { const int lb_ = 31 - __clz((int)vm); vm ^= 1u << lb_; pend = (u32)(sx + lb_); }          \
+    } while (0)
+#define S3_PUSH_FWD(endv)                                                                               \
+    do {                                                                                                \
+        if (flen < KTV) {                                  /* takes list index nfw, stores nothing */    \
+            vm |= 1u << flen; ++nfw;                                                                    \
+            vtwo = (vtwo & ~(1u << flen)) | (u32)occ32_two_ref<PT>(ix, k0, k1, kk2, 1) << flen;         \
+        } else S3_PUSH(endv);                                                                           \
+    } while (0)
 #define S3_START_BWD()                                                                                  \
     do {                                                                                                \
-        ret = i; base = nfw - 1; nprev = nfw; ncurr = 0; j = 0; i = sx - 1; last_start = 0x7fffffff;    \
-        st = S3_BWD; wb = wst;                                                                          \
-        S3_LOAD_ENTRY(0);                                                                               \
+        ret = i; base = nfw - 1; nprev = nfw - (int)__popc(vm); ncurr = 0; j = 0; i = sx - 1;           \
+        last_start = 0x7fffffff; st = S3_BWD; wb = wst; vnext = 0;                                      \
+        S3_NEXT_ENTRY();                                                                                \
     } while (0)
 #define S3_SET_INTV(b0)                                                                                 \
     do {                                                                                                \
@@ -194,7 +218,8 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         if (ptab) {                                                         // table entry: the child's bi-interval itself
             if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
             else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
-            two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
+            if (is_back && j >= nprev) two = (int)(vtwo >> ((int)pend - sx) & 1u);     // virtual entry: counted when it was made
+            else two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
         } else occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
         ++n_ext; n_two += two;
         // ------------------------------------------------------------ consume
@@ -205,7 +230,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
             if (n2 != kk2) {
                 if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; adv = false; }
                 else {
-                    S3_PUSH(i);
+                    S3_PUSH_FWD(i);
                     if (n2 < min_intv) { S3_START_BWD(); adv = false; }
                 }
             }
@@ -215,24 +240,33 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                 x = i + 1; restart = S3_P3;
             } else adv = true;
         } else {                                                            // S3_BWD, bwt.c:331-341
+            const bool none = ncurr == 0 && vnext == 0;                     // no longer match survived at this position
             if (n2 < min_intv) {
-                if (ncurr == 0 && i + 1 < last_start) {
+                if (none && i + 1 < last_start) {
                     last_start = i + 1;
                     if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
                 }
-            } else if (ncurr == 0 || n2 != last_x2) {
-                S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                    // ncurr <= j: slot already consumed
-                ++ncurr; last_x2 = n2;
+            } else if (none || n2 != last_x2) {
+                last_x2 = n2;
+                if ((int)pend - i < KTV) {                                  // the child is a table string again: stays a bit
+                    const int lb = (int)pend - sx;
+                    vnext |= 1u << lb;
+                    vtwo = (vtwo & ~(1u << lb)) | (u32)occ32_two_ref<PT>(ix, n0, n1, n2, 1) << lb;
+                } else {
+                    S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                // ncurr <= j: slot already consumed
+                    ++ncurr;
+                }
             }
-            if (++j == nprev) {                                             // bwt.c:343-344
-                if (ncurr == 0) {
+            ++j;
+            if (j >= nprev && vm == 0) {                                    // bwt.c:343-344
+                if (ncurr == 0 && vnext == 0) {
                     if (pass == 1) { x = ret; restart = S3_FWD; } else { ++k2; st = S3_TASK; i = -1; }
                 } else {                                                    // next backward position: base c joins the window
-                    nprev = ncurr; ncurr = 0; j = 0; --i;
+                    nprev = ncurr; ncurr = 0; j = 0; vm = vnext; vnext = 0; --i;
                     if (KT > 0) wb = ((u32)c << (2 * KT - 2)) | (wb >> 2);
                 }
             }
-            if (restart < 0 && st == S3_BWD) S3_LOAD_ENTRY(j);
+            if (restart < 0 && st == S3_BWD) S3_NEXT_ENTRY();
         }
         if (adv) {
             k0 = n0; k1 = n1; kk2 = n2; ++i;
@@ -245,7 +279,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
             if (b0 < 4) {
                 S3_SET_INTV((int)b0);
                 i = x + 1; st = restart;
-                if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; }
+                if (restart == S3_FWD) { sx = x; min_intv = 1; nfw = 0; vm = 0; }
             } else { st = S3_TASK; i = -1; }                                // N or end of read: slow path decides
         }
       }
@@ -255,7 +289,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         while (b > 3) {
             if (st == S3_FWD) {                                             // read end or N: bwt.c:316-318, 321
                 if (nfw - LCAP >= P.spill_cap) { atomicMax(P.overflow + 1, 1); st = S3_FIN; i = -1; continue; }
-                S3_PUSH(i);
+                S3_PUSH_FWD(i);
                 S3_START_BWD();
             } else if (st == S3_BWD) {                                      // i < 0 or N: the longest entry is emitted, sweep ends
                 if ((int)pend - (i + 1) >= min_seed_len) s3_emit(out, n_out, P.cap_out, k0, k1, kk2, i + 1, (int)pend);
@@ -296,7 +330,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                 {                                                           // bwt.c:301-304
                     const int b0 = (int)S3_QGET(sx);
                     S3_SET_INTV(b0);
-                    i = sx + 1; nfw = 0; st = S3_FWD;
+                    i = sx + 1; nfw = 0; vm = 0; st = S3_FWD;
                 }
             } else {                                                        // S3_FIN: finish this read, take the next
                 if (r >= 0) {
@@ -304,9 +338,21 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                     if (SPLIT && len >= min_seed_len) {                // append the third pass's intervals (stored at the end)
                         const int n3 = P.out3_n[r];
                         if (n + n3 > P.cap_out) { atomicMax(P.overflow, n + n3); n = n > P.cap_out ? P.cap_out : n; }
-                        else {
+                        else if (n + n3 <= P.cap_out - n3) {                // destination below the stored block
                             for (int a = 0; a < n3; ++a) {
                                 const uint4 *src = (const uint4 *)&out[P.cap_out - 1 - a];
+                                const uint4 v0 = src[0], v1 = src[1];
+                                ((uint4 *)&out[n + a])[0] = v0; ((uint4 *)&out[n + a])[1] = v1;
+                            }
+                            n += n3;
+                        } else {                                            // they overlap: reverse the block in place, move it down
+                            for (int a = 0, z = n3 - 1; a < z; ++a, --z) {
+                                uint4 *pa = (uint4 *)&out[P.cap_out - 1 - a], *pz = (uint4 *)&out[P.cap_out - 1 - z];
+                                const uint4 a0 = pa[0], a1 = pa[1], z0 = pz[0], z1 = pz[1];
+                                pa[0] = z0; pa[1] = z1; pz[0] = a0; pz[1] = a1;
+                            }
+                            for (int a = 0; a < n3; ++a) {                  // now element a sits at cap_out - n3 + a >= n + a
+                                const uint4 *src = (const uint4 *)&out[P.cap_out - n3 + a];
                                 const uint4 v0 = src[0], v1 = src[1];
                                 ((uint4 *)&out[n + a])[0] = v0; ((uint4 *)&out[n + a])[1] = v1;
                             }
@@ -520,6 +566,8 @@ static int launch_fast3_e(const SmemParams &p, int grid, int wide, int lcap, int
         return p.split_p3 ? launch_fast3_ts<E, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, true>(p, grid, smem, st);
     }
     const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
+    if (lcap == 4) return p.split_p3 ? launch_fast3_ts<E, 4, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 4, false, false>(p, grid, smem, st);
+    if (lcap == 6) return p.split_p3 ? launch_fast3_ts<E, 6, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 6, false, false>(p, grid, smem, st);
     if (lcap == 8) return p.split_p3 ? launch_fast3_ts<E, 8, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 8, false, false>(p, grid, smem, st);
     if (lcap == 12) return p.split_p3 ? launch_fast3_ts<E, 12, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 12, false, false>(p, grid, smem, st);
     return p.split_p3 ? launch_fast3_ts<E, 16, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, false>(p, grid, smem, st);

@@ -442,6 +442,36 @@ def test_seeding_variants(backend, tune):
     assert np.array_equal(n0, n1) and r0.tobytes() == r1.tobytes()
 
 
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("min_seed_len", [19, 10])
+def test_seeding_table_counters(backend, min_seed_len):
+    """The k-mer table path (and its bit-only list entries, used while min_seed_len exceeds the table depth) answers the
+    same bwt_extend calls as the plain path: same intervals, and the same extension / two-block counts (the roofline's
+    algorithmic traffic must not depend on how an extension was served)."""
+    from bwa_mem_gpu_b200 import lib as L
+    gname = "rep"
+    lib = cm.backend_lib(backend)
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    opt.min_seed_len = min_seed_len
+    seqs, off = cm.reads_for(gname, _sizes(backend, 200, 20000), seed=58, indel=0.004, n_rate=0.002)
+    a = idx.collect_intv(opt, seqs, off)
+    got = []
+    for k in (0, 12):
+        ctx = L.Context(0, lib)
+        ctx.tune("kmer_k", k)
+        ctx.upload_host_index(cm.context(backend, gname)._host_index)
+        b = ctx.collect_intv(opt, seqs, off)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        ctx.align(opt, seqs, off)
+        c = ctx.counters()
+        got.append((c["extend"], c["two_block"]))
+        ctx.close()
+    assert got[0] == got[1] and got[0][0] > 0
+
+
 def _check_reg2aln(idx, ctx, opt, seqs, off):
     regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
     a0, c0, m0 = idx.reg2aln(opt, seqs, off, regs, cnt)
