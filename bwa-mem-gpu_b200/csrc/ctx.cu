@@ -130,6 +130,8 @@ int b200_index_finish(b200_ctx *ctx, int flags)
 {
     DevIndex &ix = ctx->ix;
     const u64 seq_len = ix.seq_len;
+    for (int s = 0; s < 8; ++s)
+        for (int c = 0; c < 4; ++c) { u64 g = 0; for (int d = c + 1; d < 4; ++d) g += ix.sb_cnt[s][d]; ix.sb_gt[s][c] = g; }
     {   // occ32 re-layout for the seeding kernel (occ32.cuh); superblock bases already in ix.sb_cnt
         const u64 n_blk = (seq_len >> 6) + 2;
         if (ctx->d_bwt.bytes < ((n_blk + 1) / 2) * 64) { b200_set_error("internal: bwt padding too small"); return -1; }

@@ -27,6 +27,7 @@ struct DevIndex {
     // re-laid Occ index for the seeding kernel (built once on the device, see occ32.cuh)
     const uint4 *occ32;      // 2 x uint4 per 64-row block
     u64 sb_cnt[8][4];        // counts at the start of each 2^32-row superblock (rows < 2^35)
+    u64 sb_gt[8][4];         // sb_gt[s][c] = sum of sb_cnt[s][d] over d > c (filled by b200_index_finish)
     // bi-intervals of all strings of length 1..kmer_k (see kmer_tab.cuh); 0 = no table
     const uint4 *kmer_tab;   // entry of string W (length k): kmer_tab[(kmer_off[k] + W) * quads], quads = 1 (u32) / 2 (u64)
     int kmer_k;

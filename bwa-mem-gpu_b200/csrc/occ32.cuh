@@ -117,9 +117,7 @@ __device__ __forceinline__ void occ32_finish(const DevIndex &ix, PT x0, PT x1, P
     PT tk = ek, tl = el, sk = gk, sl = gl;
     if (sizeof(PT) == 8) {                                            // superblock bases (rows >= 2^32)
         const int s0 = (int)((u64)kp >> 32), s1 = (int)((u64)lp >> 32);
-        u64 bk_eq = ix.sb_cnt[s0][c], bl_eq = ix.sb_cnt[s1][c], bk_gt = 0, bl_gt = 0;
-        for (int d = 1; d < 4; ++d) if (d > c) { bk_gt += ix.sb_cnt[s0][d]; bl_gt += ix.sb_cnt[s1][d]; }
-        tk += (PT)bk_eq; tl += (PT)bl_eq; sk += (PT)bk_gt; sl += (PT)bl_gt;
+        tk += (PT)ix.sb_cnt[s0][c]; tl += (PT)ix.sb_cnt[s1][c]; sk += (PT)ix.sb_gt[s0][c]; sl += (PT)ix.sb_gt[s1][c];
     }
     n2 = tl - tk;                                                     // bwt.c:270
     const PT na = (PT)ix.L2[c] + 1 + tk;                              // bwt.c:269

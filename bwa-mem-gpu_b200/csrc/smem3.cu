@@ -441,12 +441,14 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
     PT k0 = 0, k1 = 0, kk2 = 0;
     u32 wf = 0;
     Occ32Blk Bk, Bl;
-    bool pending = false, ptab = false;
+    bool pending = false;
+    int ptab = 0;
     for (;;) {
         if (pending) {
             PT n0, n1, n2; int two;
             if (ptab) {
-                E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
+                if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
+                else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
                 two = occ32_two_ref<PT>(ix, k0, k1, kk2, 0);
             } else occ32_finish<PT>(ix, k0, k1, kk2, 0, c, Bk, Bl, n0, n1, n2, two);
             ++n_ext; n_two += two;
@@ -499,12 +501,14 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
         }
         if (r < 0) break;
         c = 3 - (int)b;
+        const uint4 *pk, *pl;                                               // one load group per warp, as in the main kernel
         ptab = flen < KT;
         if (ptab) {
-            const uint4 *e = ktab + (size_t)(ix.kmer_off[flen + 1] + ((wf << 2) | b)) * EQ;
-            Bk.cnt = __ldg(e);
-            if (EQ == 2) Bk.pl = __ldg(e + 1);
-        } else occ32_issue<PT>(ix, k0, k1, kk2, 0, Bk, Bl);
+            const size_t e = (size_t)(ix.kmer_off[flen + 1] + ((wf << 2) | b)) * EQ;
+            if (EQ == 1) { ptab = 1 + (int)(e & 1); pk = ktab + (e & ~(size_t)1); } else pk = ktab + e;
+            pl = pk;
+        } else occ32_addr<PT>(ix, k0, k1, kk2, 0, pk, pl);
+        occ32_load2p(pk, pl, Bk, Bl);
         pending = true;
     }
     if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
