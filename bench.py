@@ -358,12 +358,21 @@ def run_ours(a, world, cores, barrier):
             lo, hi = bounds[dv]
             c = ctxs[dv]
             c.batch_upload(seqs, off[lo: hi + 1])
+            # The algorithmic traffic of seeding (bwt_extend calls, two-block calls: a property of the input) is counted
+            # by the instrumented template of the seeding kernels in one untimed pass; every other launch, the timed
+            # ones included, runs the kernels without the counter arithmetic (tunable seed_stats).
+            c.tune("seed_stats", 1)
+            c.batch_run(opt, want_stage_ms=True)
+            cw = c.counters()
+            c.tune("seed_stats", 0)
             for _ in range(a.warmup):
                 c.batch_run(opt, want_stage_ms=True)
             bar.wait()
             for _ in range(a.steps):
                 stage[dv] += np.array(c.batch_run(opt, want_stage_ms=True))
-            cnts[dv] = c.counters()
+            cn = c.counters()
+            cn["extend"], cn["two_block"] = cw["extend"], cw["two_block"]
+            cnts[dv] = cn
         except Exception as e:  # noqa: BLE001
             errs.append(f"device {dv}: {e}")
             bar.abort()

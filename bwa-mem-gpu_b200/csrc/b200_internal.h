@@ -55,6 +55,7 @@ struct SmemParams {
     // third seeding pass (bwamem.c:167-182) in its own kernel: its intervals go to the END of the read's output slots
     // (out3_n of them, growing downwards); the main kernel then skips the pass and merges them before its final sort
     i32 *out3_n; int split_p3;
+    int count_stats;                             // smem3.cu: count extensions / two-block extensions into stats[] (tunable seed_stats)
 };
 
 struct SeedParams {

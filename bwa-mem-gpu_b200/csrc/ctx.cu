@@ -57,6 +57,7 @@ extern "C" int b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value)
     else if (!strcmp(key, "force_wide")) ctx->force_wide = (int)value;       // before the index upload
     else if (!strcmp(key, "cap_retry")) ctx->cap_retry = (int)value;
     else if (!strcmp(key, "ext_tail")) ctx->ext_tail = (int)value;
+    else if (!strcmp(key, "seed_stats")) ctx->seed_stats = (int)value;
     else if (!strcmp(key, "r2a_warp")) ctx->r2a_warp = (int)value;
 #ifndef B200_EMU
     else if (!strcmp(key, "l2_fetch")) {                                      // L2 fetch granularity hint in bytes (32 / 64 / 128), device-wide

@@ -53,6 +53,7 @@ struct b200_ctx {
     int ssw_path = 0;                          // mem_seed_sw: 0 = one alignment per lane (seedsw2.cu), 1 = lane-group restatement of the striped code (seedsw.cu)
     int ext_phased = 1;                        // byte-score extension kernel: warp-wide phases (left sides, retries, right sides, next jobs)
     int ext_sort = 1;                          // byte-score extension kernel: jobs handed out ordered by flank shape (ext3.cu)
+    int seed_stats = 0;                        // seeding kernels count bwt_extend calls / two-block calls (counters extend, two_block); off = leaner kernel
     int ext_tail = 16384;                      // byte-score extension: a round with at most this many jobs is finished, with all later rounds, by ONE launch (0 = off)
     int ext_rowsync = 1;                       // byte-score extension kernel: a lane finishes its row before the warp's control slot (ext3.cu)
     int split_p3 = 1;                          // third seeding pass in its own kernel (smem_p3_kernel) ahead of the main one

@@ -109,7 +109,7 @@ static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, in
     const bool wide = wmode != 0;
     const int pk_stride = ((ctx->max_len + 7) / 8 + 3) & ~3;                  // words per packed read, 16-byte multiple
     int lcap3 = ctx->smem_lcap > 0 ? ctx->smem_lcap : 8;      // 8: less shared memory = more L1 for the hot table levels (profiles/r4b_seed_ab.txt)
-    lcap3 = lcap3 <= 4 ? 4 : lcap3 <= 6 ? 6 : lcap3 <= 8 ? 8 : (lcap3 <= 12 ? 12 : 16);
+    lcap3 = lcap3 <= 8 ? 8 : 16;
     // reads too long to stage in shared memory: smem_fast_kernel (smem2.cu) by default -- measured faster on 1-10 kbp reads
     // (575 vs 758 ms per 200 k reads) -- or, with smem_path 3, the fast3 kernels fetching the read's 4-bit codes from global memory
     const bool fits3 = smem_fast3_bytes(wmode, lcap3, pk_stride) <= 100 * 1024;
@@ -156,7 +156,7 @@ static int run_chunk_once(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, in
             fast_blocks = (int)std::max<size_t>(1, std::min<size_t>(fast_blocks, ((size_t)8 << 30) / per_block));
         }
         if (ctx->d_spill.ensure((size_t)fast_blocks * 128 * spill_cap * (wmode == 1 ? 32 : 16))) return -1;
-        SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap;
+        SP.pk = ctx->d_pk.as<u32>(); SP.pk_stride = pk_stride; SP.spill_cap = spill_cap; SP.count_stats = ctx->seed_stats;
         SP.lists = (Intv *)ctx->d_spill.p;
         if (ctx->split_p3 && opt->max_mem_intv > 0) {                        // pass 3 first: uniform forward-only lanes
             SP.split_p3 = 1; SP.out3_n = ctx->d_retry.as<i32>();

@@ -117,7 +117,10 @@ __global__ void pack4_kernel(u8 *seq, const i64 *off, int n_reads, u32 *pk, int 
 
 // QGLOB: the read is too long to stage in shared memory (long reads): its 4-bit codes are fetched from the packed
 // copy in global memory instead (consecutive positions of a lane share a 32-byte sector, so these are L1 hits).
-template <class E, int LCAP, bool SPLIT, bool QGLOB>                        // SPLIT: pass 3 ran in smem_p3_kernel
+// STATS: count the bwt_extend calls and how many of them the reference's bwt_2occ4 would have served from two blocks (the
+// roofline's algorithmic traffic, a property of the input).  About a tenth of the kernel's instructions, so production
+// launches leave it out (SmemParams::count_stats, tunable seed_stats); bench.py counts in its warm-up pass.
+template <class E, int LCAP, bool SPLIT, bool QGLOB, bool STATS>                // SPLIT: pass 3 ran in smem_p3_kernel
 __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(s3_raw);
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
     do {                                                                                                \
         if (flen < KTV) {                                  /* takes list index nfw, stores nothing */    \
             vm |= 1u << flen; ++nfw;                                                                    \
-            vtwo = (vtwo & ~(1u << flen)) | (u32)occ32_two_ref<PT>(ix, k0, k1, kk2, 1) << flen;         \
+            if (STATS) vtwo = (vtwo & ~(1u << flen)) | (u32)occ32_two_ref<PT>(ix, k0, k1, kk2, 1) << flen; \
         } else S3_PUSH(endv);                                                                           \
     } while (0)
 #define S3_START_BWD()                                                                                  \
@@ -218,10 +221,13 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         if (ptab) {                                                         // table entry: the child's bi-interval itself
             if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
             else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
-            if (is_back && j >= nprev) two = (int)(vtwo >> ((int)pend - sx) & 1u);     // virtual entry: counted when it was made
-            else two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
+            two = 0;
+            if (STATS) {
+                if (is_back && j >= nprev) two = (int)(vtwo >> ((int)pend - sx) & 1u); // virtual entry: counted when it was made
+                else two = occ32_two_ref<PT>(ix, k0, k1, kk2, is_back);
+            }
         } else occ32_finish<PT>(ix, k0, k1, kk2, is_back, c, Bk, Bl, n0, n1, n2, two);
-        ++n_ext; n_two += two;
+        if (STATS) { ++n_ext; n_two += two; }
         // ------------------------------------------------------------ consume
         bool adv = false;                                                   // forward phases: continue with the child
         int restart = -1;                                                   // >= 0: start a new forward chain of this kind at x
@@ -251,7 +257,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                 if ((int)pend - i < KTV) {                                  // the child is a table string again: stays a bit
                     const int lb = (int)pend - sx;
                     vnext |= 1u << lb;
-                    vtwo = (vtwo & ~(1u << lb)) | (u32)occ32_two_ref<PT>(ix, n0, n1, n2, 1) << lb;
+                    if (STATS) vtwo = (vtwo & ~(1u << lb)) | (u32)occ32_two_ref<PT>(ix, n0, n1, n2, 1) << lb;
                 } else {
                     S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                // ncurr <= j: slot already consumed
                     ++ncurr;
@@ -416,13 +422,13 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         }
         pending = true;
     }
-    if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
+    if (STATS && n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
 }
 
 // Third seeding pass on its own (bwamem.c:167-182 around bwt_seed_strategy1, bwt.c:358-379): forward-only sweeps that
 // restart right after every seed, so every lane runs the same short loop -- no lists, no backward phase.  One read per
 // lane (persistent), requests issued at the bottom of the loop and consumed at the top like in the main kernel.
-template <class E, bool QGLOB>
+template <class E, bool QGLOB, bool STATS>
 __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
 {
     B200_DYN_SMEM(p3_raw);
@@ -449,9 +455,9 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
             if (ptab) {
                 if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
                 else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
-                two = occ32_two_ref<PT>(ix, k0, k1, kk2, 0);
+                two = STATS ? occ32_two_ref<PT>(ix, k0, k1, kk2, 0) : 0;
             } else occ32_finish<PT>(ix, k0, k1, kk2, 0, c, Bk, Bl, n0, n1, n2, two);
-            ++n_ext; n_two += two;
+            if (STATS) { ++n_ext; n_two += two; }
             if (n2 < max_mem_intv && i - x >= min_seed_len) {               // bwt.c:369-373
                 if (n2 > 0) {                                               // bwamem.c:174
                     if (n_out < P.cap_out) {
@@ -511,24 +517,30 @@ __global__ void __launch_bounds__(S3_THREADS) smem_p3_kernel(SmemParams P)
         occ32_load2p(pk, pl, Bk, Bl);
         pending = true;
     }
-    if (n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
+    if (STATS && n_ext) { atomicAdd(&P.stats[CNT_EXTEND], (unsigned long long)n_ext); atomicAdd(&P.stats[CNT_TWO_BLOCK], (unsigned long long)n_two); }
+}
+
+template <class E, bool QGLOB, bool STATS>
+static int launch_p3_ts(const SmemParams &p, int n_sms, cudaStream_t st)
+{
+    const size_t smem = QGLOB ? 0 : (size_t)p.pk_stride * 4 * S3_THREADS;
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute((smem_p3_kernel<E, QGLOB, STATS>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    int occ = 0;                                                            // resident blocks per SM (registers + shared memory)
+    B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (smem_p3_kernel<E, QGLOB, STATS>), S3_THREADS, smem));
+    if (occ > 0) per_sm = std::min(per_sm, occ);
+#endif
+    const int grid = std::max(1, std::min((p.n_reads + S3_THREADS - 1) / S3_THREADS, n_sms * per_sm));
+    B200_LAUNCH((smem_p3_kernel<E, QGLOB, STATS>), grid, S3_THREADS, smem, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
 }
 
 template <class E, bool QGLOB>
 static int launch_p3_t(const SmemParams &p, int n_sms, cudaStream_t st)
 {
-    const size_t smem = QGLOB ? 0 : (size_t)p.pk_stride * 4 * S3_THREADS;
-    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
-#ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute((smem_p3_kernel<E, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    int occ = 0;                                                            // resident blocks per SM (registers + shared memory)
-    B200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (smem_p3_kernel<E, QGLOB>), S3_THREADS, smem));
-    if (occ > 0) per_sm = std::min(per_sm, occ);
-#endif
-    const int grid = std::max(1, std::min((p.n_reads + S3_THREADS - 1) / S3_THREADS, n_sms * per_sm));
-    B200_LAUNCH((smem_p3_kernel<E, QGLOB>), grid, S3_THREADS, smem, st, p);
-    B200_CHECK(cudaGetLastError());
-    return 0;
+    return p.count_stats ? launch_p3_ts<E, QGLOB, true>(p, n_sms, st) : launch_p3_ts<E, QGLOB, false>(p, n_sms, st);
 }
 
 // wide: 0 = 32-bit positions, 1 = 64-bit positions with two-quad records, 2 = 64-bit positions < 2^33 with packed records
@@ -551,15 +563,21 @@ size_t smem_fast3_bytes(int wide, int lcap, int pk_stride)             // pk_str
     return (size_t)lcap * (wide == 1 ? 32 : 16) * S3_THREADS + (size_t)pk_stride * 4 * S3_THREADS;
 }
 
+template <class E, int LCAP, bool SPLIT, bool QGLOB, bool STATS>
+static int launch_fast3_tss(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
+{
+#ifndef B200_EMU
+    B200_CHECK(cudaFuncSetAttribute((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB, STATS>), cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+#endif
+    B200_LAUNCH((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB, STATS>), grid, S3_THREADS, smem, st, p);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
 template <class E, int LCAP, bool SPLIT, bool QGLOB>
 static int launch_fast3_ts(const SmemParams &p, int grid, size_t smem, cudaStream_t st)
 {
-#ifndef B200_EMU
-    B200_CHECK(cudaFuncSetAttribute((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB>), cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-#endif
-    B200_LAUNCH((smem_fast3_kernel<E, LCAP, SPLIT, QGLOB>), grid, S3_THREADS, smem, st, p);
-    B200_CHECK(cudaGetLastError());
-    return 0;
+    return p.count_stats ? launch_fast3_tss<E, LCAP, SPLIT, QGLOB, true>(p, grid, smem, st) : launch_fast3_tss<E, LCAP, SPLIT, QGLOB, false>(p, grid, smem, st);
 }
 
 template <class E>
@@ -570,10 +588,7 @@ static int launch_fast3_e(const SmemParams &p, int grid, int wide, int lcap, int
         return p.split_p3 ? launch_fast3_ts<E, 16, true, true>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, true>(p, grid, smem, st);
     }
     const size_t smem = smem_fast3_bytes(wide, lcap, p.pk_stride);
-    if (lcap == 4) return p.split_p3 ? launch_fast3_ts<E, 4, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 4, false, false>(p, grid, smem, st);
-    if (lcap == 6) return p.split_p3 ? launch_fast3_ts<E, 6, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 6, false, false>(p, grid, smem, st);
     if (lcap == 8) return p.split_p3 ? launch_fast3_ts<E, 8, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 8, false, false>(p, grid, smem, st);
-    if (lcap == 12) return p.split_p3 ? launch_fast3_ts<E, 12, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 12, false, false>(p, grid, smem, st);
     return p.split_p3 ? launch_fast3_ts<E, 16, true, false>(p, grid, smem, st) : launch_fast3_ts<E, 16, false, false>(p, grid, smem, st);
 }
 

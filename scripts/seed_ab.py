@@ -34,6 +34,7 @@ for s in a.set or [""]:
     for _ in range(a.reps):
         st += np.array(ctx.batch_run(opt, want_stage_ms=True))
     st /= a.reps
+    ctx.tune("seed_stats", 1); ctx.batch_run(opt, want_stage_ms=True)      # counters come from one extra, untimed run
     c = ctx.counters()
     if base is None:
         base = c["regs"]

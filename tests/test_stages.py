@@ -461,6 +461,7 @@ def test_seeding_table_counters(backend, min_seed_len):
     for k in (0, 12):
         ctx = L.Context(0, lib)
         ctx.tune("kmer_k", k)
+        ctx.tune("seed_stats", 1)
         ctx.upload_host_index(cm.context(backend, gname)._host_index)
         b = ctx.collect_intv(opt, seqs, off)
         for x, y in zip(a, b):
