@@ -12,6 +12,11 @@
 // keeps extending an interval that has become empty until the seed is long enough, and the (path-defined) x0 / x1 it
 // carries meanwhile are those of a forward extension from the first base, which is how the entries are built; a
 // backward sweep never uses more than x2 of an empty child.
+//
+// Every record also carries the size-change mask of its string's prefixes (bit t set when the prefixes of t and t + 1
+// bases have different interval sizes; sizes only shrink with length, so two prefixes have equal sizes exactly when no
+// bit lies between them).  With the mask of the depth-k record of a window the seeding kernel settles the duplicate test
+// of bwt.c:339 for ALL its table-range list entries of one backward position at once (smem3.cu).
 #include "b200_internal.h"
 #include "occ32.cuh"
 
@@ -22,19 +27,21 @@ __global__ void build_kmer_tab_kernel(DevIndex ix, uint4 *tab, int k, u32 off)
     if (W >> (2 * k)) return;
     int b = (int)((W >> (2 * (k - 1))) & 3);
     PT x0 = (PT)ix.L2[b] + 1, x2 = (PT)(ix.L2[b + 1] - ix.L2[b]), x1 = (PT)ix.L2[3 - b] + 1;    // bwt.c:301 (bwt_set_intv)
+    u32 chg = 0;                                                 // bit t: the prefixes of t and t + 1 bases differ in size
     for (int t = 1; t < k; ++t) {
         b = (int)((W >> (2 * (k - 1 - t))) & 3);
         PT n0, n1, n2; int two;
         occ32_child<PT>(ix, x0, x1, x2, 0, 3 - b, n0, n1, n2, two);                             // forward extension, bwt.c:310
+        chg |= (u32)(n2 != x2) << t;
         x0 = n0; x1 = n1; x2 = n2;
     }
-    if (sizeof(PT) == 4) tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, 0u);
+    if (sizeof(PT) == 4) tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, chg);
     else if (PACK33)                                             // Ent33 (smem3.cu): bit 32 of x0 / x1 / x2 in the top bits of the last word
-        tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, (u32)((u64)x0 >> 32) << 31 | ((u32)((u64)x1 >> 32) & 1u) << 30 | ((u32)((u64)x2 >> 32) & 1u) << 29);
+        tab[off + W] = make_uint4((u32)x0, (u32)x1, (u32)x2, chg | (u32)((u64)x0 >> 32) << 31 | ((u32)((u64)x1 >> 32) & 1u) << 30 | ((u32)((u64)x2 >> 32) & 1u) << 29);
     else {
         uint4 *p = tab + ((size_t)off + W) * 2;
         p[0] = make_uint4((u32)x0, (u32)((u64)x0 >> 32), (u32)x1, (u32)((u64)x1 >> 32));
-        p[1] = make_uint4((u32)x2, (u32)((u64)x2 >> 32), 0u, 0u);
+        p[1] = make_uint4((u32)x2, (u32)((u64)x2 >> 32), chg, 0u);
     }
 }
 

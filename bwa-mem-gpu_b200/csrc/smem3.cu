@@ -43,6 +43,7 @@ template <> struct Ent<u32> {
     static __device__ __forceinline__ void ld(const uint4 *p, int stride, u32 &x0, u32 &x1, u32 &x2, u32 &end)
     { const uint4 v = p[0]; x0 = v.x; x1 = v.y; x2 = v.z; end = v.w; (void)stride; }
     static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &, u32 &x0, u32 &x1, u32 &x2) { x0 = a.x; x1 = a.y; x2 = a.z; }
+    static __device__ __forceinline__ u32 tabmask(const uint4 &a, const uint4 &) { return a.w; }      // prefix size-change mask (kmer_tab.cu)
 };
 template <> struct Ent<u64> {
     typedef u64 PT;
@@ -59,6 +60,7 @@ template <> struct Ent<u64> {
     }
     static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &b, u64 &x0, u64 &x1, u64 &x2)
     { x0 = (u64)a.y << 32 | a.x; x1 = (u64)a.w << 32 | a.z; x2 = (u64)b.y << 32 | b.x; }
+    static __device__ __forceinline__ u32 tabmask(const uint4 &, const uint4 &b) { return b.z; }
 };
 struct Ent33 {
     typedef u64 PT;
@@ -73,6 +75,7 @@ struct Ent33 {
     static __device__ __forceinline__ void st(uint4 *p, int stride, u64 x0, u64 x1, u64 x2, u32 end) { p[0] = pack(x0, x1, x2, end); (void)stride; }
     static __device__ __forceinline__ void ld(const uint4 *p, int stride, u64 &x0, u64 &x1, u64 &x2, u32 &end) { unpack(p[0], x0, x1, x2, end); (void)stride; }
     static __device__ __forceinline__ void tab(const uint4 &a, const uint4 &, u64 &x0, u64 &x1, u64 &x2) { u32 e; unpack(a, x0, x1, x2, e); }
+    static __device__ __forceinline__ u32 tabmask(const uint4 &a, const uint4 &) { return a.w & 0xffffu; }
 };
 
 __device__ __forceinline__ void s3_emit(Intv *out, int &n_out, int cap_out, u64 x0, u64 x1, u64 x2, int start, int end)
@@ -219,7 +222,7 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
         // ------------------------------------------------------------ the single gather site: consume the sectors
         PT n0, n1, n2; int two;
         if (ptab) {                                                         // table entry: the child's bi-interval itself
-            if (EQ == 1) { const uint4 v = ptab == 2 ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
+            if (EQ == 1) { const uint4 v = (ptab & 2) ? Bk.pl : Bk.cnt; E::tab(v, v, n0, n1, n2); }
             else E::tab(Bk.cnt, Bk.pl, n0, n1, n2);
             two = 0;
             if (STATS) {
@@ -261,6 +264,19 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                 } else {
                     S3_STORE_ENTRY(ncurr, n0, n1, n2, pend);                // ncurr <= j: slot already consumed
                     ++ncurr;
+                }
+            }
+            if (!STATS && (ptab & 4) && n2 >= min_intv) {
+                // The longest virtual entry lives, so every shorter one does (sizes grow as strings shrink), and each is
+                // kept exactly when its size differs from its predecessor's (bwt.c:339): a set bit of the window's
+                // change mask between the two lengths.  Child length of entry L is L + (sx - i).
+                const u32 cm = (EQ == 1 ? E::tabmask((ptab & 8) ? Bl.pl : Bl.cnt, Bl.pl) : E::tabmask(Bl.cnt, Bl.pl)) >> (sx - i);
+                int lprev = (int)pend - sx;
+                while (vm) {
+                    const int lb = 31 - __clz((int)vm);
+                    vm ^= 1u << lb;
+                    if (cm & ((1u << lprev) - (1u << lb))) vnext |= 1u << lb;
+                    lprev = lb;
                 }
             }
             ++j;
@@ -415,8 +431,14 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
             if (ptab) {                                                     // child = string of cur + 1 <= KT bases: table
                 const u32 wn = is_back ? (b << (2 * cur)) | (cur ? wb >> (2 * (KT - cur)) : 0u) : (wf << 2) | b;
                 const size_t e = (size_t)(ix.kmer_off[cur + 1] + wn) * EQ;
-                if (EQ == 1) { ptab = 1 + (int)(e & 1); pk = ktab + (e & ~(size_t)1); } else pk = ktab + e;
+                if (EQ == 1) { ptab = 1 | (int)(e & 1) << 1; pk = ktab + (e & ~(size_t)1); } else pk = ktab + e;
                 pl = pk;
+                // a virtual entry with other virtual entries behind it, and the KT bases from i on all inside the forward
+                // sweep's range: fetch the window's depth-KT record too, its mask settles the others (consume step)
+                if (!STATS && is_back && j >= nprev && vm != 0 && ret - i >= KT) {
+                    const size_t ew = (size_t)(ix.kmer_off[KT] + ((b << (2 * KT - 2)) | (wb >> 2))) * EQ;
+                    if (EQ == 1) { ptab |= 4 | (int)(ew & 1) << 3; pl = ktab + (ew & ~(size_t)1); } else { ptab |= 4; pl = ktab + ew; }
+                }
             } else occ32_addr<PT>(ix, k0, k1, kk2, is_back, pk, pl);
             occ32_load2p(pk, pl, Bk, Bl);                                   // requests in flight across the back-edge
         }

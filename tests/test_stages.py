@@ -444,7 +444,7 @@ def test_seeding_variants(backend, tune):
 
 @needs_ref
 @pytest.mark.parametrize("backend", BACKENDS)
-@pytest.mark.parametrize("min_seed_len", [19, 10])
+@pytest.mark.parametrize("min_seed_len", [19, 13, 10])
 def test_seeding_table_counters(backend, min_seed_len):
     """The k-mer table path (and its bit-only list entries, used while min_seed_len exceeds the table depth) answers the
     same bwt_extend calls as the plain path: same intervals, and the same extension / two-block counts (the roofline's
@@ -455,20 +455,21 @@ def test_seeding_table_counters(backend, min_seed_len):
     idx = cm.ref_index(gname)
     opt = abi.default_opt()
     opt.min_seed_len = min_seed_len
-    seqs, off = cm.reads_for(gname, _sizes(backend, 200, 20000), seed=58, indel=0.004, n_rate=0.002)
+    seqs, off = cm.reads_for(gname, _sizes(backend, 400, 20000), seed=58, indel=0.004, n_rate=0.002)
     a = idx.collect_intv(opt, seqs, off)
     got = []
-    for k in (0, 12):
+    for k, stats in ((0, 1), (12, 1), (12, 0)):              # stats off: the production kernels (entries settled in groups)
         ctx = L.Context(0, lib)
         ctx.tune("kmer_k", k)
-        ctx.tune("seed_stats", 1)
+        ctx.tune("seed_stats", stats)
         ctx.upload_host_index(cm.context(backend, gname)._host_index)
         b = ctx.collect_intv(opt, seqs, off)
         for x, y in zip(a, b):
             assert np.array_equal(x, y)
-        ctx.align(opt, seqs, off)
-        c = ctx.counters()
-        got.append((c["extend"], c["two_block"]))
+        if stats:
+            ctx.align(opt, seqs, off)
+            c = ctx.counters()
+            got.append((c["extend"], c["two_block"]))
         ctx.close()
     assert got[0] == got[1] and got[0][0] > 0
 
