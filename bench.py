@@ -294,6 +294,12 @@ def run_ours(a, world, cores, barrier):
         raise SystemExit(f"bench.py --gpus {N}: only {torch.cuda.device_count()} CUDA devices visible")
     t_setup = time.time()
     d = ensure_index_cache(a)
+    if not a.no_sub and N == 1:                            # the paired-end sub-record's index too, while the device is still empty
+        try:
+            import bench_pe
+            ensure_index_cache(argparse.Namespace(contigs=bench_pe.CONTIGS, contig_len=bench_pe.CONTIG_LEN))
+        except (Exception, SystemExit) as e:  # noqa: BLE001
+            sys.stderr.write(f"[bench] sub-record index: {str(e)[:300]}\n")
     meta, pac, bwt_words, sa_sampled = BI.load(d)
     l_pac = meta["l_pac"]
     # ---- inputs: reads and names in pinned host memory
@@ -493,10 +499,13 @@ def run_ours(a, world, cores, barrier):
                                                "e2e_value": r["process_seqs_reads_per_s"]}
                 idx = None
     if not a.no_sub and N == 1:
+        for c in e2e_ctxs[::-1]:                           # the sub-records need the device memory: keep only the index owner
+            if c is not ctxs[0]:
+                c.close()
         try:
             import bench_sub
             out_rec["sub_records"] = bench_sub.run(a, ctxs[0], hidx, pac, cores)
-        except Exception as e:  # noqa: BLE001
+        except (Exception, SystemExit) as e:  # noqa: BLE001  (a sub-record must never cost the main line)
             out_rec["sub_records"] = {"error": str(e)[:500]}
     out_rec["setup"]["total_wall_s"] = time.time() - t_setup
     print(json.dumps(out_rec))

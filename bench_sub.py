@@ -77,13 +77,14 @@ def run(a, ctx, hidx, pac, cores):
     out = {}
     try:
         out["long_reads"] = long_reads(a, ctx, hidx, pac, cores)
-    except Exception as e:  # noqa: BLE001
+    except (Exception, SystemExit) as e:  # noqa: BLE001
         out["long_reads"] = {"error": str(e)[:400]}
+    ctx.close()                                            # frees the 3.1 Gbp index and the long-read scratch for the next record
     try:
         import bench_pe
         out["paired_end"] = bench_pe.run(a, cores)
     except ImportError:
         out["paired_end"] = {"error": "not built"}
-    except Exception as e:  # noqa: BLE001
+    except (Exception, SystemExit) as e:  # noqa: BLE001
         out["paired_end"] = {"error": str(e)[:400]}
     return out

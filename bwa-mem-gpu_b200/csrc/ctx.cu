@@ -140,7 +140,12 @@ int b200_index_finish(b200_ctx *ctx, int flags)
         if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
         ix.occ32 = ctx->d_occ32.as<uint4>();
         ix.kmer_tab = nullptr; ix.kmer_k = 0;
-        const int want_k = ctx->kmer_k >= 0 ? ctx->kmer_k : (seq_len >= 0xfffffff0ull ? 13 : 9);
+        // default depth: two below the length at which a random string becomes unique in this text (floor(log4 seq_len)),
+        // between 9 and 13: 13 at 3.1 Gbp, 11 at 100 Mbp, 9 at 5 Mbp (profiles/r6m_seed_ab.txt)
+        int auto_k = 0;
+        for (u64 t = seq_len; t >= 4; t >>= 2) ++auto_k;
+        auto_k = std::max(9, std::min(13, auto_k - 2));
+        const int want_k = ctx->kmer_k >= 0 ? ctx->kmer_k : auto_k;
         if (want_k > 0) {                                            // k-mer interval table (kmer_tab.cu)
             const int wide = b200_wide_mode(ctx);                               // same rule as the seeding kernel template (pipeline.cu)
             const int kk = want_k > 13 ? 13 : want_k;                  // kmer_off[14]
