@@ -140,15 +140,20 @@ int b200_index_finish(b200_ctx *ctx, int flags)
         if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
         ix.occ32 = ctx->d_occ32.as<uint4>();
         ix.kmer_tab = nullptr; ix.kmer_k = 0;
-        // default depth: two below the length at which a random string becomes unique in this text (floor(log4 seq_len)),
-        // between 9 and 13: 13 at 3.1 Gbp, 11 at 100 Mbp, 9 at 5 Mbp (profiles/r6m_seed_ab.txt)
+        // default depth: the length at which a random string becomes unique in this text, floor(log4 seq_len), between 9
+        // and 15: 15 at 3.1 Gbp (22.9 GB of table next to the 57 GB index), 13 at 100 Mbp (1.4 GB), 11 at 5 Mbp.  Deeper
+        // is faster up to there (profiles/r6q_seed_table_depth.txt): more list entries are bits, fewer extensions pay for
+        // two index sectors and the popcounts.
         int auto_k = 0;
         for (u64 t = seq_len; t >= 4; t >>= 2) ++auto_k;
-        auto_k = std::max(9, std::min(13, auto_k - 2));
+        auto_k = std::max(9, std::min(15, auto_k));
+#ifdef B200_EMU
+        auto_k = 9;                                                  // the emulated builder is slow; tests ask for deeper tables by name
+#endif
         const int want_k = ctx->kmer_k >= 0 ? ctx->kmer_k : auto_k;
         if (want_k > 0) {                                            // k-mer interval table (kmer_tab.cu)
             const int wide = b200_wide_mode(ctx);                               // same rule as the seeding kernel template (pipeline.cu)
-            const int kk = want_k > 13 ? 13 : want_k;                  // kmer_off[14]
+            const int kk = want_k > 15 ? 15 : want_k;                  // kmer_off[16]
             if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide == 1 ? 32 : 16))) return -1;
             if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
             ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;

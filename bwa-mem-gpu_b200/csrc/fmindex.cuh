@@ -31,7 +31,7 @@ struct DevIndex {
     // bi-intervals of all strings of length 1..kmer_k (see kmer_tab.cuh); 0 = no table
     const uint4 *kmer_tab;   // entry of string W (length k): kmer_tab[(kmer_off[k] + W) * quads], quads = 1 (u32) / 2 (u64)
     int kmer_k;
-    u32 kmer_off[14];
+    u32 kmer_off[16];        // depth <= 15: string codes and the virtual-entry masks of smem3.cu are 32-bit
 };
 
 struct Intv { u64 x0, x1, x2, info; };   // == bwtintv_t (bwt.h:62)

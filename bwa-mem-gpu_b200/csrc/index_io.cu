@@ -18,7 +18,7 @@ namespace {
 enum { A_BWT = 0, A_SA, A_PAC, A_ANN_OFF, A_ANN_LEN, A_ANN_ALT, A_OCC32, A_KMER, A_SA_FULL, A_N };
 
 struct IdxHeader {
-    char magic[8];                       // "B200IDX4"
+    char magic[8];                       // "B200IDX5"
     u64 header_bytes, file_bytes;
     DevIndex ix;                         // scalars as they are; pointers are rewritten on load
     u64 off[A_N], bytes[A_N];            // file offset / length of every array (0 = absent)
@@ -41,7 +41,7 @@ extern "C" int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_
     B200_CHECK(cudaSetDevice(ctx->device));
     IdxHeader H;
     memset(&H, 0, sizeof(H));
-    memcpy(H.magic, "B200IDX4", 8);
+    memcpy(H.magic, "B200IDX5", 8);
     H.header_bytes = sizeof(H);
     H.ix = ctx->ix;
     H.force_wide = ctx->force_wide; H.kmer_k = ctx->kmer_k; H.idx_bwt_size = ctx->idx_bwt_size;
@@ -97,7 +97,7 @@ extern "C" int b200_index_load(b200_ctx_t *ctx, const char *path, int flags)
     struct stat sb;
     IdxHeader H;
     if (fstat(fd, &sb) != 0 || (size_t)sb.st_size < sizeof(H) || pread(fd, &H, sizeof(H), 0) != (ssize_t)sizeof(H) ||
-        memcmp(H.magic, "B200IDX4", 8) != 0 || H.header_bytes != sizeof(H) || H.file_bytes > (u64)sb.st_size) {
+        memcmp(H.magic, "B200IDX5", 8) != 0 || H.header_bytes != sizeof(H) || H.file_bytes > (u64)sb.st_size) {
         close(fd); b200_set_error("b200_index_load: %s is not an index of this library version", path); return -1;
     }
     const char *map = (const char *)mmap(nullptr, (size_t)H.file_bytes, PROT_READ, MAP_PRIVATE, fd, 0);

@@ -271,13 +271,12 @@ __global__ void __launch_bounds__(S3_THREADS, E::kMinBlocks) smem_fast3_kernel(S
                 // kept exactly when its size differs from its predecessor's (bwt.c:339): a set bit of the window's
                 // change mask between the two lengths.  Child length of entry L is L + (sx - i).
                 const u32 cm = (EQ == 1 ? E::tabmask((ptab & 8) ? Bl.pl : Bl.cnt, Bl.pl) : E::tabmask(Bl.cnt, Bl.pl)) >> (sx - i);
-                int lprev = (int)pend - sx;
-                while (vm) {
-                    const int lb = 31 - __clz((int)vm);
-                    vm ^= 1u << lb;
-                    if (cm & ((1u << lprev) - (1u << lb))) vnext |= 1u << lb;
-                    lprev = lb;
-                }
+                // Entry L owns the lengths [L, next longer entry): it is kept when cm has a bit there.  Branch-free: in
+                // bit-reversed order an entry's bit sits on top of its range, and adding all-ones over the non-entry
+                // positions carries any cm bit of a range up into the entry's position, where the carry stops.
+                const u32 rv = __brev(vm), rc = __brev(cm & ((1u << ((int)pend - sx)) - 1u)), ns = ~rv;
+                vnext |= __brev((((rc & ns) + ns) & rv) | (rc & rv));
+                vm = 0;
             }
             ++j;
             if (j >= nprev && vm == 0) {                                    // bwt.c:343-344

@@ -168,7 +168,7 @@ int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src);
  * of bwa_idx_load (bwa.c:384-434) AND the derived occ32 sectors and k-mer interval table, with_full_sa != 0 also the full
  * suffix array (8 bytes per row on 64-bit indexes: 50 GB at 3.1 Gbp; without it b200_index_load with B200_IDX_FULL_SA
  * re-expands the sampled SA on the device) -- written as it lies, and read back with large copies instead of the re-layout
- * of every start.  The file is specific to this library version (magic "B200IDX4"). */
+ * of every start.  The file is specific to this library version (magic "B200IDX5"). */
 int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_sa);
 int b200_index_load(b200_ctx_t *ctx, const char *path, int flags);
 
