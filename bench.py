@@ -502,6 +502,7 @@ def run_ours(a, world, cores, barrier):
         for c in e2e_ctxs[::-1]:                           # the sub-records need the device memory: keep only the index owner
             if c is not ctxs[0]:
                 c.close()
+        ctxs[0].trim()                                     # ... without the 100 M-read batch it still holds
         try:
             import bench_sub
             out_rec["sub_records"] = bench_sub.run(a, ctxs[0], hidx, pac, cores)

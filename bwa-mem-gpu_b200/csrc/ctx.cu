@@ -125,6 +125,27 @@ extern "C" void b200_ctx_destroy(b200_ctx_t *ctx)
     delete ctx;
 }
 
+// Gives the device memory of the batch pipeline back (resident batch, stage buffers, worker2 / SAM scratch); the index and
+// the context stay usable, buffers grow again on the next call.
+extern "C" int b200_ctx_trim(b200_ctx_t *ctx)
+{
+    if (!ctx) { b200_set_error("null context"); return -1; }
+    std::lock_guard<std::mutex> lk(ctx->call_mu);
+    B200_CHECK(cudaSetDevice(ctx->device));
+    B200_CHECK(cudaStreamSynchronize(ctx->st));
+    DevBuf *bufs[] = { &ctx->d_retry, &ctx->d_pk, &ctx->d_spill, &ctx->d_jobs0, &ctx->d_jobs1, &ctx->d_jobs2, &ctx->d_jobs3, &ctx->d_jsort, &ctx->d_rstate, &ctx->d_njobs,
+                       &ctx->d_seq, &ctx->d_off, &ctx->d_intv, &ctx->d_intv_n, &ctx->d_lists, &ctx->d_seed_n, &ctx->d_seed_off,
+                       &ctx->d_l_rep, &ctx->d_seeds, &ctx->d_cseeds, &ctx->d_chains, &ctx->d_chn_n, &ctx->d_cseed_n,
+                       &ctx->d_scratch, &ctx->d_stage, &ctx->d_eh, &ctx->d_srt, &ctx->d_arena, &ctx->d_reg_off, &ctx->d_reg_n,
+                       &ctx->d_dst_off, &ctx->d_scan_tmp, &ctx->d_final, &ctx->d_final_n,
+                       &ctx->d_pa, &ctx->d_pb, &ctx->d_pc, &ctx->d_pd, &ctx->d_pe, &ctx->d_pf, &ctx->d_pg, &ctx->d_ph };
+    for (DevBuf *b : bufs) b->release();
+    for (DevBuf &b : ctx->d_r2a) b.release();
+    for (DevBuf &b : ctx->d_sam) b.release();
+    ctx->n_reads = 0; ctx->n_bytes = 0;
+    return 0;
+}
+
 // Derived device structures of an index whose reference-layout arrays are resident (uploaded or built on the device):
 // occ32 re-layout, k-mer interval table, and the full suffix array unless it is there already.
 int b200_index_finish(b200_ctx *ctx, int flags)

@@ -20,7 +20,7 @@ IDX_FULL_SA = 0x1
 E_FAIL, E_CAPACITY = -(1 << 63) + 1, -(1 << 63) + 2      # B200_E_FAIL / B200_E_CAPACITY (include/bwamem_b200.h)
 
 _SYMBOLS = [
-    "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
+    "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_tune", "b200_ctx_trim", "b200_microbench", "b200_last_error", "b200_index_upload", "b200_index_upload_raw",
     "b200_occ4_batch", "b200_2occ4_batch", "b200_extend_batch", "b200_sa_batch", "b200_smem1a_batch",
     "b200_collect_intv_batch", "b200_chain_batch", "b200_ksw_extend2_batch", "b200_ksw_align2_batch", "b200_align_batch",
     "b200_batch_upload", "b200_batch_run", "b200_batch_download", "b200_batch_counters", "b200_batch_rescue", "b200_batch_set_regs",
@@ -321,6 +321,9 @@ class Context:
         if self.h:
             self.lib.b200_ctx_destroy(self.h)
             self.h = None
+
+    def trim(self):
+        self._chk(self.lib.b200_ctx_trim(self.h), "trim")
 
     def tune(self, key: str, value: int):
         self._chk(self.lib.b200_ctx_tune(self.h, key.encode(), C.c_int64(value)), "tune")

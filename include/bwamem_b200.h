@@ -399,6 +399,9 @@ int64_t b200_align_batch(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, con
  * b200_batch_upload(), b200_batch_run() launches the whole stage pipeline without host copies and
  * b200_batch_download() fetches the regions.  stage_ms (may be NULL) receives CUDA-event times:
  * [0]=pack [1]=smem [2]=seed/sa [3]=chain [4]=extend [5]=total. */
+/* Frees the device memory of the batch pipeline held by the context (resident batch, stage and worker2 / SAM buffers);
+ * the index stays, buffers grow again on the next call.  0 on success. */
+int b200_ctx_trim(b200_ctx_t *ctx);
 int b200_batch_upload(b200_ctx_t *ctx, int n_reads, const uint8_t *seqs, const int64_t *off);
 int b200_batch_run(b200_ctx_t *ctx, const mem_opt_t *opt, float *stage_ms);
 int64_t b200_batch_download(b200_ctx_t *ctx, int64_t cap, mem_alnreg_t *out_regs, int32_t *out_n);
