@@ -56,7 +56,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sub", action="store_true", help="skip the paired-end and long-read sub-records")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables (b200_ctx_tune)")
-    ap.add_argument("--ctx-per-gpu", type=int, default=2, help="e2e: host threads (contexts sharing one index) per device")
+    ap.add_argument("--ctx-per-gpu", type=int, default=3, help="e2e: host threads (contexts sharing one index) per device")
     ap.add_argument("--check", type=int, default=20000, help="reads compared with the reference CPU code (regions and SAM text)")
     a = ap.parse_args()
     if a.small:
