@@ -508,6 +508,7 @@ def run_ours(a, world, cores, barrier):
             out_rec["sub_records"] = bench_sub.run(a, ctxs[0], hidx, pac, cores)
         except (Exception, SystemExit) as e:  # noqa: BLE001  (a sub-record must never cost the main line)
             out_rec["sub_records"] = {"error": str(e)[:500]}
+    out_rec["setup"]["host_cpus"] = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     out_rec["setup"]["total_wall_s"] = time.time() - t_setup
     print(json.dumps(out_rec))
     for c in e2e_ctxs[::-1]:
