@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sub", action="store_true", help="skip the paired-end and long-read sub-records")
     ap.add_argument("--tune", default="", help="comma-separated key=value context tunables (b200_ctx_tune)")
+    ap.add_argument("--sub-reads", type=int, default=0, help="e2e: reads per sub-batch of b200_reads_to_sam (0 = the library's rule)")
     ap.add_argument("--ctx-per-gpu", type=int, default=3, help="e2e: host threads (contexts sharing one index) per device")
     ap.add_argument("--check", type=int, default=20000, help="reads compared with the reference CPU code (regions and SAM text)")
     a = ap.parse_args()
@@ -412,7 +413,7 @@ def run_ours(a, world, cores, barrier):
             e2e_ctxs.append(c2)
     for s in range(a.warmup + a.steps):
         t0 = time.perf_counter()
-        out, _, st = L.reads_to_sam(e2e_ctxs, opt, hidx.names, seqs, off, nf, no, sam=sam, want_off=False)
+        out, _, st = L.reads_to_sam(e2e_ctxs, opt, hidx.names, seqs, off, nf, no, sam=sam, want_off=False, sub_reads=a.sub_reads)
         dt = time.perf_counter() - t0
         if s >= a.warmup:
             e2e_s.append(dt)

@@ -37,6 +37,7 @@ struct b200_ctx {
     DevBuf d_seq, d_off;
     int n_reads = 0; i64 n_bytes = 0; int max_len = 0;
     std::vector<i64> h_off;
+    std::vector<i64> h_roff; std::vector<i32> h_reg_read;   // reg2aln.cu: per-call host arrays kept across calls (no allocator churn with many host threads)
     const i64 *hoff = nullptr;                 // host view of the batch's read offsets (h_off, or the caller's array during b200_align_batch)
 
     // tunables

@@ -522,7 +522,9 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     if (pe && (!sink || (n_reads & 1) || (n_processed & 1))) { b200_set_error("paired-end worker2 needs the device consumer and whole pairs"); return -1; }
     cudaStream_t st = ctx->st;
     if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
-    std::vector<i64> roff((size_t)n_reads + 1, 0);
+    std::vector<i64> &roff = ctx->h_roff;                  // kept in the context: 8 MB blocks allocated and freed per call by
+    if (roff.size() < (size_t)n_reads + 1) roff.resize((size_t)n_reads + 1);   // dozens of host threads cost page faults and TLB shootdowns
+    roff[0] = 0;
     int max_cnt = 0;
     for (int r = 0; r < n_reads; ++r) { roff[r + 1] = roff[r] + cnt[r]; max_cnt = std::max(max_cnt, (int)cnt[r]); }
     const i64 n_regs = roff[n_reads];
@@ -545,7 +547,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     }
     if (n_regs == 0) return 0;
     if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
-    std::vector<i32> reg_read((size_t)n_regs);
+    std::vector<i32> &reg_read = ctx->h_reg_read;
+    if (reg_read.size() < (size_t)n_regs) reg_read.resize((size_t)n_regs + (size_t)n_regs / 8);
     {
         i64 g = 0;
         for (int r = 0; r < n_reads; ++r) for (int k = 0; k < cnt[r]; ++k) reg_read[g++] = r;
