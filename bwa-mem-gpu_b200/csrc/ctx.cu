@@ -93,7 +93,7 @@ extern "C" void b200_host_free(void *p) { if (p) cudaFreeHost(p); }
 // grow-only page-locked buffer owned by the context (released by b200_ctx_destroy); contents are not preserved on growth
 extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes)
 {
-    if (!ctx || slot < 0 || slot >= 12) { b200_set_error("b200_ctx_pinned: bad slot"); return nullptr; }
+    if (!ctx || slot < 0 || slot >= 16) { b200_set_error("b200_ctx_pinned: bad slot"); return nullptr; }
     if (bytes <= ctx->pin_cap[slot] && ctx->pin_p[slot]) return ctx->pin_p[slot];
     cudaSetDevice(ctx->device);
     b200_host_free(ctx->pin_p[slot]);

@@ -37,7 +37,6 @@ struct b200_ctx {
     DevBuf d_seq, d_off;
     int n_reads = 0; i64 n_bytes = 0; int max_len = 0;
     std::vector<i64> h_off;
-    std::vector<i64> h_roff; std::vector<i32> h_reg_read;   // reg2aln.cu: per-call host arrays kept across calls (no allocator churn with many host threads)
     const i64 *hoff = nullptr;                 // host view of the batch's read offsets (h_off, or the caller's array during b200_align_batch)
 
     // tunables
@@ -81,7 +80,7 @@ struct b200_ctx {
     int r2a_warp = 1;                          // reg2aln: regions with a query part > 400 bases go to the warp-per-region kernel (tunable)
     int r2a_small = 1;                         // reg2aln pass 1 with ring-sized H / E rows (tunable)
     int log_cap = 0;                           // entries of the log(i) table in d_r2a[16]
-    void *pin_p[12] = {}; size_t pin_cap[12] = {};   // page-locked host buffers of b200_align_sam_se_batch (b200_ctx_pinned)
+    void *pin_p[16] = {}; size_t pin_cap[16] = {};   // page-locked host buffers of b200_align_sam_se_batch (b200_ctx_pinned)
     // scratch for the primitive batches
     DevBuf d_pa, d_pb, d_pc, d_pd, d_pe, d_pf, d_pg, d_ph;
 };
@@ -117,3 +116,5 @@ int launch_pestat_pairs(const mem_opt_t *opt, i64 l_pac, const mem_alnreg_t *reg
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
 int b200_index_finish(b200_ctx *ctx, int flags);
 b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac);
+
+extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes);   // ctx.cu: grow-only page-locked buffer of the context (slots 0-15)

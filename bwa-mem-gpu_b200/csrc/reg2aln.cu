@@ -522,8 +522,10 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     if (pe && (!sink || (n_reads & 1) || (n_processed & 1))) { b200_set_error("paired-end worker2 needs the device consumer and whole pairs"); return -1; }
     cudaStream_t st = ctx->st;
     if (ctx->n_bytes && launch_pack_reads(ctx->d_seq.as<u8>(), ctx->n_bytes, st)) return -1;          // reads as nt4 (idempotent)
-    std::vector<i64> &roff = ctx->h_roff;                  // kept in the context: 8 MB blocks allocated and freed per call by
-    if (roff.size() < (size_t)n_reads + 1) roff.resize((size_t)n_reads + 1);   // dozens of host threads cost page faults and TLB shootdowns
+    // host arrays of the call live in page-locked buffers of the context (slots 12, 13): no 8 MB allocations per call from
+    // every host thread (page faults, TLB shootdowns), and their uploads are real asynchronous copies
+    i64 *roff = (i64 *)b200_ctx_pinned(ctx, 12, ((size_t)n_reads + 1) * 8);
+    if (!roff) return -1;
     roff[0] = 0;
     int max_cnt = 0;
     for (int r = 0; r < n_reads; ++r) { roff[r + 1] = roff[r] + cnt[r]; max_cnt = std::max(max_cnt, (int)cnt[r]); }
@@ -547,8 +549,8 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     }
     if (n_regs == 0) return 0;
     if (n_regs >= 0x7fffffff) { b200_set_error("too many regions in one call"); return -1; }
-    std::vector<i32> &reg_read = ctx->h_reg_read;
-    if (reg_read.size() < (size_t)n_regs) reg_read.resize((size_t)n_regs + (size_t)n_regs / 8);
+    i32 *reg_read = (i32 *)b200_ctx_pinned(ctx, 13, (size_t)n_regs * 4 + 4);
+    if (!reg_read) return -1;
     {
         i64 g = 0;
         for (int r = 0; r < n_reads; ++r) for (int k = 0; k < cnt[r]; ++k) reg_read[g++] = r;
@@ -599,7 +601,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
     if (d_dp.ensure(((size_t)5 * chunk + 8) * 4)) return -1;
     if (finalize) {
         if (d_roff.ensure(((size_t)n_reads + 1) * 8) || d_sel.ensure((size_t)chunk * sizeof(b200_sel_t))) return -1;
-        B200_CHECK(cudaMemcpyAsync(d_roff.p, roff.data(), ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
+        B200_CHECK(cudaMemcpyAsync(d_roff.p, roff, ((size_t)n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
         const int want = 4 * max_len + 65536;                  // log(l), l <= max(qe - qb, re - rb); the kernel checks the bound
         if (ctx->log_cap < want) {
             std::vector<double> tab((size_t)want);
@@ -655,7 +657,7 @@ static int64_t reg2aln_impl(b200_ctx_t *ctx, const mem_opt_t *opt, int n_reads, 
         if (resident)      // a copy: marking is not idempotent (sub_n accumulates), the resident regions stay as worker1 left them
             B200_CHECK(cudaMemcpyAsync(d_regs.p, ctx->d_final.as<mem_alnreg_t>() + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyDeviceToDevice, st));
         else B200_CHECK(cudaMemcpyAsync(d_regs.p, regs + g0, (size_t)n * sizeof(mem_alnreg_t), cudaMemcpyHostToDevice, st));
-        B200_CHECK(cudaMemcpyAsync(d_rr.p, reg_read.data() + g0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        B200_CHECK(cudaMemcpyAsync(d_rr.p, reg_read + g0, (size_t)n * 4, cudaMemcpyHostToDevice, st));
         B200_CHECK(cudaMemsetAsync(ctx->d_ctl.p, 0, CTL_SLOTS * 8, st));
         R2AParams P;
         memset(&P, 0, sizeof(P));
