@@ -147,7 +147,9 @@ void        b200_ctx_destroy(b200_ctx_t *ctx);
 const char *b200_last_error(void);
 /* tunables: "chunk_reads" (reads per pipeline chunk), "smem_lcap" (shared-memory list entries per read in the
  * seeding kernel; longer lists take the general kernel), "cap_intv" (interval slots per read; 0 = auto; a chunk that
- * needs more is re-run with the reported need unless "cap_retry" is 0, in which case the call fails) */
+ * needs more is re-run with the reported need unless "cap_retry" is 0, in which case the call fails), "kmer_k" (depth of the
+ * k-mer interval table, before the index upload; -1 = by index size, 9..15), "seed_stats" (1: the seeding kernels count
+ * bwt_extend calls / two-block calls for b200_batch_counters; default 0) */
 int         b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value);
 /* flags for b200_index_upload */
 #define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device */
