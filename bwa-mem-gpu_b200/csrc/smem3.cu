@@ -11,14 +11,21 @@
 //   * one register triple holds "the interval to extend next" in every phase and one index holds "the query
 //     position to extend with", so forming the request is the same three instructions for all phases;
 //   * only the child ok[c] that the algorithm consumes is computed (occ32.cuh);
+//   * extensions of short strings (up to K bases, K = depth of the k-mer interval table, kmer_tab.cu) are answered by the
+//     table; whatever a lane reads -- two index sectors, or the 32-byte sector holding a 16-byte table record -- all lanes
+//     issue it through ONE load group (loads on the two sides of a branch into the same registers wait for each other);
 //   * the read is staged once in SHARED memory as 4-bit codes ([word][thread] interleaved), so the per-step
 //     base fetch is a conflict-free LDS instead of a global byte load;
 //   * the forward change-point list lives in SHARED memory as a ring of the last LCAP entries ([slot][thread]
 //     interleaved 16/32-byte records, conflict-free 128-bit accesses); older entries spill to a per-thread
 //     global area; the backward sweep compacts the list IN PLACE (survivors overwrite consumed entries);
+//   * list entries whose string is still inside the table's range are BITS, not records ("virtual" entries, see vm below),
+//     and all of them at one backward position are settled in one iteration from the size-change mask of the window's
+//     depth-K record (bwt.c:339 needs only "same size as the next longer entry?");
 //   * positions are 32-bit when seq_len < 2^32 (template PT), 64-bit otherwise;
 //   * chain restarts (pass-1 continuation, pass-3 restart) are inlined after the consume step; only pass
-//     changes, pass-2 candidate scans and read changes take the slow path.
+//     changes, pass-2 candidate scans and read changes take the slow path;
+//   * the bwt_extend / two-block counters of the roofline are a template flag (STATS), off in production launches.
 // The emitted interval set equals the reference's; records are determined by (start,end), so after the sort
 // by `info` (bwamem.c:184) the order is unique.
 #include "b200_internal.h"

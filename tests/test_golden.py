@@ -93,3 +93,20 @@ def test_golden_align(backend):
     regs, n = ctx.align(opt, seqs, off)
     assert np.array_equal(n, g["n"])
     assert np.array_equal(regs.view(np.uint8).reshape(-1, abi.ALNREG_DTYPE.itemsize), g["regs"])
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_ctx_trim_keeps_the_index(backend):
+    """b200_ctx_trim gives the batch pipeline's device buffers back; the index stays and the next call regrows them."""
+    from bwa_mem_gpu_b200 import lib as L
+    ctx = L.Context(0, cm.backend_lib(backend))
+    ctx.upload_host_index(cm.context(backend, G)._host_index)
+    opt = abi.default_opt()
+    g = _load("align.npz")
+    seqs, off = cm.reads_for(G, 800, seed=41, indel=0.004)
+    for _ in range(2):
+        regs, n = ctx.align(opt, seqs, off)
+        assert np.array_equal(n, g["n"])
+        assert np.array_equal(regs.view(np.uint8).reshape(-1, abi.ALNREG_DTYPE.itemsize), g["regs"])
+        ctx.trim()
+    ctx.close()
