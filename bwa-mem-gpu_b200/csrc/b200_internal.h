@@ -188,3 +188,5 @@ int launch_occ_batch(const DevIndex &ix, i64 n, const u64 *k, const u64 *l, u64 
 int launch_extend_batch(const DevIndex &ix, i64 n, const u64 *ik, int is_back, u64 *ok, cudaStream_t st);
 int launch_sa_batch(const DevIndex &ix, i64 n, const u64 *k, u64 *out, int use_full, cudaStream_t st);
 int launch_build_full_sa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st);
+size_t sa40_bytes(u64 n_rows);
+int launch_pack_sa40(const void *in, int in_is64, u32 *out, u64 n_rows, cudaStream_t st);

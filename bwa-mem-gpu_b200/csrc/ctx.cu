@@ -146,6 +146,25 @@ extern "C" int b200_ctx_trim(b200_ctx_t *ctx)
     return 0;
 }
 
+// The full suffix array of a text of 2^32 or more rows as 5 bytes per row instead of 8 (50 -> 31 GB at 3.1 Gbp, on the
+// device, in the index file and in the device-to-device fan-out); a lookup is two aligned 32-bit loads (fmindex.cuh).  With
+// force_wide (tests) a 4-byte array is packed too, so that small genomes exercise the path.
+int b200_pack_full_sa(b200_ctx *ctx)
+{
+    DevIndex &ix = ctx->ix;
+    const bool from64 = ix.sa_full64 != nullptr;
+    if (!from64 && !(ix.sa_full32 && ctx->force_wide)) return 0;
+    const u64 n = ix.seq_len + 1;
+    DevBuf packed;
+    if (packed.ensure_exact(sa40_bytes(n))) return -1;
+    if (launch_pack_sa40(from64 ? (const void *)ix.sa_full64 : (const void *)ix.sa_full32, from64, packed.as<u32>(), n, ctx->st)) { packed.release(); return -1; }
+    if (cudaStreamSynchronize(ctx->st) != cudaSuccess) { packed.release(); b200_set_error("packing the suffix array failed"); return -1; }
+    ctx->d_sa_full.release();
+    ctx->d_sa_full = packed;
+    ix.sa_full40 = ctx->d_sa_full.as<u32>(); ix.sa_full32 = nullptr; ix.sa_full64 = nullptr;
+    return 0;
+}
+
 // Derived device structures of an index whose reference-layout arrays are resident (uploaded or built on the device):
 // occ32 re-layout, k-mer interval table, and the full suffix array unless it is there already.
 int b200_index_finish(b200_ctx *ctx, int flags)
@@ -157,7 +176,7 @@ int b200_index_finish(b200_ctx *ctx, int flags)
     {   // occ32 re-layout for the seeding kernel (occ32.cuh); superblock bases already in ix.sb_cnt
         const u64 n_blk = (seq_len >> 6) + 2;
         if (ctx->d_bwt.bytes < ((n_blk + 1) / 2) * 64) { b200_set_error("internal: bwt padding too small"); return -1; }
-        if (ctx->d_occ32.ensure((size_t)n_blk * 32)) return -1;
+        if (ctx->d_occ32.ensure_exact((size_t)n_blk * 32)) return -1;
         if (launch_build_occ32(ix, ctx->d_occ32.as<uint4>(), n_blk, ctx->st)) return -1;
         ix.occ32 = ctx->d_occ32.as<uint4>();
         ix.kmer_tab = nullptr; ix.kmer_k = 0;
@@ -175,7 +194,7 @@ int b200_index_finish(b200_ctx *ctx, int flags)
         if (want_k > 0) {                                            // k-mer interval table (kmer_tab.cu)
             const int wide = b200_wide_mode(ctx);                               // same rule as the seeding kernel template (pipeline.cu)
             const int kk = want_k > 15 ? 15 : want_k;                  // kmer_off[16]
-            if (ctx->d_kmer.ensure(kmer_tab_entries(kk) * (wide == 1 ? 32 : 16))) return -1;
+            if (ctx->d_kmer.ensure_exact(kmer_tab_entries(kk) * (wide == 1 ? 32 : 16))) return -1;
             if (launch_build_kmer_tab(ix, ctx->d_kmer.as<uint4>(), kk, wide, ctx->st)) return -1;
             ix.kmer_tab = ctx->d_kmer.as<uint4>(); ix.kmer_k = kk;
         }
@@ -200,14 +219,14 @@ int b200_index_finish(b200_ctx *ctx, int flags)
         }
 #endif
     }
-    if ((flags & B200_IDX_FULL_SA) && !ix.sa_full32 && !ix.sa_full64) {
+    if ((flags & B200_IDX_FULL_SA) && !ix.sa_full32 && !ix.sa_full64 && !ix.sa_full40) {
         const bool narrow = seq_len < 0xffffffffull;
-        if (ctx->d_sa_full.ensure((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
+        if (ctx->d_sa_full.ensure_exact((size_t)(seq_len + 1) * (narrow ? 4 : 8))) return -1;
         if (launch_build_full_sa(ix, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
         if (narrow) ix.sa_full32 = ctx->d_sa_full.as<u32>(); else ix.sa_full64 = ctx->d_sa_full.as<u64>();
     }
     B200_CHECK(cudaStreamSynchronize(ctx->st));
-    return 0;
+    return b200_pack_full_sa(ctx);
 }
 
 extern "C" int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_size, uint64_t primary,
@@ -332,7 +351,7 @@ extern "C" int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src)
     const int nb = (int)(sizeof(sb) / sizeof(sb[0]));
     for (int i = 0; i < nb; ++i) {
         if (!sb[i]->p) continue;
-        if (db[i]->ensure(sb[i]->bytes)) return -1;
+        if (db[i]->ensure_exact(sb[i]->bytes)) return -1;
         B200_CHECK(cudaMemcpyPeerAsync(db[i]->p, dst->device, sb[i]->p, src->device, sb[i]->bytes, dst->st));
     }
     B200_CHECK(cudaStreamSynchronize(dst->st));
@@ -347,10 +366,11 @@ extern "C" int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src)
     DevIndex ix = src->ix;
     ix.bwt = (const uint4 *)move(src->ix.bwt); ix.sa = (const u64 *)move(src->ix.sa);
     ix.sa_full32 = (const u32 *)move(src->ix.sa_full32); ix.sa_full64 = (const u64 *)move(src->ix.sa_full64);
+    ix.sa_full40 = (const u32 *)move(src->ix.sa_full40);
     ix.pac = (const u8 *)move(src->ix.pac); ix.ann_off = (const i64 *)move(src->ix.ann_off);
     ix.ann_len = (const i32 *)move(src->ix.ann_len); ix.ann_alt = (const i32 *)move(src->ix.ann_alt);
     ix.occ32 = (const uint4 *)move(src->ix.occ32); ix.kmer_tab = (const uint4 *)move(src->ix.kmer_tab);
-    if (!ix.bwt || !ix.pac || !ix.occ32 || (src->ix.kmer_tab && !ix.kmer_tab) || (src->ix.sa_full64 && !ix.sa_full64) || (src->ix.sa_full32 && !ix.sa_full32)) {
+    if (!ix.bwt || !ix.pac || !ix.occ32 || (src->ix.kmer_tab && !ix.kmer_tab) || (src->ix.sa_full64 && !ix.sa_full64) || (src->ix.sa_full32 && !ix.sa_full32) || (src->ix.sa_full40 && !ix.sa_full40)) {
         b200_set_error("b200_index_replicate: an index array lies outside the context's buffers"); return -1;
     }
     dst->ix = ix;

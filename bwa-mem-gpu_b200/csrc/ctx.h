@@ -17,6 +17,15 @@ struct DevBuf {
         bytes = want;
         return 0;
     }
+    int ensure_exact(size_t need)      // the same without the growth slack (index arrays: tens of GB, sized once)
+    {
+        if (need <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        if (cudaMalloc(&p, need + 256) != cudaSuccess) { p = nullptr; b200_set_error("cudaMalloc(%zu) failed", need + 256); return -1; }
+        bytes = need + 256;
+        return 0;
+    }
     void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
     template <class T> T *as() const { return (T *)p; }
 };
@@ -115,6 +124,7 @@ int launch_pestat_pairs(const mem_opt_t *opt, i64 l_pac, const mem_alnreg_t *reg
 
 int b200_run_chunk(b200_ctx *ctx, const mem_opt_t *opt, int r0, int n, int stop_after, float *stage_ms);
 int b200_index_finish(b200_ctx *ctx, int flags);
+int b200_pack_full_sa(b200_ctx *ctx);              // ctx.cu: 8-byte (or, with force_wide, 4-byte) full SA -> 5 bytes per row
 b200_ctx *b200_ctx_for_bwt(const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac);
 
 extern "C" void *b200_ctx_pinned(b200_ctx_t *ctx, int slot, size_t bytes);   // ctx.cu: grow-only page-locked buffer of the context (slots 0-15)

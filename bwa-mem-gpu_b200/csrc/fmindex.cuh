@@ -17,7 +17,8 @@ struct DevIndex {
     u64 n_sa;
     int sa_intv;
     const u32 *sa_full32;    // optional full SA (seq_len+1 entries) when seq_len < 2^32
-    const u64 *sa_full64;    // optional full SA otherwise
+    const u64 *sa_full64;    // optional full SA otherwise (transient: b200_pack_full_sa turns it into sa_full40)
+    const u32 *sa_full40;    // full SA as 5 bytes per row, little-endian, rows packed back to back (seq_len < 2^40); row 0 is special-cased
     const u8 *pac;           // 2-bit packed forward reference
     i64 l_pac;
     int n_seqs;
@@ -175,6 +176,13 @@ __device__ __forceinline__ u64 dev_sa_walk(const DevIndex &ix, u64 k, int *steps
 __device__ __forceinline__ u64 dev_sa(const DevIndex &ix, u64 k, int *steps)
 {
     if (ix.sa_full32) { if (steps) *steps = 0; return k == 0 ? (u64)-1 : (u64)ix.sa_full32[k]; }
+    if (ix.sa_full40) {                                             // 40 bits at byte 5k: always inside two aligned words
+        if (steps) *steps = 0;
+        if (k == 0) return (u64)-1;                                 // bwt->sa[0] = (bwtint_t)-1 (bwt.c:71)
+        const u64 b = k * 5;
+        const u32 *w = ix.sa_full40 + (b >> 2);
+        return (((u64)__ldg(w + 1) << 32 | __ldg(w)) >> ((int)(b & 3) * 8)) & 0xffffffffffull;
+    }
     if (ix.sa_full64) { if (steps) *steps = 0; return ix.sa_full64[k]; }
     return dev_sa_walk(ix, k, steps);
 }

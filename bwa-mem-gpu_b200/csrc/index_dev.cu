@@ -444,7 +444,7 @@ extern "C" int b200_index_build_device(b200_ctx_t *ctx, const uint8_t *pac, int6
     const bool narrow = n < 0xffffffffull;
     const size_t pac_bytes = (size_t)(l_pac / 4 + 1);
     if (ctx->d_bwt.ensure(bwt_bytes) || ctx->d_sa.ensure((size_t)n_sa * 8) || ctx->d_pac.ensure(pac_bytes) ||
-        ctx->d_sa_full.ensure((size_t)(n + 1) * (narrow ? 4 : 8)) ||
+        ctx->d_sa_full.ensure_exact((size_t)(n + 1) * (narrow ? 4 : 8)) ||
         ctx->d_ann_off.ensure((size_t)n_seqs * 8) || ctx->d_ann_len.ensure((size_t)n_seqs * 4) || ctx->d_ann_alt.ensure((size_t)n_seqs * 4)) return -1;
     B200_CHECK(cudaMemsetAsync(ctx->d_bwt.p, 0, bwt_bytes, st));
     B200_CHECK(cudaMemcpyAsync(ctx->d_pac.p, pac, pac_bytes, cudaMemcpyHostToDevice, st));

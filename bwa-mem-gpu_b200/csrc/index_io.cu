@@ -18,13 +18,13 @@ namespace {
 enum { A_BWT = 0, A_SA, A_PAC, A_ANN_OFF, A_ANN_LEN, A_ANN_ALT, A_OCC32, A_KMER, A_SA_FULL, A_N };
 
 struct IdxHeader {
-    char magic[8];                       // "B200IDX5"
+    char magic[8];                       // "B200IDX6"
     u64 header_bytes, file_bytes;
     DevIndex ix;                         // scalars as they are; pointers are rewritten on load
     u64 off[A_N], bytes[A_N];            // file offset / length of every array (0 = absent)
     u64 ptr_off[A_N];                    // offset of the pointer the kernels use inside its array (arrays are padded in front of nothing today: 0)
     i32 force_wide, kmer_k; u64 idx_bwt_size;
-    i32 sa_full_is64, pad;
+    i32 sa_full_kind, pad;               // 0 = u32 per row, 1 = u64, 2 = 5 bytes per row
 };
 
 DevBuf *buf_of(b200_ctx *c, int a)
@@ -41,11 +41,11 @@ extern "C" int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_
     B200_CHECK(cudaSetDevice(ctx->device));
     IdxHeader H;
     memset(&H, 0, sizeof(H));
-    memcpy(H.magic, "B200IDX5", 8);
+    memcpy(H.magic, "B200IDX6", 8);
     H.header_bytes = sizeof(H);
     H.ix = ctx->ix;
     H.force_wide = ctx->force_wide; H.kmer_k = ctx->kmer_k; H.idx_bwt_size = ctx->idx_bwt_size;
-    H.sa_full_is64 = ctx->ix.sa_full64 != nullptr;
+    H.sa_full_kind = ctx->ix.sa_full40 ? 2 : ctx->ix.sa_full64 ? 1 : 0;
     // the bytes the kernels may touch of every array: what the context allocated for it (allocations are grow-only and
     // padded; the used part is recomputed here so that a re-used, larger buffer does not bloat the file)
     const DevIndex &ix = ctx->ix;
@@ -56,7 +56,7 @@ extern "C" int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_
     used[A_ANN_OFF] = (u64)ix.n_seqs * 8; used[A_ANN_LEN] = (u64)ix.n_seqs * 4; used[A_ANN_ALT] = (u64)ix.n_seqs * 4;
     used[A_OCC32] = n_blk * 32;
     used[A_KMER] = ix.kmer_tab ? (u64)kmer_tab_entries(ix.kmer_k) * (b200_wide_mode(ctx) == 1 ? 32 : 16) : 0;
-    used[A_SA_FULL] = with_full_sa ? (ix.sa_full64 ? (ix.seq_len + 1) * 8 : ix.sa_full32 ? (ix.seq_len + 1) * 4 : 0) : 0;
+    used[A_SA_FULL] = with_full_sa ? (ix.sa_full40 ? (u64)sa40_bytes(ix.seq_len + 1) : ix.sa_full64 ? (ix.seq_len + 1) * 8 : ix.sa_full32 ? (ix.seq_len + 1) * 4 : 0) : 0;
     u64 pos = (sizeof(H) + 4095) / 4096 * 4096;
     for (int a = 0; a < A_N; ++a) {
         DevBuf *b = buf_of(ctx, a);
@@ -97,7 +97,7 @@ extern "C" int b200_index_load(b200_ctx_t *ctx, const char *path, int flags)
     struct stat sb;
     IdxHeader H;
     if (fstat(fd, &sb) != 0 || (size_t)sb.st_size < sizeof(H) || pread(fd, &H, sizeof(H), 0) != (ssize_t)sizeof(H) ||
-        memcmp(H.magic, "B200IDX5", 8) != 0 || H.header_bytes != sizeof(H) || H.file_bytes > (u64)sb.st_size) {
+        memcmp(H.magic, "B200IDX6", 8) != 0 || H.header_bytes != sizeof(H) || H.file_bytes > (u64)sb.st_size) {
         close(fd); b200_set_error("b200_index_load: %s is not an index of this library version", path); return -1;
     }
     const char *map = (const char *)mmap(nullptr, (size_t)H.file_bytes, PROT_READ, MAP_PRIVATE, fd, 0);
@@ -109,7 +109,7 @@ extern "C" int b200_index_load(b200_ctx_t *ctx, const char *path, int flags)
     for (int a = 0; a < A_N && !rc; ++a) {
         DevBuf *b = buf_of(ctx, a);
         if (!H.bytes[a]) continue;
-        if (b->ensure((size_t)H.bytes[a])) { rc = -1; break; }
+        if (b->ensure_exact((size_t)H.bytes[a])) { rc = -1; break; }
         if (cudaMemcpyAsync(b->p, map + H.off[a], (size_t)H.bytes[a], cudaMemcpyHostToDevice, ctx->st) != cudaSuccess) { b200_set_error("b200_index_load: upload failed"); rc = -1; }
     }
     if (!rc && cudaStreamSynchronize(ctx->st) != cudaSuccess) { b200_set_error("b200_index_load: upload failed"); rc = -1; }
@@ -121,18 +121,23 @@ extern "C" int b200_index_load(b200_ctx_t *ctx, const char *path, int flags)
     ix.occ32 = ctx->d_occ32.as<uint4>();
     ix.kmer_tab = H.bytes[A_KMER] ? ctx->d_kmer.as<uint4>() : nullptr;
     if (!ix.kmer_tab) ix.kmer_k = 0;
-    ix.sa_full32 = nullptr; ix.sa_full64 = nullptr;
-    if (H.bytes[A_SA_FULL]) { if (H.sa_full_is64) ix.sa_full64 = ctx->d_sa_full.as<u64>(); else ix.sa_full32 = ctx->d_sa_full.as<u32>(); }
+    ix.sa_full32 = nullptr; ix.sa_full64 = nullptr; ix.sa_full40 = nullptr;
+    if (H.bytes[A_SA_FULL]) {
+        if (H.sa_full_kind == 2) ix.sa_full40 = ctx->d_sa_full.as<u32>();
+        else if (H.sa_full_kind == 1) ix.sa_full64 = ctx->d_sa_full.as<u64>();
+        else ix.sa_full32 = ctx->d_sa_full.as<u32>();
+    }
     ctx->ix = ix;
     ctx->force_wide = H.force_wide; ctx->kmer_k = H.kmer_k; ctx->idx_bwt_size = H.idx_bwt_size;
     ctx->bwt_identity = nullptr; ctx->stub_pac = false;
-    if ((flags & B200_IDX_FULL_SA) && !ix.sa_full32 && !ix.sa_full64) {           // the file was saved without it: expand the sampled SA on the device
+    if ((flags & B200_IDX_FULL_SA) && !ix.sa_full32 && !ix.sa_full64 && !ix.sa_full40) {   // the file was saved without it: expand the sampled SA on the device
         DevIndex &jx = ctx->ix;
         const bool narrow = jx.seq_len < 0xffffffffull;
-        if (ctx->d_sa_full.ensure((size_t)(jx.seq_len + 1) * (narrow ? 4 : 8))) return -1;
+        if (ctx->d_sa_full.ensure_exact((size_t)(jx.seq_len + 1) * (narrow ? 4 : 8))) return -1;
         if (launch_build_full_sa(jx, narrow ? ctx->d_sa_full.as<u32>() : nullptr, narrow ? nullptr : ctx->d_sa_full.as<u64>(), ctx->st)) return -1;
         if (narrow) jx.sa_full32 = ctx->d_sa_full.as<u32>(); else jx.sa_full64 = ctx->d_sa_full.as<u64>();
         B200_CHECK(cudaStreamSynchronize(ctx->st));
+        if (b200_pack_full_sa(ctx)) return -1;
     }
     ctx->has_index = true;
     return 0;

@@ -98,6 +98,35 @@ int launch_sa_batch(const DevIndex &ix, i64 n, const u64 *k, u64 *out, int use_f
     B200_CHECK(cudaGetLastError());
     return 0;
 }
+// Full SA as 5 bytes per row: four rows = five 32-bit words, one thread per group of four (no two threads share a word).
+template <class T>
+__global__ void pack_sa40_kernel(const T *in, u32 *out, u64 n)
+{
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 g = (u64)blockIdx.x * blockDim.x + threadIdx.x; g * 4 < n; g += stride) {
+        u64 v[4];
+        for (int t = 0; t < 4; ++t) { const u64 r = g * 4 + t; v[t] = r < n ? (u64)in[r] & 0xffffffffffull : 0; }
+        u32 *o = out + g * 5;
+        o[0] = (u32)v[0];
+        o[1] = (u32)(v[0] >> 32) | (u32)(v[1] << 8);
+        o[2] = (u32)(v[1] >> 24) | (u32)(v[2] << 16);
+        o[3] = (u32)(v[2] >> 16) | (u32)(v[3] << 24);
+        o[4] = (u32)(v[3] >> 8);
+    }
+}
+
+size_t sa40_bytes(u64 n_rows) { return (size_t)((n_rows + 3) / 4) * 20 + 16; }      // whole groups + one spare word for the two-word read of the last row
+
+int launch_pack_sa40(const void *in, int in_is64, u32 *out, u64 n_rows, cudaStream_t st)
+{
+    const u64 groups = (n_rows + 3) / 4;
+    const int grid = (int)std::min<u64>((groups + 255) / 256, (u64)148 * 64);
+    if (in_is64) B200_LAUNCH((pack_sa40_kernel<u64>), grid, 256, 0, st, (const u64 *)in, out, n_rows);
+    else B200_LAUNCH((pack_sa40_kernel<u32>), grid, 256, 0, st, (const u32 *)in, out, n_rows);
+    B200_CHECK(cudaGetLastError());
+    return 0;
+}
+
 int launch_build_full_sa(const DevIndex &ix, u32 *out32, u64 *out64, cudaStream_t st)
 {
     u64 n = ix.seq_len + 1;

@@ -152,7 +152,7 @@ const char *b200_last_error(void);
  * bwt_extend calls / two-block calls for b200_batch_counters; default 0) */
 int         b200_ctx_tune(b200_ctx_t *ctx, const char *key, int64_t value);
 /* flags for b200_index_upload */
-#define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device */
+#define B200_IDX_FULL_SA   0x1   /* expand sa[] (every 32nd) into a full suffix array on the device: 4 bytes per row, 5 when seq_len >= 2^32 */
 int b200_index_upload(b200_ctx_t *ctx, const bwt_t *bwt, const bntseq_t *bns, const uint8_t *pac, int flags);
 /* same, from flat arrays (no reference structs needed) */
 int b200_index_upload_raw(b200_ctx_t *ctx, const uint32_t *bwt, uint64_t bwt_size, uint64_t primary,
@@ -170,7 +170,7 @@ int b200_index_replicate(b200_ctx_t *dst, b200_ctx_t *src);
  * of bwa_idx_load (bwa.c:384-434) AND the derived occ32 sectors and k-mer interval table, with_full_sa != 0 also the full
  * suffix array (8 bytes per row on 64-bit indexes: 50 GB at 3.1 Gbp; without it b200_index_load with B200_IDX_FULL_SA
  * re-expands the sampled SA on the device) -- written as it lies, and read back with large copies instead of the re-layout
- * of every start.  The file is specific to this library version (magic "B200IDX5"). */
+ * of every start.  The file is specific to this library version (magic "B200IDX6"). */
 int b200_index_save(b200_ctx_t *ctx, const char *path, int with_full_sa);
 int b200_index_load(b200_ctx_t *ctx, const char *path, int flags);
 

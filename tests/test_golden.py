@@ -110,3 +110,28 @@ def test_ctx_trim_keeps_the_index(backend):
         assert np.array_equal(regs.view(np.uint8).reshape(-1, abi.ALNREG_DTYPE.itemsize), g["regs"])
         ctx.trim()
     ctx.close()
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_full_sa_five_bytes_per_row(backend):
+    """The full suffix array packed to 5 bytes per row (what an index of 2^32 or more rows gets; forced here with
+    force_wide): every lookup equals the bwt_sa walk (bwt.c:86-96) and the golden values, including row 0, the last
+    row, and rows at all four byte alignments of the packed words."""
+    from bwa_mem_gpu_b200 import lib as L
+    g = _load("fmindex.npz")
+    ctx = L.Context(0, cm.backend_lib(backend))
+    ctx.tune("force_wide", 1)
+    h = cm.context(backend, G)._host_index
+    ctx.upload_host_index(h)
+    assert np.array_equal(ctx.sa_lookup(g["sa_k"], use_full=True), g["sa"])
+    rng = np.random.default_rng(5)
+    k = np.concatenate([np.arange(0, 64, dtype=np.uint64), np.arange(h.seq_len - 63, h.seq_len + 1, dtype=np.uint64),
+                        rng.integers(0, h.seq_len + 1, 20000, dtype=np.uint64)])
+    assert np.array_equal(ctx.sa_lookup(k, use_full=True), ctx.sa_lookup(k, use_full=False))
+    opt = abi.default_opt()
+    ga = _load("align.npz")
+    seqs, off = cm.reads_for(G, 800, seed=41, indel=0.004)
+    regs, n = ctx.align(opt, seqs, off)
+    assert np.array_equal(n, ga["n"])
+    assert np.array_equal(regs.view(np.uint8).reshape(-1, abi.ALNREG_DTYPE.itemsize), ga["regs"])
+    ctx.close()
