@@ -474,6 +474,54 @@ def test_seeding_table_counters(backend, min_seed_len):
     assert got[0] == got[1] and got[0][0] > 0
 
 
+def _ragged_noisy_reads(gname, n, seed):
+    """Reads of 12-170 bases cut from the genome (both strands), 2 % substitutions and 3 % N: sweeps that start, stop and
+    restart inside the k-mer table's range in every combination."""
+    rng = np.random.default_rng(seed)
+    g = np.concatenate(cm.genome(gname))
+    parts = []
+    for _ in range(n):
+        ln = int(rng.integers(12, 171))
+        p = int(rng.integers(0, len(g) - ln))
+        r = g[p: p + ln].copy()
+        if rng.random() < 0.5:
+            r = (3 - r)[::-1].copy()
+        m = rng.random(ln) < 0.02
+        r[m] = (r[m] + rng.integers(1, 4, int(m.sum()))) % 4
+        r[rng.random(ln) < 0.03] = 4
+        parts.append(r.astype(np.uint8))
+    seqs = np.ascontiguousarray(np.concatenate(parts))
+    off = np.concatenate([[0], np.cumsum([len(x) for x in parts])]).astype(np.int64)
+    return seqs, off
+
+
+@needs_ref
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("optset", [dict(), dict(min_seed_len=13), dict(min_seed_len=13, split_factor=1.0, split_width=30),
+                                    dict(min_seed_len=14, max_mem_intv=0), dict(min_seed_len=15, max_mem_intv=200, split_width=2)])
+def test_seeding_ragged_reads_table_depths(backend, optset):
+    """mem_collect_intv on short, N-rich, ragged reads with table depths below, at and above typical sweep lengths and
+    re-seeding / third-pass options moved around: the production kernels (bit entries, group decisions) against the
+    reference, interval for interval."""
+    from bwa_mem_gpu_b200 import lib as L
+    gname = "rep"
+    lib = cm.backend_lib(backend)
+    idx = cm.ref_index(gname)
+    opt = abi.default_opt()
+    for k, v in optset.items():
+        setattr(opt, k, v)
+    seqs, off = _ragged_noisy_reads(gname, _sizes(backend, 500, 30000), seed=63)
+    a = idx.collect_intv(opt, seqs, off)
+    for depth in (5, 9, 12):
+        ctx = L.Context(0, lib)
+        ctx.tune("kmer_k", depth)
+        ctx.upload_host_index(cm.context(backend, gname)._host_index)
+        b = ctx.collect_intv(opt, seqs, off)
+        ctx.close()
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), depth
+
+
 def _check_reg2aln(idx, ctx, opt, seqs, off):
     regs, cnt = idx.align(opt, seqs, off, n_threads=8, cap_per_read=512)
     a0, c0, m0 = idx.reg2aln(opt, seqs, off, regs, cnt)
